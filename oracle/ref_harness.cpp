@@ -1,0 +1,130 @@
+// oracle/ref_harness.cpp — TEST INFRASTRUCTURE ONLY (never linked into the product).
+//
+// A thin extern "C" harness around the *unmodified* jhhung/kISS headers, compiled
+// from where they lie under /root/reference by oracle/build_ref.sh into
+// oracle/_ref/libkiss_ref.so.  It exposes the reference's own suffix_sort path
+// (kiss1_suffix_array_dna: kiss1_core.hpp:229-268, kiss2_suffix_array_dna:
+// kiss2_core.hpp:888-896) plus a stage-by-stage replay of the kiss1 driver that
+// snapshots the intermediate arrays, so that the C restatement (oracle/kiss_oracle.c)
+// and the CUDA kernels can be pinned stage by stage.
+//
+// Nothing in here restates the algorithm: every stage is a call into the
+// reference's function templates.
+#define SPDLOG_ACTIVE_LEVEL SPDLOG_LEVEL_OFF
+#include <biovoltron/algo/sort/kiss1_sorter.hpp>
+#include <biovoltron/algo/sort/kiss2_sorter.hpp>
+
+#include <chrono>
+#include <cstdint>
+#include <cstring>
+
+using biovoltron::kiss::vector;
+namespace kiss = biovoltron::kiss;
+
+static double now_s() {
+  using namespace std::chrono;
+  return duration<double>(steady_clock::now().time_since_epoch()).count();
+}
+
+extern "C" {
+
+// Full reference path, PARALLEL_SORTING.  SA_out has n+1 slots.  Returns seconds spent in
+// kiss1_suffix_array_dna (the region suffix_sort.hpp:57-61 / experiment/src/kiss-1.cpp:42-47 time).
+double ref_kiss1_suffix_array_dna(const uint8_t* S_, uint64_t n, uint32_t k, uint64_t threads,
+                                  uint32_t* SA_out) {
+  vector<uint8_t> S(S_, S_ + n);
+  vector<uint32_t> SA;
+  double t0 = now_s();
+  kiss::kiss1_suffix_array_dna<uint8_t, uint32_t>(S, SA, k, threads);
+  double t1 = now_s();
+  if (SA_out) std::memcpy(SA_out, SA.data(), sizeof(uint32_t) * SA.size());
+  return t1 - t0;
+}
+
+// Full reference path, PREFIX_DOUBLING.
+double ref_kiss2_suffix_array_dna(const uint8_t* S_, uint64_t n, uint32_t k, uint64_t threads,
+                                  uint32_t* SA_out) {
+  vector<uint8_t> S(S_, S_ + n);
+  vector<uint32_t> SA;
+  double t0 = now_s();
+  kiss::kiss2_suffix_array_dna<uint8_t, uint32_t>(S, SA, k, threads);
+  double t1 = now_s();
+  if (SA_out) std::memcpy(SA_out, SA.data(), sizeof(uint32_t) * (n + 1));
+  return t1 - t0;
+}
+
+// Stage replay of kiss1_suffix_array_dna (kiss1_core.hpp:229-268), same calls in the same
+// order, with snapshots.  Any out pointer may be NULL.
+//   lms_out      : m entries  — get_lms output (ascending positions, sentinel n last)
+//   sorted_out   : m entries  — after lms_suffix_direct_sort_dna (sorted_out[0] == n)
+//   placed_out   : n+1        — after put_lms_suffix (EMPTY = 0xFFFFFFFF elsewhere)
+//   sa_out       : n+1        — after induced_sort
+//   counters_out : 5*256 u32  — sum over threads of ThreadState::bucket (kiss_common.hpp:519,529-536)
+//   stage_sec    : 5 doubles  — resize, get_lms, lms sort, put, induce
+// Returns m (LMS count including the sentinel).  n must be > 0.
+uint32_t ref_kiss1_stages(const uint8_t* S_, uint64_t n_, uint32_t k, uint64_t threads,
+                          uint32_t* lms_out, uint32_t* sorted_out, uint32_t* placed_out,
+                          uint32_t* sa_out, uint32_t* counters_out, double* stage_sec) {
+  vector<uint8_t> S(S_, S_ + n_);
+  vector<uint32_t> SA;
+  uint32_t n = (uint32_t)S.size();
+  SA.reserve((size_t)n + 1);
+  auto states = vector<kiss::ThreadState<uint32_t>>(threads);
+  double t[6];
+  t[0] = now_s();
+  SA.resize((size_t)n + 1);
+  t[1] = now_s();
+  auto m = kiss::get_lms(S, SA, states);
+  t[2] = now_s();
+  if (lms_out) std::memcpy(lms_out, SA.data(), sizeof(uint32_t) * m);
+  if (counters_out) {
+    std::memset(counters_out, 0, sizeof(uint32_t) * 5 * 256);
+    for (auto& st : states)
+      for (size_t i = 0; i < 5 * 256; i++) counters_out[i] += st.bucket[i];
+  }
+  double t2b = now_s();
+  auto buffer = std::ranges::subrange(std::begin(SA) + (n / 2), std::end(SA));
+  auto output_SA = std::ranges::subrange(std::begin(SA), std::begin(SA) + (n / 2));
+  kiss::lms_suffix_direct_sort_dna<uint8_t, uint32_t>(S, output_SA, buffer, m, k, threads, states);
+  t[3] = now_s();
+  if (sorted_out) std::memcpy(sorted_out, SA.data(), sizeof(uint32_t) * m);
+  double t3b = now_s();
+  auto SA1 = std::ranges::subrange(SA.begin() + 1, SA.begin() + m);
+  kiss::put_lms_suffix(S, SA, SA1, states);
+  t[4] = now_s();
+  if (placed_out) std::memcpy(placed_out, SA.data(), sizeof(uint32_t) * ((size_t)n + 1));
+  double t4b = now_s();
+  kiss::induced_sort(S, SA, states);
+  t[5] = now_s();
+  if (sa_out) std::memcpy(sa_out, SA.data(), sizeof(uint32_t) * ((size_t)n + 1));
+  if (stage_sec) {
+    stage_sec[0] = t[1] - t[0];
+    stage_sec[1] = t[2] - t[1];
+    stage_sec[2] = t[3] - t2b;
+    stage_sec[3] = t[4] - t3b;
+    stage_sec[4] = t[5] - t4b;
+  }
+  return m;
+}
+
+// put_lms_suffix + induced_sort of the reference applied to a caller-supplied sorted LMS
+// list (sorted[0] must be n).  Used to validate an LMS order model independently of the
+// reference's comparator.
+void ref_induce_from_sorted_lms(const uint8_t* S_, uint64_t n_, uint64_t threads,
+                                const uint32_t* sorted, uint32_t* sa_out) {
+  vector<uint8_t> S(S_, S_ + n_);
+  vector<uint32_t> SA;
+  uint32_t n = (uint32_t)S.size();
+  auto states = vector<kiss::ThreadState<uint32_t>>(threads);
+  SA.resize((size_t)n + 1);
+  auto m = kiss::get_lms(S, SA, states);
+  std::memcpy(SA.data(), sorted, sizeof(uint32_t) * m);
+  auto SA1 = std::ranges::subrange(SA.begin() + 1, SA.begin() + m);
+  kiss::put_lms_suffix(S, SA, SA1, states);
+  kiss::induced_sort(S, SA, states);
+  std::memcpy(sa_out, SA.data(), sizeof(uint32_t) * ((size_t)n + 1));
+}
+
+int ref_abi_version() { return 1; }
+
+}  // extern "C"
