@@ -1,0 +1,149 @@
+/*
+ * kiss_b200.h — C ABI of the B200-native suffix_sort path (libkiss_b200.so).
+ *
+ * This is the drop-in boundary for jhhung/kISS's `suffix_sort` hot path.  Every entry point names the
+ * reference interface it replaces (paths relative to the reference's include/biovoltron/algo/sort/
+ * unless stated otherwise).  Plain pointers and sizes only; no CPU fallback exists behind any of
+ * these: every call runs CUDA kernels on the selected device or returns an error code.
+ *
+ * Conventions
+ *   - Text `S` is one code per byte, values 0..3 (A C G T), exactly what the reference's callers
+ *     pass after `c % 4` (include/command/suffix_sort.hpp:33).  Only the low two bits are used.
+ *   - Suffix array entries are uint32_t; `KISS_B200_EMPTY` (0xFFFFFFFF) is the reference's
+ *     `EMPTY<uint32_t>` (constant.hpp:19-20), so n + 1 must be < 2^32 - 1.
+ *   - k is the reference's `size_type k`; 0xFFFFFFFF means unbounded (`-k -1`,
+ *     include/command/suffix_sort.hpp:35,59).
+ *   - "host" pointers are ordinary host memory; "dev" pointers are device memory on the context's GPU.
+ *   - All functions return 0 (KISS_B200_OK) or a negative error code; `kiss_b200_strerror` names it and
+ *     `kiss_b200_last_error` gives the detailed message of the calling thread's last failure.
+ */
+#ifndef KISS_B200_H
+#define KISS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KISS_B200_EMPTY 0xFFFFFFFFu
+
+/* -s / --sorting-algorithm (reference: include/utils/options.hpp:67-81 SortingAlgorithm) */
+#define KISS_B200_PARALLEL_SORTING 0
+#define KISS_B200_PREFIX_DOUBLING 1
+
+enum {
+  KISS_B200_OK = 0,
+  KISS_B200_ERR_ARG = -1,          /* null pointer, bad enum value */
+  KISS_B200_ERR_TOO_LARGE = -2,    /* n + 1 >= 2^32 - 1 (EMPTY would collide, constant.hpp:19-20) */
+  KISS_B200_ERR_CUDA = -3,         /* a CUDA runtime call or kernel failed */
+  KISS_B200_ERR_NOMEM = -4,        /* device allocation failed (reference: std::bad_alloc, structs.hpp:32-38) */
+  KISS_B200_ERR_UNSUPPORTED = -5,  /* bounded k so large that > 16384 LMS suffixes lie within D(k) of the text end */
+  KISS_B200_ERR_NO_DEVICE = -6     /* no CUDA device / the CUDA library cannot run: there is no CPU fallback */
+};
+
+typedef struct kiss_b200_ctx kiss_b200_ctx;
+
+/* Per-stage device times (seconds, CUDA events on the context's stream), the same split the
+ * reference logs with --verbose (kiss1_core.hpp:244-267; README.md:95-100). */
+typedef struct kiss_b200_timings {
+  double h2d;            /* host variant only: copy of S to the device */
+  double pack;           /* 2-bit packing (reference: PackedDNAString ctor, structs.hpp:84-116) */
+  double get_lms;        /* reference: get_lms, kiss_common.hpp:543-579 */
+  double lms_sort;       /* reference: lms_suffix_direct_sort_dna, kiss1_core.hpp:23-145 */
+  double put_lms;        /* reference: put_lms_suffix, kiss_common.hpp:445-481 */
+  double induce;         /* reference: induced_sort, kiss_common.hpp:422-442 */
+  double d2h;            /* host variant only: copy of SA back to the host */
+  double total_device;   /* pack .. induce */
+  uint64_t n;            /* text length */
+  uint64_t m;            /* LMS count including the sentinel (what get_lms returns, kiss_common.hpp:578) */
+  uint64_t lms_sort_tied;   /* LMS suffixes still tied after the first 16-base radix key */
+  uint64_t lms_sort_rounds; /* refinement rounds run for the large tied groups */
+  uint64_t waves_L, waves_S; /* induction waves (maximal filled runs, kiss_common.hpp:389-393) */
+  uint64_t kernel_launches; /* kernels launched by this call */
+} kiss_b200_timings;
+
+/* ---- context ----------------------------------------------------------------------------------
+ * Owns the stream, the events and all device scratch; scratch is grown on demand and reused by
+ * later calls (the reference allocates per call: kiss1_core.hpp:241-247).  One host thread per
+ * context. */
+int kiss_b200_create(kiss_b200_ctx** out, int device);
+void kiss_b200_destroy(kiss_b200_ctx* ctx);
+const char* kiss_b200_strerror(int code);
+const char* kiss_b200_last_error(void);
+int kiss_b200_abi_version(void);
+/* CUDA stream (cudaStream_t) all work of this context is issued on */
+void* kiss_b200_stream(kiss_b200_ctx* ctx);
+
+/* ---- the path ---------------------------------------------------------------------------------
+ * kiss_b200_suffix_sort_dna_u32: replaces
+ *   KISS1Sorter<uint32_t>::get_suffix_array_dna(const kiss::vector<uint8_t>& S, uint32_t k, size_t threads)
+ *     (kiss1_sorter.hpp:20-27) -> kiss::kiss1_suffix_array_dna (kiss1_core.hpp:229-268)   [algo 0]
+ *   KISS2Sorter<uint32_t>::get_suffix_array_dna (kiss2_sorter.hpp:20-27)
+ *     -> kiss::kiss2_suffix_array_dna (kiss2_core.hpp:888-896)                             [algo 1]
+ * S_host: n codes; SA_host: n + 1 slots, filled with the suffix array (SA[0] = n); n == 0 gives {0}
+ * (kiss1_core.hpp:237-238).  `t` may be NULL. */
+int kiss_b200_suffix_sort_dna_u32(kiss_b200_ctx* ctx, const uint8_t* S_host, uint64_t n, uint32_t k,
+                                  int algo, uint32_t* SA_host, kiss_b200_timings* t);
+
+/* Same, text and suffix array resident in device memory (no PCIe in the timed region).
+ * S_dev must be 16-byte aligned. */
+int kiss_b200_suffix_sort_dna_u32_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, uint32_t k,
+                                      int algo, uint32_t* SA_dev, kiss_b200_timings* t);
+
+/* ASCII front end: bytes of sequence text (aA cC gG tT, anything else -> A) are coded on the device
+ * exactly as Codec::to_int followed by `% 4` does (include/biovoltron/utility/istring.hpp:27-46,
+ * include/command/suffix_sort.hpp:33), then sorted as above. */
+int kiss_b200_suffix_sort_ascii_u32(kiss_b200_ctx* ctx, const char* seq_host, uint64_t n, uint32_t k,
+                                    int algo, uint32_t* SA_host, kiss_b200_timings* t);
+
+/* ---- stage-level entries (used by the parity tests and the multi-GPU LMS sort) -------------------
+ * Each one runs pack + the named stage(s) on the device and copies the stage's result to the host.
+ *
+ * kiss_b200_get_lms: reference get_lms (kiss_common.hpp:543-579).  lms_host receives the LMS positions
+ * ascending followed by the sentinel n (capacity n/2 + 2); *m_out = their number including the sentinel;
+ * count4 / lms_count4 receive the per-symbol totals the reference keeps in ThreadState::bucket
+ * (kiss_common.hpp:519, 529-536).  Any output pointer may be NULL. */
+int kiss_b200_get_lms(kiss_b200_ctx* ctx, const uint8_t* S_host, uint64_t n, uint32_t* lms_host,
+                      uint64_t* m_out, uint64_t* count4, uint64_t* lms_count4);
+
+/* kiss_b200_sorted_lms: get_lms + lms_suffix_direct_sort_dna (kiss1_core.hpp:23-145).  sorted_host
+ * receives the m LMS suffixes in the reference's order, sorted_host[0] == n. */
+int kiss_b200_sorted_lms(kiss_b200_ctx* ctx, const uint8_t* S_host, uint64_t n, uint32_t k, int algo,
+                         uint32_t* sorted_host, uint64_t* m_out);
+
+/* kiss_b200_put_lms: ... + put_lms_suffix (kiss_common.hpp:445-481): SA_host (n + 1) holds the sorted LMS
+ * suffixes at their bucket ends, SA[0] = n, KISS_B200_EMPTY everywhere else. */
+int kiss_b200_put_lms(kiss_b200_ctx* ctx, const uint8_t* S_host, uint64_t n, uint32_t k, int algo,
+                      uint32_t* SA_host);
+
+/* kiss_b200_induce_from_sorted_lms: put_lms_suffix + induced_sort (kiss_common.hpp:422-481) from a
+ * caller-supplied order of the LMS suffixes (sorted_host[0] == n, m entries). */
+int kiss_b200_induce_from_sorted_lms(kiss_b200_ctx* ctx, const uint8_t* S_host, uint64_t n,
+                                     const uint32_t* sorted_host, uint64_t m, uint32_t* SA_host);
+
+/* ---- device-resident stage API for the sharded LMS sort (one process per GPU) --------------------
+ * kiss_b200_prepare_dev: pack + get_lms on this GPU for the whole text; keeps packed text and the
+ * text-ordered LMS list in the context.  *m_out includes the sentinel. */
+int kiss_b200_prepare_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, uint32_t k, uint64_t* m_out);
+/* Sort by the reference's LMS order an arbitrary subset of the long LMS suffixes given as device
+ * positions in ascending text order (the shard a rank received); result in place. */
+int kiss_b200_sort_lms_subset_dev(kiss_b200_ctx* ctx, uint32_t* pos_dev, uint64_t count, kiss_b200_timings* t);
+/* First 16-base radix keys of the context's text-ordered long LMS suffixes (device pointers owned by the
+ * context, valid until the next prepare): used to pick splitters and to bucket positions by destination. */
+int kiss_b200_lms_keys_dev(kiss_b200_ctx* ctx, const uint32_t** keys_dev, const uint32_t** pos_dev,
+                           uint64_t* n_long);
+/* Finish on this GPU from a fully sorted list of the long LMS suffixes (device, n_long entries):
+ * short-suffix insertion, placement and induction into SA_dev (n + 1). */
+int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_long_dev, uint64_t n_long,
+                                     uint32_t* SA_dev, kiss_b200_timings* t);
+
+/* ---- synthetic inputs ---------------------------------------------------------
+ * Fill S_dev[0..n) with the counter-hash uniform stream `seed` (identical to tests/textgen.py uniform). */
+int kiss_b200_synth_uniform_dev(kiss_b200_ctx* ctx, uint8_t* S_dev, uint64_t n, uint64_t seed);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KISS_B200_H */

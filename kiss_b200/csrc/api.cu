@@ -1,0 +1,788 @@
+// api.cu — the context, the pipeline driver and the extern "C" boundary (include/kiss_b200.h).
+//
+// Driver = kiss1_suffix_array_dna (kiss1_core.hpp:229-268): get_lms -> lms_suffix_direct_sort_dna ->
+// put_lms_suffix -> induced_sort, each stage a set of kernels on one stream.  There is no CPU path: every
+// entry either runs the kernels or returns an error code.
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "../../include/kiss_b200.h"
+#include "kernels.h"
+
+using namespace kiss;
+
+#define SHORT_MAX 16384u
+
+static thread_local std::string g_last_error;
+
+namespace {
+
+// stream-ordered scratch; everything still owned is released when the call ends
+struct Pool {
+  cudaStream_t st;
+  std::vector<void*> ptrs;
+  explicit Pool(cudaStream_t s) : st(s) {}
+  template <typename T>
+  T* alloc(u64 count) {
+    void* p = nullptr;
+    u64 bytes = (count ? count : 1) * sizeof(T);
+    bytes = (bytes + 255) & ~255ull;
+    CK(cudaMallocAsync(&p, bytes, st));
+    ptrs.push_back(p);
+    return static_cast<T*>(p);
+  }
+  void release(void* p) {
+    for (size_t i = 0; i < ptrs.size(); i++)
+      if (ptrs[i] == p) {
+        ptrs[i] = ptrs.back();
+        ptrs.pop_back();
+        cudaFreeAsync(p, st);
+        return;
+      }
+  }
+  // hand ownership to the caller
+  void keep(void* p) {
+    for (size_t i = 0; i < ptrs.size(); i++)
+      if (ptrs[i] == p) {
+        ptrs[i] = ptrs.back();
+        ptrs.pop_back();
+        return;
+      }
+  }
+  ~Pool() {
+    for (void* p : ptrs) cudaFreeAsync(p, st);
+  }
+};
+
+}  // namespace
+
+struct kiss_b200_ctx {
+  int device = 0;
+  cudaStream_t st = nullptr;
+  cudaEvent_t ev[8] = {};
+  u32* pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs
+  // state kept between prepare_dev and finish_from_sorted_dev
+  struct Prepared {
+    bool valid = false;
+    u64 n = 0, m1 = 0;      // m1 = LMS count without the sentinel
+    u32 n_long = 0;
+    u64* T = nullptr;
+    u32* pos = nullptr;     // text-ordered LMS positions (m1)
+    u32* key = nullptr;     // their first-16-base keys
+    u64 counters[8] = {};
+    SortParams sp = {};
+  } prep;
+};
+
+namespace {
+
+struct Sync {
+  kiss_b200_ctx* c;
+  // copy `cnt` u32 from the device and wait for them
+  void read(const u32* dev, u32 cnt, u32* out) {
+    CK(cudaMemcpyAsync(c->pinned, dev, cnt * sizeof(u32), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    for (u32 i = 0; i < cnt; i++) out[i] = c->pinned[i];
+  }
+};
+
+u64 depth_of(u32 k) { return 125ull * ((u64)k / 125ull + 1ull); }  // kiss1_core.hpp:94-120, constant.hpp:29
+
+void free_prepared(kiss_b200_ctx* c) {
+  auto& p = c->prep;
+  if (p.T) cudaFreeAsync(p.T, c->st);
+  if (p.pos) cudaFreeAsync(p.pos, c->st);
+  if (p.key) cudaFreeAsync(p.key, c->st);
+  p = kiss_b200_ctx::Prepared();
+}
+
+// ---- pack + get_lms.  Leaves T, pos, key owned by ctx->prep.
+void do_prepare(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, float* t_pack, float* t_lms) {
+  free_prepared(c);
+  cudaStream_t st = c->st;
+  Pool pool(st);
+  Sync sync{c};
+  auto& P = c->prep;
+  P.n = n;
+  CK(cudaEventRecord(c->ev[0], st));
+  u64* T = pool.alloc<u64>(packed_words(n));
+  pack_codes(dS, n, T, st);
+  CK(cudaEventRecord(c->ev[1], st));
+
+  u64 nchunks = lms_chunks(n), nwords = (n + 31) / 32;
+  u8* gp = pool.alloc<u8>(nchunks);
+  u64* lmsmask = pool.alloc<u64>(nwords);
+  u32* chunk_cnt = pool.alloc<u32>(nchunks + 1);
+  u64* counters = pool.alloc<u64>(8);
+  u32* partials = pool.alloc<u32>(scan_partials_len(nchunks));
+  u32* total = pool.alloc<u32>(4);
+  CK(cudaMemsetAsync(counters, 0, 8 * sizeof(u64), st));
+  lms_classify(T, n, gp, lmsmask, chunk_cnt, counters, st);
+  scan_excl_u32(chunk_cnt, nchunks, partials, total, st);
+  u32 m1;
+  sync.read(total, 1, &m1);
+  CK(cudaMemcpyAsync(P.counters, counters, 8 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+  u32* pos = pool.alloc<u32>((u64)m1 + 1);
+  u32* key = pool.alloc<u32>((u64)m1 + 1);
+  lms_emit(T, n, lmsmask, chunk_cnt /* now exclusive offsets */, pos, key, st);
+
+  // depth and the long / short split
+  bool unbounded = (algo == KISS_B200_PREFIX_DOUBLING) || ((u64)k >= n);
+  P.sp.T = T; P.sp.n = n; P.sp.k = k;
+  u32 n_long;
+  if (unbounded) {
+    P.sp.D = KISS_UNBOUNDED;
+    n_long = m1;
+    CK(cudaStreamSynchronize(st));
+  } else {
+    P.sp.D = depth_of(k);
+    if (n >= P.sp.D && m1) {
+      count_le(pos, m1, (u32)(n - P.sp.D), total, st);
+      sync.read(total, 1, &n_long);
+    } else {
+      n_long = 0;
+      CK(cudaStreamSynchronize(st));
+    }
+  }
+  CK(cudaEventRecord(c->ev[2], st));
+  CK(cudaEventSynchronize(c->ev[2]));
+  if (t_pack) CK(cudaEventElapsedTime(t_pack, c->ev[0], c->ev[1]));
+  if (t_lms) CK(cudaEventElapsedTime(t_lms, c->ev[1], c->ev[2]));
+  P.m1 = m1; P.n_long = n_long; P.T = T; P.pos = pos; P.key = key; P.valid = true;
+  pool.keep(T); pool.keep(pos); pool.keep(key);
+}
+
+}  // namespace
+
+namespace {
+
+struct SortStats { u64 tied = 0, rounds = 0; };
+
+// one level of group handling; returns the number of big groups (their list in gl.big)
+template <typename K>
+u32 run_groups(kiss_b200_ctx* c, const K* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl);
+
+template <>
+u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl) {
+  Sync sync{c};
+  CK(cudaMemsetAsync(gl.counters, 0, 4 * sizeof(u32), c->st));
+  groups_tiny_u32(keys, pos, N, sp, h, gl, c->st);
+  u32 cn[4];
+  sync.read(gl.counters, 4, cn);
+  if (cn[3]) throw CudaError(-3, "internal: group list overflow");
+  if (!cn[0] || h >= sp.D) return 0;
+  groups_classify_u32(keys, N, cn[0], gl, c->st);
+  sync.read(gl.counters, 4, cn);
+  groups_medium(pos, gl.med, cn[1], sp, h, c->st);
+  return cn[2];
+}
+template <>
+u32 run_groups<u64>(kiss_b200_ctx* c, const u64* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl) {
+  Sync sync{c};
+  CK(cudaMemsetAsync(gl.counters, 0, 4 * sizeof(u32), c->st));
+  groups_tiny_u64(keys, pos, N, sp, h, gl, c->st);
+  u32 cn[4];
+  sync.read(gl.counters, 4, cn);
+  if (cn[3]) throw CudaError(-3, "internal: group list overflow");
+  if (!cn[0] || h >= sp.D) return 0;
+  groups_classify_u64(keys, N, cn[0], gl, c->st);
+  sync.read(gl.counters, 4, cn);
+  groups_medium(pos, gl.med, cn[1], sp, h, c->st);
+  return cn[2];
+}
+
+GroupLists alloc_lists(Pool& pool, u32 N, u64* tied) {
+  GroupLists gl;
+  gl.gcap = N / (TINY_MAX + 1) + 1;
+  gl.glist = pool.alloc<u32>(gl.gcap);
+  gl.med = pool.alloc<u32>(2ull * gl.gcap);
+  gl.big = pool.alloc<u32>(2ull * (N / (MED_MAX + 1) + 1));
+  gl.counters = pool.alloc<u32>(4);
+  gl.tied = tied;
+  return gl;
+}
+void free_lists(Pool& pool, GroupLists& gl) {
+  pool.release(gl.glist); pool.release(gl.med); pool.release(gl.big); pool.release(gl.counters);
+}
+
+// Sort `N` long LMS suffixes given in ascending text order with their first-16-base keys.
+// On return *out_pos points at the sorted positions (one of pos / pos_alt).
+void sort_long_lms(kiss_b200_ctx* c, Pool& pool, u32* key, u32* pos, u32 N, const SortParams& sp, u32** out_pos,
+                   SortStats* stats) {
+  cudaStream_t st = c->st;
+  Sync sync{c};
+  *out_pos = pos;
+  if (N == 0) return;
+  u32* key_alt = pool.alloc<u32>(N);
+  u32* pos_alt = pool.alloc<u32>(N);
+  u64 ntiles = radix_tiles(N);
+  u32* H = pool.alloc<u32>(256 * ntiles);
+  u32* partials = pool.alloc<u32>(scan_partials_len(256 * ntiles));
+  radix_sort_u32(key, pos, key_alt, pos_alt, N, 0, 32, H, partials, st);
+  pool.release(H);
+  pool.release(partials);
+  // `key` / `pos` now name the sorted buffers
+  *out_pos = pos;
+
+  u64* tied = pool.alloc<u64>(1);
+  CK(cudaMemsetAsync(tied, 0, sizeof(u64), st));
+  u64 h = 16;
+  GroupLists gl = alloc_lists(pool, N, tied);
+  u32 nbig = run_groups<u32>(c, key, pos, N, sp, h, gl);
+
+  // radix rounds over the big groups
+  struct Level { u64 *wkey = nullptr, *wkey_alt = nullptr; u32 *wpos = nullptr, *wpos_alt = nullptr, *wslot = nullptr; u32 total = 0; };
+  Level prev;
+  const u32* pos_prev = pos;
+  const u32* slot_prev = nullptr;
+  GroupLists gl_prev = gl;
+  while (nbig) {
+    stats->rounds++;
+    u32* boff = pool.alloc<u32>(nbig + 1);
+    u32* bpart = pool.alloc<u32>(scan_partials_len(nbig));
+    u32* btot = pool.alloc<u32>(1);
+    big_sizes(gl_prev.big, nbig, boff, st);
+    scan_excl_u32(boff, nbig, bpart, btot, st);
+    u32 total;
+    sync.read(btot, 1, &total);
+    Level cur;
+    cur.total = total;
+    cur.wkey = pool.alloc<u64>(total); cur.wkey_alt = pool.alloc<u64>(total);
+    cur.wpos = pool.alloc<u32>(total); cur.wpos_alt = pool.alloc<u32>(total);
+    cur.wslot = pool.alloc<u32>(total);
+    big_fill(pos_prev, slot_prev, gl_prev.big, boff, nbig, sp, h, cur.wkey, cur.wpos, cur.wslot, st);
+    int nb = 0;
+    while (nb < 31 && (1u << nb) < nbig) nb++;
+    u64 wt = radix_tiles(total);
+    u32* H2 = pool.alloc<u32>(256 * wt);
+    u32* part2 = pool.alloc<u32>(scan_partials_len(256 * wt));
+    radix_sort_u64(cur.wkey, cur.wpos, cur.wkey_alt, cur.wpos_alt, total, 0, 33 + nb, H2, part2, st);
+    pool.release(H2); pool.release(part2); pool.release(boff); pool.release(bpart); pool.release(btot);
+    h += 16;
+    GroupLists gl_cur = alloc_lists(pool, total, tied);
+    u32 nbig_next = 0;
+    if (h < sp.D) nbig_next = run_groups<u64>(c, cur.wkey, cur.wpos, total, sp, h, gl_cur);
+    big_writeback(pos, cur.wslot, cur.wpos, total, st);
+    // retire the previous level
+    free_lists(pool, gl_prev);
+    if (prev.wkey) {
+      pool.release(prev.wkey); pool.release(prev.wkey_alt); pool.release(prev.wpos); pool.release(prev.wpos_alt);
+      pool.release(prev.wslot);
+    }
+    prev = cur;
+    gl_prev = gl_cur;
+    pos_prev = cur.wpos;
+    slot_prev = cur.wslot;
+    nbig = nbig_next;
+  }
+  u64 tied_h;
+  CK(cudaMemcpyAsync(&tied_h, tied, sizeof(u64), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  stats->tied = tied_h;
+}
+
+Buckets make_buckets(const u64 counters[8], u64 n) {
+  Buckets bk;
+  u64 acc = 1;  // slot 0 holds the sentinel (kiss_common.hpp:463: scan with initial value 1)
+  for (int s = 0; s < 4; s++) {
+    bk.B[s] = acc;
+    acc += counters[s];
+  }
+  bk.B[4] = acc;  // == n + 1
+  (void)n;
+  u64 off = 0;
+  for (int s = 0; s < 4; s++) {
+    bk.lms_count[s] = counters[4 + s];
+    bk.lms_off[s] = off;
+    off += counters[4 + s];
+  }
+  return bk;
+}
+
+struct InduceStats { u64 waves_L = 0, waves_S = 0; };
+
+void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets& bk, u32* SA, InduceStats* is) {
+  cudaStream_t st = c->st;
+  WaveScratch ws;
+  u64 maxlen = n + 1;
+  ws.side = pool.alloc<u8>(maxlen);
+  u64 nt = wave_tiles(maxlen);
+  ws.C = pool.alloc<u32>(4 * nt + 4);
+  ws.partials = pool.alloc<u32>(scan_partials_len(4 * nt));
+  ws.scan_total = pool.alloc<u32>(1);
+  ws.tot_dev = pool.alloc<u32>(4);
+  ws.tot_host = c->pinned + 32;
+  u32 tot[4];
+  u64 Lc[4], nL[4], Sc[4];
+  for (int s = 0; s < 4; s++) Lc[s] = bk.B[s];
+  // L pass (kiss_common.hpp:372-403)
+  induce_wave(SA, T, 0, 1, false, 0xFu, Lc, ws, tot, st);
+  for (int s = 0; s < 4; s++) Lc[s] += tot[s];
+  is->waves_L++;
+  for (int cb = 0; cb < 4; cb++) {
+    u64 p = bk.B[cb];
+    while (p < Lc[cb]) {
+      u64 q = Lc[cb];
+      induce_wave(SA, T, p, q - p, false, (0xFu << cb) & 0xFu, Lc, ws, tot, st);
+      for (int s = 0; s < 4; s++) Lc[s] += tot[s];
+      p = q;
+      is->waves_L++;
+    }
+    if (bk.lms_count[cb]) {
+      induce_wave(SA, T, bk.B[cb + 1] - bk.lms_count[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
+      for (int s = 0; s < 4; s++) Lc[s] += tot[s];
+      is->waves_L++;
+    }
+  }
+  for (int s = 0; s < 4; s++) {
+    nL[s] = Lc[s] - bk.B[s];
+    Sc[s] = bk.B[s + 1];
+  }
+  // S pass (kiss_common.hpp:192-224); the LMS slots are simply overwritten (induced_clear, :405-420)
+  for (int cb = 3; cb >= 0; cb--) {
+    u64 p = bk.B[cb + 1];
+    while (Sc[cb] < p) {
+      u64 q = Sc[cb];
+      induce_wave(SA, T, q, p - q, true, (1u << (cb + 1)) - 1u, Sc, ws, tot, st);
+      for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
+      p = q;
+      is->waves_S++;
+    }
+    if (cb > 0 && nL[cb]) {
+      induce_wave(SA, T, bk.B[cb], nL[cb], true, (1u << cb) - 1u, Sc, ws, tot, st);
+      for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
+      is->waves_S++;
+    }
+  }
+  for (int s = 0; s < 4; s++)
+    if (Sc[s] != bk.B[s] + nL[s]) throw CudaError(-3, "internal: induction did not fill every bucket");
+}
+
+// lms sort of the prepared text: sorted long suffixes + ordered shorts + their insertion points
+struct SortedLms {
+  u32* longs = nullptr; u32 nl = 0;
+  u32* shorts = nullptr; u32* ins = nullptr; u32 ns = 0;
+};
+
+void do_shorts(kiss_b200_ctx* c, Pool& pool, const u32* shorts_text, u32 ns, const u32* longs, u32 nl,
+               const SortParams& sp, SortedLms* out) {
+  out->ns = ns;
+  if (!ns) return;
+  u32* rank0 = pool.alloc<u32>(ns);
+  out->shorts = pool.alloc<u32>(ns);
+  out->ins = pool.alloc<u32>(ns);
+  shorts_order(shorts_text, ns, sp, rank0, out->shorts, c->st);
+  shorts_insertions(out->shorts, ns, longs, nl, sp, out->ins, c->st);
+}
+
+void do_sort(kiss_b200_ctx* c, Pool& pool, SortedLms* out, SortStats* stats) {
+  auto& P = c->prep;
+  u32 ns = (u32)(P.m1 - P.n_long);
+  if (ns > SHORT_MAX)
+    throw CudaError(KISS_B200_ERR_UNSUPPORTED, "bounded k too large: more than 16384 LMS suffixes within D(k) of the text end");
+  // the shorts are the tail of the text-ordered list; copy them out before the sort permutes the buffers
+  u32* shorts_text = pool.alloc<u32>(ns);
+  if (ns) CK(cudaMemcpyAsync(shorts_text, P.pos + P.n_long, ns * sizeof(u32), cudaMemcpyDeviceToDevice, c->st));
+  u32* sorted;
+  sort_long_lms(c, pool, P.key, P.pos, P.n_long, P.sp, &sorted, stats);
+  out->longs = sorted;
+  out->nl = P.n_long;
+  do_shorts(c, pool, shorts_text, ns, sorted, P.n_long, P.sp, out);
+}
+
+void fill_timings(kiss_b200_timings* t, float pack, float lms, float sort, float put, float induce) {
+  t->pack = pack * 1e-3; t->get_lms = lms * 1e-3; t->lms_sort = sort * 1e-3; t->put_lms = put * 1e-3;
+  t->induce = induce * 1e-3;
+  t->total_device = t->pack + t->get_lms + t->lms_sort + t->put_lms + t->induce;
+}
+
+enum Stop { STOP_LMS, STOP_SORT, STOP_PUT, STOP_FULL };
+
+// the whole path on device-resident data; `stage_out` receives the stage's array when stopping early
+void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* dSA, Stop stop, kiss_b200_timings* t) {
+  cudaStream_t st = c->st;
+  u64 launches0 = g_launches;
+  float t_pack = 0, t_lms = 0, t_sort = 0, t_put = 0, t_ind = 0;
+  do_prepare(c, dS, n, k, algo, &t_pack, &t_lms);
+  auto& P = c->prep;
+  SortStats ss;
+  InduceStats is;
+  if (stop != STOP_LMS) {
+    Pool pool(st);
+    SortedLms sl;
+    CK(cudaEventRecord(c->ev[3], st));
+    do_sort(c, pool, &sl, &ss);
+    CK(cudaEventRecord(c->ev[4], st));
+    Buckets bk = make_buckets(P.counters, n);
+    if (stop == STOP_SORT) {
+      // merged list, sentinel first: "place" into a linear array
+      Buckets lin = bk;
+      lin.B[1] = P.m1 + 1; lin.lms_count[0] = P.m1; lin.lms_off[0] = 0;
+      lin.lms_off[1] = lin.lms_off[2] = lin.lms_off[3] = ~0ull;
+      place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, lin, n, dSA, st);
+    } else {
+      if (stop == STOP_PUT) CK(cudaMemsetAsync(dSA, 0xFF, (n + 1) * sizeof(u32), st));
+      place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, n, dSA, st);
+    }
+    CK(cudaEventRecord(c->ev[5], st));
+    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, dSA, &is);
+    CK(cudaEventRecord(c->ev[6], st));
+    CK(cudaEventSynchronize(c->ev[6]));
+    CK(cudaEventElapsedTime(&t_sort, c->ev[3], c->ev[4]));
+    CK(cudaEventElapsedTime(&t_put, c->ev[4], c->ev[5]));
+    CK(cudaEventElapsedTime(&t_ind, c->ev[5], c->ev[6]));
+  }
+  if (t) {
+    fill_timings(t, t_pack, t_lms, t_sort, t_put, t_ind);
+    t->n = n; t->m = P.m1 + 1;
+    t->lms_sort_tied = ss.tied; t->lms_sort_rounds = ss.rounds;
+    t->waves_L = is.waves_L; t->waves_S = is.waves_S;
+    t->kernel_launches = g_launches - launches0;
+  }
+}
+
+int check_n(u64 n) {
+  if (n + 1 >= 0xFFFFFFFFull) {
+    g_last_error = "text too long for 32-bit suffix indices (EMPTY = 0xFFFFFFFF is reserved)";
+    return KISS_B200_ERR_TOO_LARGE;
+  }
+  return 0;
+}
+
+template <typename F>
+int guarded(kiss_b200_ctx* c, F&& f) {
+  if (!c) { g_last_error = "null context"; return KISS_B200_ERR_ARG; }
+  try {
+    CK(cudaSetDevice(c->device));
+    f();
+    return KISS_B200_OK;
+  } catch (const CudaError& e) {
+    g_last_error = e.what();
+    cudaGetLastError();
+    return e.code;
+  } catch (const std::bad_alloc&) {
+    g_last_error = "host allocation failed";
+    return KISS_B200_ERR_NOMEM;
+  } catch (const std::exception& e) {
+    g_last_error = e.what();
+    return KISS_B200_ERR_CUDA;
+  }
+}
+
+double elapsed_s(kiss_b200_ctx* c, int a, int b) {
+  float ms = 0;
+  cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]);
+  return ms * 1e-3;
+}
+
+// host text -> device, run, device SA -> host
+void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* out_host, u64 out_count_hint, Stop stop,
+              bool ascii, kiss_b200_timings* t, uint64_t* m_out) {
+  cudaStream_t st = c->st;
+  Pool pool(st);
+  u8* dS = pool.alloc<u8>(n + 16);
+  cudaEvent_t e0, e1, e2, e3;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2)); CK(cudaEventCreate(&e3));
+  CK(cudaEventRecord(e0, st));
+  if (n) CK(cudaMemcpyAsync(dS, S_host, n, cudaMemcpyHostToDevice, st));
+  if (ascii) {
+    u8* dC = pool.alloc<u8>(n + 16);
+    ascii_to_codes(dS, n, dC, st);
+    dS = dC;
+  }
+  CK(cudaEventRecord(e1, st));
+  u64 out_n = (stop == STOP_LMS || stop == STOP_SORT) ? n / 2 + 2 : n + 1;
+  u32* dOut = pool.alloc<u32>(out_n);
+  kiss_b200_timings tt;
+  memset(&tt, 0, sizeof(tt));
+  run_pipeline(c, dS, n, k, algo, dOut, stop, &tt);
+  u64 m = c->prep.m1 + 1;
+  u64 cnt = out_n;
+  if (stop == STOP_LMS) {
+    // text-ordered list + sentinel
+    cnt = m;
+    if (c->prep.m1) CK(cudaMemcpyAsync(dOut, c->prep.pos, c->prep.m1 * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    u32 nn = (u32)n;
+    CK(cudaMemcpyAsync(dOut + c->prep.m1, &nn, sizeof(u32), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+  } else if (stop == STOP_SORT) {
+    cnt = m;
+  }
+  (void)out_count_hint;
+  CK(cudaEventRecord(e2, st));
+  if (out_host) CK(cudaMemcpyAsync(out_host, dOut, cnt * sizeof(u32), cudaMemcpyDeviceToHost, st));
+  CK(cudaEventRecord(e3, st));
+  CK(cudaEventSynchronize(e3));
+  float h2d = 0, d2h = 0;
+  cudaEventElapsedTime(&h2d, e0, e1);
+  cudaEventElapsedTime(&d2h, e2, e3);
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
+  tt.h2d = h2d * 1e-3; tt.d2h = d2h * 1e-3;
+  if (t) *t = tt;
+  if (m_out) *m_out = m;
+}
+
+}  // namespace
+
+// ======================================================================================= extern "C"
+extern "C" {
+
+int kiss_b200_abi_version(void) { return 1; }
+
+const char* kiss_b200_strerror(int code) {
+  switch (code) {
+    case KISS_B200_OK: return "ok";
+    case KISS_B200_ERR_ARG: return "invalid argument";
+    case KISS_B200_ERR_TOO_LARGE: return "text too large for 32-bit suffix indices";
+    case KISS_B200_ERR_CUDA: return "CUDA error";
+    case KISS_B200_ERR_NOMEM: return "out of memory";
+    case KISS_B200_ERR_UNSUPPORTED: return "unsupported k";
+    case KISS_B200_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
+    default: return "unknown error";
+  }
+}
+
+const char* kiss_b200_last_error(void) { return g_last_error.c_str(); }
+
+int kiss_b200_create(kiss_b200_ctx** out, int device) {
+  if (!out) { g_last_error = "null out pointer"; return KISS_B200_ERR_ARG; }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0 || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    g_last_error = std::string("no usable CUDA device ") + std::to_string(device) + " (" +
+                   (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0 or index out of range") +
+                   "); kiss_b200 has no CPU fallback";
+    return KISS_B200_ERR_NO_DEVICE;
+  }
+  kiss_b200_ctx* c = new kiss_b200_ctx();
+  c->device = device;
+  try {
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    for (auto& ev : c->ev) CK(cudaEventCreate(&ev));
+    CK(cudaHostAlloc((void**)&c->pinned, 64 * sizeof(u32), cudaHostAllocDefault));
+    cudaMemPool_t mp;
+    CK(cudaDeviceGetDefaultMemPool(&mp, device));
+    u64 thr = ~0ull;  // keep freed scratch cached in the pool between calls
+    CK(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &thr));
+    radix_init();
+  } catch (const CudaError& err) {
+    g_last_error = err.what();
+    delete c;
+    return err.code;
+  }
+  *out = c;
+  return KISS_B200_OK;
+}
+
+void kiss_b200_destroy(kiss_b200_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  free_prepared(c);
+  if (c->st) cudaStreamSynchronize(c->st);
+  for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+  if (c->pinned) cudaFreeHost(c->pinned);
+  if (c->st) cudaStreamDestroy(c->st);
+  delete c;
+}
+
+void* kiss_b200_stream(kiss_b200_ctx* c) { return c ? (void*)c->st : nullptr; }
+
+static int trivial_n0(u32* SA_host, kiss_b200_timings* t) {
+  if (SA_host) SA_host[0] = 0;  // kiss1_core.hpp:237-238
+  if (t) { memset(t, 0, sizeof(*t)); t->m = 1; }
+  return KISS_B200_OK;
+}
+
+int kiss_b200_suffix_sort_dna_u32(kiss_b200_ctx* c, const uint8_t* S_host, uint64_t n, uint32_t k, int algo,
+                                  uint32_t* SA_host, kiss_b200_timings* t) {
+  if (!SA_host || (n && !S_host) || (algo != 0 && algo != 1)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  if (n == 0) return c ? trivial_n0(SA_host, t) : KISS_B200_ERR_ARG;
+  return guarded(c, [&] { run_host(c, S_host, n, k, algo, SA_host, n + 1, STOP_FULL, false, t, nullptr); });
+}
+
+int kiss_b200_suffix_sort_ascii_u32(kiss_b200_ctx* c, const char* seq_host, uint64_t n, uint32_t k, int algo,
+                                    uint32_t* SA_host, kiss_b200_timings* t) {
+  if (!SA_host || (n && !seq_host) || (algo != 0 && algo != 1)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  if (n == 0) return c ? trivial_n0(SA_host, t) : KISS_B200_ERR_ARG;
+  return guarded(c, [&] { run_host(c, (const u8*)seq_host, n, k, algo, SA_host, n + 1, STOP_FULL, true, t, nullptr); });
+}
+
+int kiss_b200_suffix_sort_dna_u32_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, uint32_t k, int algo,
+                                      uint32_t* SA_dev, kiss_b200_timings* t) {
+  if (!SA_dev || (n && !S_dev) || (algo != 0 && algo != 1)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (((uintptr_t)S_dev & 15) != 0) { g_last_error = "S_dev must be 16-byte aligned"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  return guarded(c, [&] {
+    if (n == 0) {
+      CK(cudaMemsetAsync(SA_dev, 0, sizeof(u32), c->st));
+      CK(cudaStreamSynchronize(c->st));
+      if (t) { memset(t, 0, sizeof(*t)); t->m = 1; }
+      return;
+    }
+    run_pipeline(c, S_dev, n, k, algo, SA_dev, STOP_FULL, t);
+    free_prepared(c);
+  });
+}
+
+int kiss_b200_get_lms(kiss_b200_ctx* c, const uint8_t* S_host, uint64_t n, uint32_t* lms_host, uint64_t* m_out,
+                      uint64_t* count4, uint64_t* lms_count4) {
+  if (n && !S_host) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  if (n == 0) {
+    if (lms_host) lms_host[0] = 0;
+    if (m_out) *m_out = 1;
+    for (int s = 0; s < 4; s++) { if (count4) count4[s] = 0; if (lms_count4) lms_count4[s] = 0; }
+    return KISS_B200_OK;
+  }
+  return guarded(c, [&] {
+    run_host(c, S_host, n, 0xFFFFFFFFu, 0, lms_host, 0, STOP_LMS, false, nullptr, m_out);
+    for (int s = 0; s < 4; s++) {
+      if (count4) count4[s] = c->prep.counters[s];
+      if (lms_count4) lms_count4[s] = c->prep.counters[4 + s];
+    }
+    free_prepared(c);
+  });
+}
+
+int kiss_b200_sorted_lms(kiss_b200_ctx* c, const uint8_t* S_host, uint64_t n, uint32_t k, int algo,
+                         uint32_t* sorted_host, uint64_t* m_out) {
+  if (!sorted_host || (n && !S_host) || (algo != 0 && algo != 1)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  if (n == 0) { sorted_host[0] = 0; if (m_out) *m_out = 1; return KISS_B200_OK; }
+  return guarded(c, [&] {
+    run_host(c, S_host, n, k, algo, sorted_host, 0, STOP_SORT, false, nullptr, m_out);
+    free_prepared(c);
+  });
+}
+
+int kiss_b200_put_lms(kiss_b200_ctx* c, const uint8_t* S_host, uint64_t n, uint32_t k, int algo, uint32_t* SA_host) {
+  if (!SA_host || (n && !S_host) || (algo != 0 && algo != 1)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  if (n == 0) { SA_host[0] = 0; return KISS_B200_OK; }
+  return guarded(c, [&] {
+    run_host(c, S_host, n, k, algo, SA_host, 0, STOP_PUT, false, nullptr, nullptr);
+    free_prepared(c);
+  });
+}
+
+int kiss_b200_induce_from_sorted_lms(kiss_b200_ctx* c, const uint8_t* S_host, uint64_t n, const uint32_t* sorted_host,
+                                     uint64_t m, uint32_t* SA_host) {
+  if (!SA_host || !sorted_host || (n && !S_host) || m == 0) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  if (n == 0) { SA_host[0] = 0; return KISS_B200_OK; }
+  return guarded(c, [&] {
+    cudaStream_t st = c->st;
+    Pool pool(st);
+    u8* dS = pool.alloc<u8>(n + 16);
+    CK(cudaMemcpyAsync(dS, S_host, n, cudaMemcpyHostToDevice, st));
+    do_prepare(c, dS, n, 0xFFFFFFFFu, 0, nullptr, nullptr);
+    if (c->prep.m1 + 1 != m) throw CudaError(KISS_B200_ERR_ARG, "sorted list length differs from the LMS count of the text");
+    u32* dsorted = pool.alloc<u32>(m);
+    CK(cudaMemcpyAsync(dsorted, sorted_host, m * sizeof(u32), cudaMemcpyHostToDevice, st));
+    u32* dSA = pool.alloc<u32>(n + 1);
+    Buckets bk = make_buckets(c->prep.counters, n);
+    place_sorted(dsorted + 1, (u32)(m - 1), bk, n, dSA, st);
+    InduceStats is;
+    do_induce(c, pool, c->prep.T, n, bk, dSA, &is);
+    CK(cudaMemcpyAsync(SA_host, dSA, (n + 1) * sizeof(u32), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    free_prepared(c);
+  });
+}
+
+int kiss_b200_prepare_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, uint32_t k, uint64_t* m_out) {
+  if (!S_dev || n == 0) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  return guarded(c, [&] {
+    do_prepare(c, S_dev, n, k, 0, nullptr, nullptr);
+    if (m_out) *m_out = c->prep.m1 + 1;
+  });
+}
+
+int kiss_b200_lms_keys_dev(kiss_b200_ctx* c, const uint32_t** keys_dev, const uint32_t** pos_dev, uint64_t* n_long) {
+  if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
+  if (keys_dev) *keys_dev = c->prep.key;
+  if (pos_dev) *pos_dev = c->prep.pos;
+  if (n_long) *n_long = c->prep.n_long;
+  return KISS_B200_OK;
+}
+
+int kiss_b200_sort_lms_subset_dev(kiss_b200_ctx* c, uint32_t* pos_dev, uint64_t count, kiss_b200_timings* t) {
+  if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
+  if (count && !pos_dev) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (count > 0x80000000ull) { g_last_error = "subset too large"; return KISS_B200_ERR_TOO_LARGE; }
+  return guarded(c, [&] {
+    cudaStream_t st = c->st;
+    Pool pool(st);
+    u64 l0 = g_launches;
+    CK(cudaEventRecord(c->ev[3], st));
+    u32* key = pool.alloc<u32>(count);
+    gather_keys(c->prep.sp.T, pos_dev, (u32)count, key, st);
+    u32* sorted;
+    SortStats ss;
+    sort_long_lms(c, pool, key, pos_dev, (u32)count, c->prep.sp, &sorted, &ss);
+    if (sorted != pos_dev && count)
+      CK(cudaMemcpyAsync(pos_dev, sorted, count * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    CK(cudaEventRecord(c->ev[4], st));
+    CK(cudaEventSynchronize(c->ev[4]));
+    if (t) {
+      memset(t, 0, sizeof(*t));
+      t->lms_sort = elapsed_s(c, 3, 4);
+      t->total_device = t->lms_sort;
+      t->n = c->prep.n; t->m = c->prep.m1 + 1;
+      t->lms_sort_tied = ss.tied; t->lms_sort_rounds = ss.rounds;
+      t->kernel_launches = g_launches - l0;
+    }
+  });
+}
+
+int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_long_dev, uint64_t n_long,
+                                     uint32_t* SA_dev, kiss_b200_timings* t) {
+  if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
+  if (!SA_dev || (n_long && !sorted_long_dev) || n_long != c->prep.n_long) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  return guarded(c, [&] {
+    cudaStream_t st = c->st;
+    Pool pool(st);
+    auto& P = c->prep;
+    u64 l0 = g_launches;
+    u32 ns = (u32)(P.m1 - P.n_long);
+    if (ns > SHORT_MAX) throw CudaError(KISS_B200_ERR_UNSUPPORTED, "bounded k too large");
+    CK(cudaEventRecord(c->ev[4], st));
+    SortedLms sl;
+    sl.longs = const_cast<u32*>(sorted_long_dev);
+    sl.nl = P.n_long;
+    do_shorts(c, pool, P.pos + P.n_long, ns, sorted_long_dev, P.n_long, P.sp, &sl);
+    Buckets bk = make_buckets(P.counters, P.n);
+    place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, P.n, SA_dev, st);
+    CK(cudaEventRecord(c->ev[5], st));
+    InduceStats is;
+    do_induce(c, pool, P.T, P.n, bk, SA_dev, &is);
+    CK(cudaEventRecord(c->ev[6], st));
+    CK(cudaEventSynchronize(c->ev[6]));
+    if (t) {
+      memset(t, 0, sizeof(*t));
+      t->put_lms = elapsed_s(c, 4, 5);
+      t->induce = elapsed_s(c, 5, 6);
+      t->total_device = t->put_lms + t->induce;
+      t->n = P.n; t->m = P.m1 + 1;
+      t->waves_L = is.waves_L; t->waves_S = is.waves_S;
+      t->kernel_launches = g_launches - l0;
+    }
+  });
+}
+
+int kiss_b200_synth_uniform_dev(kiss_b200_ctx* c, uint8_t* S_dev, uint64_t n, uint64_t seed) {
+  if (!S_dev && n) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  return guarded(c, [&] {
+    synth_uniform(S_dev, n, seed, c->st);
+    CK(cudaStreamSynchronize(c->st));
+  });
+}
+
+}  // extern "C"

@@ -1,0 +1,226 @@
+// induce.cu — K4 placement and K5 induction.
+//
+// Replaces put_lms_suffix (kiss_common.hpp:445-481) and induced_sort (kiss_common.hpp:422-442: induced_L
+// 372-403 / 226-246, induced_clear 405-420, induced_S 192-224 / 40-61).
+//
+// The reference scans SA slot by slot and, for a filled slot v, appends v-1 to the cursor of its bucket when
+// the type test holds (L pass: S[v-1] >= S[v], :241; S pass: S[v-1] <= S[v], :55-56).  A maximal run of filled
+// slots can be processed as one *wave* (the reference's own block scheme, :389-393 / :209-213): everything a
+// wave appends lands on slots that were empty when the wave was cut.  Here a wave is a stable 4-way multisplit
+// on the GPU: per 2048-entry tile count the induced suffixes per symbol, scan the tile counts, scatter with
+// ballot ranks.  Wave boundaries are the bucket cursors themselves, so no EMPTY markers, no induced_clear and
+// none of the reference's artefact EMPTY writes (:241) are needed; the S pass overwrites the LMS slots.
+// SURVEY.md A.4 holds the equivalence argument; tests/model_gpu_algo.py is the same schedule in numpy.
+//
+// Algorithmic bytes per scanned entry: 4 (SA read) + 0.25 (packed text, random) + 4 per induced suffix.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace kiss {
+
+// ------------------------------------------------------------------------------------------- placement
+__device__ __forceinline__ u64 lms_slot(const Buckets& bk, u64 r) {
+  // r = rank among the sorted LMS suffixes (sentinel excluded); they are grouped by first symbol
+  int c = 0;
+#pragma unroll
+  for (int s = 1; s < 4; s++)
+    if (r >= bk.lms_off[s]) c = s;
+  return bk.B[c + 1] - bk.lms_count[c] + (r - bk.lms_off[c]);
+}
+
+__global__ void __launch_bounds__(256) k_place_lms(const u32* __restrict__ longs, u32 nl,
+                                                  const u32* __restrict__ sorted_shorts, const u32* __restrict__ ins,
+                                                  u32 ns, Buckets bk, u64 n, u32* __restrict__ SA) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) SA[0] = (u32)n;
+  if (i < nl) {
+    // shorts emitted before long i: those with ins <= i  (ins is non-decreasing)
+    u32 lo = 0, hi = ns;
+    while (lo < hi) {
+      u32 mid = lo + (hi - lo) / 2;
+      if (ins[mid] <= (u32)i) lo = mid + 1; else hi = mid;
+    }
+    SA[lms_slot(bk, i + lo)] = longs[i];
+  } else if (i < (u64)nl + ns) {
+    u32 s = (u32)(i - nl);
+    SA[lms_slot(bk, (u64)ins[s] + s)] = sorted_shorts[s];
+  }
+}
+
+void place_lms(const u32* longs, u32 nl, const u32* sorted_shorts, const u32* ins, u32 ns, Buckets bk, u64 n, u32* SA,
+               cudaStream_t st) {
+  u64 tot = (u64)nl + ns;
+  if (tot == 0) tot = 1;
+  k_place_lms<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(longs, nl, sorted_shorts, ins, ns, bk, n, SA);
+  CK_LAUNCH(); g_launches++;
+}
+
+void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, cudaStream_t st) {
+  place_lms(sorted, cnt, nullptr, nullptr, 0, bk, n, SA, st);
+}
+
+// ------------------------------------------------------------------------------------------- waves
+#define WAVE_THREADS 256
+#define WAVE_ITEMS 8
+#define WAVE_WARPS 8
+
+struct WaveArgs {
+  u32* SA;
+  const u64* T;
+  u64 lo;       // first slot of the wave
+  u64 len;      // number of slots
+  u32 down;     // scan from the top slot downwards
+  u32 symmask;  // symbols that may be induced
+  u64 cur[4];   // bucket cursors
+};
+
+// symbol (0..3) the entry at logical index j induces into, or 4
+__device__ __forceinline__ u32 wave_symbol(const WaveArgs& a, u64 j, u32& v) {
+  u64 slot = a.down ? a.lo + a.len - 1 - j : a.lo + j;
+  v = a.SA[slot];
+  if (v == 0 || v == KISS_EMPTY) return 4;
+  u32 c = base_at(a.T, (u64)v - 1);
+  return ((a.symmask >> c) & 1u) ? c : 4u;
+}
+
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_count(WaveArgs a, u8* __restrict__ side, u32* __restrict__ C,
+                                                            u32 ntiles) {
+  __shared__ u32 wsum[WAVE_WARPS][4];
+  const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const u64 j0 = (u64)blockIdx.x * WAVE_TILE + w * (32 * WAVE_ITEMS);
+  u32 cnt[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int r = 0; r < WAVE_ITEMS; r++) {
+    u64 j = j0 + r * 32 + lane;
+    u32 cu = 4, v;
+    if (j < a.len) {
+      cu = wave_symbol(a, j, v);
+      side[j] = (u8)cu;
+    }
+#pragma unroll
+    for (u32 s = 0; s < 4; s++) cnt[s] += __popc(__ballot_sync(0xffffffffu, cu == s));
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < 4; s++) wsum[w][s] = cnt[s];
+  }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    u32 t = 0;
+#pragma unroll
+    for (int ww = 0; ww < WAVE_WARPS; ww++) t += wsum[ww][threadIdx.x];
+    C[(u64)threadIdx.x * ntiles + blockIdx.x] = t;
+  }
+}
+
+// per-symbol totals from the scanned counter matrix
+__global__ void k_wave_totals(const u32* __restrict__ E, u32 ntiles, const u32* __restrict__ grand, u32* __restrict__ tot) {
+  u32 s = threadIdx.x;
+  if (s < 4) {
+    u32 beg = E[(u64)s * ntiles];
+    u32 end = (s < 3) ? E[(u64)(s + 1) * ntiles] : *grand;
+    tot[s] = end - beg;
+  }
+}
+
+// shared by the tiled and the single-block kernels: rank and write the tile's induced suffixes
+__device__ __forceinline__ void wave_scatter_tile(const WaveArgs& a, const u8* __restrict__ side, u64 tile,
+                                                  const u32 tile_off[4], u32 (*wsum)[4]) {
+  const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const u64 j0 = tile * WAVE_TILE + w * (32 * WAVE_ITEMS);
+  const u32 lt = (1u << lane) - 1u;
+  u32 sym[WAVE_ITEMS];
+  u32 cnt[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int r = 0; r < WAVE_ITEMS; r++) {
+    u64 j = j0 + r * 32 + lane;
+    u32 cu = (j < a.len) ? (u32)side[j] : 4u;
+    sym[r] = cu;
+#pragma unroll
+    for (u32 s = 0; s < 4; s++) cnt[s] += __popc(__ballot_sync(0xffffffffu, cu == s));
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < 4; s++) wsum[w][s] = cnt[s];
+  }
+  __syncthreads();
+  u32 run[4];
+#pragma unroll
+  for (int s = 0; s < 4; s++) {
+    u32 t = tile_off[s];
+    for (u32 ww = 0; ww < w; ww++) t += wsum[ww][s];
+    run[s] = t;
+  }
+#pragma unroll
+  for (int r = 0; r < WAVE_ITEMS; r++) {
+    u64 j = j0 + r * 32 + lane;
+    u32 cu = sym[r];
+    u32 b0 = __ballot_sync(0xffffffffu, cu == 0), b1 = __ballot_sync(0xffffffffu, cu == 1);
+    u32 b2 = __ballot_sync(0xffffffffu, cu == 2), b3 = __ballot_sync(0xffffffffu, cu == 3);
+    if (cu < 4) {
+      u32 bm = cu == 0 ? b0 : cu == 1 ? b1 : cu == 2 ? b2 : b3;
+      u32 off = (cu == 0 ? run[0] : cu == 1 ? run[1] : cu == 2 ? run[2] : run[3]) + __popc(bm & lt);
+      u64 slot = a.down ? a.lo + a.len - 1 - j : a.lo + j;
+      u32 v = a.SA[slot];
+      u64 cur = cu == 0 ? a.cur[0] : cu == 1 ? a.cur[1] : cu == 2 ? a.cur[2] : a.cur[3];
+      u64 dst = a.down ? cur - 1 - off : cur + off;
+      a.SA[dst] = v - 1;
+    }
+    run[0] += __popc(b0); run[1] += __popc(b1); run[2] += __popc(b2); run[3] += __popc(b3);
+  }
+}
+
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_scatter(WaveArgs a, const u8* __restrict__ side,
+                                                              const u32* __restrict__ E, u32 ntiles) {
+  __shared__ u32 wsum[WAVE_WARPS][4];
+  u32 tile_off[4];
+#pragma unroll
+  for (int s = 0; s < 4; s++) tile_off[s] = E[(u64)s * ntiles + blockIdx.x] - E[(u64)s * ntiles];
+  wave_scatter_tile(a, side, blockIdx.x, tile_off, wsum);
+}
+
+// a wave of at most one tile: count + scatter in one block, totals written to tot[4]
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_small(WaveArgs a, u8* __restrict__ side, u32* __restrict__ tot) {
+  __shared__ u32 wsum[WAVE_WARPS][4];
+  for (u32 j = threadIdx.x; j < a.len; j += WAVE_THREADS) {
+    u32 v;
+    side[j] = (u8)wave_symbol(a, j, v);
+  }
+  __syncthreads();
+  u32 tile_off[4] = {0, 0, 0, 0};
+  wave_scatter_tile(a, side, 0, tile_off, wsum);
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    u32 t = 0;
+    for (int ww = 0; ww < WAVE_WARPS; ww++) t += wsum[ww][threadIdx.x];
+    tot[threadIdx.x] = t;
+  }
+}
+
+void induce_wave(u32* SA, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4], WaveScratch ws,
+                 u32 tot[4], cudaStream_t st) {
+  tot[0] = tot[1] = tot[2] = tot[3] = 0;
+  if (len == 0) return;
+  WaveArgs a;
+  a.SA = SA; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
+  for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
+  if (len <= WAVE_TILE) {
+    k_wave_small<<<1, WAVE_THREADS, 0, st>>>(a, ws.side, ws.tot_dev);
+    CK_LAUNCH(); g_launches++;
+  } else {
+    u32 ntiles = (u32)wave_tiles(len);
+    k_wave_count<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.side, ws.C, ntiles);
+    CK_LAUNCH();
+    scan_excl_u32(ws.C, (u64)4 * ntiles, ws.partials, ws.scan_total, st);
+    k_wave_totals<<<1, 32, 0, st>>>(ws.C, ntiles, ws.scan_total, ws.tot_dev);
+    CK_LAUNCH();
+    k_wave_scatter<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.side, ws.C, ntiles);
+    CK_LAUNCH();
+    g_launches += 3;
+  }
+  CK(cudaMemcpyAsync(ws.tot_host, ws.tot_dev, 4 * sizeof(u32), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  for (int s = 0; s < 4; s++) tot[s] = ws.tot_host[s];
+}
+
+}  // namespace kiss

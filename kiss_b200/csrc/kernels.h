@@ -1,0 +1,129 @@
+// kernels.h — host-side launchers of the sm_100a kernels (internal; the public boundary is
+// include/kiss_b200.h).  Every launcher enqueues on `st` and never synchronises unless it says so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <stdexcept>
+#include <string>
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+typedef unsigned char u8;
+
+namespace kiss {
+
+struct CudaError : std::runtime_error {
+  int code;
+  CudaError(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+void cuda_check(cudaError_t e, const char* what, const char* file, int line);
+#define CK(x) ::kiss::cuda_check((x), #x, __FILE__, __LINE__)
+#define CK_LAUNCH() ::kiss::cuda_check(cudaGetLastError(), "kernel launch", __FILE__, __LINE__)
+
+extern thread_local u64 g_launches;  // kernels launched by this thread (reported as gpu_launches)
+
+// ---------------------------------------------------------------- scan.cu
+// in-place exclusive prefix sum of data[0..N); `partials` needs N/4096 + 2 entries of scratch;
+// the grand total goes to *total_dev when non-null.
+void scan_excl_u32(u32* data, u64 N, u32* partials, u32* total_dev, cudaStream_t st);
+inline u64 scan_partials_len(u64 N) { return N / 4096 + 2; }
+
+// ---------------------------------------------------------------- radix.cu
+// Stable LSD radix sort of (key, val) pairs on key bits [bit_lo, bit_hi), 8 bits per pass.
+// Buffers are swapped per pass; on return keys/vals point at the sorted data.
+// H needs 256 * ceil(N/4096) entries, partials scan_partials_len(that).
+inline u64 radix_tiles(u64 N) { return (N + 4095) / 4096; }
+void radix_sort_u32(u32*& keys, u32*& vals, u32*& keys_alt, u32*& vals_alt, u32 N, int bit_lo, int bit_hi,
+                    u32* H, u32* partials, cudaStream_t st);
+void radix_sort_u64(u64*& keys, u32*& vals, u64*& keys_alt, u32*& vals_alt, u32 N, int bit_lo, int bit_hi,
+                    u32* H, u32* partials, cudaStream_t st);
+void radix_init();  // opt in to > 48 KB dynamic shared memory (once per process)
+
+// ---------------------------------------------------------------- pack.cu
+u64 packed_words(u64 n);  // words in the packed text including padding
+void pack_codes(const u8* S, u64 n, u64* T, cudaStream_t st);
+void ascii_to_codes(const u8* ascii, u64 n, u8* S, cudaStream_t st);
+void synth_uniform(u8* S, u64 n, u64 seed, cudaStream_t st);
+
+// ---------------------------------------------------------------- lms.cu
+#define LMS_CHUNK_WORDS 64ull
+inline u64 lms_chunks(u64 n) { return ((n + 31) / 32 + LMS_CHUNK_WORDS - 1) / LMS_CHUNK_WORDS; }
+// Classify + count: fills lmsmask (one u64 per text word, low field bits), chunk_cnt (LMS per chunk) and
+// counters[8] = count[4], lms_count[4] (must be zeroed by the caller).  gp: 1 byte per chunk of scratch.
+void lms_classify(const u64* T, u64 n, u8* gp, u64* lmsmask, u32* chunk_cnt, u64* counters, cudaStream_t st);
+// Emit LMS positions (ascending) and their first-16-base keys from lmsmask and the exclusive chunk offsets.
+void lms_emit(const u64* T, u64 n, const u64* lmsmask, const u32* chunk_off, u32* pos, u32* key, cudaStream_t st);
+// *out = number of entries of the ascending list pos[0..cnt) that are <= limit
+void count_le(const u32* pos, u32 cnt, u32 limit, u32* out, cudaStream_t st);
+
+// ---------------------------------------------------------------- lms_sort.cu
+struct SortParams {
+  const u64* T;
+  u64 n;
+  u64 D;  // comparison depth in bases; KISS_UNBOUNDED = compare to the end of the text
+  u32 k;  // the caller's k (only the short-suffix comparator needs it)
+};
+#define KISS_UNBOUNDED 0xFFFFFFFFFFFFFFFFull
+#define TINY_MAX 8u
+#define MED_MAX 2048u
+
+struct GroupLists {  // device
+  u32* glist;        // starts of groups larger than TINY_MAX
+  u32 gcap;
+  u32* med;          // (start, size) pairs
+  u32* big;          // (start, size) pairs
+  u32* counters;     // [0] = #glist, [1] = #med, [2] = #big, [3] = overflow flag
+  u64* tied;         // statistics: elements found in groups
+};
+void groups_tiny_u32(const u32* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st);
+void groups_tiny_u64(const u64* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st);
+void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st);
+void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st);
+void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st);
+// sizes[g] = big[2g+1]
+void big_sizes(const u32* big, u32 nbig, u32* sizes, cudaStream_t st);
+// worklist of the big groups: wkey = gid << 33 | (1 + next 16 bases at depth h, or 0 when the suffix has
+// ended), wpos = suffix, wslot = slot in the main array
+void big_fill(const u32* pos_prev, const u32* slot_prev, const u32* big, const u32* boff, u32 nbig, SortParams sp,
+              u64 h, u64* wkey, u32* wpos, u32* wslot, cudaStream_t st);
+void big_writeback(u32* pos_main, const u32* wslot, const u32* wpos, u32 total, cudaStream_t st);
+
+// key[i] = first 16 bases of suffix pos[i]
+void gather_keys(const u64* T, const u32* pos, u32 N, u32* key, cudaStream_t st);
+
+// short suffixes (fewer than D bases left): exact reference comparator (kiss1_core.hpp:94-135)
+void shorts_order(const u32* shorts, u32 ns, SortParams sp, u32* rank0, u32* sorted_shorts, cudaStream_t st);
+void shorts_insertions(const u32* sorted_shorts, u32 ns, const u32* longs, u32 nl, SortParams sp, u32* ins,
+                       cudaStream_t st);
+
+// ---------------------------------------------------------------- induce.cu
+struct Buckets {
+  u64 B[5];          // bucket starts in SA; B[4] = n + 1
+  u64 lms_count[4];
+  u64 lms_off[4];    // exclusive prefix of lms_count
+};
+// K4: merge the sorted long LMS suffixes with the inserted short ones and drop them at their bucket ends
+void place_lms(const u32* longs, u32 nl, const u32* sorted_shorts, const u32* ins, u32 ns, Buckets bk, u64 n,
+               u32* SA, cudaStream_t st);
+// place an already complete order (sentinel excluded)
+void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, cudaStream_t st);
+
+struct WaveScratch {
+  u8* side;    // one byte per entry of the largest wave
+  u32* C;      // 4 * tiles counters
+  u32* partials;
+  u32* scan_total;
+  u32* tot_dev;   // 4
+  u32* tot_host;  // 4, pinned
+};
+#define WAVE_TILE 2048u
+inline u64 wave_tiles(u64 len) { return (len + WAVE_TILE - 1) / WAVE_TILE; }
+// One induction wave over SA[lo, lo+len) (scanned downwards when `down`): every entry v > 0 whose preceding
+// symbol S[v-1] is in `symmask` appends v-1 at cur[S[v-1]] (upwards) or below it (downwards).  Synchronises
+// the stream and returns the per-symbol counts in tot[4].
+void induce_wave(u32* SA, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4], WaveScratch ws,
+                 u32 tot[4], cudaStream_t st);
+
+}  // namespace kiss

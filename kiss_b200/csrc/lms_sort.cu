@@ -1,0 +1,317 @@
+// lms_sort.cu — K3: the k-ordered LMS sort beyond the first radix key.
+//
+// Replaces lms_suffix_direct_sort_dna (kiss1_core.hpp:23-145).  The reference's order is:
+// the first D(k) = 125 * (k/125 + 1) bases, then the text position — the comparator lambda
+// (kiss1_core.hpp:94-135) compares whole 125-base blocks while sorted_len <= k.  For suffixes with fewer than
+// D(k) bases left the lambda's depth shrinks; those few ("short" suffixes, at most D/2 of them) are ordered
+// with a literal restatement of the lambda and inserted into the sorted long ones.
+//
+// After the stable LSD radix sort on the first 16 bases (radix.cu) equal keys are adjacent and in ascending
+// text position.  Groups of equal keys are finished by size:
+//   tiny   (<= 8)     one thread, insertion sort with the word-wise suffix comparator
+//   medium (<= 2048)  one block, bitonic sort in shared memory with the same comparator
+//   big               radix rounds: composite key (group id, next 16 bases) sorted with the LSD sort, the
+//                     resulting sub-groups go through the same three cases at the next depth
+// All paths are stable with respect to text position, which is the reference's final tie-break (:131-133).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace kiss {
+
+// true iff suffix p sorts before suffix q; both are known equal on their first h bases.
+// Bounded mode: both suffixes have at least D bases.  Unbounded (D = KISS_UNBOUNDED): the shorter suffix
+// first when one is a prefix of the other (kiss1_core.hpp:134).
+__device__ __forceinline__ bool suffix_less(const SortParams& sp, u32 p, u32 q, u64 h) {
+  for (u64 off = h; off < sp.D; off += 32) {
+    if ((u64)p + off >= sp.n || (u64)q + off >= sp.n) return p > q;
+    u64 a = word_at(sp.T, (u64)p + off), b = word_at(sp.T, (u64)q + off);
+    u64 rem = sp.D - off;
+    if (rem < 32) {
+      u64 mk = ~0ull << (64 - 2 * rem);
+      a &= mk;
+      b &= mk;
+    }
+    if (a != b) return a < b;
+  }
+  return p < q;
+}
+
+// ------------------------------------------------------------------------------------------- tiny groups
+template <typename K>
+__global__ void __launch_bounds__(256) k_groups_tiny(const K* __restrict__ keys, u32* __restrict__ pos, u32 N,
+                                                    SortParams sp, u64 h, GroupLists gl) {
+  u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  K k = keys[i];
+  if (i > 0 && keys[i - 1] == k) return;        // not a group head
+  if (i + 1 >= N || keys[i + 1] != k) return;   // singleton
+  u32 g = 2;
+  while (g <= TINY_MAX && i + g < N && keys[i + g] == k) g++;
+  if (g > TINY_MAX) {
+    u32 idx = atomicAdd(&gl.counters[0], 1u);
+    if (idx < gl.gcap) gl.glist[idx] = i; else gl.counters[3] = 1;
+    return;
+  }
+  atomicAdd(gl.tied, (u64)g);
+  if (h >= sp.D) return;  // fully compared: the stable order (ascending position) is final
+  for (u32 a = 1; a < g; a++) {
+    u32 x = pos[i + a];
+    u32 b = a;
+    while (b > 0) {
+      u32 y = pos[i + b - 1];
+      if (!suffix_less(sp, x, y, h)) break;
+      pos[i + b] = y;
+      b--;
+    }
+    pos[i + b] = x;
+  }
+}
+
+template <typename K>
+__global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ keys, u32 N, u32 ng, GroupLists gl) {
+  u32 g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= ng) return;
+  u64 start = gl.glist[g];
+  K k = keys[start];
+  // keys[start + TINY_MAX] == k is known; gallop, then bisect for the first index whose key differs
+  u64 lo = start + TINY_MAX, hi, step = TINY_MAX;
+  for (;;) {
+    u64 nx = lo + step;
+    if (nx >= N) { hi = N; break; }
+    if (keys[nx] != k) { hi = nx; break; }
+    lo = nx;
+    step <<= 1;
+  }
+  while (hi - lo > 1) {
+    u64 mid = lo + (hi - lo) / 2;
+    if (keys[mid] == k) lo = mid; else hi = mid;
+  }
+  u32 size = (u32)(hi - start);
+  atomicAdd(gl.tied, (u64)size);
+  if (size <= MED_MAX) {
+    u32 j = atomicAdd(&gl.counters[1], 1u);
+    gl.med[2 * j] = (u32)start;
+    gl.med[2 * j + 1] = size;
+  } else {
+    u32 j = atomicAdd(&gl.counters[2], 1u);
+    gl.big[2 * j] = (u32)start;
+    gl.big[2 * j + 1] = size;
+  }
+}
+
+void groups_tiny_u32(const u32* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st) {
+  if (!N) return;
+  k_groups_tiny<u32><<<(N + 255) / 256, 256, 0, st>>>(keys, pos, N, sp, h, gl);
+  CK_LAUNCH(); g_launches++;
+}
+void groups_tiny_u64(const u64* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st) {
+  if (!N) return;
+  k_groups_tiny<u64><<<(N + 255) / 256, 256, 0, st>>>(keys, pos, N, sp, h, gl);
+  CK_LAUNCH(); g_launches++;
+}
+void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st) {
+  if (!ng) return;
+  k_groups_classify<u32><<<(ng + 127) / 128, 128, 0, st>>>(keys, N, ng, gl);
+  CK_LAUNCH(); g_launches++;
+}
+void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st) {
+  if (!ng) return;
+  k_groups_classify<u64><<<(ng + 127) / 128, 128, 0, st>>>(keys, N, ng, gl);
+  CK_LAUNCH(); g_launches++;
+}
+
+// ------------------------------------------------------------------------------------------- medium groups
+__global__ void __launch_bounds__(256) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med, u32 nmed,
+                                                      SortParams sp, u64 h) {
+  __shared__ u32 s[MED_MAX];
+  for (u32 gi = blockIdx.x; gi < nmed; gi += gridDim.x) {
+    u32 start = med[2 * gi], size = med[2 * gi + 1];
+    u32 P = 16;
+    while (P < size) P <<= 1;
+    for (u32 i = threadIdx.x; i < P; i += blockDim.x) s[i] = i < size ? pos[start + i] : KISS_EMPTY;
+    __syncthreads();
+    for (u32 k2 = 2; k2 <= P; k2 <<= 1) {
+      for (u32 j = k2 >> 1; j > 0; j >>= 1) {
+        for (u32 i = threadIdx.x; i < P; i += blockDim.x) {
+          u32 ixj = i ^ j;
+          if (ixj > i) {
+            u32 a = s[i], b = s[ixj];
+            bool asc = (i & k2) == 0;
+            // b_before_a: must the pair be swapped for ascending order?
+            bool b_lt_a;
+            if (b == KISS_EMPTY) b_lt_a = false;
+            else if (a == KISS_EMPTY) b_lt_a = true;
+            else b_lt_a = suffix_less(sp, b, a, h);
+            if (b_lt_a == asc) { s[i] = b; s[ixj] = a; }
+          }
+        }
+        __syncthreads();
+      }
+    }
+    for (u32 i = threadIdx.x; i < size; i += blockDim.x) pos[start + i] = s[i];
+    __syncthreads();
+  }
+}
+
+void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st) {
+  if (!nmed || h >= sp.D) return;
+  u32 grid = nmed < 1048576u ? nmed : 1048576u;
+  k_groups_medium<<<grid, 256, 0, st>>>(pos, med, nmed, sp, h);
+  CK_LAUNCH(); g_launches++;
+}
+
+// ------------------------------------------------------------------------------------------- big groups
+__global__ void k_big_sizes(const u32* __restrict__ big, u32 nbig, u32* __restrict__ sizes) {
+  u32 g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < nbig) sizes[g] = big[2 * g + 1];
+}
+void big_sizes(const u32* big, u32 nbig, u32* sizes, cudaStream_t st) {
+  if (!nbig) return;
+  k_big_sizes<<<(nbig + 255) / 256, 256, 0, st>>>(big, nbig, sizes);
+  CK_LAUNCH(); g_launches++;
+}
+
+__global__ void __launch_bounds__(256) k_big_fill(const u32* __restrict__ pos_prev, const u32* __restrict__ slot_prev,
+                                                 const u32* __restrict__ big, const u32* __restrict__ boff, u32 nbig,
+                                                 SortParams sp, u64 h, u64* __restrict__ wkey, u32* __restrict__ wpos,
+                                                 u32* __restrict__ wslot) {
+  for (u32 g = blockIdx.x; g < nbig; g += gridDim.x) {
+    u32 start = big[2 * g], size = big[2 * g + 1], off = boff[g];
+    for (u32 j = threadIdx.x; j < size; j += blockDim.x) {
+      u32 p = pos_prev[start + j];
+      u64 c33;
+      if ((u64)p + h >= sp.n) {
+        c33 = 0;  // the suffix ended: it is a proper prefix of the others in its group, hence first
+      } else {
+        u32 c = (u32)(word_at(sp.T, (u64)p + h) >> 32);
+        u64 rem = sp.D - h;
+        if (rem < 16) c &= ~0u << (32 - 2 * (u32)rem);
+        c33 = 1ull + c;
+      }
+      wkey[off + j] = ((u64)g << 33) | c33;
+      wpos[off + j] = p;
+      wslot[off + j] = slot_prev ? slot_prev[start + j] : start + j;
+    }
+  }
+}
+
+void big_fill(const u32* pos_prev, const u32* slot_prev, const u32* big, const u32* boff, u32 nbig, SortParams sp,
+              u64 h, u64* wkey, u32* wpos, u32* wslot, cudaStream_t st) {
+  if (!nbig) return;
+  u32 grid = nbig < 65535u * 16u ? nbig : 65535u * 16u;
+  k_big_fill<<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, sp, h, wkey, wpos, wslot);
+  CK_LAUNCH(); g_launches++;
+}
+
+__global__ void k_big_writeback(u32* __restrict__ pos_main, const u32* __restrict__ wslot,
+                                const u32* __restrict__ wpos, u32 total) {
+  u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < total) pos_main[wslot[t]] = wpos[t];
+}
+void big_writeback(u32* pos_main, const u32* wslot, const u32* wpos, u32 total, cudaStream_t st) {
+  if (!total) return;
+  k_big_writeback<<<(total + 255) / 256, 256, 0, st>>>(pos_main, wslot, wpos, total);
+  CK_LAUNCH(); g_launches++;
+}
+
+__global__ void k_gather_keys(const u64* __restrict__ T, const u32* __restrict__ pos, u32 N, u32* __restrict__ key) {
+  u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) key[i] = (u32)(word_at(T, pos[i]) >> 32);
+}
+void gather_keys(const u64* T, const u32* pos, u32 N, u32* key, cudaStream_t st) {
+  if (!N) return;
+  k_gather_keys<<<(N + 255) / 256, 256, 0, st>>>(T, pos, N, key);
+  CK_LAUNCH(); g_launches++;
+}
+
+// ------------------------------------------------------------------------------------------- short suffixes
+// Literal restatement of the reference's comparator lambda (kiss1_core.hpp:94-135) on the packed text,
+// preceded by the first-10-bases bucket order of the counting sort that runs before it (:41-83,
+// structs.hpp:175-184; zero padding past the end).
+__device__ bool ref_less(const SortParams& sp, u32 i, u32 j) {
+  const u64 n = sp.n, k = sp.k;
+  u32 pi = (u32)(word_at(sp.T, i) >> 44), pj = (u32)(word_at(sp.T, j) >> 44);
+  if (pi != pj) return pi < pj;
+  u64 sorted_len = 0, a = i, b = j;
+  while (sorted_len <= k && a + 125 <= n && b + 125 <= n) {  // :96-98
+#pragma unroll
+    for (int w = 0; w < 4; w++) {                            // 125 bases = 3 words + 29 bases
+      u64 x = word_at(sp.T, a + 32 * w), y = word_at(sp.T, b + 32 * w);
+      if (w == 3) { x &= ~0ull << 6; y &= ~0ull << 6; }
+      if (x != y) return x < y;                              // :104-114
+    }
+    sorted_len += 125; a += 125; b += 125;                   // :117-119
+  }
+  while (sorted_len + 1 <= k && a < n && b < n) {            // :121-130
+    u32 ca = base_at(sp.T, a), cb = base_at(sp.T, b);
+    if (ca != cb) return ca < cb;
+    sorted_len++; a++; b++;
+  }
+  if (sorted_len >= k) return a < b;                         // :131-133
+  return a == n;                                             // :134
+}
+
+__global__ void __launch_bounds__(128) k_short_rank(const u32* __restrict__ shorts, u32 ns, SortParams sp,
+                                                   u32* __restrict__ rank0) {
+  u32 s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= ns) return;
+  u32 me = shorts[s], r = 0;
+  for (u32 t = 0; t < ns; t++)
+    if (t != s && ref_less(sp, shorts[t], me)) r++;
+  rank0[s] = r;
+}
+// make the ranks a permutation even if the comparator is not a strict weak order
+__global__ void __launch_bounds__(128) k_short_place(const u32* __restrict__ shorts, u32 ns, const u32* __restrict__ rank0,
+                                                    u32* __restrict__ sorted_shorts) {
+  u32 s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= ns) return;
+  u32 r0 = rank0[s], r = 0;
+  for (u32 t = 0; t < ns; t++) {
+    u32 rt = rank0[t];
+    if (rt < r0 || (rt == r0 && t < s)) r++;
+  }
+  sorted_shorts[r] = shorts[s];
+}
+
+void shorts_order(const u32* shorts, u32 ns, SortParams sp, u32* rank0, u32* sorted_shorts, cudaStream_t st) {
+  if (!ns) return;
+  k_short_rank<<<(ns + 127) / 128, 128, 0, st>>>(shorts, ns, sp, rank0);
+  CK_LAUNCH();
+  k_short_place<<<(ns + 127) / 128, 128, 0, st>>>(shorts, ns, rank0, sorted_shorts);
+  CK_LAUNCH();
+  g_launches += 2;
+}
+
+// ins[s] = first index of the sorted long list whose suffix is not before short s
+__global__ void __launch_bounds__(128) k_short_ins(const u32* __restrict__ sorted_shorts, u32 ns,
+                                                  const u32* __restrict__ longs, u32 nl, SortParams sp,
+                                                  u32* __restrict__ ins) {
+  u32 s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= ns) return;
+  u32 me = sorted_shorts[s], lo = 0, hi = nl;
+  while (lo < hi) {
+    u32 mid = lo + (hi - lo) / 2;
+    if (ref_less(sp, longs[mid], me)) lo = mid + 1; else hi = mid;
+  }
+  ins[s] = lo;
+}
+// running maximum: short s is emitted no earlier than the shorts before it
+__global__ void k_short_mono(u32* __restrict__ ins, u32 ns) {
+  u32 mx = 0;
+  for (u32 s = 0; s < ns; s++) {
+    mx = max(mx, ins[s]);
+    ins[s] = mx;
+  }
+}
+
+void shorts_insertions(const u32* sorted_shorts, u32 ns, const u32* longs, u32 nl, SortParams sp, u32* ins,
+                       cudaStream_t st) {
+  if (!ns) return;
+  k_short_ins<<<(ns + 127) / 128, 128, 0, st>>>(sorted_shorts, ns, longs, nl, sp, ins);
+  CK_LAUNCH();
+  k_short_mono<<<1, 1, 0, st>>>(ins, ns);
+  CK_LAUNCH();
+  g_launches += 2;
+}
+
+}  // namespace kiss

@@ -1,0 +1,247 @@
+// radix.cu — device-wide exclusive scan and the stable LSD radix sort of (key, value) pairs used by the
+// k-ordered LMS sort (replaces the reference's 2^20-bucket counting sort + per-bucket std::sort,
+// kiss1_core.hpp:41-83, 137-142).  Hand-written for sm_100a; no CUB.
+//
+// One radix pass = digit histogram per 4096-key tile (k_radix_hist), one exclusive scan over the
+// digit-major [256][tiles] counter matrix, and a scatter (k_radix_scatter) that ranks the tile's keys
+// stably with warp match/ballot, stages the tile in shared memory in digit order and writes each digit's
+// run with coalesced stores.  Algorithmic bytes per pass and key: sizeof(K) (histogram read)
+// + 2 * (sizeof(K) + 4) (scatter read + write).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace kiss {
+
+thread_local u64 g_launches = 0;
+
+void cuda_check(cudaError_t e, const char* what, const char* file, int line) {
+  if (e == cudaSuccess) return;
+  std::string m = std::string(cudaGetErrorName(e)) + ": " + cudaGetErrorString(e) + " at " + file + ":" +
+                  std::to_string(line) + " (" + what + ")";
+  int code = (e == cudaErrorMemoryAllocation) ? -4 : -3;
+  throw CudaError(code, m);
+}
+
+// =================================================================================== scan
+#define SCAN_THREADS 256
+#define SCAN_ITEMS 16
+#define SCAN_TILE 4096
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(const u32* __restrict__ in, u64 N, u32* __restrict__ partials) {
+  __shared__ u32 ws[33];
+  u64 base = (u64)blockIdx.x * SCAN_TILE;
+  u32 s = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; i++) {
+    u64 idx = base + (u64)i * SCAN_THREADS + threadIdx.x;
+    if (idx < N) s += in[idx];
+  }
+  u32 tot;
+  block_excl_scan(s, ws, tot);
+  if (threadIdx.x == 0) partials[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(1024) k_scan_partials(u32* __restrict__ partials, u32 P, u32* __restrict__ total_out) {
+  __shared__ u32 ws[33];
+  u32 carry = 0;
+  for (u32 base = 0; base < P; base += 1024) {
+    u32 idx = base + threadIdx.x;
+    u32 v = idx < P ? partials[idx] : 0;
+    u32 tot;
+    u32 ex = block_excl_scan(v, ws, tot);
+    if (idx < P) partials[idx] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0 && total_out) *total_out = carry;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_down(u32* __restrict__ data, u64 N, const u32* __restrict__ partials) {
+  __shared__ u32 ws[33];
+  u64 base = (u64)blockIdx.x * SCAN_TILE + (u64)threadIdx.x * SCAN_ITEMS;
+  u32 v[SCAN_ITEMS];
+  bool full = base + SCAN_ITEMS <= N;
+  if (full) {
+    const uint4* p = reinterpret_cast<const uint4*>(data + base);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS / 4; i++) {
+      uint4 q = p[i];
+      v[4 * i] = q.x; v[4 * i + 1] = q.y; v[4 * i + 2] = q.z; v[4 * i + 3] = q.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < N) ? data[base + i] : 0;
+  }
+  u32 s = 0;
+#pragma unroll
+  for (int i = 0; i < SCAN_ITEMS; i++) { u32 t = v[i]; v[i] = s; s += t; }
+  u32 tot;
+  u32 ex = block_excl_scan(s, ws, tot) + partials[blockIdx.x];
+  if (full) {
+    uint4* p = reinterpret_cast<uint4*>(data + base);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS / 4; i++)
+      p[i] = make_uint4(v[4 * i] + ex, v[4 * i + 1] + ex, v[4 * i + 2] + ex, v[4 * i + 3] + ex);
+  } else {
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++)
+      if (base + i < N) data[base + i] = v[i] + ex;
+  }
+}
+
+void scan_excl_u32(u32* data, u64 N, u32* partials, u32* total_dev, cudaStream_t st) {
+  if (N == 0) {
+    if (total_dev) CK(cudaMemsetAsync(total_dev, 0, sizeof(u32), st));
+    return;
+  }
+  u32 P = (u32)((N + SCAN_TILE - 1) / SCAN_TILE);
+  k_scan_reduce<<<P, SCAN_THREADS, 0, st>>>(data, N, partials);
+  CK_LAUNCH();
+  k_scan_partials<<<1, 1024, 0, st>>>(partials, P, total_dev);
+  CK_LAUNCH();
+  k_scan_down<<<P, SCAN_THREADS, 0, st>>>(data, N, partials);
+  CK_LAUNCH();
+  g_launches += 3;
+}
+
+// =================================================================================== radix
+#define RADIX_THREADS 256
+#define RADIX_ITEMS 16
+#define RADIX_TILE 4096
+#define RADIX_WARPS 8
+
+template <typename K>
+__global__ void __launch_bounds__(RADIX_THREADS) k_radix_hist(const K* __restrict__ kin, u32 N, int shift, u32 mask,
+                                                             u32* __restrict__ H, u32 ntiles) {
+  __shared__ u32 hist[256];
+  const u32 tid = threadIdx.x, tile = blockIdx.x;
+  hist[tid] = 0;
+  __syncthreads();
+  const u32 tile_base = tile * RADIX_TILE;
+#pragma unroll 4
+  for (u32 i = 0; i < RADIX_ITEMS; i++) {
+    u32 e = tile_base + i * RADIX_THREADS + tid;
+    bool valid = e < N;
+    u32 d = valid ? ((u32)(kin[e] >> shift) & mask) : 256u;
+    u32 peers = __match_any_sync(0xffffffffu, d);
+    if (valid && (u32)(__ffs(peers) - 1) == (tid & 31)) atomicAdd(&hist[d], (u32)__popc(peers));
+  }
+  __syncthreads();
+  H[(u64)tid * ntiles + tile] = hist[tid];
+}
+
+template <typename K>
+__global__ void __launch_bounds__(RADIX_THREADS) k_radix_scatter(const K* __restrict__ kin, const u32* __restrict__ vin,
+                                                                K* __restrict__ kout, u32* __restrict__ vout, u32 N,
+                                                                int shift, u32 mask, const u32* __restrict__ H,
+                                                                u32 ntiles) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  K* skeys = reinterpret_cast<K*>(smem_raw);
+  u32* svals = reinterpret_cast<u32*>(skeys + RADIX_TILE);
+  u32* wcnt = svals + RADIX_TILE;          // [RADIX_WARPS][256]
+  u32* texcl = wcnt + RADIX_WARPS * 256;   // [256] exclusive digit offsets inside the tile
+  u32* dbase = texcl + 256;                // [256] global base of the digit run minus texcl
+  u32* ws = dbase + 256;                   // [33]
+
+  const u32 tid = threadIdx.x, tile = blockIdx.x, w = tid >> 5, lane = tid & 31;
+  const u32 tile_base = tile * RADIX_TILE;
+  const u32 tile_n = min((u32)RADIX_TILE, N - tile_base);
+  for (u32 i = tid; i < RADIX_WARPS * 256; i += RADIX_THREADS) wcnt[i] = 0;
+  __syncthreads();
+
+  K keys[RADIX_ITEMS];
+  u32 rank[RADIX_ITEMS];
+  const u32 wbase = tile_base + w * (32 * RADIX_ITEMS);
+  const u32 lt_mask = (1u << lane) - 1u;
+#pragma unroll
+  for (int r = 0; r < RADIX_ITEMS; r++) {
+    u32 e = wbase + r * 32 + lane;
+    bool valid = e < N;
+    K key = valid ? kin[e] : (K)0;
+    keys[r] = key;
+    u32 d = (u32)(key >> shift) & mask;
+    u32 peers = __match_any_sync(0xffffffffu, valid ? d : 256u);
+    u32 leader = (u32)__ffs(peers) - 1u;
+    u32 old = 0;
+    if (lane == leader && valid) {
+      old = wcnt[w * 256 + d];
+      wcnt[w * 256 + d] = old + (u32)__popc(peers);
+    }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rank[r] = old + (u32)__popc(peers & lt_mask);
+    __syncwarp();
+  }
+  __syncthreads();
+  {
+    u32 run = 0;
+#pragma unroll
+    for (int ww = 0; ww < RADIX_WARPS; ww++) {
+      u32 c = wcnt[ww * 256 + tid];
+      wcnt[ww * 256 + tid] = run;
+      run += c;
+    }
+    u32 tot;
+    u32 ex = block_excl_scan(run, ws, tot);
+    texcl[tid] = ex;
+    dbase[tid] = H[(u64)tid * ntiles + tile] - ex;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < RADIX_ITEMS; r++) {
+    u32 e = wbase + r * 32 + lane;
+    if (e < N) {
+      u32 d = (u32)(keys[r] >> shift) & mask;
+      u32 lp = texcl[d] + wcnt[w * 256 + d] + rank[r];
+      skeys[lp] = keys[r];
+      svals[lp] = vin[e];
+    }
+  }
+  __syncthreads();
+  for (u32 j = tid; j < tile_n; j += RADIX_THREADS) {
+    K key = skeys[j];
+    u32 d = (u32)(key >> shift) & mask;
+    u32 dst = dbase[d] + j;
+    kout[dst] = key;
+    vout[dst] = svals[j];
+  }
+}
+
+template <typename K>
+static size_t radix_smem() {
+  return RADIX_TILE * (sizeof(K) + 4) + (RADIX_WARPS * 256 + 256 + 256 + 40) * 4;
+}
+
+void radix_init() {
+  CK(cudaFuncSetAttribute(k_radix_scatter<u32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem<u32>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter<u64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem<u64>()));
+}
+
+template <typename K>
+static void radix_sort_impl(K*& keys, u32*& vals, K*& keys_alt, u32*& vals_alt, u32 N, int bit_lo, int bit_hi, u32* H,
+                            u32* partials, cudaStream_t st) {
+  if (N == 0) return;
+  u32 ntiles = (u32)radix_tiles(N);
+  for (int shift = bit_lo; shift < bit_hi; shift += 8) {
+    int bits = bit_hi - shift < 8 ? bit_hi - shift : 8;
+    u32 mask = (1u << bits) - 1u;
+    k_radix_hist<K><<<ntiles, RADIX_THREADS, 0, st>>>(keys, N, shift, mask, H, ntiles);
+    CK_LAUNCH();
+    scan_excl_u32(H, (u64)256 * ntiles, partials, nullptr, st);
+    k_radix_scatter<K><<<ntiles, RADIX_THREADS, radix_smem<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift, mask,
+                                                                      H, ntiles);
+    CK_LAUNCH();
+    g_launches += 2;
+    K* tk = keys; keys = keys_alt; keys_alt = tk;
+    u32* tv = vals; vals = vals_alt; vals_alt = tv;
+  }
+}
+
+void radix_sort_u32(u32*& keys, u32*& vals, u32*& keys_alt, u32*& vals_alt, u32 N, int bit_lo, int bit_hi, u32* H,
+                    u32* partials, cudaStream_t st) {
+  radix_sort_impl<u32>(keys, vals, keys_alt, vals_alt, N, bit_lo, bit_hi, H, partials, st);
+}
+void radix_sort_u64(u64*& keys, u32*& vals, u64*& keys_alt, u32*& vals_alt, u32 N, int bit_lo, int bit_hi, u32* H,
+                    u32* partials, cudaStream_t st) {
+  radix_sort_impl<u64>(keys, vals, keys_alt, vals_alt, N, bit_lo, bit_hi, H, partials, st);
+}
+
+}  // namespace kiss

@@ -1,0 +1,168 @@
+"""Host-side mirror of the reference's sorter facades over the C ABI.
+
+Reference interface (include/biovoltron/algo/sort/kiss1_sorter.hpp:7-50):
+
+    template<typename size_type = std::uint32_t> struct KISS1Sorter {
+      static auto get_suffix_array_dna(const kiss::vector<uint8_t>& S, size_type k = 256u,
+                                       size_t num_threads = hardware_concurrency()) -> SA_t;
+      static auto prepare_aligned_ref(istring_view ref) -> kiss::vector<uint8_t>;
+    };
+
+Same names and argument meaning here; `num_threads` is accepted and ignored (the GPU path has no host
+threads, and the reference's result does not depend on it).  Errors the reference raises as
+exceptions (std::bad_alloc, structs.hpp:32-38) surface as KissB200Error.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _cabi
+from ._cabi import PARALLEL_SORTING, PREFIX_DOUBLING, Timings, check, lib
+
+
+def _codes(S):
+    """what every reference caller does before the sorter: codes 0..3, contiguous bytes
+    (include/command/suffix_sort.hpp:33, kiss1_sorter.hpp:46-49)"""
+    if isinstance(S, (bytes, bytearray, memoryview)):
+        S = np.frombuffer(S, dtype=np.uint8)
+    S = np.ascontiguousarray(S, dtype=np.uint8)
+    return S
+
+
+class Context:
+    """one GPU context (stream + cached device scratch); not thread-safe, like the reference's call"""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        check(lib().kiss_b200_create(C.byref(self._h), int(device)))
+        self.device = device
+        self.last_timings = None
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().kiss_b200_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    # ---- the path
+    def suffix_array_dna(self, S, k=256, algo=PARALLEL_SORTING, out=None):
+        S = _codes(S)
+        n = S.size
+        SA = np.empty(n + 1, np.uint32) if out is None else out
+        t = Timings()
+        check(lib().kiss_b200_suffix_sort_dna_u32(self._h, S.ctypes.data, n, k & 0xFFFFFFFF, algo, SA.ctypes.data,
+                                                  C.byref(t)))
+        self.last_timings = t.as_dict()
+        return SA
+
+    def suffix_array_ascii(self, seq, k=256, algo=PARALLEL_SORTING):
+        b = np.frombuffer(seq if isinstance(seq, (bytes, bytearray)) else seq.encode(), dtype=np.uint8)
+        b = np.ascontiguousarray(b)
+        SA = np.empty(b.size + 1, np.uint32)
+        t = Timings()
+        check(lib().kiss_b200_suffix_sort_ascii_u32(self._h, b.ctypes.data, b.size, k & 0xFFFFFFFF, algo,
+                                                    SA.ctypes.data, C.byref(t)))
+        self.last_timings = t.as_dict()
+        return SA
+
+    def suffix_array_dna_dev(self, S_ptr, n, SA_ptr, k=256, algo=PARALLEL_SORTING):
+        """device-resident variant: S_ptr / SA_ptr are device addresses (e.g. torch tensor.data_ptr())"""
+        t = Timings()
+        check(lib().kiss_b200_suffix_sort_dna_u32_dev(self._h, S_ptr, n, k & 0xFFFFFFFF, algo, SA_ptr, C.byref(t)))
+        self.last_timings = t.as_dict()
+        return self.last_timings
+
+    # ---- stage-level entries (parity tests)
+    def get_lms(self, S):
+        S = _codes(S)
+        n = S.size
+        lms = np.empty(n // 2 + 2, np.uint32)
+        m = C.c_uint64()
+        cnt = np.zeros(4, np.uint64)
+        lcnt = np.zeros(4, np.uint64)
+        check(lib().kiss_b200_get_lms(self._h, S.ctypes.data, n, lms.ctypes.data, C.byref(m), cnt.ctypes.data,
+                                      lcnt.ctypes.data))
+        return lms[:m.value].copy(), cnt, lcnt
+
+    def sorted_lms(self, S, k=256, algo=PARALLEL_SORTING):
+        S = _codes(S)
+        n = S.size
+        out = np.empty(n // 2 + 2, np.uint32)
+        m = C.c_uint64()
+        check(lib().kiss_b200_sorted_lms(self._h, S.ctypes.data, n, k & 0xFFFFFFFF, algo, out.ctypes.data, C.byref(m)))
+        return out[:m.value].copy()
+
+    def put_lms(self, S, k=256, algo=PARALLEL_SORTING):
+        S = _codes(S)
+        SA = np.empty(S.size + 1, np.uint32)
+        check(lib().kiss_b200_put_lms(self._h, S.ctypes.data, S.size, k & 0xFFFFFFFF, algo, SA.ctypes.data))
+        return SA
+
+    def induce_from_sorted_lms(self, S, sorted_lms):
+        S = _codes(S)
+        srt = np.ascontiguousarray(sorted_lms, dtype=np.uint32)
+        SA = np.empty(S.size + 1, np.uint32)
+        check(lib().kiss_b200_induce_from_sorted_lms(self._h, S.ctypes.data, S.size, srt.ctypes.data, srt.size,
+                                                     SA.ctypes.data))
+        return SA
+
+    # ---- device-resident stage API (sharded LMS sort)
+    def prepare_dev(self, S_ptr, n, k=256):
+        m = C.c_uint64()
+        check(lib().kiss_b200_prepare_dev(self._h, S_ptr, n, k & 0xFFFFFFFF, C.byref(m)))
+        return m.value
+
+    def lms_keys_dev(self):
+        kp, pp, nl = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        check(lib().kiss_b200_lms_keys_dev(self._h, C.byref(kp), C.byref(pp), C.byref(nl)))
+        return kp.value, pp.value, nl.value
+
+    def sort_lms_subset_dev(self, pos_ptr, count):
+        t = Timings()
+        check(lib().kiss_b200_sort_lms_subset_dev(self._h, pos_ptr, count, C.byref(t)))
+        return t.as_dict()
+
+    def finish_from_sorted_dev(self, sorted_ptr, n_long, SA_ptr):
+        t = Timings()
+        check(lib().kiss_b200_finish_from_sorted_dev(self._h, sorted_ptr, n_long, SA_ptr, C.byref(t)))
+        return t.as_dict()
+
+    def synth_uniform_dev(self, S_ptr, n, seed):
+        check(lib().kiss_b200_synth_uniform_dev(self._h, S_ptr, n, seed))
+
+
+_default = None
+
+
+def default_context():
+    global _default
+    if _default is None:
+        _default = Context(0)
+    return _default
+
+
+class KISS1Sorter:
+    """kiss1_sorter.hpp:7-50 (PARALLEL_SORTING)"""
+    algo = PARALLEL_SORTING
+
+    @classmethod
+    def get_suffix_array_dna(cls, S, k=256, num_threads=None):
+        return default_context().suffix_array_dna(S, k, cls.algo)
+
+    @staticmethod
+    def prepare_aligned_ref(ref):
+        return _codes(ref).copy()
+
+
+class KISS2Sorter(KISS1Sorter):
+    """kiss2_sorter.hpp:7-50 (PREFIX_DOUBLING)"""
+    algo = PREFIX_DOUBLING

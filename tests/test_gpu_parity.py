@@ -1,0 +1,125 @@
+"""GPU parity tests (run on the B200 box: `pytest -m gpu`): the CUDA path through the C ABI against the
+oracle (oracle/kiss_oracle.c, pinned to the reference in tests/test_oracle.py) stage by stage."""
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+import textgen as tg
+
+pytestmark = pytest.mark.gpu
+
+KS = [256, 32, 125, 124, 2, 0xFFFFFFFF]
+
+CASES = [
+    ("uniform1", lambda: tg.uniform(1, 1)),
+    ("uniform2", lambda: tg.uniform(2, 2)),
+    ("uniform7", lambda: tg.uniform(3, 7)),
+    ("uniform100", lambda: tg.uniform(4, 100)),
+    ("uniform1000", lambda: tg.uniform(5, 1000)),
+    ("uniform4097", lambda: tg.uniform(6, 4097)),
+    ("uniform200k", lambda: tg.uniform(7, 200_000)),
+    ("repeats", lambda: tg.planted_repeats(8, 300_000, unit_len=3000, copies=40)),
+    ("repeats_mut", lambda: tg.planted_repeats(9, 300_000, unit_len=3000, copies=40, mutate_every=300)),
+    ("tandem", lambda: tg.tandem(10, 200_000)),
+    ("low_entropy", lambda: np.concatenate([tg.low_entropy(11, 50_000), tg.uniform(12, 1024)])),
+    ("mixed", lambda: tg.mixed(13, 150_000)),
+    ("all_A", lambda: np.zeros(500, np.uint8)),
+    ("all_T", lambda: np.full(500, 3, np.uint8)),
+    ("periodic_CA", lambda: np.concatenate([tg.periodic(5000, [1, 0]), tg.uniform(14, 700)])),
+    ("periodic_big", lambda: np.concatenate([tg.periodic(40_000, [2, 0, 1]), tg.uniform(15, 900)])),
+    ("homopolymers", lambda: tg.tandem(16, 120_000, arrays=12, max_unit=1, max_len=9000)),
+]
+IDS = [c[0] for c in CASES]
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import kiss_b200
+    c = kiss_b200.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("name,gen", CASES, ids=IDS)
+def test_get_lms(ctx, name, gen):
+    S = gen()
+    lms, cnt, lcnt = ctx.get_lms(S)
+    o_lms, o_cnt, o_lcnt = ol.oracle_get_lms(S)
+    assert np.array_equal(lms, o_lms)
+    assert cnt.tolist() == o_cnt.tolist()
+    assert lcnt.tolist() == o_lcnt.tolist()
+
+
+@pytest.mark.parametrize("k", KS)
+@pytest.mark.parametrize("name,gen", CASES, ids=IDS)
+def test_sorted_lms(ctx, name, gen, k):
+    S = gen()
+    o = ol.oracle_kiss1(S, k=k, stages=True)
+    got = ctx.sorted_lms(S, k)
+    assert got.size == o["m"]
+    bad = np.nonzero(got != o["sorted"])[0]
+    assert bad.size == 0, f"{bad.size} mismatches, first at {bad[:5]}: got {got[bad[:5]]} want {o['sorted'][bad[:5]]}"
+
+
+@pytest.mark.parametrize("name,gen", CASES, ids=IDS)
+def test_put_lms(ctx, name, gen):
+    S = gen()
+    o = ol.oracle_kiss1(S, k=256, stages=True)
+    assert np.array_equal(ctx.put_lms(S, 256), o["placed"])
+
+
+@pytest.mark.parametrize("name,gen", CASES, ids=IDS)
+def test_induce_from_oracle_sorted_lms(ctx, name, gen):
+    S = gen()
+    o = ol.oracle_kiss1(S, k=256, stages=True)
+    got = ctx.induce_from_sorted_lms(S, o["sorted"])
+    bad = np.nonzero(got != o["sa"])[0]
+    assert bad.size == 0, f"{bad.size} mismatches, first at {bad[:5]}"
+
+
+@pytest.mark.parametrize("k", KS)
+@pytest.mark.parametrize("name,gen", CASES, ids=IDS)
+def test_full_suffix_array(ctx, name, gen, k):
+    S = gen()
+    want = ol.oracle_kiss1(S, k=k)
+    got = ctx.suffix_array_dna(S, k)
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, f"{bad.size} mismatches, first at {bad[:5]}"
+
+
+def test_empty_text(ctx):
+    assert ctx.suffix_array_dna(np.zeros(0, np.uint8)).tolist() == [0]  # kiss1_core.hpp:237-238
+
+
+def test_prefix_doubling_is_the_true_suffix_array(ctx):
+    import kiss_b200
+    S = tg.planted_repeats(31, 100_000, unit_len=2000, copies=30)
+    want = ol.oracle_kiss1(S, k=0xFFFFFFFF)
+    got = ctx.suffix_array_dna(S, 256, kiss_b200.PREFIX_DOUBLING)
+    assert np.array_equal(got, want)
+
+
+def test_ascii_front_end(ctx):
+    S = tg.mixed(41, 30_000)
+    txt = np.frombuffer(b"ACGT", np.uint8)[S].copy()
+    txt[100:110] = ord("N")      # N -> A  (istring.hpp:28-36 gives 4, suffix_sort.hpp:33 takes % 4)
+    txt[200:300] |= 0x20         # lower case
+    S2 = S.copy()
+    S2[100:110] = 0
+    want = ol.oracle_kiss1(S2, k=256)
+    got = ctx.suffix_array_ascii(txt.tobytes(), 256)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("name,n,gen", [
+    ("uniform_5M", 5_000_000, lambda n: tg.uniform(51, n)),
+    ("repeats_5M", 5_000_000, lambda n: tg.planted_repeats(52, n, unit_len=5000, copies=100)),
+    ("mixed_3M", 3_000_000, lambda n: tg.mixed(53, n)),
+], ids=["uniform_5M", "repeats_5M", "mixed_3M"])
+def test_medium_sizes_bit_exact(ctx, name, n, gen):
+    S = gen(n)
+    want = ol.oracle_kiss1(S, k=256)
+    got = ctx.suffix_array_dna(S, 256)
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, f"{bad.size} mismatches, first at {bad[:5]}"
+    assert ol.fnv1a(got) == ol.fnv1a(want)
