@@ -302,11 +302,10 @@ Buckets make_buckets(const u64 counters[8], u64 n) {
 
 struct InduceStats { u64 waves_L = 0, waves_S = 0; };
 
-void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets& bk, u32* SA, InduceStats* is) {
+void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets& bk, u32* SA, u32* CTX, InduceStats* is) {
   cudaStream_t st = c->st;
   WaveScratch ws;
   u64 maxlen = n + 1;
-  ws.side = pool.alloc<u8>(maxlen);
   u64 nt = wave_tiles(maxlen);
   ws.C = pool.alloc<u32>(4 * nt + 4);
   ws.partials = pool.alloc<u32>(scan_partials_len(4 * nt));
@@ -317,20 +316,20 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
   u64 Lc[4], nL[4], Sc[4];
   for (int s = 0; s < 4; s++) Lc[s] = bk.B[s];
   // L pass (kiss_common.hpp:372-403)
-  induce_wave(SA, T, 0, 1, false, 0xFu, Lc, ws, tot, st);
+  induce_wave(SA, CTX, T, 0, 1, false, 0xFu, Lc, ws, tot, st);
   for (int s = 0; s < 4; s++) Lc[s] += tot[s];
   is->waves_L++;
   for (int cb = 0; cb < 4; cb++) {
     u64 p = bk.B[cb];
     while (p < Lc[cb]) {
       u64 q = Lc[cb];
-      induce_wave(SA, T, p, q - p, false, (0xFu << cb) & 0xFu, Lc, ws, tot, st);
+      induce_wave(SA, CTX, T, p, q - p, false, (0xFu << cb) & 0xFu, Lc, ws, tot, st);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
       p = q;
       is->waves_L++;
     }
     if (bk.lms_count[cb]) {
-      induce_wave(SA, T, bk.B[cb + 1] - bk.lms_count[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
+      induce_wave(SA, CTX, T, bk.B[cb + 1] - bk.lms_count[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
       is->waves_L++;
     }
@@ -344,13 +343,13 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
     u64 p = bk.B[cb + 1];
     while (Sc[cb] < p) {
       u64 q = Sc[cb];
-      induce_wave(SA, T, q, p - q, true, (1u << (cb + 1)) - 1u, Sc, ws, tot, st);
+      induce_wave(SA, CTX, T, q, p - q, true, (1u << (cb + 1)) - 1u, Sc, ws, tot, st);
       for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
       p = q;
       is->waves_S++;
     }
     if (cb > 0 && nL[cb]) {
-      induce_wave(SA, T, bk.B[cb], nL[cb], true, (1u << cb) - 1u, Sc, ws, tot, st);
+      induce_wave(SA, CTX, T, bk.B[cb], nL[cb], true, (1u << cb) - 1u, Sc, ws, tot, st);
       for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
       is->waves_S++;
     }
@@ -411,6 +410,7 @@ void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* d
   if (stop != STOP_LMS) {
     Pool pool(st);
     SortedLms sl;
+    u32* dCTX = nullptr;
     CK(cudaEventRecord(c->ev[3], st));
     do_sort(c, pool, &sl, &ss);
     CK(cudaEventRecord(c->ev[4], st));
@@ -420,13 +420,14 @@ void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* d
       Buckets lin = bk;
       lin.B[1] = P.m1 + 1; lin.lms_count[0] = P.m1; lin.lms_off[0] = 0;
       lin.lms_off[1] = lin.lms_off[2] = lin.lms_off[3] = ~0ull;
-      place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, lin, n, dSA, st);
+      place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, lin, n, dSA, nullptr, st);
     } else {
       if (stop == STOP_PUT) CK(cudaMemsetAsync(dSA, 0xFF, (n + 1) * sizeof(u32), st));
-      place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, n, dSA, st);
+      if (stop == STOP_FULL) dCTX = pool.alloc<u32>(n + 1);
+      place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, n, dSA, dCTX, st);
     }
     CK(cudaEventRecord(c->ev[5], st));
-    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, dSA, &is);
+    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, dSA, dCTX, &is);
     CK(cudaEventRecord(c->ev[6], st));
     CK(cudaEventSynchronize(c->ev[6]));
     CK(cudaEventElapsedTime(&t_sort, c->ev[3], c->ev[4]));
@@ -687,9 +688,10 @@ int kiss_b200_induce_from_sorted_lms(kiss_b200_ctx* c, const uint8_t* S_host, ui
     CK(cudaMemcpyAsync(dsorted, sorted_host, m * sizeof(u32), cudaMemcpyHostToDevice, st));
     u32* dSA = pool.alloc<u32>(n + 1);
     Buckets bk = make_buckets(c->prep.counters, n);
-    place_sorted(dsorted + 1, (u32)(m - 1), bk, n, dSA, st);
+    u32* dCTX = pool.alloc<u32>(n + 1);
+    place_sorted(dsorted + 1, (u32)(m - 1), bk, n, dSA, dCTX, st);
     InduceStats is;
-    do_induce(c, pool, c->prep.T, n, bk, dSA, &is);
+    do_induce(c, pool, c->prep.T, n, bk, dSA, dCTX, &is);
     CK(cudaMemcpyAsync(SA_host, dSA, (n + 1) * sizeof(u32), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     free_prepared(c);
@@ -759,10 +761,11 @@ int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_lo
     sl.nl = P.n_long;
     do_shorts(c, pool, P.pos + P.n_long, ns, sorted_long_dev, P.n_long, P.sp, &sl);
     Buckets bk = make_buckets(P.counters, P.n);
-    place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, P.n, SA_dev, st);
+    u32* dCTX = pool.alloc<u32>(P.n + 1);
+    place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, P.n, SA_dev, dCTX, st);
     CK(cudaEventRecord(c->ev[5], st));
     InduceStats is;
-    do_induce(c, pool, P.T, P.n, bk, SA_dev, &is);
+    do_induce(c, pool, P.T, P.n, bk, SA_dev, dCTX, &is);
     CK(cudaEventRecord(c->ev[6], st));
     CK(cudaEventSynchronize(c->ev[6]));
     if (t) {

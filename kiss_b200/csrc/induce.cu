@@ -12,7 +12,8 @@
 // none of the reference's artefact EMPTY writes (:241) are needed; the S pass overwrites the LMS slots.
 // SURVEY.md A.4 holds the equivalence argument; tests/model_gpu_algo.py is the same schedule in numpy.
 //
-// Algorithmic bytes per scanned entry: 4 (SA read) + 0.25 (packed text, random) + 4 per induced suffix.
+// Algorithmic bytes per scanned entry: 4 (SA read) + 0.25 (packed text) + 4 per induced suffix; the context
+// array adds 4 + 4 of streaming traffic and removes all but ~0.3 n of the random text gathers.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -28,44 +29,71 @@ __device__ __forceinline__ u64 lms_slot(const Buckets& bk, u64 r) {
   return bk.B[c + 1] - bk.lms_count[c] + (r - bk.lms_off[c]);
 }
 
+#define PLACE_INS_SMEM 2048u
 __global__ void __launch_bounds__(256) k_place_lms(const u32* __restrict__ longs, u32 nl,
                                                   const u32* __restrict__ sorted_shorts, const u32* __restrict__ ins,
-                                                  u32 ns, Buckets bk, u64 n, u32* __restrict__ SA) {
+                                                  u32 ns, Buckets bk, u64 n, u32* __restrict__ SA,
+                                                  u32* __restrict__ CTX) {
+  __shared__ u32 sins[PLACE_INS_SMEM];
+  const bool cached = ns <= PLACE_INS_SMEM;
+  if (cached)
+    for (u32 t = threadIdx.x; t < ns; t += blockDim.x) sins[t] = ins[t];
+  __syncthreads();
+  const u32* I = cached ? sins : ins;
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) SA[0] = (u32)n;
+  if (i == 0) {
+    SA[0] = (u32)n;
+    if (CTX) CTX[0] = 1u;
+  }
+  u64 slot;
+  u32 val;
   if (i < nl) {
     // shorts emitted before long i: those with ins <= i  (ins is non-decreasing)
     u32 lo = 0, hi = ns;
+    if (ns && (u32)i < I[0]) hi = 0;
+    else if (ns && (u32)i >= I[ns - 1]) lo = ns;
     while (lo < hi) {
       u32 mid = lo + (hi - lo) / 2;
-      if (ins[mid] <= (u32)i) lo = mid + 1; else hi = mid;
+      if (I[mid] <= (u32)i) lo = mid + 1; else hi = mid;
     }
-    SA[lms_slot(bk, i + lo)] = longs[i];
+    slot = lms_slot(bk, i + lo);
+    val = longs[i];
   } else if (i < (u64)nl + ns) {
     u32 s = (u32)(i - nl);
-    SA[lms_slot(bk, (u64)ins[s] + s)] = sorted_shorts[s];
+    slot = lms_slot(bk, (u64)I[s] + s);
+    val = sorted_shorts[s];
+  } else {
+    return;
   }
+  SA[slot] = val;
+  if (CTX) CTX[slot] = 1u;  // context not fetched yet (see the waves below)
 }
 
 void place_lms(const u32* longs, u32 nl, const u32* sorted_shorts, const u32* ins, u32 ns, Buckets bk, u64 n, u32* SA,
-               cudaStream_t st) {
+               u32* CTX, cudaStream_t st) {
   u64 tot = (u64)nl + ns;
   if (tot == 0) tot = 1;
-  k_place_lms<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(longs, nl, sorted_shorts, ins, ns, bk, n, SA);
+  k_place_lms<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(longs, nl, sorted_shorts, ins, ns, bk, n, SA, CTX);
   CK_LAUNCH(); g_launches++;
 }
 
-void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, cudaStream_t st) {
-  place_lms(sorted, cnt, nullptr, nullptr, 0, bk, n, SA, st);
+void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, u32* CTX, cudaStream_t st) {
+  place_lms(sorted, cnt, nullptr, nullptr, 0, bk, n, SA, CTX, st);
 }
 
 // ------------------------------------------------------------------------------------------- waves
+// Every SA entry v travels with a context word CTX = 1 << 2L | (S[v-L] .. S[v-1]) holding the L <= 15 bases
+// that precede v (S[v-1] in the low two bits).  Scanning v needs only S[v-1] (the bucket gives S[v]), and the
+// suffix v-1 it induces inherits CTX >> 2 — so the packed text is gathered (one random 32-byte sector) only
+// when a context runs out (CTX == 1): once per LMS suffix and once per 15 steps of a chain, instead of once
+// per scanned entry as in the reference's prepare loops (kiss_common.hpp:63-113, 278-325).
 #define WAVE_THREADS 256
 #define WAVE_ITEMS 8
 #define WAVE_WARPS 8
 
 struct WaveArgs {
   u32* SA;
+  u32* CTX;
   const u64* T;
   u64 lo;       // first slot of the wave
   u64 len;      // number of slots
@@ -74,17 +102,33 @@ struct WaveArgs {
   u64 cur[4];   // bucket cursors
 };
 
-// symbol (0..3) the entry at logical index j induces into, or 4
-__device__ __forceinline__ u32 wave_symbol(const WaveArgs& a, u64 j, u32& v) {
-  u64 slot = a.down ? a.lo + a.len - 1 - j : a.lo + j;
-  v = a.SA[slot];
-  if (v == 0 || v == KISS_EMPTY) return 4;
-  u32 c = base_at(a.T, (u64)v - 1);
-  return ((a.symmask >> c) & 1u) ? c : 4u;
+__device__ __forceinline__ u32 ctx_gather(const u64* __restrict__ T, u32 v) {
+  if (v >= 15) return (1u << 30) | (u32)(word_at(T, (u64)v - 15) >> 34);
+  if (v == 0) return 1u;
+  return (1u << (2 * v)) | (u32)(__ldg(T) >> (64 - 2 * v));
 }
 
-__global__ void __launch_bounds__(WAVE_THREADS) k_wave_count(WaveArgs a, u8* __restrict__ side, u32* __restrict__ C,
-                                                            u32 ntiles) {
+__device__ __forceinline__ u64 wave_slot(const WaveArgs& a, u64 j) { return a.down ? a.lo + a.len - 1 - j : a.lo + j; }
+
+// context of the entry at `slot`, refreshed from the text (and stored back) when it has run out
+__device__ __forceinline__ u32 wave_ctx_refresh(const WaveArgs& a, u64 slot) {
+  u32 c = a.CTX[slot];
+  if (c == 1u) {
+    u32 v = a.SA[slot];
+    if (v != 0 && v != KISS_EMPTY) {
+      c = ctx_gather(a.T, v);
+      a.CTX[slot] = c;
+    }
+  }
+  return c;
+}
+// symbol (0..3) the entry induces into, or 4
+__device__ __forceinline__ u32 ctx_symbol(u32 c, u32 symmask) {
+  u32 cu = c & 3u;
+  return (c > 1u && ((symmask >> cu) & 1u)) ? cu : 4u;
+}
+
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_count(WaveArgs a, u32* __restrict__ C, u32 ntiles) {
   __shared__ u32 wsum[WAVE_WARPS][4];
   const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const u64 j0 = (u64)blockIdx.x * WAVE_TILE + w * (32 * WAVE_ITEMS);
@@ -92,11 +136,8 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_count(WaveArgs a, u8* __r
 #pragma unroll
   for (int r = 0; r < WAVE_ITEMS; r++) {
     u64 j = j0 + r * 32 + lane;
-    u32 cu = 4, v;
-    if (j < a.len) {
-      cu = wave_symbol(a, j, v);
-      side[j] = (u8)cu;
-    }
+    u32 cu = 4;
+    if (j < a.len) cu = ctx_symbol(wave_ctx_refresh(a, wave_slot(a, j)), a.symmask);
 #pragma unroll
     for (u32 s = 0; s < 4; s++) cnt[s] += __popc(__ballot_sync(0xffffffffu, cu == s));
   }
@@ -123,98 +164,119 @@ __global__ void k_wave_totals(const u32* __restrict__ E, u32 ntiles, const u32* 
   }
 }
 
-// shared by the tiled and the single-block kernels: rank and write the tile's induced suffixes
-__device__ __forceinline__ void wave_scatter_tile(const WaveArgs& a, const u8* __restrict__ side, u64 tile,
-                                                  const u32 tile_off[4], u32 (*wsum)[4]) {
+struct WaveSmem {
+  u32 wsum[WAVE_WARPS][4];
+  u32 sb[5];
+  u32 sSA[WAVE_TILE];
+  u32 sCTX[WAVE_TILE];
+};
+
+// rank the tile's induced suffixes (contexts must be fresh), stage them in shared memory grouped by symbol,
+// then write each symbol's run with coalesced stores.  Returns nothing; sm.sb[s+1]-sm.sb[s] = tile count of s.
+__device__ __forceinline__ void wave_scatter_tile(const WaveArgs& a, u64 tile, const u32 tile_off[4], WaveSmem& sm) {
   const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const u64 j0 = tile * WAVE_TILE + w * (32 * WAVE_ITEMS);
   const u32 lt = (1u << lane) - 1u;
-  u32 sym[WAVE_ITEMS];
+  u32 sym[WAVE_ITEMS], cx[WAVE_ITEMS], val[WAVE_ITEMS];
   u32 cnt[4] = {0, 0, 0, 0};
 #pragma unroll
   for (int r = 0; r < WAVE_ITEMS; r++) {
     u64 j = j0 + r * 32 + lane;
-    u32 cu = (j < a.len) ? (u32)side[j] : 4u;
+    u32 c = 1u, v = 0;
+    if (j < a.len) {
+      u64 slot = wave_slot(a, j);
+      c = a.CTX[slot];
+      v = a.SA[slot];
+    }
+    cx[r] = c;
+    val[r] = v;
+    u32 cu = ctx_symbol(c, a.symmask);
     sym[r] = cu;
 #pragma unroll
     for (u32 s = 0; s < 4; s++) cnt[s] += __popc(__ballot_sync(0xffffffffu, cu == s));
   }
   if (lane == 0) {
 #pragma unroll
-    for (int s = 0; s < 4; s++) wsum[w][s] = cnt[s];
+    for (int s = 0; s < 4; s++) sm.wsum[w][s] = cnt[s];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u32 acc = 0;
+    for (int s = 0; s < 4; s++) {
+      sm.sb[s] = acc;
+      for (int ww = 0; ww < WAVE_WARPS; ww++) acc += sm.wsum[ww][s];
+    }
+    sm.sb[4] = acc;
   }
   __syncthreads();
   u32 run[4];
 #pragma unroll
   for (int s = 0; s < 4; s++) {
-    u32 t = tile_off[s];
-    for (u32 ww = 0; ww < w; ww++) t += wsum[ww][s];
+    u32 t = sm.sb[s];
+    for (u32 ww = 0; ww < w; ww++) t += sm.wsum[ww][s];
     run[s] = t;
   }
 #pragma unroll
   for (int r = 0; r < WAVE_ITEMS; r++) {
-    u64 j = j0 + r * 32 + lane;
     u32 cu = sym[r];
     u32 b0 = __ballot_sync(0xffffffffu, cu == 0), b1 = __ballot_sync(0xffffffffu, cu == 1);
     u32 b2 = __ballot_sync(0xffffffffu, cu == 2), b3 = __ballot_sync(0xffffffffu, cu == 3);
     if (cu < 4) {
       u32 bm = cu == 0 ? b0 : cu == 1 ? b1 : cu == 2 ? b2 : b3;
-      u32 off = (cu == 0 ? run[0] : cu == 1 ? run[1] : cu == 2 ? run[2] : run[3]) + __popc(bm & lt);
-      u64 slot = a.down ? a.lo + a.len - 1 - j : a.lo + j;
-      u32 v = a.SA[slot];
-      u64 cur = cu == 0 ? a.cur[0] : cu == 1 ? a.cur[1] : cu == 2 ? a.cur[2] : a.cur[3];
-      u64 dst = a.down ? cur - 1 - off : cur + off;
-      a.SA[dst] = v - 1;
+      u32 lp = (cu == 0 ? run[0] : cu == 1 ? run[1] : cu == 2 ? run[2] : run[3]) + __popc(bm & lt);
+      sm.sSA[lp] = val[r] - 1u;
+      sm.sCTX[lp] = cx[r] >> 2;
     }
     run[0] += __popc(b0); run[1] += __popc(b1); run[2] += __popc(b2); run[3] += __popc(b3);
   }
+  __syncthreads();
+  const u32 total = sm.sb[4];
+  for (u32 idx = threadIdx.x; idx < total; idx += WAVE_THREADS) {
+    u32 s = (idx >= sm.sb[1]) + (idx >= sm.sb[2]) + (idx >= sm.sb[3]);
+    u32 off = tile_off[s] + (idx - sm.sb[s]);
+    u64 cur = s == 0 ? a.cur[0] : s == 1 ? a.cur[1] : s == 2 ? a.cur[2] : a.cur[3];
+    u64 dst = a.down ? cur - 1 - off : cur + off;
+    a.SA[dst] = sm.sSA[idx];
+    a.CTX[dst] = sm.sCTX[idx];
+  }
 }
 
-__global__ void __launch_bounds__(WAVE_THREADS) k_wave_scatter(WaveArgs a, const u8* __restrict__ side,
-                                                              const u32* __restrict__ E, u32 ntiles) {
-  __shared__ u32 wsum[WAVE_WARPS][4];
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_scatter(WaveArgs a, const u32* __restrict__ E, u32 ntiles) {
+  __shared__ WaveSmem sm;
   u32 tile_off[4];
 #pragma unroll
   for (int s = 0; s < 4; s++) tile_off[s] = E[(u64)s * ntiles + blockIdx.x] - E[(u64)s * ntiles];
-  wave_scatter_tile(a, side, blockIdx.x, tile_off, wsum);
+  wave_scatter_tile(a, blockIdx.x, tile_off, sm);
 }
 
-// a wave of at most one tile: count + scatter in one block, totals written to tot[4]
-__global__ void __launch_bounds__(WAVE_THREADS) k_wave_small(WaveArgs a, u8* __restrict__ side, u32* __restrict__ tot) {
-  __shared__ u32 wsum[WAVE_WARPS][4];
-  for (u32 j = threadIdx.x; j < a.len; j += WAVE_THREADS) {
-    u32 v;
-    side[j] = (u8)wave_symbol(a, j, v);
-  }
+// a wave of at most one tile: refresh + scatter in one block, totals written to tot[4]
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_small(WaveArgs a, u32* __restrict__ tot) {
+  __shared__ WaveSmem sm;
+  for (u32 j = threadIdx.x; j < a.len; j += WAVE_THREADS) wave_ctx_refresh(a, wave_slot(a, j));
   __syncthreads();
   u32 tile_off[4] = {0, 0, 0, 0};
-  wave_scatter_tile(a, side, 0, tile_off, wsum);
-  __syncthreads();
-  if (threadIdx.x < 4) {
-    u32 t = 0;
-    for (int ww = 0; ww < WAVE_WARPS; ww++) t += wsum[ww][threadIdx.x];
-    tot[threadIdx.x] = t;
-  }
+  wave_scatter_tile(a, 0, tile_off, sm);
+  if (threadIdx.x < 4) tot[threadIdx.x] = sm.sb[threadIdx.x + 1] - sm.sb[threadIdx.x];
 }
 
-void induce_wave(u32* SA, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4], WaveScratch ws,
-                 u32 tot[4], cudaStream_t st) {
+void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4],
+                 WaveScratch ws, u32 tot[4], cudaStream_t st) {
   tot[0] = tot[1] = tot[2] = tot[3] = 0;
   if (len == 0) return;
   WaveArgs a;
-  a.SA = SA; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
+  a.SA = SA; a.CTX = CTX; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
   if (len <= WAVE_TILE) {
-    k_wave_small<<<1, WAVE_THREADS, 0, st>>>(a, ws.side, ws.tot_dev);
+    k_wave_small<<<1, WAVE_THREADS, 0, st>>>(a, ws.tot_dev);
     CK_LAUNCH(); g_launches++;
   } else {
     u32 ntiles = (u32)wave_tiles(len);
-    k_wave_count<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.side, ws.C, ntiles);
+    k_wave_count<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.C, ntiles);
     CK_LAUNCH();
     scan_excl_u32(ws.C, (u64)4 * ntiles, ws.partials, ws.scan_total, st);
     k_wave_totals<<<1, 32, 0, st>>>(ws.C, ntiles, ws.scan_total, ws.tot_dev);
     CK_LAUNCH();
-    k_wave_scatter<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.side, ws.C, ntiles);
+    k_wave_scatter<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.C, ntiles);
     CK_LAUNCH();
     g_launches += 3;
   }

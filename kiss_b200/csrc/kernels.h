@@ -105,13 +105,13 @@ struct Buckets {
   u64 lms_off[4];    // exclusive prefix of lms_count
 };
 // K4: merge the sorted long LMS suffixes with the inserted short ones and drop them at their bucket ends
+// (CTX, when non-null, receives the "context not fetched" marker for every placed suffix)
 void place_lms(const u32* longs, u32 nl, const u32* sorted_shorts, const u32* ins, u32 ns, Buckets bk, u64 n,
-               u32* SA, cudaStream_t st);
+               u32* SA, u32* CTX, cudaStream_t st);
 // place an already complete order (sentinel excluded)
-void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, cudaStream_t st);
+void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, u32* CTX, cudaStream_t st);
 
 struct WaveScratch {
-  u8* side;    // one byte per entry of the largest wave
   u32* C;      // 4 * tiles counters
   u32* partials;
   u32* scan_total;
@@ -123,7 +123,8 @@ inline u64 wave_tiles(u64 len) { return (len + WAVE_TILE - 1) / WAVE_TILE; }
 // One induction wave over SA[lo, lo+len) (scanned downwards when `down`): every entry v > 0 whose preceding
 // symbol S[v-1] is in `symmask` appends v-1 at cur[S[v-1]] (upwards) or below it (downwards).  Synchronises
 // the stream and returns the per-symbol counts in tot[4].
-void induce_wave(u32* SA, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4], WaveScratch ws,
-                 u32 tot[4], cudaStream_t st);
+// CTX is the per-entry context array (n + 1 words, see induce.cu).
+void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4],
+                 WaveScratch ws, u32 tot[4], cudaStream_t st);
 
 }  // namespace kiss

@@ -158,17 +158,20 @@ void lms_classify(const u64* T, u64 n, u8* gp, u64* lmsmask, u32* chunk_cnt, u64
   g_launches += 3;
 }
 
-// pass E: positions (ascending) and first-16-base keys
-__global__ void __launch_bounds__(256) k_lms_emit(const u64* __restrict__ T, u64 nwords, u64 nchunks,
-                                                 const u64* __restrict__ lmsmask, const u32* __restrict__ chunk_off,
-                                                 u32* __restrict__ pos, u32* __restrict__ key) {
-  u64 c = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= nchunks) return;
-  u64 w0 = c * LMS_CHUNK_WORDS, w1 = min(nwords, w0 + LMS_CHUNK_WORDS);
-  u32 off = chunk_off[c];
-  for (u64 j = w0; j < w1; j++) {
-    u64 mk = lmsmask[j];
-    if (!mk) continue;
+// pass E: positions (ascending) and first-16-base keys.  One block = 256 mask words (4 chunks); the positions
+// of the tile are staged in shared memory and written with coalesced stores.
+#define EMIT_WORDS 256
+__global__ void __launch_bounds__(EMIT_WORDS) k_lms_emit(const u64* __restrict__ T, u64 nwords,
+                                                        const u64* __restrict__ lmsmask,
+                                                        const u32* __restrict__ chunk_off, u32* __restrict__ pos,
+                                                        u32* __restrict__ key) {
+  __shared__ u32 ws[33];
+  __shared__ u32 spos[EMIT_WORDS * 16], skey[EMIT_WORDS * 16];  // at most 16 LMS positions per 32 bases
+  const u64 j = (u64)blockIdx.x * EMIT_WORDS + threadIdx.x;
+  u64 mk = j < nwords ? lmsmask[j] : 0ull;
+  u32 total;
+  u32 ex = block_excl_scan((u32)__popcll(mk), ws, total);
+  if (mk) {
     u64 a = T[j], b = T[j + 1];
     while (mk) {
       int lz = __clzll((long long)mk);
@@ -176,17 +179,24 @@ __global__ void __launch_bounds__(256) k_lms_emit(const u64* __restrict__ T, u64
       mk &= ~(1ull << (63 - lz));
       u32 sh = 2 * f;
       u64 wv = sh ? ((a << sh) | (b >> (64 - sh))) : a;
-      pos[off] = (u32)(j * 32 + f);
-      key[off] = (u32)(wv >> 32);
-      off++;
+      spos[ex] = (u32)(j * 32 + f);
+      skey[ex] = (u32)(wv >> 32);
+      ex++;
     }
+  }
+  __syncthreads();
+  const u32 off = chunk_off[(u64)blockIdx.x * (EMIT_WORDS / LMS_CHUNK_WORDS)];
+  for (u32 t = threadIdx.x; t < total; t += EMIT_WORDS) {
+    pos[off + t] = spos[t];
+    key[off + t] = skey[t];
   }
 }
 
 void lms_emit(const u64* T, u64 n, const u64* lmsmask, const u32* chunk_off, u32* pos, u32* key, cudaStream_t st) {
-  u64 nwords = (n + 31) / 32, nchunks = lms_chunks(n);
-  if (nchunks == 0) return;
-  k_lms_emit<<<(unsigned)((nchunks + 255) / 256), 256, 0, st>>>(T, nwords, nchunks, lmsmask, chunk_off, pos, key);
+  u64 nwords = (n + 31) / 32;
+  if (nwords == 0) return;
+  k_lms_emit<<<(unsigned)((nwords + EMIT_WORDS - 1) / EMIT_WORDS), EMIT_WORDS, 0, st>>>(T, nwords, lmsmask, chunk_off,
+                                                                                       pos, key);
   CK_LAUNCH();
   g_launches++;
 }

@@ -37,34 +37,80 @@ __device__ __forceinline__ bool suffix_less(const SortParams& sp, u32 p, u32 q, 
 }
 
 // ------------------------------------------------------------------------------------------- tiny groups
+// One block looks at 256 consecutive sorted keys (+ a halo).  Every element whose key equals a neighbour's
+// fetches its next 32 bases in parallel (independent gathers, no dependent chains); then the first element of
+// each group of <= TINY_MAX orders the group in shared memory by (next word, deeper words, position).
+#define TG_THREADS 256
 template <typename K>
-__global__ void __launch_bounds__(256) k_groups_tiny(const K* __restrict__ keys, u32* __restrict__ pos, u32 N,
-                                                    SortParams sp, u64 h, GroupLists gl) {
-  u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N) return;
-  K k = keys[i];
-  if (i > 0 && keys[i - 1] == k) return;        // not a group head
-  if (i + 1 >= N || keys[i + 1] != k) return;   // singleton
+__global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict__ keys, u32* __restrict__ pos, u32 N,
+                                                           SortParams sp, u64 h, GroupLists gl) {
+  __shared__ K skey[TG_THREADS + TINY_MAX + 2];   // keys[base-1 .. base+TG_THREADS+TINY_MAX]
+  __shared__ u32 spos[TG_THREADS + TINY_MAX];
+  __shared__ u64 sw[TG_THREADS + TINY_MAX];
+  const u32 tid = threadIdx.x;
+  const u64 base = (u64)blockIdx.x * TG_THREADS;
+  for (u32 j = tid; j < TG_THREADS + TINY_MAX + 2; j += TG_THREADS) {
+    u64 idx = base + j;  // = element index + 1
+    skey[j] = (idx >= 1 && idx - 1 < N) ? keys[idx - 1] : (K)0;
+  }
+  __syncthreads();
+  const bool deep = h < sp.D;
+  for (u32 t = tid; t < TG_THREADS + TINY_MAX; t += TG_THREADS) {
+    u64 e = base + t;
+    if (e < N) {
+      K k = skey[t + 1];
+      bool pe = e > 0 && skey[t] == k, ne = e + 1 < N && skey[t + 2] == k;
+      if ((pe || ne) && deep) {
+        u32 p = pos[e];
+        u64 wv = word_at(sp.T, (u64)p + h);
+        u64 rem = sp.D - h;
+        if (rem < 32) wv &= ~0ull << (64 - 2 * rem);
+        spos[t] = p;
+        sw[t] = wv;
+      }
+    }
+  }
+  __syncthreads();
+  const u64 e = base + tid;
+  if (e >= N) return;
+  const K k = skey[tid + 1];
+  if (e > 0 && skey[tid] == k) return;            // not a group head
+  if (e + 1 >= N || skey[tid + 2] != k) return;   // singleton
   u32 g = 2;
-  while (g <= TINY_MAX && i + g < N && keys[i + g] == k) g++;
+  while (g <= TINY_MAX && e + g < N && skey[tid + 1 + g] == k) g++;
   if (g > TINY_MAX) {
     u32 idx = atomicAdd(&gl.counters[0], 1u);
-    if (idx < gl.gcap) gl.glist[idx] = i; else gl.counters[3] = 1;
+    if (idx < gl.gcap) gl.glist[idx] = (u32)e; else gl.counters[3] = 1;
     return;
   }
   atomicAdd(gl.tied, (u64)g);
-  if (h >= sp.D) return;  // fully compared: the stable order (ascending position) is final
+  if (!deep) return;  // fully compared: the stable order (ascending position) is final
+  // near the end of the text (unbounded mode) or of the compared depth: plain comparator on positions
+  bool slow = false;
+  for (u32 a = 0; a < g; a++) slow |= ((u64)spos[tid + a] + h + 32 > sp.n);
+  bool changed = false;
   for (u32 a = 1; a < g; a++) {
-    u32 x = pos[i + a];
+    u32 xp = spos[tid + a];
+    u64 xw = sw[tid + a];
     u32 b = a;
     while (b > 0) {
-      u32 y = pos[i + b - 1];
-      if (!suffix_less(sp, x, y, h)) break;
-      pos[i + b] = y;
+      u32 yp = spos[tid + b - 1];
+      u64 yw = sw[tid + b - 1];
+      bool less = slow ? suffix_less(sp, xp, yp, h)
+                       : (xw != yw ? xw < yw : suffix_less(sp, xp, yp, h + 32));
+      if (!less) break;
+      spos[tid + b] = yp;
+      sw[tid + b] = yw;
       b--;
     }
-    pos[i + b] = x;
+    if (b != a) {
+      spos[tid + b] = xp;
+      sw[tid + b] = xw;
+      changed = true;
+    }
   }
+  if (changed)
+    for (u32 a = 0; a < g; a++) pos[e + a] = spos[tid + a];
 }
 
 template <typename K>

@@ -112,21 +112,28 @@ void scan_excl_u32(u32* data, u64 N, u32* partials, u32* total_dev, cudaStream_t
 template <typename K>
 __global__ void __launch_bounds__(RADIX_THREADS) k_radix_hist(const K* __restrict__ kin, u32 N, int shift, u32 mask,
                                                              u32* __restrict__ H, u32 ntiles) {
-  __shared__ u32 hist[256];
-  const u32 tid = threadIdx.x, tile = blockIdx.x;
-  hist[tid] = 0;
+  __shared__ u32 hist[RADIX_WARPS][256];  // one sub-histogram per warp keeps shared-memory atomics uncontended
+  const u32 tid = threadIdx.x, tile = blockIdx.x, w = tid >> 5;
+#pragma unroll
+  for (int ww = 0; ww < RADIX_WARPS; ww++) hist[ww][tid] = 0;
   __syncthreads();
   const u32 tile_base = tile * RADIX_TILE;
-#pragma unroll 4
-  for (u32 i = 0; i < RADIX_ITEMS; i++) {
+  K keys[RADIX_ITEMS];
+#pragma unroll
+  for (int i = 0; i < RADIX_ITEMS; i++) {
     u32 e = tile_base + i * RADIX_THREADS + tid;
-    bool valid = e < N;
-    u32 d = valid ? ((u32)(kin[e] >> shift) & mask) : 256u;
-    u32 peers = __match_any_sync(0xffffffffu, d);
-    if (valid && (u32)(__ffs(peers) - 1) == (tid & 31)) atomicAdd(&hist[d], (u32)__popc(peers));
+    keys[i] = e < N ? kin[e] : (K)0;
+  }
+#pragma unroll
+  for (int i = 0; i < RADIX_ITEMS; i++) {
+    u32 e = tile_base + i * RADIX_THREADS + tid;
+    if (e < N) atomicAdd(&hist[w][(u32)(keys[i] >> shift) & mask], 1u);
   }
   __syncthreads();
-  H[(u64)tid * ntiles + tile] = hist[tid];
+  u32 t = 0;
+#pragma unroll
+  for (int ww = 0; ww < RADIX_WARPS; ww++) t += hist[ww][tid];
+  H[(u64)tid * ntiles + tile] = t;
 }
 
 template <typename K>
@@ -149,15 +156,25 @@ __global__ void __launch_bounds__(RADIX_THREADS) k_radix_scatter(const K* __rest
   __syncthreads();
 
   K keys[RADIX_ITEMS];
+  u32 vals[RADIX_ITEMS];
   u32 rank[RADIX_ITEMS];
   const u32 wbase = tile_base + w * (32 * RADIX_ITEMS);
   const u32 lt_mask = (1u << lane) - 1u;
 #pragma unroll
   for (int r = 0; r < RADIX_ITEMS; r++) {
     u32 e = wbase + r * 32 + lane;
+    keys[r] = e < N ? kin[e] : (K)0;
+  }
+#pragma unroll
+  for (int r = 0; r < RADIX_ITEMS; r++) {
+    u32 e = wbase + r * 32 + lane;
+    vals[r] = e < N ? vin[e] : 0u;
+  }
+#pragma unroll
+  for (int r = 0; r < RADIX_ITEMS; r++) {
+    u32 e = wbase + r * 32 + lane;
     bool valid = e < N;
-    K key = valid ? kin[e] : (K)0;
-    keys[r] = key;
+    K key = keys[r];
     u32 d = (u32)(key >> shift) & mask;
     u32 peers = __match_any_sync(0xffffffffu, valid ? d : 256u);
     u32 leader = (u32)__ffs(peers) - 1u;
@@ -192,7 +209,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) k_radix_scatter(const K* __rest
       u32 d = (u32)(keys[r] >> shift) & mask;
       u32 lp = texcl[d] + wcnt[w * 256 + d] + rank[r];
       skeys[lp] = keys[r];
-      svals[lp] = vin[e];
+      svals[lp] = vals[r];
     }
   }
   __syncthreads();
