@@ -21,12 +21,13 @@ namespace kiss {
 
 // ------------------------------------------------------------------------------------------- placement
 __device__ __forceinline__ u64 lms_slot(const Buckets& bk, u64 r) {
-  // r = rank among the sorted LMS suffixes (sentinel excluded); they are grouped by first symbol
-  int c = 0;
-#pragma unroll
-  for (int s = 1; s < 4; s++)
-    if (r >= bk.lms_off[s]) c = s;
-  return bk.B[c + 1] - bk.lms_count[c] + (r - bk.lms_off[c]);
+  // r = rank among the sorted LMS suffixes (sentinel excluded); they are grouped by first symbol.
+  // (selects, not indexing: a dynamically indexed kernel parameter is spilled to local memory)
+  u64 end = bk.B[1], cnt = bk.lms_count[0], off = bk.lms_off[0];
+  if (r >= bk.lms_off[1]) { end = bk.B[2]; cnt = bk.lms_count[1]; off = bk.lms_off[1]; }
+  if (r >= bk.lms_off[2]) { end = bk.B[3]; cnt = bk.lms_count[2]; off = bk.lms_off[2]; }
+  if (r >= bk.lms_off[3]) { end = bk.B[4]; cnt = bk.lms_count[3]; off = bk.lms_off[3]; }
+  return end - cnt + (r - off);
 }
 
 #define PLACE_INS_SMEM 2048u
@@ -233,7 +234,8 @@ __device__ __forceinline__ void wave_scatter_tile(const WaveArgs& a, u64 tile, c
   const u32 total = sm.sb[4];
   for (u32 idx = threadIdx.x; idx < total; idx += WAVE_THREADS) {
     u32 s = (idx >= sm.sb[1]) + (idx >= sm.sb[2]) + (idx >= sm.sb[3]);
-    u32 off = tile_off[s] + (idx - sm.sb[s]);
+    u32 toff = s == 0 ? tile_off[0] : s == 1 ? tile_off[1] : s == 2 ? tile_off[2] : tile_off[3];
+    u32 off = toff + (idx - sm.sb[s]);
     u64 cur = s == 0 ? a.cur[0] : s == 1 ? a.cur[1] : s == 2 ? a.cur[2] : a.cur[3];
     u64 dst = a.down ? cur - 1 - off : cur + off;
     a.SA[dst] = sm.sSA[idx];

@@ -47,7 +47,9 @@ __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict_
   __shared__ K skey[TG_THREADS + TINY_MAX + 2];   // keys[base-1 .. base+TG_THREADS+TINY_MAX]
   __shared__ u32 spos[TG_THREADS + TINY_MAX];
   __shared__ u64 sw[TG_THREADS + TINY_MAX];
+  __shared__ u32 s_tied;
   const u32 tid = threadIdx.x;
+  if (tid == 0) s_tied = 0;
   const u64 base = (u64)blockIdx.x * TG_THREADS;
   for (u32 j = tid; j < TG_THREADS + TINY_MAX + 2; j += TG_THREADS) {
     u64 idx = base + j;  // = element index + 1
@@ -72,45 +74,52 @@ __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict_
   }
   __syncthreads();
   const u64 e = base + tid;
-  if (e >= N) return;
-  const K k = skey[tid + 1];
-  if (e > 0 && skey[tid] == k) return;            // not a group head
-  if (e + 1 >= N || skey[tid + 2] != k) return;   // singleton
-  u32 g = 2;
-  while (g <= TINY_MAX && e + g < N && skey[tid + 1 + g] == k) g++;
-  if (g > TINY_MAX) {
-    u32 idx = atomicAdd(&gl.counters[0], 1u);
-    if (idx < gl.gcap) gl.glist[idx] = (u32)e; else gl.counters[3] = 1;
-    return;
+  bool head = false;
+  K k = (K)0;
+  if (e < N) {
+    k = skey[tid + 1];
+    head = !(e > 0 && skey[tid] == k) && (e + 1 < N && skey[tid + 2] == k);
   }
-  atomicAdd(gl.tied, (u64)g);
-  if (!deep) return;  // fully compared: the stable order (ascending position) is final
-  // near the end of the text (unbounded mode) or of the compared depth: plain comparator on positions
-  bool slow = false;
-  for (u32 a = 0; a < g; a++) slow |= ((u64)spos[tid + a] + h + 32 > sp.n);
-  bool changed = false;
-  for (u32 a = 1; a < g; a++) {
-    u32 xp = spos[tid + a];
-    u64 xw = sw[tid + a];
-    u32 b = a;
-    while (b > 0) {
-      u32 yp = spos[tid + b - 1];
-      u64 yw = sw[tid + b - 1];
-      bool less = slow ? suffix_less(sp, xp, yp, h)
-                       : (xw != yw ? xw < yw : suffix_less(sp, xp, yp, h + 32));
-      if (!less) break;
-      spos[tid + b] = yp;
-      sw[tid + b] = yw;
-      b--;
-    }
-    if (b != a) {
-      spos[tid + b] = xp;
-      sw[tid + b] = xw;
-      changed = true;
+  if (head) {
+    u32 g = 2;
+    while (g <= TINY_MAX && e + g < N && skey[tid + 1 + g] == k) g++;
+    if (g > TINY_MAX) {
+      u32 idx = atomicAdd(&gl.counters[0], 1u);
+      if (idx < gl.gcap) gl.glist[idx] = (u32)e; else gl.counters[3] = 1;
+    } else {
+      atomicAdd(&s_tied, g);
+      if (deep) {  // otherwise fully compared: the stable order (ascending position) is final
+        // near the end of the text (unbounded mode) or of the compared depth: plain comparator on positions
+        bool slow = false;
+        for (u32 a = 0; a < g; a++) slow |= ((u64)spos[tid + a] + h + 32 > sp.n);
+        bool changed = false;
+        for (u32 a = 1; a < g; a++) {
+          u32 xp = spos[tid + a];
+          u64 xw = sw[tid + a];
+          u32 b = a;
+          while (b > 0) {
+            u32 yp = spos[tid + b - 1];
+            u64 yw = sw[tid + b - 1];
+            bool less = slow ? suffix_less(sp, xp, yp, h)
+                             : (xw != yw ? xw < yw : suffix_less(sp, xp, yp, h + 32));
+            if (!less) break;
+            spos[tid + b] = yp;
+            sw[tid + b] = yw;
+            b--;
+          }
+          if (b != a) {
+            spos[tid + b] = xp;
+            sw[tid + b] = xw;
+            changed = true;
+          }
+        }
+        if (changed)
+          for (u32 a = 0; a < g; a++) pos[e + a] = spos[tid + a];
+      }
     }
   }
-  if (changed)
-    for (u32 a = 0; a < g; a++) pos[e + a] = spos[tid + a];
+  __syncthreads();
+  if (tid == 0 && s_tied) atomicAdd(gl.tied, (u64)s_tied);
 }
 
 template <typename K>

@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) k_radix_hist(const K* __restric
 }
 
 template <typename K>
-__global__ void __launch_bounds__(RADIX_THREADS) k_radix_scatter(const K* __restrict__ kin, const u32* __restrict__ vin,
+__global__ void __launch_bounds__(RADIX_THREADS, 3) k_radix_scatter(const K* __restrict__ kin, const u32* __restrict__ vin,
                                                                 K* __restrict__ kout, u32* __restrict__ vout, u32 N,
                                                                 int shift, u32 mask, const u32* __restrict__ H,
                                                                 u32 ntiles) {
@@ -156,7 +156,6 @@ __global__ void __launch_bounds__(RADIX_THREADS) k_radix_scatter(const K* __rest
   __syncthreads();
 
   K keys[RADIX_ITEMS];
-  u32 vals[RADIX_ITEMS];
   u32 rank[RADIX_ITEMS];
   const u32 wbase = tile_base + w * (32 * RADIX_ITEMS);
   const u32 lt_mask = (1u << lane) - 1u;
@@ -168,15 +167,18 @@ __global__ void __launch_bounds__(RADIX_THREADS) k_radix_scatter(const K* __rest
 #pragma unroll
   for (int r = 0; r < RADIX_ITEMS; r++) {
     u32 e = wbase + r * 32 + lane;
-    vals[r] = e < N ? vin[e] : 0u;
-  }
-#pragma unroll
-  for (int r = 0; r < RADIX_ITEMS; r++) {
-    u32 e = wbase + r * 32 + lane;
     bool valid = e < N;
     K key = keys[r];
     u32 d = (u32)(key >> shift) & mask;
-    u32 peers = __match_any_sync(0xffffffffu, valid ? d : 256u);
+    // lanes holding the same digit: one ballot per digit bit (MATCH.ANY runs on the slow ADU pipe:
+    // 77 % busy in the first ncu capture, profiles/r1_v1_radix_scatter.txt)
+    u32 peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int b = 0; b < 8; b++) {
+      bool bit = (d >> b) & 1u;
+      u32 bal = __ballot_sync(0xffffffffu, bit);
+      peers &= bit ? bal : ~bal;
+    }
     u32 leader = (u32)__ffs(peers) - 1u;
     u32 old = 0;
     if (lane == leader && valid) {
@@ -209,7 +211,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) k_radix_scatter(const K* __rest
       u32 d = (u32)(keys[r] >> shift) & mask;
       u32 lp = texcl[d] + wcnt[w * 256 + d] + rank[r];
       skeys[lp] = keys[r];
-      svals[lp] = vals[r];
+      svals[lp] = vin[e];
     }
   }
   __syncthreads();
