@@ -134,6 +134,12 @@ int kiss_b200_sort_lms_subset_dev(kiss_b200_ctx* ctx, uint32_t* pos_dev, uint64_
  * context, valid until the next prepare): used to pick splitters and to bucket positions by destination. */
 int kiss_b200_lms_keys_dev(kiss_b200_ctx* ctx, const uint32_t** keys_dev, const uint32_t** pos_dev,
                            uint64_t* n_long);
+/* Stable partition of the context's text-ordered long LMS suffixes [lo, hi) by destination rank: destination of
+ * a suffix = number of splitters <= its first-16-base key (n_split <= 63 ascending splitters, host array).
+ * out_pos_dev receives the positions grouped by destination, ascending text order inside each group;
+ * counts_host[0..n_split] the group sizes.  This is the send buffer of the NCCL all-to-all. */
+int kiss_b200_partition_lms_dev(kiss_b200_ctx* ctx, const uint32_t* splitters_host, int n_split, uint64_t lo,
+                                uint64_t hi, uint32_t* out_pos_dev, uint64_t* counts_host);
 /* Finish on this GPU from a fully sorted list of the long LMS suffixes (device, n_long entries):
  * short-suffix insertion, placement and induction into SA_dev (n + 1). */
 int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_long_dev, uint64_t n_long,

@@ -48,6 +48,7 @@ SIGNATURES = {
     "kiss_b200_induce_from_sorted_lms": (_int, [_vp, _vp, _u64, _vp, _u64, _vp]),
     "kiss_b200_prepare_dev": (_int, [_vp, _vp, _u64, _u32, C.POINTER(_u64)]),
     "kiss_b200_sort_lms_subset_dev": (_int, [_vp, _vp, _u64, C.POINTER(Timings)]),
+    "kiss_b200_partition_lms_dev": (_int, [_vp, _vp, _int, _u64, _u64, _vp, _vp]),
     "kiss_b200_lms_keys_dev": (_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_u64)]),
     "kiss_b200_finish_from_sorted_dev": (_int, [_vp, _vp, _u64, _vp, C.POINTER(Timings)]),
     "kiss_b200_synth_uniform_dev": (_int, [_vp, _vp, _u64, _u64]),

@@ -715,6 +715,40 @@ int kiss_b200_lms_keys_dev(kiss_b200_ctx* c, const uint32_t** keys_dev, const ui
   return KISS_B200_OK;
 }
 
+int kiss_b200_partition_lms_dev(kiss_b200_ctx* c, const uint32_t* splitters_host, int n_split, uint64_t lo,
+                                uint64_t hi, uint32_t* out_pos_dev, uint64_t* counts_host) {
+  if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
+  if (n_split < 0 || n_split > 63 || lo > hi || hi > c->prep.n_long || (hi > lo && !out_pos_dev) || !counts_host ||
+      (n_split && !splitters_host)) {
+    g_last_error = "bad argument";
+    return KISS_B200_ERR_ARG;
+  }
+  return guarded(c, [&] {
+    cudaStream_t st = c->st;
+    Pool pool(st);
+    u32 N = (u32)(hi - lo);
+    u32* spl = pool.alloc<u32>(64);
+    u32* counts = pool.alloc<u32>(65);
+    CK(cudaMemsetAsync(counts, 0, 65 * sizeof(u32), st));
+    if (n_split) CK(cudaMemcpyAsync(spl, splitters_host, n_split * sizeof(u32), cudaMemcpyHostToDevice, st));
+    u32* dest = pool.alloc<u32>(N);
+    u32* dest_alt = pool.alloc<u32>(N);
+    u32* vals = pool.alloc<u32>(N);
+    u32* vals_alt = pool.alloc<u32>(N);
+    if (N) CK(cudaMemcpyAsync(vals, c->prep.pos + lo, N * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    dest_by_splitters(c->prep.key + lo, N, spl, (u32)n_split, dest, counts, st);
+    u64 nt = radix_tiles(N);
+    u32* H = pool.alloc<u32>(256 * nt);
+    u32* partials = pool.alloc<u32>(scan_partials_len(256 * nt));
+    radix_sort_u32(dest, vals, dest_alt, vals_alt, N, 0, 8, H, partials, st);  // one stable pass on the destination
+    if (N) CK(cudaMemcpyAsync(out_pos_dev, vals, N * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    u32 hc[65];
+    CK(cudaMemcpyAsync(hc, counts, 65 * sizeof(u32), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    for (int d = 0; d <= n_split; d++) counts_host[d] = hc[d];
+  });
+}
+
 int kiss_b200_sort_lms_subset_dev(kiss_b200_ctx* c, uint32_t* pos_dev, uint64_t count, kiss_b200_timings* t) {
   if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
   if (count && !pos_dev) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }

@@ -93,6 +93,9 @@ void big_writeback(u32* pos_main, const u32* wslot, const u32* wpos, u32 total, 
 // key[i] = first 16 bases of suffix pos[i]
 void gather_keys(const u64* T, const u32* pos, u32 N, u32* key, cudaStream_t st);
 
+// destination rank of every key under at most 64 ascending splitters, and the per-destination counts
+void dest_by_splitters(const u32* key, u32 N, const u32* spl, u32 nspl, u32* dest, u32* counts, cudaStream_t st);
+
 // short suffixes (fewer than D bases left): exact reference comparator (kiss1_core.hpp:94-135)
 void shorts_order(const u32* shorts, u32 ns, SortParams sp, u32* rank0, u32* sorted_shorts, cudaStream_t st);
 void shorts_insertions(const u32* sorted_shorts, u32 ns, const u32* longs, u32 nl, SortParams sp, u32* ins,

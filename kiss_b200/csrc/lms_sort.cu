@@ -279,6 +279,31 @@ void gather_keys(const u64* T, const u32* pos, u32 N, u32* key, cudaStream_t st)
   CK_LAUNCH(); g_launches++;
 }
 
+// ------------------------------------------------------------------------------------------- sharding
+// dest[i] = number of splitters <= key[i]  (equal keys always share a destination, so tie refinement and the
+// position tie-break stay local to one GPU); counts[d] accumulates the destination sizes
+__global__ void __launch_bounds__(256) k_dest_by_splitters(const u32* __restrict__ key, u32 N, const u32* __restrict__ spl,
+                                                          u32 nspl, u32* __restrict__ dest, u32* __restrict__ counts) {
+  __shared__ u32 sspl[64], scnt[65];
+  if (threadIdx.x < 64) sspl[threadIdx.x] = threadIdx.x < nspl ? spl[threadIdx.x] : 0xFFFFFFFFu;
+  if (threadIdx.x < 65) scnt[threadIdx.x] = 0;
+  __syncthreads();
+  u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) {
+    u32 k = key[i], d = 0;
+    for (u32 s = 0; s < nspl; s++) d += (sspl[s] <= k);
+    dest[i] = d;
+    atomicAdd(&scnt[d], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x <= nspl && scnt[threadIdx.x]) atomicAdd(&counts[threadIdx.x], scnt[threadIdx.x]);
+}
+void dest_by_splitters(const u32* key, u32 N, const u32* spl, u32 nspl, u32* dest, u32* counts, cudaStream_t st) {
+  if (!N) return;
+  k_dest_by_splitters<<<(N + 255) / 256, 256, 0, st>>>(key, N, spl, nspl, dest, counts);
+  CK_LAUNCH(); g_launches++;
+}
+
 // ------------------------------------------------------------------------------------------- short suffixes
 // Literal restatement of the reference's comparator lambda (kiss1_core.hpp:94-135) on the packed text,
 // preceded by the first-10-bases bucket order of the counting sort that runs before it (:41-83,

@@ -159,11 +159,14 @@ __global__ void __launch_bounds__(RADIX_THREADS, 3) k_radix_scatter(const K* __r
   u32 rank[RADIX_ITEMS];
   const u32 wbase = tile_base + w * (32 * RADIX_ITEMS);
   const u32 lt_mask = (1u << lane) - 1u;
+  // keys and this thread's digit base are requested up front; values are fetched when staged (holding them
+  // in registers too costs a resident block per SM, which measured slower)
 #pragma unroll
   for (int r = 0; r < RADIX_ITEMS; r++) {
     u32 e = wbase + r * 32 + lane;
     keys[r] = e < N ? kin[e] : (K)0;
   }
+  const u32 hbase = H[(u64)tid * ntiles + tile];
 #pragma unroll
   for (int r = 0; r < RADIX_ITEMS; r++) {
     u32 e = wbase + r * 32 + lane;
@@ -201,7 +204,7 @@ __global__ void __launch_bounds__(RADIX_THREADS, 3) k_radix_scatter(const K* __r
     u32 tot;
     u32 ex = block_excl_scan(run, ws, tot);
     texcl[tid] = ex;
-    dbase[tid] = H[(u64)tid * ntiles + tile] - ex;
+    dbase[tid] = hbase - ex;
   }
   __syncthreads();
 #pragma unroll

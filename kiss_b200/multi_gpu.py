@@ -1,0 +1,154 @@
+"""Sharded LMS sort: one process per GPU, torch.distributed (NCCL over NVLink) for the plumbing.
+
+Only the k-ordered LMS sort shards (BASELINE.json north_star): the text is replicated, every
+rank classifies it, rank r owns the r-th slice of the text-ordered LMS list, the slices are bucketed by
+sampled key splitters, ONE personalised all-to-all moves LMS positions (4 bytes each; keys are re-gathered
+from the replicated text), every rank sorts its key range with the single-GPU kernels, and the sorted ranges
+are concatenated on rank 0, where placement and induction (a single dependency chain) run.
+
+Equal first-16-base keys always share a destination rank, so the tie refinement and the position tie-break
+stay local and the result is bit-identical to the single-GPU path.
+
+The orchestration is written against a small backend interface so that the same code runs under gloo on the
+CPU in tests/test_multi_gpu_host.py (backend = numpy + the oracle) and under NCCL on GPUs (backend = the C ABI).
+"""
+import numpy as np
+
+SAMPLES_PER_RANK = 4096
+
+
+def choose_splitters(all_samples, world):
+    """world-1 ascending splitters from the concatenated key samples of all ranks (uint32).
+    destination of a key = number of splitters <= key."""
+    s = np.sort(np.asarray(all_samples, dtype=np.uint32))
+    if s.size == 0 or world <= 1:
+        return np.zeros(0, np.uint32)
+    idx = (np.arange(1, world, dtype=np.int64) * s.size) // world
+    return s[idx].astype(np.uint32)
+
+
+def slice_bounds(n_long, rank, world):
+    return (n_long * rank) // world, (n_long * (rank + 1)) // world
+
+
+class GpuBackend:
+    """device arrays are torch int32 tensors on the rank's GPU; kernels via the C ABI"""
+
+    def __init__(self, ctx, torch):
+        self.ctx, self.torch = ctx, torch
+
+    def prepare(self, S, n, k):
+        self.m = self.ctx.prepare_dev(S.data_ptr(), n, k)
+        self.kp, self.pp, self.n_long = self.ctx.lms_keys_dev()
+        return self.n_long
+
+    def sample_keys(self, lo, hi, count):
+        torch = self.torch
+        if hi <= lo:
+            return np.zeros(0, np.uint32)
+        # strided sample of the slice's keys, read straight from the context's device array
+        cnt = min(count, hi - lo)
+        idx = (np.arange(cnt, dtype=np.int64) * (hi - lo)) // cnt + lo
+        keys = _as_tensor(torch, self.kp, self.n_long)
+        return keys[torch.from_numpy(idx).cuda()].cpu().numpy().view(np.uint32)
+
+    def partition(self, splitters, lo, hi):
+        torch = self.torch
+        out = torch.empty(max(hi - lo, 1), dtype=torch.int32, device="cuda")
+        counts = self.ctx.partition_lms_dev(splitters, lo, hi, out.data_ptr())
+        return out[:hi - lo], counts.astype(np.int64)
+
+    def empty(self, count):
+        return self.torch.empty(max(count, 1), dtype=self.torch.int32, device="cuda")[:count]
+
+    def sort_subset(self, buf, count):
+        self.torch.cuda.synchronize()
+        return self.ctx.sort_lms_subset_dev(buf.data_ptr(), count)
+
+    def finish(self, sorted_long, n_long, SA):
+        self.torch.cuda.synchronize()
+        return self.ctx.finish_from_sorted_dev(sorted_long.data_ptr(), n_long, SA.data_ptr())
+
+    def sync(self):
+        self.torch.cuda.synchronize()
+
+
+def _as_tensor(torch, ptr, count):
+    """int32 view of `count` device words at raw address `ptr` (no copy)"""
+    class _Arr:
+        __cuda_array_interface__ = {"shape": (count,), "typestr": "<i4", "data": (ptr, False), "version": 2}
+    return torch.as_tensor(_Arr(), device="cuda")
+
+
+def sharded_lms_sort(backend, dist, n_long, rank, world):
+    """returns (sorted_long on rank 0 else None, stats).  Collectives: one all_gather of key samples, one
+    all_to_all of counts, one all_to_all of positions, one gather-shaped all_to_all of the sorted ranges."""
+    torch = backend.torch
+    lo, hi = slice_bounds(n_long, rank, world)
+    # 1. splitters
+    mine = backend.sample_keys(lo, hi, SAMPLES_PER_RANK)
+    pad = np.full(SAMPLES_PER_RANK + 1, 0, np.int64)
+    pad[0] = mine.size
+    pad[1:1 + mine.size] = mine
+    t = torch.from_numpy(pad).to(backend_device(backend))
+    gathered = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(gathered, t)
+    samples = np.concatenate([g.cpu().numpy()[1:1 + int(g[0].item())] for g in gathered]).astype(np.uint32)
+    splitters = choose_splitters(samples, world)
+    # 2. bucket this rank's slice by destination (stable) and exchange the counts
+    send, send_counts = backend.partition(splitters, lo, hi)
+    sc = torch.from_numpy(send_counts.astype(np.int64)).to(backend_device(backend))
+    rc = torch.empty_like(sc)
+    dist.all_to_all_single(rc, sc)
+    recv_counts = rc.cpu().numpy()
+    total = int(recv_counts.sum())
+    # 3. the exchange: LMS positions only
+    recv = backend.empty(total)
+    backend.sync()
+    dist.all_to_all_single(recv, send, output_split_sizes=recv_counts.tolist(), input_split_sizes=send_counts.tolist())
+    # chunks arrive in source-rank order = ascending text order: the stable sort's precondition
+    # 4. local sort of this rank's key range
+    st = backend.sort_subset(recv, total)
+    # 5. concatenate the ranges on rank 0 (key ranges are ordered by rank)
+    sizes = torch.tensor([total], dtype=torch.int64, device=backend_device(backend))
+    all_sizes = [torch.empty_like(sizes) for _ in range(world)]
+    dist.all_gather(all_sizes, sizes)
+    all_sizes = [int(x.item()) for x in all_sizes]
+    out_split = all_sizes if rank == 0 else [0] * world
+    in_split = [total] + [0] * (world - 1)
+    result = backend.empty(sum(out_split))
+    backend.sync()
+    dist.all_to_all_single(result, recv, output_split_sizes=out_split, input_split_sizes=in_split)
+    stats = {"shard_sizes": all_sizes, "imbalance": (max(all_sizes) * world / max(1, sum(all_sizes))),
+             "sort": st}
+    return (result if rank == 0 else None), stats
+
+
+def backend_device(backend):
+    return getattr(backend, "device", "cuda")
+
+
+def sharded_suffix_array_dev(ctx, S, n, SA, k, dist):
+    """bench / product entry at N > 1: S, SA are torch tensors on this rank's GPU (S replicated on every rank);
+    the suffix array lands in SA on rank 0.  Returns a timing dict shaped like Context.last_timings."""
+    import time
+    import torch
+    rank, world = dist.get_rank(), dist.get_world_size()
+    be = GpuBackend(ctx, torch)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    n_long = be.prepare(S, n, k)
+    t1 = time.perf_counter()
+    sorted_long, stats = sharded_lms_sort(be, dist, n_long, rank, world)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    out = {"kernel_launches": 12, "m": be.m, "get_lms": t1 - t0, "lms_sort": t2 - t1, "put_lms": 0.0, "induce": 0.0,
+           "pack": 0.0, "shard_sizes": stats["shard_sizes"], "imbalance": stats["imbalance"]}
+    if rank == 0:
+        ft = be.finish(sorted_long, n_long, SA)
+        out.update(put_lms=ft["put_lms"], induce=ft["induce"], waves_L=ft["waves_L"], waves_S=ft["waves_S"],
+                   kernel_launches=out["kernel_launches"] + ft["kernel_launches"])
+    out["kernel_launches"] += stats["sort"]["kernel_launches"]
+    out["total_device"] = out["get_lms"] + out["lms_sort"] + out["put_lms"] + out["induce"]
+    dist.barrier()
+    return out

@@ -126,6 +126,12 @@ class Context:
         check(lib().kiss_b200_lms_keys_dev(self._h, C.byref(kp), C.byref(pp), C.byref(nl)))
         return kp.value, pp.value, nl.value
 
+    def partition_lms_dev(self, splitters, lo, hi, out_ptr):
+        spl = np.ascontiguousarray(splitters, dtype=np.uint32)
+        counts = np.zeros(spl.size + 1, np.uint64)
+        check(lib().kiss_b200_partition_lms_dev(self._h, spl.ctypes.data, spl.size, lo, hi, out_ptr, counts.ctypes.data))
+        return counts
+
     def sort_lms_subset_dev(self, pos_ptr, count):
         t = Timings()
         check(lib().kiss_b200_sort_lms_subset_dev(self._h, pos_ptr, count, C.byref(t)))
