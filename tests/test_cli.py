@@ -1,0 +1,82 @@
+"""`kISS suffix_sort` command (kiss_b200/host/kiss_main.cpp) against the reference CLI's semantics
+(include/utils/options.hpp, include/command/suffix_sort.hpp, include/utils/io.hpp)."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+import textgen as tg
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+KISS = os.path.join(ROOT, "kiss_b200", "kISS")
+
+
+def run(*args):
+    return subprocess.run([KISS, *args], capture_output=True, text=True, timeout=300)
+
+
+def test_version_and_help_exit_1():
+    r = run("-v")
+    assert r.returncode == 1 and r.stdout.strip() == "1.0.0"     # options.hpp:255-264
+    r = run("--help")
+    assert r.returncode == 1 and "suffix_sort" in r.stdout
+    r = run()
+    assert r.returncode == 1
+
+
+def test_bad_arguments_print_help_and_exit_1():
+    r = run("suffix_sort", "-s", "bogus", "x.fa")                # options.hpp:67-81, 240-244
+    assert r.returncode == 1 and "sorting-algorithm" in r.stderr
+    r = run("suffix_sort", "--nope", "x.fa")
+    assert r.returncode == 1
+
+
+def test_generic_flag_is_refused(tmp_path):
+    f = tmp_path / "t.txt"
+    f.write_text("ACGT\n")
+    r = run("-g", "suffix_sort", str(f))                         # suffix_sort.hpp:26-28
+    assert r.returncode != 0 and "Generic sorting and indexing are currently not supported." in r.stderr
+
+
+def test_unknown_command():
+    r = run("frobnicate", "x")
+    assert r.returncode != 0 and "frobnicate" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["fasta", "text"])
+def test_suffix_sort_file(tmp_path, mode):
+    S = tg.mixed(61, 50_000)
+    txt = np.frombuffer(b"ACGT", np.uint8)[S].copy()
+    txt[500:520] = ord("N")                                      # N -> A
+    txt[1000:1100] |= 0x20                                       # lower case
+    S[500:520] = 0
+    lines = [txt[i:i + 70].tobytes().decode() for i in range(0, txt.size, 70)]
+    f = tmp_path / ("t.fa" if mode == "fasta" else "t.txt")
+    if mode == "fasta":                                          # io.hpp:8-11: records concatenated, headers dropped
+        half = len(lines) // 2
+        f.write_text(">chr1 first\n" + "\n".join(lines[:half]) + "\n>chr2\n" + "\n".join(lines[half:]) + "\n")
+    else:
+        f.write_text("\n".join(lines) + "\n")
+    out = tmp_path / "sa.bin"
+    for algo, k in (("parallel_sorting", "256"), ("PREFIX_DOUBLING", "-1")):
+        r = run("--verbose", "suffix_sort", str(f), "-k", k, "-s", algo, "--out", str(out))
+        assert r.returncode == 0, r.stderr
+        kk = 256 if k == "256" else 2 ** 64 - 1
+        assert re.search(rf"\[info\] \[suffix_sort.hpp:61\] n = {S.size}, k = {kk}, suffix sorting elapsed [0-9.]+", r.stderr)
+        assert "induced_sort elapsed" in r.stderr
+        sa = np.fromfile(out, dtype=np.uint32)
+        assert np.array_equal(sa, ol.oracle_kiss1(S, k=0xFFFFFFFF if k == "-1" else 256))
+
+
+@pytest.mark.gpu
+def test_empty_file(tmp_path):
+    f = tmp_path / "e.txt"
+    f.write_text("")
+    out = tmp_path / "sa.bin"
+    r = run("suffix_sort", str(f), "--out", str(out))
+    assert r.returncode == 0 and "n = 0" in r.stderr
+    assert np.fromfile(out, dtype=np.uint32).tolist() == [0]     # kiss1_core.hpp:237-238
