@@ -34,7 +34,7 @@ SEED = 2
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--n", type=int, default=N_DEFAULT)
@@ -68,7 +68,10 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.time(), line.strip()))
+
+    def window(self, t0, t1):
+        self.t0, self.t1 = t0, t1
 
     def stop(self):
         if not self.proc:
@@ -80,7 +83,9 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        t0, t1 = getattr(self, "t0", 0.0), getattr(self, "t1", 1e18)
+        inside = [r for (t, r) in self.rows if t0 <= t <= t1 + 0.15]
+        for r in (inside or [r for (_, r) in self.rows]):
             f = [x.strip() for x in r.split(",")]
             if len(f) < 7:
                 continue
@@ -193,11 +198,13 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    clocks = ClockSampler(local)
+    clocks.start()
     for _ in range(args.warmup):
         step()
     barrier()
-    clocks = ClockSampler(local)
-    clocks.start()
+    ctx.profile_enable(True)
+    wall0 = time.time()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage = {}
     launches = 0
@@ -211,8 +218,11 @@ def run_b200(args):
         last = t
     e1.record(lib_stream)
     barrier()
+    clocks.window(wall0, time.time())
     ms = e0.elapsed_time(e1)
     clk = clocks.stop()
+    prof = ctx.profile()
+    ctx.profile_enable(False)
     if dist is not None:
         tt = torch.tensor([ms], device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -235,19 +245,44 @@ def run_b200(args):
     }
 
     if rank == 0:
-        # whole-path roofline (HBM bound): algorithmic bytes / device time vs the measured copy peak
+        # roofline of the dominant kernel class: algorithmic bytes per launch / its mean launch duration, measured
+        # live with CUDA events around every launch (kiss_b200_profile_*), vs the measured copy bandwidth
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
+        n_long = m - 1
+        alg = {  # bytes per launch (DESIGN.md "Kernels")
+            "k_radix_scatter": 2 * (4 + 4) * n_long,            # read + write of (key32, pos32) per pass
+            "k_radix_hist": 4 * n_long,
+            "k_groups_tiny": (4 + 4) * n_long,
+            "k_place_lms": (4 + 4 + 4) * n_long,
+        }
+        # induction: per scanned entry 4 (SA) + 4 (context), per induced suffix 4 + 4; summed over all waves
+        scanned = (n + 1) + (n // 2 + m)
+        if "k_wave_scatter" in prof:
+            alg["k_wave_scatter"] = (8 * scanned + 8 * n) / prof["k_wave_scatter"][1]
+        if "k_wave_count" in prof:
+            alg["k_wave_count"] = (4 * scanned + 0.25 * n) / prof["k_wave_count"][1]
+        kernels = {}
+        for name, (tot_ms, cnt) in prof.items():
+            kernels[name] = {"ms_per_step": tot_ms / args.steps, "launches_per_step": cnt / args.steps}
+            if name in alg:
+                gbs = alg[name] / (tot_ms / cnt * 1e-3) / 1e9
+                kernels[name].update(alg_bytes_per_launch=alg[name], achieved_gbs=gbs, frac=gbs / peak)
+        line["kernels"] = kernels
+        dom = max((k for k in kernels if "achieved_gbs" in kernels[k]), key=lambda k: kernels[k]["ms_per_step"])
+        traffic = {"k_radix_scatter": 4.70e9}.get(dom)  # dram read+write per launch, ncu --set full (profiles/)
+        line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
+                            "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": traffic,
+                            "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
+                            "share_of_step": kernels[dom]["ms_per_step"] / ms_step}
         balg = b200_alg_bytes(n, m)
         dev_s = stage.get("total_device", ms * 1e-3) / args.steps
-        ach = balg / dev_s / 1e9
-        line["roofline"] = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                            "traffic": None, "kernel": "whole path (18 n + 28 m algorithmic bytes)",
-                            "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"}
+        line["roofline_whole_path"] = {"alg_bytes": balg, "achieved": balg / dev_s / 1e9, "frac": balg / dev_s / 1e9 / peak,
+                                       "note": "B_alg = 18 n + 28 m (SURVEY.md 8(d))"}
 
     # ---- end to end through the host C ABI (pinned host buffers, H2D + D2H inside the timed region)
     if world == 1 and not args.no_e2e:

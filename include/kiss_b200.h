@@ -145,6 +145,13 @@ int kiss_b200_partition_lms_dev(kiss_b200_ctx* ctx, const uint32_t* splitters_ho
 int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_long_dev, uint64_t n_long,
                                      uint32_t* SA_dev, kiss_b200_timings* t);
 
+/* ---- per-kernel timing ---------------------------------------------------------------------------
+ * When enabled, every launch of the main kernel classes is bracketed by CUDA events on the context's stream and
+ * the durations are accumulated per class (bench.py's roofline numbers).  enable() also clears the totals.
+ * profile_read: idx = 0, 1, ... until it returns KISS_B200_ERR_ARG. */
+int kiss_b200_profile_enable(kiss_b200_ctx* ctx, int on);
+int kiss_b200_profile_read(kiss_b200_ctx* ctx, int idx, const char** name, double* ms, uint64_t* launches);
+
 /* ---- synthetic inputs ---------------------------------------------------------
  * Fill S_dev[0..n) with the counter-hash uniform stream `seed` (identical to tests/textgen.py uniform). */
 int kiss_b200_synth_uniform_dev(kiss_b200_ctx* ctx, uint8_t* S_dev, uint64_t n, uint64_t seed);

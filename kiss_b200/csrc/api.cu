@@ -62,6 +62,7 @@ struct kiss_b200_ctx {
   cudaStream_t st = nullptr;
   cudaEvent_t ev[8] = {};
   u32* pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs
+  Profiler prof;          // optional per-kernel timing
   // state kept between prepare_dev and finish_from_sorted_dev
   struct Prepared {
     bool valid = false;
@@ -456,7 +457,10 @@ int guarded(kiss_b200_ctx* c, F&& f) {
   if (!c) { g_last_error = "null context"; return KISS_B200_ERR_ARG; }
   try {
     CK(cudaSetDevice(c->device));
+    g_prof = &c->prof;
     f();
+    cudaStreamSynchronize(c->st);
+    c->prof.collect();
     return KISS_B200_OK;
   } catch (const CudaError& e) {
     g_last_error = e.what();
@@ -812,6 +816,21 @@ int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_lo
       t->kernel_launches = g_launches - l0;
     }
   });
+}
+
+int kiss_b200_profile_enable(kiss_b200_ctx* c, int on) {
+  if (!c) { g_last_error = "null context"; return KISS_B200_ERR_ARG; }
+  c->prof.on = on != 0;
+  c->prof.reset();
+  return KISS_B200_OK;
+}
+
+int kiss_b200_profile_read(kiss_b200_ctx* c, int idx, const char** name, double* ms, uint64_t* launches) {
+  if (!c || idx < 0 || idx >= PK_COUNT) return KISS_B200_ERR_ARG;
+  if (name) *name = prof_name(idx);
+  if (ms) *ms = c->prof.ms[idx];
+  if (launches) *launches = c->prof.launches[idx];
+  return KISS_B200_OK;
 }
 
 int kiss_b200_synth_uniform_dev(kiss_b200_ctx* c, uint8_t* S_dev, uint64_t n, uint64_t seed) {

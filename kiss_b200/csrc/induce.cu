@@ -74,6 +74,7 @@ void place_lms(const u32* longs, u32 nl, const u32* sorted_shorts, const u32* in
                u32* CTX, cudaStream_t st) {
   u64 tot = (u64)nl + ns;
   if (tot == 0) tot = 1;
+  ProfScope ps(PK_PLACE, st);
   k_place_lms<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(longs, nl, sorted_shorts, ins, ns, bk, n, SA, CTX);
   CK_LAUNCH(); g_launches++;
 }
@@ -269,17 +270,24 @@ void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u3
   a.SA = SA; a.CTX = CTX; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
   if (len <= WAVE_TILE) {
+    ProfScope ps(PK_WAVE_SMALL, st);
     k_wave_small<<<1, WAVE_THREADS, 0, st>>>(a, ws.tot_dev);
     CK_LAUNCH(); g_launches++;
   } else {
     u32 ntiles = (u32)wave_tiles(len);
-    k_wave_count<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.C, ntiles);
-    CK_LAUNCH();
+    {
+      ProfScope ps(PK_WAVE_COUNT, st);
+      k_wave_count<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.C, ntiles);
+      CK_LAUNCH();
+    }
     scan_excl_u32(ws.C, (u64)4 * ntiles, ws.partials, ws.scan_total, st);
     k_wave_totals<<<1, 32, 0, st>>>(ws.C, ntiles, ws.scan_total, ws.tot_dev);
     CK_LAUNCH();
-    k_wave_scatter<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.C, ntiles);
-    CK_LAUNCH();
+    {
+      ProfScope ps(PK_WAVE_SCATTER, st);
+      k_wave_scatter<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.C, ntiles);
+      CK_LAUNCH();
+    }
     g_launches += 3;
   }
   CK(cudaMemcpyAsync(ws.tot_host, ws.tot_dev, 4 * sizeof(u32), cudaMemcpyDeviceToHost, st));

@@ -6,6 +6,7 @@
 
 #include <stdexcept>
 #include <string>
+#include <vector>
 
 typedef unsigned long long u64;
 typedef unsigned int u32;
@@ -23,6 +24,34 @@ void cuda_check(cudaError_t e, const char* what, const char* file, int line);
 #define CK_LAUNCH() ::kiss::cuda_check(cudaGetLastError(), "kernel launch", __FILE__, __LINE__)
 
 extern thread_local u64 g_launches;  // kernels launched by this thread (reported as gpu_launches)
+
+// ---- optional per-kernel timing (CUDA events around each launch of a kernel class, on the launching stream)
+enum ProfKernel { PK_PACK, PK_LMS_CLASSIFY, PK_LMS_EMIT, PK_SCAN, PK_RADIX_HIST, PK_RADIX_SCATTER, PK_GROUPS_TINY,
+                  PK_GROUPS_MEDIUM, PK_GROUPS_OTHER, PK_SHORTS, PK_PLACE, PK_WAVE_COUNT, PK_WAVE_SCATTER, PK_WAVE_SMALL,
+                  PK_COUNT };
+const char* prof_name(int id);
+struct Profiler {
+  bool on = false;
+  struct Rec { int id; cudaEvent_t a, b; };
+  std::vector<Rec> recs;
+  std::vector<cudaEvent_t> pool;
+  double ms[PK_COUNT] = {};
+  u64 launches[PK_COUNT] = {};
+  cudaEvent_t get();
+  void collect();   // call after the stream has been synchronised
+  void reset();
+  ~Profiler();
+};
+extern thread_local Profiler* g_prof;
+struct ProfScope {
+  Profiler* p; int id; cudaStream_t st; cudaEvent_t a;
+  ProfScope(int id_, cudaStream_t st_) : p(g_prof && g_prof->on ? g_prof : nullptr), id(id_), st(st_), a(nullptr) {
+    if (p) { a = p->get(); cudaEventRecord(a, st); }
+  }
+  ~ProfScope() {
+    if (p) { cudaEvent_t b = p->get(); cudaEventRecord(b, st); p->recs.push_back({id, a, b}); }
+  }
+};
 
 // ---------------------------------------------------------------- scan.cu
 // in-place exclusive prefix sum of data[0..N); `partials` needs N/4096 + 2 entries of scratch;

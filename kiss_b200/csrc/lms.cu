@@ -148,6 +148,7 @@ __global__ void __launch_bounds__(256) k_lms_mask(const u64* __restrict__ T, u64
 void lms_classify(const u64* T, u64 n, u8* gp, u64* lmsmask, u32* chunk_cnt, u64* counters, cudaStream_t st) {
   u64 nwords = (n + 31) / 32, nchunks = lms_chunks(n);
   if (nchunks == 0) return;
+  ProfScope ps(PK_LMS_CLASSIFY, st);
   unsigned grid = (unsigned)((nchunks + 255) / 256);
   k_lms_summary<<<grid, 256, 0, st>>>(T, n, nwords, nchunks, gp);
   CK_LAUNCH();
@@ -195,6 +196,7 @@ __global__ void __launch_bounds__(EMIT_WORDS) k_lms_emit(const u64* __restrict__
 void lms_emit(const u64* T, u64 n, const u64* lmsmask, const u32* chunk_off, u32* pos, u32* key, cudaStream_t st) {
   u64 nwords = (n + 31) / 32;
   if (nwords == 0) return;
+  ProfScope ps(PK_LMS_EMIT, st);
   k_lms_emit<<<(unsigned)((nwords + EMIT_WORDS - 1) / EMIT_WORDS), EMIT_WORDS, 0, st>>>(T, nwords, lmsmask, chunk_off,
                                                                                        pos, key);
   CK_LAUNCH();

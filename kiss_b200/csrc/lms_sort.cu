@@ -156,21 +156,25 @@ __global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ k
 
 void groups_tiny_u32(const u32* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st) {
   if (!N) return;
+  ProfScope ps(PK_GROUPS_TINY, st);
   k_groups_tiny<u32><<<(N + 255) / 256, 256, 0, st>>>(keys, pos, N, sp, h, gl);
   CK_LAUNCH(); g_launches++;
 }
 void groups_tiny_u64(const u64* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st) {
   if (!N) return;
+  ProfScope ps(PK_GROUPS_TINY, st);
   k_groups_tiny<u64><<<(N + 255) / 256, 256, 0, st>>>(keys, pos, N, sp, h, gl);
   CK_LAUNCH(); g_launches++;
 }
 void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st) {
   if (!ng) return;
+  ProfScope ps(PK_GROUPS_OTHER, st);
   k_groups_classify<u32><<<(ng + 127) / 128, 128, 0, st>>>(keys, N, ng, gl);
   CK_LAUNCH(); g_launches++;
 }
 void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st) {
   if (!ng) return;
+  ProfScope ps(PK_GROUPS_OTHER, st);
   k_groups_classify<u64><<<(ng + 127) / 128, 128, 0, st>>>(keys, N, ng, gl);
   CK_LAUNCH(); g_launches++;
 }
@@ -210,6 +214,7 @@ __global__ void __launch_bounds__(256) k_groups_medium(u32* __restrict__ pos, co
 
 void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st) {
   if (!nmed || h >= sp.D) return;
+  ProfScope ps(PK_GROUPS_MEDIUM, st);
   u32 grid = nmed < 1048576u ? nmed : 1048576u;
   k_groups_medium<<<grid, 256, 0, st>>>(pos, med, nmed, sp, h);
   CK_LAUNCH(); g_launches++;
@@ -222,6 +227,7 @@ __global__ void k_big_sizes(const u32* __restrict__ big, u32 nbig, u32* __restri
 }
 void big_sizes(const u32* big, u32 nbig, u32* sizes, cudaStream_t st) {
   if (!nbig) return;
+  ProfScope ps(PK_GROUPS_OTHER, st);
   k_big_sizes<<<(nbig + 255) / 256, 256, 0, st>>>(big, nbig, sizes);
   CK_LAUNCH(); g_launches++;
 }
@@ -253,6 +259,7 @@ __global__ void __launch_bounds__(256) k_big_fill(const u32* __restrict__ pos_pr
 void big_fill(const u32* pos_prev, const u32* slot_prev, const u32* big, const u32* boff, u32 nbig, SortParams sp,
               u64 h, u64* wkey, u32* wpos, u32* wslot, cudaStream_t st) {
   if (!nbig) return;
+  ProfScope ps(PK_GROUPS_OTHER, st);
   u32 grid = nbig < 65535u * 16u ? nbig : 65535u * 16u;
   k_big_fill<<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, sp, h, wkey, wpos, wslot);
   CK_LAUNCH(); g_launches++;
@@ -265,6 +272,7 @@ __global__ void k_big_writeback(u32* __restrict__ pos_main, const u32* __restric
 }
 void big_writeback(u32* pos_main, const u32* wslot, const u32* wpos, u32 total, cudaStream_t st) {
   if (!total) return;
+  ProfScope ps(PK_GROUPS_OTHER, st);
   k_big_writeback<<<(total + 255) / 256, 256, 0, st>>>(pos_main, wslot, wpos, total);
   CK_LAUNCH(); g_launches++;
 }
@@ -355,6 +363,7 @@ __global__ void __launch_bounds__(128) k_short_place(const u32* __restrict__ sho
 
 void shorts_order(const u32* shorts, u32 ns, SortParams sp, u32* rank0, u32* sorted_shorts, cudaStream_t st) {
   if (!ns) return;
+  ProfScope ps(PK_SHORTS, st);
   k_short_rank<<<(ns + 127) / 128, 128, 0, st>>>(shorts, ns, sp, rank0);
   CK_LAUNCH();
   k_short_place<<<(ns + 127) / 128, 128, 0, st>>>(shorts, ns, rank0, sorted_shorts);
@@ -387,6 +396,7 @@ __global__ void k_short_mono(u32* __restrict__ ins, u32 ns) {
 void shorts_insertions(const u32* sorted_shorts, u32 ns, const u32* longs, u32 nl, SortParams sp, u32* ins,
                        cudaStream_t st) {
   if (!ns) return;
+  ProfScope ps(PK_SHORTS, st);
   k_short_ins<<<(ns + 127) / 128, 128, 0, st>>>(sorted_shorts, ns, longs, nl, sp, ins);
   CK_LAUNCH();
   k_short_mono<<<1, 1, 0, st>>>(ins, ns);

@@ -43,6 +43,7 @@ void pack_codes(const u8* S, u64 n, u64* T, cudaStream_t st) {
   CK(cudaMemsetAsync(T + tail_from, 0, (nw - tail_from) * sizeof(u64), st));
   u64 n16 = (n + 15) / 16;
   if (n16 == 0) return;
+  ProfScope ps(PK_PACK, st);
   k_pack_codes<<<(unsigned)((n16 + 255) / 256), 256, 0, st>>>(S, n, reinterpret_cast<u32*>(T), n16);
   CK_LAUNCH();
   g_launches++;

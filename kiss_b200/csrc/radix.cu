@@ -13,6 +13,35 @@
 namespace kiss {
 
 thread_local u64 g_launches = 0;
+thread_local Profiler* g_prof = nullptr;
+
+const char* prof_name(int id) {
+  static const char* names[PK_COUNT] = {"k_pack_codes", "k_lms_summary+carry+mask", "k_lms_emit", "k_scan_*", "k_radix_hist",
+                                        "k_radix_scatter", "k_groups_tiny", "k_groups_medium", "k_groups_classify+big_*",
+                                        "k_short_*", "k_place_lms", "k_wave_count", "k_wave_scatter", "k_wave_small"};
+  return (id >= 0 && id < PK_COUNT) ? names[id] : "?";
+}
+cudaEvent_t Profiler::get() {
+  if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  return e;
+}
+void Profiler::collect() {
+  for (auto& r : recs) {
+    float t = 0;
+    if (cudaEventElapsedTime(&t, r.a, r.b) == cudaSuccess) { ms[r.id] += t; launches[r.id]++; }
+    pool.push_back(r.a); pool.push_back(r.b);
+  }
+  recs.clear();
+}
+void Profiler::reset() {
+  for (int i = 0; i < PK_COUNT; i++) { ms[i] = 0; launches[i] = 0; }
+}
+Profiler::~Profiler() {
+  collect();
+  for (auto e : pool) cudaEventDestroy(e);
+}
 
 void cuda_check(cudaError_t e, const char* what, const char* file, int line) {
   if (e == cudaSuccess) return;
@@ -93,6 +122,7 @@ void scan_excl_u32(u32* data, u64 N, u32* partials, u32* total_dev, cudaStream_t
     if (total_dev) CK(cudaMemsetAsync(total_dev, 0, sizeof(u32), st));
     return;
   }
+  ProfScope ps(PK_SCAN, st);
   u32 P = (u32)((N + SCAN_TILE - 1) / SCAN_TILE);
   k_scan_reduce<<<P, SCAN_THREADS, 0, st>>>(data, N, partials);
   CK_LAUNCH();
@@ -245,12 +275,18 @@ static void radix_sort_impl(K*& keys, u32*& vals, K*& keys_alt, u32*& vals_alt, 
   for (int shift = bit_lo; shift < bit_hi; shift += 8) {
     int bits = bit_hi - shift < 8 ? bit_hi - shift : 8;
     u32 mask = (1u << bits) - 1u;
-    k_radix_hist<K><<<ntiles, RADIX_THREADS, 0, st>>>(keys, N, shift, mask, H, ntiles);
-    CK_LAUNCH();
+    {
+      ProfScope ps(PK_RADIX_HIST, st);
+      k_radix_hist<K><<<ntiles, RADIX_THREADS, 0, st>>>(keys, N, shift, mask, H, ntiles);
+      CK_LAUNCH();
+    }
     scan_excl_u32(H, (u64)256 * ntiles, partials, nullptr, st);
-    k_radix_scatter<K><<<ntiles, RADIX_THREADS, radix_smem<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift, mask,
-                                                                      H, ntiles);
-    CK_LAUNCH();
+    {
+      ProfScope ps(PK_RADIX_SCATTER, st);
+      k_radix_scatter<K><<<ntiles, RADIX_THREADS, radix_smem<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift,
+                                                                        mask, H, ntiles);
+      CK_LAUNCH();
+    }
     g_launches += 2;
     K* tk = keys; keys = keys_alt; keys_alt = tk;
     u32* tv = vals; vals = vals_alt; vals_alt = tv;

@@ -142,6 +142,19 @@ class Context:
         check(lib().kiss_b200_finish_from_sorted_dev(self._h, sorted_ptr, n_long, SA_ptr, C.byref(t)))
         return t.as_dict()
 
+    def profile_enable(self, on=True):
+        check(lib().kiss_b200_profile_enable(self._h, 1 if on else 0))
+
+    def profile(self):
+        """{kernel class: (total ms, launches)} accumulated since profile_enable()"""
+        out, i = {}, 0
+        name, ms, cnt = C.c_char_p(), C.c_double(), C.c_uint64()
+        while lib().kiss_b200_profile_read(self._h, i, C.byref(name), C.byref(ms), C.byref(cnt)) == 0:
+            if cnt.value:
+                out[name.value.decode()] = (ms.value, cnt.value)
+            i += 1
+        return out
+
     def synth_uniform_dev(self, S_ptr, n, seed):
         check(lib().kiss_b200_synth_uniform_dev(self._h, S_ptr, n, seed))
 
