@@ -4,6 +4,7 @@
 // put_lms_suffix -> induced_sort, each stage a set of kernels on one stream.  There is no CPU path: every
 // entry either runs the kernels or returns an error code.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -313,6 +314,15 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
   ws.scan_total = pool.alloc<u32>(1);
   ws.tot_dev = pool.alloc<u32>(4);
   ws.tot_host = c->pinned + 32;
+  const char* mode = getenv("KISS_B200_WAVES");
+  ws.fused = !(mode && std::string(mode) == "classic");
+  ws.status = pool.alloc<u64>(4 * nt + 4);
+  ws.state = pool.alloc<u32>(2);
+  u32 tile_base = 0, epoch = 0;
+  ws.tile_base = &tile_base;
+  ws.epoch = &epoch;
+  CK(cudaMemsetAsync(ws.status, 0, (4 * nt + 4) * sizeof(u64), st));
+  CK(cudaMemsetAsync(ws.state, 0, 2 * sizeof(u32), st));
   u32 tot[4];
   u64 Lc[4], nL[4], Sc[4];
   for (int s = 0; s < 4; s++) Lc[s] = bk.B[s];
@@ -355,6 +365,9 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
       is->waves_S++;
     }
   }
+  u32 wd[2];
+  Sync{c}.read(ws.state, 2, wd);
+  if (wd[1]) throw CudaError(-3, "internal: induction look-back watchdog fired");
   for (int s = 0; s < 4; s++)
     if (Sc[s] != bk.B[s] + nL[s]) throw CudaError(-3, "internal: induction did not fill every bucket");
 }

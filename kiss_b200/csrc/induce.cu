@@ -90,7 +90,7 @@ void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, u32* C
 // when a context runs out (CTX == 1): once per LMS suffix and once per 15 steps of a chain, instead of once
 // per scanned entry as in the reference's prepare loops (kiss_common.hpp:63-113, 278-325).
 #define WAVE_THREADS 256
-#define WAVE_ITEMS 8
+#define WAVE_ITEMS 16
 #define WAVE_WARPS 8
 
 struct WaveArgs {
@@ -262,6 +262,135 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_small(WaveArgs a, u32* __
   if (threadIdx.x < 4) tot[threadIdx.x] = sm.sb[threadIdx.x + 1] - sm.sb[threadIdx.x];
 }
 
+// ---- single-pass wave: count, decoupled look-back across tiles, scatter — one read of (CTX, SA) per entry.
+// Tiles take their index from an atomic ticket (so a tile never waits on one that has not started), publish
+// their per-symbol counts in a 64-bit status word [epoch:30 | flag:2 | count:32] and look back over their
+// predecessors' words for the exclusive prefix.  The epoch (one per wave) makes stale words of earlier waves
+// read as "empty", so the status array is zeroed once per call, not per wave.
+#define WF_AGG 1ull
+#define WF_INCL 2ull
+__device__ __forceinline__ u64 wf_pack(u32 epoch, u64 flag, u32 v) { return ((u64)epoch << 34) | (flag << 32) | v; }
+
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __restrict__ status, u32* __restrict__ state,
+                                                            u32 tile_base, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
+  __shared__ WaveSmem sm;
+  __shared__ u32 s_tile;
+  __shared__ u32 s_off[4];
+  if (threadIdx.x == 0) s_tile = atomicAdd(&state[0], 1u) - tile_base;
+  __syncthreads();
+  const u32 tile = s_tile;
+  const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const u64 j0 = (u64)tile * WAVE_TILE + w * (32 * WAVE_ITEMS);
+  const u32 lt = (1u << lane) - 1u;
+  u32 sym[WAVE_ITEMS], cx[WAVE_ITEMS], val[WAVE_ITEMS];
+  u32 cnt[4] = {0, 0, 0, 0};
+#pragma unroll
+  for (int r = 0; r < WAVE_ITEMS; r++) {
+    u64 j = j0 + r * 32 + lane;
+    u32 c = 1u, v = 0;
+    if (j < a.len) {
+      u64 slot = wave_slot(a, j);
+      c = a.CTX[slot];
+      v = a.SA[slot];
+    }
+    cx[r] = c;
+    val[r] = v;
+  }
+#pragma unroll
+  for (int r = 0; r < WAVE_ITEMS; r++) {
+    u32 c = cx[r], v = val[r];
+    if (c == 1u && v != 0 && v != KISS_EMPTY && j0 + r * 32 + lane < a.len) c = ctx_gather(a.T, v);  // context ran out
+    cx[r] = c;
+    u32 cu = ctx_symbol(c, a.symmask);
+    sym[r] = cu;
+#pragma unroll
+    for (u32 s = 0; s < 4; s++) cnt[s] += __popc(__ballot_sync(0xffffffffu, cu == s));
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < 4; s++) sm.wsum[w][s] = cnt[s];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u32 acc = 0;
+    for (int s = 0; s < 4; s++) {
+      sm.sb[s] = acc;
+      for (int ww = 0; ww < WAVE_WARPS; ww++) acc += sm.wsum[ww][s];
+    }
+    sm.sb[4] = acc;
+  }
+  __syncthreads();
+  // ---- look-back: warp s (< 4) resolves symbol s
+  if (w < 4) {
+    const u32 s = w;
+    const u32 mine = sm.sb[s + 1] - sm.sb[s];
+    volatile u64* st = status;
+    if (lane == 0) st[(u64)tile * 4 + s] = wf_pack(epoch, tile == 0 ? WF_INCL : WF_AGG, mine);
+    u32 excl = 0;
+    if (tile > 0) {
+      long long base = (long long)tile - 1;
+      u32 spins = 0;
+      for (;;) {
+        long long t = base - lane;
+        u64 word = 0;
+        bool ready;
+        do {
+          word = (t >= 0) ? st[(u64)t * 4 + s] : wf_pack(epoch, WF_INCL, 0);
+          ready = (u32)(word >> 34) == epoch && ((word >> 32) & 3ull) != 0;
+          if (++spins > (1u << 24)) { state[1] = 1u; ready = true; word = wf_pack(epoch, WF_INCL, 0); }  // watchdog: never hang
+        } while (!__all_sync(0xffffffffu, ready));
+        u32 incl = __ballot_sync(0xffffffffu, ((word >> 32) & 3ull) == WF_INCL);
+        u32 v = (u32)word;
+        if (incl) {
+          u32 first = __ffs(incl) - 1;  // nearest predecessor holding an inclusive prefix
+          if (lane > first) v = 0;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        excl += v;
+        if (incl) break;
+        base -= 32;
+      }
+      if (lane == 0) st[(u64)tile * 4 + s] = wf_pack(epoch, WF_INCL, excl + mine);
+    }
+    if (lane == 0) {
+      s_off[s] = excl;
+      if (tile == ntiles - 1) tot[s] = excl + mine;
+    }
+  }
+  __syncthreads();
+  u32 run[4];
+#pragma unroll
+  for (int s = 0; s < 4; s++) {
+    u32 t = sm.sb[s];
+    for (u32 ww = 0; ww < w; ww++) t += sm.wsum[ww][s];
+    run[s] = t;
+  }
+#pragma unroll
+  for (int r = 0; r < WAVE_ITEMS; r++) {
+    u32 cu = sym[r];
+    u32 b0 = __ballot_sync(0xffffffffu, cu == 0), b1 = __ballot_sync(0xffffffffu, cu == 1);
+    u32 b2 = __ballot_sync(0xffffffffu, cu == 2), b3 = __ballot_sync(0xffffffffu, cu == 3);
+    if (cu < 4) {
+      u32 bm = cu == 0 ? b0 : cu == 1 ? b1 : cu == 2 ? b2 : b3;
+      u32 lp = (cu == 0 ? run[0] : cu == 1 ? run[1] : cu == 2 ? run[2] : run[3]) + __popc(bm & lt);
+      sm.sSA[lp] = val[r] - 1u;
+      sm.sCTX[lp] = cx[r] >> 2;
+    }
+    run[0] += __popc(b0); run[1] += __popc(b1); run[2] += __popc(b2); run[3] += __popc(b3);
+  }
+  __syncthreads();
+  const u32 total = sm.sb[4];
+  for (u32 idx = threadIdx.x; idx < total; idx += WAVE_THREADS) {
+    u32 s = (idx >= sm.sb[1]) + (idx >= sm.sb[2]) + (idx >= sm.sb[3]);
+    u32 off = s_off[s] + (idx - sm.sb[s]);
+    u64 cur = s == 0 ? a.cur[0] : s == 1 ? a.cur[1] : s == 2 ? a.cur[2] : a.cur[3];
+    u64 dst = a.down ? cur - 1 - off : cur + off;
+    a.SA[dst] = sm.sSA[idx];
+    a.CTX[dst] = sm.sCTX[idx];
+  }
+}
+
 void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4],
                  WaveScratch ws, u32 tot[4], cudaStream_t st) {
   tot[0] = tot[1] = tot[2] = tot[3] = 0;
@@ -269,7 +398,13 @@ void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u3
   WaveArgs a;
   a.SA = SA; a.CTX = CTX; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
-  if (len <= WAVE_TILE) {
+  if (ws.fused) {
+    u32 ntiles = (u32)wave_tiles(len);
+    ProfScope ps(len <= WAVE_TILE ? PK_WAVE_SMALL : PK_WAVE_SCATTER, st);
+    k_wave_fused<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ++*ws.epoch, ws.tot_dev);
+    CK_LAUNCH(); g_launches++;
+    *ws.tile_base += ntiles;
+  } else if (len <= WAVE_TILE) {
     ProfScope ps(PK_WAVE_SMALL, st);
     k_wave_small<<<1, WAVE_THREADS, 0, st>>>(a, ws.tot_dev);
     CK_LAUNCH(); g_launches++;

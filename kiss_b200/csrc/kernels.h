@@ -149,8 +149,14 @@ struct WaveScratch {
   u32* scan_total;
   u32* tot_dev;   // 4
   u32* tot_host;  // 4, pinned
+  // single-pass (decoupled look-back) waves
+  bool fused;
+  u64* status;    // 4 words per tile of the largest wave, zeroed once per call
+  u32* state;     // [0] tile ticket, [1] watchdog flag; zeroed once per call
+  u32* tile_base; // host: tickets handed out so far
+  u32* epoch;     // host: wave number
 };
-#define WAVE_TILE 2048u
+#define WAVE_TILE 4096u
 inline u64 wave_tiles(u64 len) { return (len + WAVE_TILE - 1) / WAVE_TILE; }
 // One induction wave over SA[lo, lo+len) (scanned downwards when `down`): every entry v > 0 whose preceding
 // symbol S[v-1] is in `symmask` appends v-1 at cur[S[v-1]] (upwards) or below it (downwards).  Synchronises
