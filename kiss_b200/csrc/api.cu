@@ -19,40 +19,112 @@ static thread_local std::string g_last_error;
 
 namespace {
 
-// stream-ordered scratch; everything still owned is released when the call ends
+// Device scratch.  One arena per context, kept between calls and sub-allocated on the host (first fit + merge),
+// so the steady state makes no driver allocation at all (cudaMallocAsync pool growth showed up as 2-18 ms of
+// jitter in the get_lms stage).  What does not fit goes through the stream-ordered allocator for this call and
+// the arena is regrown to the observed peak once it is idle.
+struct Arena {
+  char* base = nullptr;
+  u64 cap = 0, peak = 0, live_extra = 0;
+  struct Blk { u64 off, size; bool used; };
+  std::vector<Blk> blks;
+  u64 top() const { return blks.empty() ? 0 : blks.back().off + blks.back().size; }
+  void note() {
+    u64 need = top() + live_extra;
+    if (need > peak) peak = need;
+  }
+  void* take(u64 bytes) {
+    for (size_t i = 0; i < blks.size(); i++)
+      if (!blks[i].used && blks[i].size >= bytes) {
+        if (blks[i].size > bytes) {
+          Blk rest{blks[i].off + bytes, blks[i].size - bytes, false};
+          blks[i].size = bytes;
+          blks.insert(blks.begin() + i + 1, rest);
+        }
+        blks[i].used = true;
+        return base + blks[i].off;
+      }
+    u64 t = top();
+    if (base && t + bytes <= cap) {
+      blks.push_back({t, bytes, true});
+      note();
+      return base + t;
+    }
+    return nullptr;
+  }
+  bool owns(void* p) const { return base && (char*)p >= base && (char*)p < base + cap; }
+  void give(void* p) {
+    u64 off = (u64)((char*)p - base);
+    for (size_t i = 0; i < blks.size(); i++)
+      if (blks[i].off == off) {
+        blks[i].used = false;
+        if (i + 1 < blks.size() && !blks[i + 1].used) { blks[i].size += blks[i + 1].size; blks.erase(blks.begin() + i + 1); }
+        if (i > 0 && !blks[i - 1].used) { blks[i - 1].size += blks[i].size; blks.erase(blks.begin() + i); }
+        while (!blks.empty() && !blks.back().used) blks.pop_back();
+        return;
+      }
+  }
+  bool idle() const { return blks.empty() && live_extra == 0; }
+  // regrow to the observed peak (call only when idle and the stream is quiescent)
+  void settle() {
+    if (!idle() || peak <= cap) return;
+    if (base) cudaFree(base);
+    base = nullptr;
+    cap = 0;
+    u64 want = peak + peak / 16 + (64ull << 20);
+    void* p = nullptr;
+    if (cudaMalloc(&p, want) == cudaSuccess) { base = (char*)p; cap = want; } else cudaGetLastError();
+  }
+  ~Arena() { if (base) cudaFree(base); }
+};
+
 struct Pool {
   cudaStream_t st;
-  std::vector<void*> ptrs;
-  explicit Pool(cudaStream_t s) : st(s) {}
+  Arena* ar;
+  std::vector<std::pair<void*, u64>> ptrs;
+  Pool(cudaStream_t s, Arena* a) : st(s), ar(a) {}
   template <typename T>
   T* alloc(u64 count) {
-    void* p = nullptr;
     u64 bytes = (count ? count : 1) * sizeof(T);
     bytes = (bytes + 255) & ~255ull;
-    CK(cudaMallocAsync(&p, bytes, st));
-    ptrs.push_back(p);
+    void* p = ar->take(bytes);
+    if (!p) {
+      CK(cudaMallocAsync(&p, bytes, st));
+      ar->live_extra += bytes;
+      ar->note();
+    }
+    ptrs.push_back({p, bytes});
     return static_cast<T*>(p);
+  }
+  static void free_ptr(Arena* ar, cudaStream_t st, void* p, u64 bytes) {
+    if (ar->owns(p)) ar->give(p);
+    else { cudaFreeAsync(p, st); ar->live_extra -= bytes; }
   }
   void release(void* p) {
     for (size_t i = 0; i < ptrs.size(); i++)
-      if (ptrs[i] == p) {
+      if (ptrs[i].first == p) {
+        u64 bytes = ptrs[i].second;
         ptrs[i] = ptrs.back();
         ptrs.pop_back();
-        cudaFreeAsync(p, st);
+        free_ptr(ar, st, p, bytes);
         return;
       }
   }
-  // hand ownership to the caller
-  void keep(void* p) {
+  // hand ownership to the caller (who frees with Pool::free_ptr); returns the block size
+  u64 keep(void* p) {
     for (size_t i = 0; i < ptrs.size(); i++)
-      if (ptrs[i] == p) {
+      if (ptrs[i].first == p) {
+        u64 bytes = ptrs[i].second;
         ptrs[i] = ptrs.back();
         ptrs.pop_back();
-        return;
+        return bytes;
       }
+    return 0;
   }
   ~Pool() {
-    for (void* p : ptrs) cudaFreeAsync(p, st);
+    // everything of this call is enqueued on one stream, so host-side reuse of a block by a later allocation
+    // is ordered after its last use
+    for (auto& pr : ptrs) free_ptr(ar, st, pr.first, pr.second);
   }
 };
 
@@ -64,6 +136,7 @@ struct kiss_b200_ctx {
   cudaEvent_t ev[8] = {};
   u32* pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs
   Profiler prof;          // optional per-kernel timing
+  Arena arena;
   // state kept between prepare_dev and finish_from_sorted_dev
   struct Prepared {
     bool valid = false;
@@ -72,6 +145,7 @@ struct kiss_b200_ctx {
     u64* T = nullptr;
     u32* pos = nullptr;     // text-ordered LMS positions (m1)
     u32* key = nullptr;     // their first-16-base keys
+    u64 bT = 0, bpos = 0, bkey = 0;  // block sizes (arena bookkeeping)
     u64 counters[8] = {};
     SortParams sp = {};
   } prep;
@@ -93,17 +167,21 @@ u64 depth_of(u32 k) { return 125ull * ((u64)k / 125ull + 1ull); }  // kiss1_core
 
 void free_prepared(kiss_b200_ctx* c) {
   auto& p = c->prep;
-  if (p.T) cudaFreeAsync(p.T, c->st);
-  if (p.pos) cudaFreeAsync(p.pos, c->st);
-  if (p.key) cudaFreeAsync(p.key, c->st);
+  if (p.T) Pool::free_ptr(&c->arena, c->st, p.T, p.bT);
+  if (p.pos) Pool::free_ptr(&c->arena, c->st, p.pos, p.bpos);
+  if (p.key) Pool::free_ptr(&c->arena, c->st, p.key, p.bkey);
   p = kiss_b200_ctx::Prepared();
 }
 
 // ---- pack + get_lms.  Leaves T, pos, key owned by ctx->prep.
 void do_prepare(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, float* t_pack, float* t_lms) {
   free_prepared(c);
+  if (c->arena.idle() && c->arena.peak > c->arena.cap) {
+    cudaStreamSynchronize(c->st);
+    c->arena.settle();
+  }
   cudaStream_t st = c->st;
-  Pool pool(st);
+  Pool pool(st, &c->arena);
   Sync sync{c};
   auto& P = c->prep;
   P.n = n;
@@ -152,7 +230,7 @@ void do_prepare(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, float* t
   if (t_pack) CK(cudaEventElapsedTime(t_pack, c->ev[0], c->ev[1]));
   if (t_lms) CK(cudaEventElapsedTime(t_lms, c->ev[1], c->ev[2]));
   P.m1 = m1; P.n_long = n_long; P.T = T; P.pos = pos; P.key = key; P.valid = true;
-  pool.keep(T); pool.keep(pos); pool.keep(key);
+  P.bT = pool.keep(T); P.bpos = pool.keep(pos); P.bkey = pool.keep(key);
 }
 
 }  // namespace
@@ -422,7 +500,7 @@ void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* d
   SortStats ss;
   InduceStats is;
   if (stop != STOP_LMS) {
-    Pool pool(st);
+    Pool pool(st, &c->arena);
     SortedLms sl;
     u32* dCTX = nullptr;
     CK(cudaEventRecord(c->ev[3], st));
@@ -474,6 +552,7 @@ int guarded(kiss_b200_ctx* c, F&& f) {
     f();
     cudaStreamSynchronize(c->st);
     c->prof.collect();
+    c->arena.settle();
     return KISS_B200_OK;
   } catch (const CudaError& e) {
     g_last_error = e.what();
@@ -498,7 +577,7 @@ double elapsed_s(kiss_b200_ctx* c, int a, int b) {
 void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* out_host, u64 out_count_hint, Stop stop,
               bool ascii, kiss_b200_timings* t, uint64_t* m_out) {
   cudaStream_t st = c->st;
-  Pool pool(st);
+  Pool pool(st, &c->arena);
   u8* dS = pool.alloc<u8>(n + 16);
   cudaEvent_t e0, e1, e2, e3;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2)); CK(cudaEventCreate(&e3));
@@ -696,7 +775,7 @@ int kiss_b200_induce_from_sorted_lms(kiss_b200_ctx* c, const uint8_t* S_host, ui
   if (n == 0) { SA_host[0] = 0; return KISS_B200_OK; }
   return guarded(c, [&] {
     cudaStream_t st = c->st;
-    Pool pool(st);
+    Pool pool(st, &c->arena);
     u8* dS = pool.alloc<u8>(n + 16);
     CK(cudaMemcpyAsync(dS, S_host, n, cudaMemcpyHostToDevice, st));
     do_prepare(c, dS, n, 0xFFFFFFFFu, 0, nullptr, nullptr);
@@ -742,7 +821,7 @@ int kiss_b200_partition_lms_dev(kiss_b200_ctx* c, const uint32_t* splitters_host
   }
   return guarded(c, [&] {
     cudaStream_t st = c->st;
-    Pool pool(st);
+    Pool pool(st, &c->arena);
     u32 N = (u32)(hi - lo);
     u32* spl = pool.alloc<u32>(64);
     u32* counts = pool.alloc<u32>(65);
@@ -772,7 +851,7 @@ int kiss_b200_sort_lms_subset_dev(kiss_b200_ctx* c, uint32_t* pos_dev, uint64_t 
   if (count > 0x80000000ull) { g_last_error = "subset too large"; return KISS_B200_ERR_TOO_LARGE; }
   return guarded(c, [&] {
     cudaStream_t st = c->st;
-    Pool pool(st);
+    Pool pool(st, &c->arena);
     u64 l0 = g_launches;
     CK(cudaEventRecord(c->ev[3], st));
     u32* key = pool.alloc<u32>(count);
@@ -801,7 +880,7 @@ int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_lo
   if (!SA_dev || (n_long && !sorted_long_dev) || n_long != c->prep.n_long) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   return guarded(c, [&] {
     cudaStream_t st = c->st;
-    Pool pool(st);
+    Pool pool(st, &c->arena);
     auto& P = c->prep;
     u64 l0 = g_launches;
     u32 ns = (u32)(P.m1 - P.n_long);

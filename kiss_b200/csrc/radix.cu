@@ -7,6 +7,8 @@
 // stably with warp match/ballot, stages the tile in shared memory in digit order and writes each digit's
 // run with coalesced stores.  Algorithmic bytes per pass and key: sizeof(K) (histogram read)
 // + 2 * (sizeof(K) + 4) (scatter read + write).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -257,6 +259,147 @@ __global__ void __launch_bounds__(RADIX_THREADS, 3) k_radix_scatter(const K* __r
   }
 }
 
+// ---- persistent, double-buffered scatter.  The one-tile-per-block kernel above is latency bound (long-scoreboard
+// stalls, 3 resident blocks per SM, profiles/r1_v2_radix_scatter.txt): loads, ranking and stores of a tile run one
+// after the other.  Here each block walks tiles b, b+G, b+2G, ... and fetches the NEXT tile's keys and values
+// with cp.async into the other half of a double buffer while it ranks and writes the current one, so every
+// resident block always has a full tile (32-48 KB) in flight.
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(sa), "l"(gmem));
+}
+template <typename E>
+__device__ __forceinline__ void tile_fetch(E* sdst, const E* __restrict__ g, u32 tile_base, u32 nvalid) {
+  constexpr u32 PER = 16 / sizeof(E);
+  const E* src = g + tile_base;
+  for (u32 c = threadIdx.x; c < RADIX_TILE / PER; c += RADIX_THREADS) {
+    u32 e0 = c * PER;
+    if (e0 + PER <= nvalid) {
+      cp_async16(sdst + e0, src + e0);
+    } else {
+      for (u32 t = 0; t < PER; t++)
+        if (e0 + t < nvalid) sdst[e0 + t] = src[e0 + t];
+    }
+  }
+}
+
+template <typename K>
+__global__ void __launch_bounds__(RADIX_THREADS, (sizeof(K) == 4 ? 3 : 2))
+k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __restrict__ kout, u32* __restrict__ vout,
+                  u32 N, int shift, u32 mask, const u32* __restrict__ H, u32 ntiles) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  K* kbuf0 = reinterpret_cast<K*>(smem_raw);
+  K* kbuf1 = kbuf0 + RADIX_TILE;
+  u32* vbuf0 = reinterpret_cast<u32*>(kbuf1 + RADIX_TILE);
+  u32* vbuf1 = vbuf0 + RADIX_TILE;
+  u32* wcnt = vbuf1 + RADIX_TILE;          // [RADIX_WARPS][256]
+  u32* texcl = wcnt + RADIX_WARPS * 256;   // [256]
+  u32* dbase = texcl + 256;                // [256]
+  u32* ws = dbase + 256;                   // [33]
+
+  const u32 tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  const u32 lt_mask = (1u << lane) - 1u;
+  u32 tile = blockIdx.x;
+  if (tile >= ntiles) return;
+  {
+    u32 tb = tile * RADIX_TILE, nv = min((u32)RADIX_TILE, N - tb);
+    tile_fetch<K>(kbuf0, kin, tb, nv);
+    tile_fetch<u32>(vbuf0, vin, tb, nv);
+    asm volatile("cp.async.commit_group;\n" ::);
+  }
+  u32 hb_next = H[(u64)tid * ntiles + tile];
+  for (u32 it = 0; tile < ntiles; tile += gridDim.x, it++) {
+    K* kb = (it & 1) ? kbuf1 : kbuf0;
+    u32* vb = (it & 1) ? vbuf1 : vbuf0;
+    const u32 hbase = hb_next;
+    const u32 tile_base = tile * RADIX_TILE;
+    const u32 tile_n = min((u32)RADIX_TILE, N - tile_base);
+    asm volatile("cp.async.wait_group 0;\n" ::);
+    __syncthreads();  // the whole tile has landed
+    K keys[RADIX_ITEMS];
+    u32 vals[RADIX_ITEMS];
+    u32 rank[RADIX_ITEMS];
+    const u32 lbase = w * (32 * RADIX_ITEMS);
+#pragma unroll
+    for (int r = 0; r < RADIX_ITEMS; r++) {
+      keys[r] = kb[lbase + r * 32 + lane];
+      vals[r] = vb[lbase + r * 32 + lane];
+    }
+    for (u32 i = tid; i < RADIX_WARPS * 256; i += RADIX_THREADS) wcnt[i] = 0;
+    __syncthreads();  // registers hold the tile: its buffer becomes the staging area
+    {
+      u32 next = tile + gridDim.x;
+      if (next < ntiles) {
+        u32 tb = next * RADIX_TILE, nv = min((u32)RADIX_TILE, N - tb);
+        tile_fetch<K>((it & 1) ? kbuf0 : kbuf1, kin, tb, nv);
+        tile_fetch<u32>((it & 1) ? vbuf0 : vbuf1, vin, tb, nv);
+        hb_next = H[(u64)tid * ntiles + next];
+      }
+      asm volatile("cp.async.commit_group;\n" ::);
+    }
+#pragma unroll
+    for (int r = 0; r < RADIX_ITEMS; r++) {
+      bool valid = lbase + r * 32 + lane < tile_n;
+      u32 d = (u32)(keys[r] >> shift) & mask;
+      u32 peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+      for (int b = 0; b < 8; b++) {
+        bool bit = (d >> b) & 1u;
+        u32 bal = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? bal : ~bal;
+      }
+      u32 leader = (u32)__ffs(peers) - 1u;
+      u32 old = 0;
+      if (lane == leader && valid) {
+        old = wcnt[w * 256 + d];
+        wcnt[w * 256 + d] = old + (u32)__popc(peers);
+      }
+      old = __shfl_sync(0xffffffffu, old, leader);
+      rank[r] = old + (u32)__popc(peers & lt_mask);
+      __syncwarp();
+    }
+    __syncthreads();
+    {
+      u32 run = 0;
+#pragma unroll
+      for (int ww = 0; ww < RADIX_WARPS; ww++) {
+        u32 c = wcnt[ww * 256 + tid];
+        wcnt[ww * 256 + tid] = run;
+        run += c;
+      }
+      u32 tot;
+      u32 ex = block_excl_scan(run, ws, tot);
+      texcl[tid] = ex;
+      dbase[tid] = hbase - ex;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RADIX_ITEMS; r++) {
+      if (lbase + r * 32 + lane < tile_n) {
+        u32 d = (u32)(keys[r] >> shift) & mask;
+        u32 lp = texcl[d] + wcnt[w * 256 + d] + rank[r];
+        kb[lp] = keys[r];
+        vb[lp] = vals[r];
+      }
+    }
+    __syncthreads();
+    for (u32 j = tid; j < tile_n; j += RADIX_THREADS) {
+      K key = kb[j];
+      u32 d = (u32)(key >> shift) & mask;
+      u32 dst = dbase[d] + j;
+      kout[dst] = key;
+      vout[dst] = vb[j];
+    }
+    // no barrier needed here: the next iteration only touches this buffer again after its own barriers
+  }
+}
+
+template <typename K>
+static size_t radix_smem_p() {
+  return 2 * RADIX_TILE * (sizeof(K) + 4) + (RADIX_WARPS * 256 + 256 + 256 + 40) * 4;
+}
+static int g_radix_grid[2] = {0, 0};  // resident blocks of the persistent kernel (u32, u64 keys)
+
 template <typename K>
 static size_t radix_smem() {
   return RADIX_TILE * (sizeof(K) + 4) + (RADIX_WARPS * 256 + 256 + 256 + 40) * 4;
@@ -265,6 +408,15 @@ static size_t radix_smem() {
 void radix_init() {
   CK(cudaFuncSetAttribute(k_radix_scatter<u32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter<u64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem<u64>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
+  int dev = 0, sms = 0, b32 = 0, b64 = 0;
+  CK(cudaGetDevice(&dev));
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b32, k_radix_scatter_p<u32>, RADIX_THREADS, radix_smem_p<u32>()));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b64, k_radix_scatter_p<u64>, RADIX_THREADS, radix_smem_p<u64>()));
+  g_radix_grid[0] = sms * (b32 > 0 ? b32 : 1);
+  g_radix_grid[1] = sms * (b64 > 0 ? b64 : 1);
 }
 
 template <typename K>
@@ -283,8 +435,17 @@ static void radix_sort_impl(K*& keys, u32*& vals, K*& keys_alt, u32*& vals_alt, 
     scan_excl_u32(H, (u64)256 * ntiles, partials, nullptr, st);
     {
       ProfScope ps(PK_RADIX_SCATTER, st);
-      k_radix_scatter<K><<<ntiles, RADIX_THREADS, radix_smem<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift,
-                                                                        mask, H, ntiles);
+      static const bool classic = getenv("KISS_B200_RADIX") && std::string(getenv("KISS_B200_RADIX")) == "classic";
+      bool aligned = (((uintptr_t)keys | (uintptr_t)vals) & 15) == 0;
+      if (classic || !aligned) {
+        k_radix_scatter<K><<<ntiles, RADIX_THREADS, radix_smem<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift,
+                                                                          mask, H, ntiles);
+      } else {
+        u32 grid = (u32)g_radix_grid[sizeof(K) == 4 ? 0 : 1];
+        if (grid > ntiles) grid = ntiles;
+        k_radix_scatter_p<K><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift,
+                                                                            mask, H, ntiles);
+      }
       CK_LAUNCH();
     }
     g_launches += 2;
