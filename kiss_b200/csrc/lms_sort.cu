@@ -41,82 +41,94 @@ __device__ __forceinline__ bool suffix_less(const SortParams& sp, u32 p, u32 q, 
 // fetches its next 32 bases in parallel (independent gathers, no dependent chains); then the first element of
 // each group of <= TINY_MAX orders the group in shared memory by (next word, deeper words, position).
 #define TG_THREADS 256
+#define TG_ITEMS 8
+#define TG_TILE (TG_THREADS * TG_ITEMS)
 template <typename K>
 __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict__ keys, u32* __restrict__ pos, u32 N,
                                                            SortParams sp, u64 h, GroupLists gl) {
-  __shared__ K skey[TG_THREADS + TINY_MAX + 2];   // keys[base-1 .. base+TG_THREADS+TINY_MAX]
-  __shared__ u32 spos[TG_THREADS + TINY_MAX];
-  __shared__ u64 sw[TG_THREADS + TINY_MAX];
+  __shared__ K skey[TG_TILE + TINY_MAX + 2];   // keys[base-1 .. base+TG_TILE+TINY_MAX]
+  __shared__ u32 spos[TG_TILE + TINY_MAX];
+  __shared__ u64 sw[TG_TILE + TINY_MAX];
   __shared__ u32 s_tied;
   const u32 tid = threadIdx.x;
   if (tid == 0) s_tied = 0;
-  const u64 base = (u64)blockIdx.x * TG_THREADS;
-  for (u32 j = tid; j < TG_THREADS + TINY_MAX + 2; j += TG_THREADS) {
+  const u64 base = (u64)blockIdx.x * TG_TILE;
+  for (u32 j = tid; j < TG_TILE + TINY_MAX + 2; j += TG_THREADS) {
     u64 idx = base + j;  // = element index + 1
     skey[j] = (idx >= 1 && idx - 1 < N) ? keys[idx - 1] : (K)0;
   }
   __syncthreads();
   const bool deep = h < sp.D;
-  for (u32 t = tid; t < TG_THREADS + TINY_MAX; t += TG_THREADS) {
-    u64 e = base + t;
-    if (e < N) {
-      K k = skey[t + 1];
-      bool pe = e > 0 && skey[t] == k, ne = e + 1 < N && skey[t + 2] == k;
-      if ((pe || ne) && deep) {
-        u32 p = pos[e];
-        u64 wv = word_at(sp.T, (u64)p + h);
-        u64 rem = sp.D - h;
+  const u64 rem = sp.D - h;
+  if (deep) {
+    // all tied elements of the tile fetch position and next word; loads of one thread are independent
+    u32 p[TG_ITEMS + 1];
+    bool tied[TG_ITEMS + 1];
+#pragma unroll
+    for (int it = 0; it <= TG_ITEMS; it++) {
+      u32 t = tid + it * TG_THREADS;
+      u64 e = base + t;
+      tied[it] = false;
+      p[it] = 0;
+      if (t < TG_TILE + TINY_MAX && e < N) {
+        K k = skey[t + 1];
+        tied[it] = (e > 0 && skey[t] == k) || (e + 1 < N && skey[t + 2] == k);
+        if (tied[it]) p[it] = pos[e];
+      }
+    }
+#pragma unroll
+    for (int it = 0; it <= TG_ITEMS; it++) {
+      if (tied[it]) {
+        u32 t = tid + it * TG_THREADS;
+        u64 wv = word_at(sp.T, (u64)p[it] + h);
         if (rem < 32) wv &= ~0ull << (64 - 2 * rem);
-        spos[t] = p;
+        spos[t] = p[it];
         sw[t] = wv;
       }
     }
   }
   __syncthreads();
-  const u64 e = base + tid;
-  bool head = false;
-  K k = (K)0;
-  if (e < N) {
-    k = skey[tid + 1];
-    head = !(e > 0 && skey[tid] == k) && (e + 1 < N && skey[tid + 2] == k);
-  }
-  if (head) {
+#pragma unroll 1
+  for (int it = 0; it < TG_ITEMS; it++) {
+    const u32 t = tid + it * TG_THREADS;
+    const u64 e = base + t;
+    if (e >= N) continue;
+    const K k = skey[t + 1];
+    if ((e > 0 && skey[t] == k) || !(e + 1 < N && skey[t + 2] == k)) continue;  // not the head of a group
     u32 g = 2;
-    while (g <= TINY_MAX && e + g < N && skey[tid + 1 + g] == k) g++;
+    while (g <= TINY_MAX && e + g < N && skey[t + 1 + g] == k) g++;
     if (g > TINY_MAX) {
       u32 idx = atomicAdd(&gl.counters[0], 1u);
       if (idx < gl.gcap) gl.glist[idx] = (u32)e; else gl.counters[3] = 1;
-    } else {
-      atomicAdd(&s_tied, g);
-      if (deep) {  // otherwise fully compared: the stable order (ascending position) is final
-        // near the end of the text (unbounded mode) or of the compared depth: plain comparator on positions
-        bool slow = false;
-        for (u32 a = 0; a < g; a++) slow |= ((u64)spos[tid + a] + h + 32 > sp.n);
-        bool changed = false;
-        for (u32 a = 1; a < g; a++) {
-          u32 xp = spos[tid + a];
-          u64 xw = sw[tid + a];
-          u32 b = a;
-          while (b > 0) {
-            u32 yp = spos[tid + b - 1];
-            u64 yw = sw[tid + b - 1];
-            bool less = slow ? suffix_less(sp, xp, yp, h)
-                             : (xw != yw ? xw < yw : suffix_less(sp, xp, yp, h + 32));
-            if (!less) break;
-            spos[tid + b] = yp;
-            sw[tid + b] = yw;
-            b--;
-          }
-          if (b != a) {
-            spos[tid + b] = xp;
-            sw[tid + b] = xw;
-            changed = true;
-          }
-        }
-        if (changed)
-          for (u32 a = 0; a < g; a++) pos[e + a] = spos[tid + a];
+      continue;
+    }
+    atomicAdd(&s_tied, g);
+    if (!deep) continue;  // fully compared: the stable order (ascending position) is final
+    // near the end of the text (unbounded mode) or of the compared depth: plain comparator on positions
+    bool slow = false;
+    for (u32 a = 0; a < g; a++) slow |= ((u64)spos[t + a] + h + 32 > sp.n);
+    bool changed = false;
+    for (u32 a = 1; a < g; a++) {
+      u32 xp = spos[t + a];
+      u64 xw = sw[t + a];
+      u32 b = a;
+      while (b > 0) {
+        u32 yp = spos[t + b - 1];
+        u64 yw = sw[t + b - 1];
+        bool less = slow ? suffix_less(sp, xp, yp, h) : (xw != yw ? xw < yw : suffix_less(sp, xp, yp, h + 32));
+        if (!less) break;
+        spos[t + b] = yp;
+        sw[t + b] = yw;
+        b--;
+      }
+      if (b != a) {
+        spos[t + b] = xp;
+        sw[t + b] = xw;
+        changed = true;
       }
     }
+    if (changed)
+      for (u32 a = 0; a < g; a++) pos[e + a] = spos[t + a];
   }
   __syncthreads();
   if (tid == 0 && s_tied) atomicAdd(gl.tied, (u64)s_tied);
@@ -157,13 +169,13 @@ __global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ k
 void groups_tiny_u32(const u32* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st) {
   if (!N) return;
   ProfScope ps(PK_GROUPS_TINY, st);
-  k_groups_tiny<u32><<<(N + 255) / 256, 256, 0, st>>>(keys, pos, N, sp, h, gl);
+  k_groups_tiny<u32><<<(N + TG_TILE - 1) / TG_TILE, TG_THREADS, 0, st>>>(keys, pos, N, sp, h, gl);
   CK_LAUNCH(); g_launches++;
 }
 void groups_tiny_u64(const u64* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st) {
   if (!N) return;
   ProfScope ps(PK_GROUPS_TINY, st);
-  k_groups_tiny<u64><<<(N + 255) / 256, 256, 0, st>>>(keys, pos, N, sp, h, gl);
+  k_groups_tiny<u64><<<(N + TG_TILE - 1) / TG_TILE, TG_THREADS, 0, st>>>(keys, pos, N, sp, h, gl);
   CK_LAUNCH(); g_launches++;
 }
 void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st) {
