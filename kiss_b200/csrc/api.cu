@@ -666,6 +666,7 @@ int kiss_b200_create(kiss_b200_ctx** out, int device) {
     u64 thr = ~0ull;  // keep freed scratch cached in the pool between calls
     CK(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &thr));
     radix_init();
+    if (const char* g = getenv("KISS_B200_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(g));
   } catch (const CudaError& err) {
     g_last_error = err.what();
     delete c;
@@ -713,7 +714,7 @@ int kiss_b200_suffix_sort_ascii_u32(kiss_b200_ctx* c, const char* seq_host, uint
 int kiss_b200_suffix_sort_dna_u32_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, uint32_t k, int algo,
                                       uint32_t* SA_dev, kiss_b200_timings* t) {
   if (!SA_dev || (n && !S_dev) || (algo != 0 && algo != 1)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
-  if (((uintptr_t)S_dev & 15) != 0) { g_last_error = "S_dev must be 16-byte aligned"; return KISS_B200_ERR_ARG; }
+  if ((((uintptr_t)S_dev | (uintptr_t)SA_dev) & 15) != 0) { g_last_error = "S_dev and SA_dev must be 16-byte aligned"; return KISS_B200_ERR_ARG; }
   if (int r = check_n(n)) return r;
   return guarded(c, [&] {
     if (n == 0) {
@@ -877,7 +878,7 @@ int kiss_b200_sort_lms_subset_dev(kiss_b200_ctx* c, uint32_t* pos_dev, uint64_t 
 int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_long_dev, uint64_t n_long,
                                      uint32_t* SA_dev, kiss_b200_timings* t) {
   if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
-  if (!SA_dev || (n_long && !sorted_long_dev) || n_long != c->prep.n_long) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (!SA_dev || (n_long && !sorted_long_dev) || n_long != c->prep.n_long || ((uintptr_t)SA_dev & 15)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   return guarded(c, [&] {
     cudaStream_t st = c->st;
     Pool pool(st, &c->arena);

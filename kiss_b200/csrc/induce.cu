@@ -274,51 +274,86 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_small(WaveArgs a, u32* __
 #define WF_INCL 2ull
 __device__ __forceinline__ u64 wf_pack(u32 epoch, u64 flag, u32 v) { return ((u64)epoch << 34) | (flag << 32) | v; }
 
+// Thread t of a tile owns 16 CONSECUTIVE slots (four 16-byte loads per array), so ranking needs no warp votes:
+// a packed 4 x 16-bit counter per thread, one warp scan and one cross-warp prefix give every induced suffix its
+// place in the tile (the first version spent 68 % of its issue slots on ballots and popcounts,
+// profiles/r1_v3_wave_fused.txt).  Tiles are cut on 4-slot boundaries of the absolute slot index; the slots
+// outside [lo, lo+len) at either end are masked.
+template <bool DOWN>
 __global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __restrict__ status, u32* __restrict__ state,
                                                             u32 tile_base, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
   __shared__ WaveSmem sm;
+  __shared__ u64 s_wsum[WAVE_WARPS];
   __shared__ u32 s_tile;
   __shared__ u32 s_off[4];
   if (threadIdx.x == 0) s_tile = atomicAdd(&state[0], 1u) - tile_base;
   __syncthreads();
   const u32 tile = s_tile;
   const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const u64 j0 = (u64)tile * WAVE_TILE + w * (32 * WAVE_ITEMS);
-  const u32 lt = (1u << lane) - 1u;
-  u32 sym[WAVE_ITEMS], cx[WAVE_ITEMS], val[WAVE_ITEMS];
-  u32 cnt[4] = {0, 0, 0, 0};
+  const u64 hi = a.lo + a.len;
+  // logical index q of the aligned wave: up: slot = abase + q; down: slot = atop - 1 - q
+  const u64 abase = a.lo & ~3ull, atop = (hi + 3) & ~3ull;
+  const u64 q0 = (u64)tile * WAVE_TILE + (u64)threadIdx.x * WAVE_ITEMS;
+  u32 cx[WAVE_ITEMS], val[WAVE_ITEMS];
+  {
+    // address-ascending block of 16 slots owned by this thread (signed: the last tile of a downward wave may
+    // reach below slot 0)
+    typedef long long s64;
+    const s64 first = DOWN ? (s64)atop - (s64)q0 - WAVE_ITEMS : (s64)abase + (s64)q0;
+    const s64 slo = (s64)a.lo, shi = (s64)hi;
 #pragma unroll
-  for (int r = 0; r < WAVE_ITEMS; r++) {
-    u64 j = j0 + r * 32 + lane;
-    u32 c = 1u, v = 0;
-    if (j < a.len) {
-      u64 slot = wave_slot(a, j);
-      c = a.CTX[slot];
-      v = a.SA[slot];
+    for (int g = 0; g < WAVE_ITEMS / 4; g++) {
+      u32 c4[4] = {1u, 1u, 1u, 1u}, v4[4] = {0u, 0u, 0u, 0u};
+      const s64 s0 = first + 4 * g;
+      if (s0 >= slo && s0 + 4 <= shi) {
+        uint4 c = *reinterpret_cast<const uint4*>(a.CTX + s0);
+        uint4 v = *reinterpret_cast<const uint4*>(a.SA + s0);
+        c4[0] = c.x; c4[1] = c.y; c4[2] = c.z; c4[3] = c.w;
+        v4[0] = v.x; v4[1] = v.y; v4[2] = v.z; v4[3] = v.w;
+      } else if (s0 + 4 > slo && s0 < shi) {
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+          s64 sl = s0 + e;
+          if (sl >= slo && sl < shi) { c4[e] = a.CTX[sl]; v4[e] = a.SA[sl]; }
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        const int i = DOWN ? (WAVE_ITEMS - 1 - (4 * g + e)) : (4 * g + e);  // scan order inside the thread
+        cx[i] = c4[e];
+        val[i] = v4[e];
+      }
     }
-    cx[r] = c;
-    val[r] = v;
   }
+  // symbols + packed per-thread counts (field s = bits 16s..16s+15)
+  u64 symbits = 0, P = 0;
 #pragma unroll
-  for (int r = 0; r < WAVE_ITEMS; r++) {
-    u32 c = cx[r], v = val[r];
-    if (c == 1u && v != 0 && v != KISS_EMPTY && j0 + r * 32 + lane < a.len) c = ctx_gather(a.T, v);  // context ran out
-    cx[r] = c;
+  for (int i = 0; i < WAVE_ITEMS; i++) {
+    u32 c = cx[i], v = val[i];
+    if (c == 1u && v != 0 && v != KISS_EMPTY) {  // context ran out (entries outside the wave have v == 0)
+      c = ctx_gather(a.T, v);
+      cx[i] = c;
+    }
     u32 cu = ctx_symbol(c, a.symmask);
-    sym[r] = cu;
-#pragma unroll
-    for (u32 s = 0; s < 4; s++) cnt[s] += __popc(__ballot_sync(0xffffffffu, cu == s));
+    symbits |= (u64)cu << (4 * i);
+    P += (cu < 4) ? (1ull << (16 * cu)) : 0ull;
   }
-  if (lane == 0) {
+  // exclusive scan of P over the threads of the warp, warp totals to shared memory
+  u64 incl = P;
 #pragma unroll
-    for (int s = 0; s < 4; s++) sm.wsum[w][s] = cnt[s];
+  for (int o = 1; o < 32; o <<= 1) {
+    u64 t = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane >= o) incl += t;
   }
+  if (lane == 31) s_wsum[w] = incl;
   __syncthreads();
   if (threadIdx.x == 0) {
+    u64 totp = 0;
+    for (int ww = 0; ww < WAVE_WARPS; ww++) totp += s_wsum[ww];  // fields <= 4096: no carry between fields
     u32 acc = 0;
     for (int s = 0; s < 4; s++) {
       sm.sb[s] = acc;
-      for (int ww = 0; ww < WAVE_WARPS; ww++) acc += sm.wsum[ww][s];
+      acc += (u32)(totp >> (16 * s)) & 0xFFFFu;
     }
     sm.sb[4] = acc;
   }
@@ -342,16 +377,16 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __
           ready = (u32)(word >> 34) == epoch && ((word >> 32) & 3ull) != 0;
           if (++spins > (1u << 24)) { state[1] = 1u; ready = true; word = wf_pack(epoch, WF_INCL, 0); }  // watchdog: never hang
         } while (!__all_sync(0xffffffffu, ready));
-        u32 incl = __ballot_sync(0xffffffffu, ((word >> 32) & 3ull) == WF_INCL);
+        u32 inclm = __ballot_sync(0xffffffffu, ((word >> 32) & 3ull) == WF_INCL);
         u32 v = (u32)word;
-        if (incl) {
-          u32 first = __ffs(incl) - 1;  // nearest predecessor holding an inclusive prefix
+        if (inclm) {
+          u32 first = __ffs(inclm) - 1;  // nearest predecessor holding an inclusive prefix
           if (lane > first) v = 0;
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
         excl += v;
-        if (incl) break;
+        if (inclm) break;
         base -= 32;
       }
       if (lane == 0) st[(u64)tile * 4 + s] = wf_pack(epoch, WF_INCL, excl + mine);
@@ -361,26 +396,20 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __
       if (tile == ntiles - 1) tot[s] = excl + mine;
     }
   }
-  __syncthreads();
-  u32 run[4];
+  // tile-local position of this thread's first induced suffix per symbol (packed): symbol base + earlier warps
+  // + earlier threads of the warp
+  u64 R = incl - P;
+  for (u32 ww = 0; ww < w; ww++) R += s_wsum[ww];
+  R += (u64)sm.sb[0] | ((u64)sm.sb[1] << 16) | ((u64)sm.sb[2] << 32) | ((u64)sm.sb[3] << 48);
 #pragma unroll
-  for (int s = 0; s < 4; s++) {
-    u32 t = sm.sb[s];
-    for (u32 ww = 0; ww < w; ww++) t += sm.wsum[ww][s];
-    run[s] = t;
-  }
-#pragma unroll
-  for (int r = 0; r < WAVE_ITEMS; r++) {
-    u32 cu = sym[r];
-    u32 b0 = __ballot_sync(0xffffffffu, cu == 0), b1 = __ballot_sync(0xffffffffu, cu == 1);
-    u32 b2 = __ballot_sync(0xffffffffu, cu == 2), b3 = __ballot_sync(0xffffffffu, cu == 3);
+  for (int i = 0; i < WAVE_ITEMS; i++) {
+    u32 cu = (u32)(symbits >> (4 * i)) & 7u;
     if (cu < 4) {
-      u32 bm = cu == 0 ? b0 : cu == 1 ? b1 : cu == 2 ? b2 : b3;
-      u32 lp = (cu == 0 ? run[0] : cu == 1 ? run[1] : cu == 2 ? run[2] : run[3]) + __popc(bm & lt);
-      sm.sSA[lp] = val[r] - 1u;
-      sm.sCTX[lp] = cx[r] >> 2;
+      u32 lp = (u32)(R >> (16 * cu)) & 0xFFFFu;
+      R += 1ull << (16 * cu);
+      sm.sSA[lp] = val[i] - 1u;
+      sm.sCTX[lp] = cx[i] >> 2;
     }
-    run[0] += __popc(b0); run[1] += __popc(b1); run[2] += __popc(b2); run[3] += __popc(b3);
   }
   __syncthreads();
   const u32 total = sm.sb[4];
@@ -388,7 +417,7 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __
     u32 s = (idx >= sm.sb[1]) + (idx >= sm.sb[2]) + (idx >= sm.sb[3]);
     u32 off = s_off[s] + (idx - sm.sb[s]);
     u64 cur = s == 0 ? a.cur[0] : s == 1 ? a.cur[1] : s == 2 ? a.cur[2] : a.cur[3];
-    u64 dst = a.down ? cur - 1 - off : cur + off;
+    u64 dst = DOWN ? cur - 1 - off : cur + off;
     a.SA[dst] = sm.sSA[idx];
     a.CTX[dst] = sm.sCTX[idx];
   }
@@ -402,9 +431,13 @@ void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u3
   a.SA = SA; a.CTX = CTX; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
   if (ws.fused) {
-    u32 ntiles = (u32)wave_tiles(len);
+    u64 len_al = down ? (((lo + len + 3) & ~3ull) - lo) : (lo + len - (lo & ~3ull));
+    u32 ntiles = (u32)wave_tiles(len_al);
     ProfScope ps(len <= WAVE_TILE ? PK_WAVE_SMALL : PK_WAVE_SCATTER, st);
-    k_wave_fused<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ++*ws.epoch, ws.tot_dev);
+    if (down)
+      k_wave_fused<true><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ++*ws.epoch, ws.tot_dev);
+    else
+      k_wave_fused<false><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ++*ws.epoch, ws.tot_dev);
     CK_LAUNCH(); g_launches++;
     *ws.tile_base += ntiles;
   } else if (len <= WAVE_TILE) {
