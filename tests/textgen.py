@@ -101,3 +101,62 @@ def mixed(seed, n):
     mask = uniform(seed + 2, n // 64 + 1).repeat(64)[:n] == 0
     S[mask] = T[mask]
     return S
+
+
+def chm13_like(seed, n, base=None, families=64, tandem_arrays=2000, segdups=500, hp_runs=2000):
+    """uniform background + interspersed repeat families (copies mutated 2-15 %, ~35 % of n),
+    tandem arrays (unit 2..2000, length 1 kb..1 Mb, 0-2 % divergence, ~10 %), exact segmental duplications
+    (10-100 kb), homopolymer runs <= 64; the last 4096 bases stay uniform.  `base` (uint8, modified in place)
+    may hold the uniform stream already (e.g. generated on the GPU).  Sizes scale down with n."""
+    S = uniform(seed, n).copy() if base is None else base
+    if n < 100_000:
+        return S
+    rng = np.random.default_rng(seed)
+    lim = n - 4096
+    scale = min(1.0, n / 3.1e9)
+
+    def mutate(seg, rate):
+        k = rng.binomial(seg.size, rate)
+        if k:
+            p = rng.integers(0, seg.size, k)
+            seg[p] = (seg[p] + rng.integers(1, 4, k).astype(np.uint8)) & 3
+
+    # (a) interspersed families
+    target = int(0.35 * n)
+    lens = [300, 1000, 6000]
+    cons = [rng.integers(0, 4, lens[f % 3]).astype(np.uint8) for f in range(families)]
+    done = 0
+    while done < target:
+        f = int(rng.integers(0, families))
+        c = cons[f].copy()
+        mutate(c, float(rng.uniform(0.02, 0.15)))
+        p = int(rng.integers(0, lim - c.size))
+        S[p:p + c.size] = c
+        done += c.size
+    # (b) tandem arrays
+    target = int(0.10 * n)
+    done = 0
+    na = max(4, int(tandem_arrays * scale))
+    for _ in range(na):
+        if done >= target:
+            break
+        ul = int(np.exp(rng.uniform(np.log(2), np.log(2000))))
+        L = int(np.exp(rng.uniform(np.log(1000), np.log(1_000_000))))
+        L = min(L, lim // 8)
+        unit = rng.integers(0, 4, ul).astype(np.uint8)
+        arr = np.tile(unit, L // ul + 1)[:L]
+        mutate(arr, float(rng.uniform(0.0, 0.02)))
+        p = int(rng.integers(0, lim - L))
+        S[p:p + L] = arr
+        done += L
+    # (c) exact segmental duplications
+    for _ in range(max(2, int(segdups * scale))):
+        L = int(rng.integers(10_000, 100_000))
+        a, b = int(rng.integers(0, lim - L)), int(rng.integers(0, lim - L))
+        S[b:b + L] = S[a:a + L].copy()
+    # (d) homopolymer runs capped at 64
+    for _ in range(max(4, int(hp_runs * scale))):
+        L = int(rng.integers(8, 65))
+        p = int(rng.integers(0, lim - L))
+        S[p:p + L] = int(rng.integers(0, 4))
+    return S

@@ -1,0 +1,82 @@
+#!/usr/bin/env python
+"""Full-size parity: the CUDA path against the REFERENCE ITSELF (oracle/_ref/libkiss_ref.so, all host threads) on
+the BASELINE.json configurations, bit-exact over the whole suffix array, plus the size-independent properties
+(SA[0] = n, permutation).  Run on the GPU box:  python tools/validate_large.py [c1|c2|c3|c3small ...]
+Prints one JSON line per configuration (kept under profiles/)."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import kiss_b200  # noqa: E402
+import oracle_lib as ol  # noqa: E402
+import textgen as tg  # noqa: E402
+import torch  # noqa: E402
+
+CONFIGS = {
+    "c1": dict(n=48_800_648, seed=1, kind="uniform", k=256),          # drosophila stand-in (README.md:88)
+    "c2": dict(n=1_000_000_000, seed=2, kind="uniform", k=256),
+    "c3small": dict(n=200_000_000, seed=3, kind="chm13", k=256),
+    "c3": dict(n=3_117_292_070, seed=3, kind="chm13", k=256),         # README.md:101
+    "c3k32": dict(n=500_000_000, seed=3, kind="chm13", k=32),
+}
+
+
+def text(ctx, cfg):
+    n = cfg["n"]
+    d = torch.empty(n + 64, dtype=torch.uint8, device="cuda")
+    ctx.synth_uniform_dev(d.data_ptr(), n, cfg["seed"])
+    S = d[:n].cpu().numpy()
+    del d
+    torch.cuda.empty_cache()
+    if cfg["kind"] == "chm13":
+        S = tg.chm13_like(cfg["seed"], n, base=S)
+    return S
+
+
+def is_permutation(sa, n):
+    flags = torch.zeros(n + 1, dtype=torch.bool, device="cuda")
+    step = 1 << 27
+    for i in range(0, n + 1, step):
+        idx = torch.from_numpy(sa[i:i + step].astype(np.int64)).cuda()
+        flags[idx] = True
+    return bool(flags.all().item())
+
+
+def main():
+    names = sys.argv[1:] or ["c1"]
+    ctx = kiss_b200.Context(0)
+    for name in names:
+        cfg = CONFIGS[name]
+        S = text(ctx, cfg)
+        n = S.size
+        t0 = time.perf_counter()
+        sa = ctx.suffix_array_dna(S, cfg["k"])
+        t_gpu = time.perf_counter() - t0
+        tm = ctx.last_timings
+        out = dict(config=name, **cfg, m=tm["m"], gpu_host_call_s=t_gpu, gpu_device_s=tm["total_device"],
+                   lms_sort_s=tm["lms_sort"], induce_s=tm["induce"], tied=tm["lms_sort_tied"], rounds=tm["lms_sort_rounds"],
+                   waves=[tm["waves_L"], tm["waves_S"]], sa0_is_n=bool(int(sa[0]) == n), permutation=is_permutation(sa, n))
+        if ol.have_ref():
+            ref = np.empty(n + 1, np.uint32)
+            threads = os.cpu_count()
+            sec = ol.ref().ref_kiss1_suffix_array_dna(S.ctypes.data, n, cfg["k"], threads, ref.ctypes.data)
+            out.update(reference_s=sec, reference_threads=threads, bit_exact=bool(np.array_equal(sa, ref)),
+                       speedup_host_call=sec / t_gpu, speedup_device=sec / tm["total_device"])
+            if not out["bit_exact"]:
+                bad = np.nonzero(sa != ref)[0]
+                out["mismatches"] = int(bad.size)
+                out["first_bad"] = [int(x) for x in bad[:5]]
+            del ref
+        print(json.dumps(out), flush=True)
+        del sa, S
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
