@@ -134,7 +134,7 @@ struct kiss_b200_ctx {
   int device = 0;
   cudaStream_t st = nullptr;
   cudaEvent_t ev[8] = {};
-  u32* pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs
+  u32* pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs (+ 8 u64 for the wave tail)
   Profiler prof;          // optional per-kernel timing
   Arena arena;
   // state kept between prepare_dev and finish_from_sorted_dev
@@ -394,6 +394,8 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
   ws.tot_host = c->pinned + 32;
   const char* mode = getenv("KISS_B200_WAVES");
   ws.fused = !(mode && std::string(mode) == "classic");
+  ws.tail_dev = pool.alloc<u64>(8);
+  ws.tail_host = reinterpret_cast<u64*>(c->pinned + 64);
   ws.status = pool.alloc<u64>(4 * nt + 4);
   ws.state = pool.alloc<u32>(2);
   u32 tile_base = 0, epoch = 0;
@@ -412,6 +414,10 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
     u64 p = bk.B[cb];
     while (p < Lc[cb]) {
       u64 q = Lc[cb];
+      if (ws.fused && q - p <= WAVE_TAIL_LIMIT) {
+        is->waves_L += induce_tail(SA, CTX, T, (u32)cb, &p, false, (0xFu << cb) & 0xFu, Lc, ws, st);
+        continue;
+      }
       induce_wave(SA, CTX, T, p, q - p, false, (0xFu << cb) & 0xFu, Lc, ws, tot, st);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
       p = q;
@@ -432,6 +438,10 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
     u64 p = bk.B[cb + 1];
     while (Sc[cb] < p) {
       u64 q = Sc[cb];
+      if (ws.fused && p - q <= WAVE_TAIL_LIMIT) {
+        is->waves_S += induce_tail(SA, CTX, T, (u32)cb, &p, true, (1u << (cb + 1)) - 1u, Sc, ws, st);
+        continue;
+      }
       induce_wave(SA, CTX, T, q, p - q, true, (1u << (cb + 1)) - 1u, Sc, ws, tot, st);
       for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
       p = q;
@@ -660,7 +670,7 @@ int kiss_b200_create(kiss_b200_ctx** out, int device) {
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
     for (auto& ev : c->ev) CK(cudaEventCreate(&ev));
-    CK(cudaHostAlloc((void**)&c->pinned, 64 * sizeof(u32), cudaHostAllocDefault));
+    CK(cudaHostAlloc((void**)&c->pinned, 64 * sizeof(u32) + 8 * sizeof(u64), cudaHostAllocDefault));
     cudaMemPool_t mp;
     CK(cudaDeviceGetDefaultMemPool(&mp, device));
     u64 thr = ~0ull;  // keep freed scratch cached in the pool between calls

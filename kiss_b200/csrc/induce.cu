@@ -279,16 +279,24 @@ __device__ __forceinline__ u64 wf_pack(u32 epoch, u64 flag, u32 v) { return ((u6
 // place in the tile (the first version spent 68 % of its issue slots on ballots and popcounts,
 // profiles/r1_v3_wave_fused.txt).  Tiles are cut on 4-slot boundaries of the absolute slot index; the slots
 // outside [lo, lo+len) at either end are masked.
-template <bool DOWN>
-__global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __restrict__ status, u32* __restrict__ state,
-                                                            u32 tile_base, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
-  __shared__ WaveSmem sm;
-  __shared__ u64 s_wsum[WAVE_WARPS];
-  __shared__ u32 s_tile;
-  __shared__ u32 s_off[4];
-  if (threadIdx.x == 0) s_tile = atomicAdd(&state[0], 1u) - tile_base;
-  __syncthreads();
-  const u32 tile = s_tile;
+struct WaveShared {
+  WaveSmem sm;
+  u64 wsum[WAVE_WARPS];
+  u32 off[4];
+  u32 tile;
+  // on-device tail loop
+  u64 cur[4];
+  u64 p;
+  u32 nwaves;
+};
+
+// one tile of a wave.  LOOKBACK = false: the wave is this single tile (no status traffic); tot[] gets the counts.
+template <bool DOWN, bool LOOKBACK>
+__device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, WaveShared& sh, u64* __restrict__ status,
+                                          u32* __restrict__ state, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
+  WaveSmem& sm = sh.sm;
+  u64* s_wsum = sh.wsum;
+  u32* s_off = sh.off;
   const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const u64 hi = a.lo + a.len;
   // logical index q of the aligned wave: up: slot = abase + q; down: slot = atop - 1 - q
@@ -359,7 +367,12 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __
   }
   __syncthreads();
   // ---- look-back: warp s (< 4) resolves symbol s
-  if (w < 4) {
+  if (!LOOKBACK) {
+    if (threadIdx.x < 4) {
+      s_off[threadIdx.x] = 0;
+      tot[threadIdx.x] = sm.sb[threadIdx.x + 1] - sm.sb[threadIdx.x];
+    }
+  } else if (w < 4) {
     const u32 s = w;
     const u32 mine = sm.sb[s + 1] - sm.sb[s];
     volatile u64* st = status;
@@ -421,6 +434,74 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __
     a.SA[dst] = sm.sSA[idx];
     a.CTX[dst] = sm.sCTX[idx];
   }
+}
+
+template <bool DOWN>
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __restrict__ status, u32* __restrict__ state,
+                                                            u32 tile_base, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
+  __shared__ WaveShared sh;
+  if (threadIdx.x == 0) sh.tile = atomicAdd(&state[0], 1u) - tile_base;
+  __syncthreads();
+  wave_tile<DOWN, true>(a, sh.tile, sh, status, state, ntiles, epoch, tot);
+}
+
+// The tail of a bucket: once a wave fits one tile every later wave of the bucket does too (wave sizes never
+// grow inside a bucket), so ONE block runs them back to back on the device — no host round trip per wave.
+// Homopolymer runs produce one tiny wave per base: this is what keeps them cheap.
+// out[0] = next wave start p, out[1..4] = cursors, out[5] = waves run.
+#define WAVE_TAIL_MAX (WAVE_TILE - 8)
+template <bool DOWN>
+__global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 bucket, u64 p0, u32 max_waves,
+                                                           u64* __restrict__ out) {
+  __shared__ WaveShared sh;
+  __shared__ u32 s_tot[4];
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 4; s++) sh.cur[s] = a0.cur[s];
+    sh.p = p0;
+    sh.nwaves = 0;
+  }
+  for (;;) {
+    __syncthreads();
+    const u64 cc = sh.cur[bucket], p = sh.p;
+    const u64 len = DOWN ? p - cc : cc - p;
+    if (len == 0 || len > WAVE_TAIL_MAX || sh.nwaves >= max_waves) break;
+    WaveArgs a = a0;
+    a.lo = DOWN ? cc : p;
+    a.len = len;
+    a.cur[0] = sh.cur[0]; a.cur[1] = sh.cur[1]; a.cur[2] = sh.cur[2]; a.cur[3] = sh.cur[3];
+    __syncthreads();
+    wave_tile<DOWN, false>(a, 0, sh, nullptr, nullptr, 1, 0, s_tot);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      sh.p = cc;
+      for (int s = 0; s < 4; s++) sh.cur[s] = DOWN ? sh.cur[s] - s_tot[s] : sh.cur[s] + s_tot[s];
+      sh.nwaves++;
+    }
+  }
+  if (threadIdx.x == 0) {
+    out[0] = sh.p;
+    for (int s = 0; s < 4; s++) out[1 + s] = sh.cur[s];
+    out[5] = sh.nwaves;
+  }
+}
+
+// host side of the tail: returns the number of waves run; p and cur[] are updated
+u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, u32 symmask, u64 cur[4],
+                WaveScratch ws, cudaStream_t st) {
+  WaveArgs a;
+  a.SA = SA; a.CTX = CTX; a.T = T; a.lo = 0; a.len = 0; a.down = down ? 1u : 0u; a.symmask = symmask;
+  for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
+  {
+    ProfScope ps(PK_WAVE_SMALL, st);
+    if (down) k_wave_tail<true><<<1, WAVE_THREADS, 0, st>>>(a, bucket, *p, 1u << 20, ws.tail_dev);
+    else k_wave_tail<false><<<1, WAVE_THREADS, 0, st>>>(a, bucket, *p, 1u << 20, ws.tail_dev);
+    CK_LAUNCH(); g_launches++;
+  }
+  CK(cudaMemcpyAsync(ws.tail_host, ws.tail_dev, 6 * sizeof(u64), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  *p = ws.tail_host[0];
+  for (int s = 0; s < 4; s++) cur[s] = ws.tail_host[1 + s];
+  return (u32)ws.tail_host[5];
 }
 
 void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4],

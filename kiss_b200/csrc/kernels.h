@@ -155,6 +155,8 @@ struct WaveScratch {
   u32* state;     // [0] tile ticket, [1] watchdog flag; zeroed once per call
   u32* tile_base; // host: tickets handed out so far
   u32* epoch;     // host: wave number
+  u64* tail_dev;  // 6 words: result of the on-device tail loop
+  u64* tail_host; // pinned
 };
 #define WAVE_TILE 4096u
 inline u64 wave_tiles(u64 len) { return (len + WAVE_TILE - 1) / WAVE_TILE; }
@@ -164,5 +166,11 @@ inline u64 wave_tiles(u64 len) { return (len + WAVE_TILE - 1) / WAVE_TILE; }
 // CTX is the per-entry context array (n + 1 words, see induce.cu).
 void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4],
                  WaveScratch ws, u32 tot[4], cudaStream_t st);
+
+// Run every remaining wave of `bucket` on the device while it fits one tile (see k_wave_tail): the wave starts
+// at *p and ends at cur[bucket].  Returns the number of waves; updates *p and cur[].
+#define WAVE_TAIL_LIMIT (WAVE_TILE - 8)
+u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, u32 symmask, u64 cur[4],
+                WaveScratch ws, cudaStream_t st);
 
 }  // namespace kiss

@@ -49,7 +49,9 @@ def is_permutation(sa, n):
 
 
 def main():
-    names = sys.argv[1:] or ["c1"]
+    args = sys.argv[1:]
+    profile = "--profile" in args
+    names = [a for a in args if not a.startswith("--")] or ["c1"]
     ctx = kiss_b200.Context(0)
     for name in names:
         cfg = CONFIGS[name]
@@ -62,7 +64,13 @@ def main():
         out = dict(config=name, **cfg, m=tm["m"], gpu_host_call_s=t_gpu, gpu_device_s=tm["total_device"],
                    lms_sort_s=tm["lms_sort"], induce_s=tm["induce"], tied=tm["lms_sort_tied"], rounds=tm["lms_sort_rounds"],
                    waves=[tm["waves_L"], tm["waves_S"]], sa0_is_n=bool(int(sa[0]) == n), permutation=is_permutation(sa, n))
-        if ol.have_ref():
+        if profile:  # second call with CUDA events around every launch (kernel class -> [ms, launches])
+            ctx.profile_enable(True)
+            ctx.suffix_array_dna(S, cfg["k"])
+            out["kernels"] = {k: [round(v[0], 3), v[1]] for k, v in ctx.profile().items()}
+            out["profiled_stages_s"] = {k: ctx.last_timings[k] for k in ("get_lms", "lms_sort", "put_lms", "induce")}
+            ctx.profile_enable(False)
+        if ol.have_ref() and "--noref" not in args:
             ref = np.empty(n + 1, np.uint32)
             threads = os.cpu_count()
             sec = ol.ref().ref_kiss1_suffix_array_dna(S.ctypes.data, n, cfg["k"], threads, ref.ctypes.data)
