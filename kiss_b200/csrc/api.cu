@@ -382,18 +382,15 @@ Buckets make_buckets(const u64 counters[8], u64 n) {
 
 struct InduceStats { u64 waves_L = 0, waves_S = 0; };
 
-void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets& bk, u32* SA, u32* CTX, InduceStats* is) {
+// `lms` = the sorted LMS suffixes (sentinel excluded), grouped by first symbol: bk.lms_off / bk.lms_count
+void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets& bk, const u32* lms, u32* SA, u32* CTX,
+               InduceStats* is) {
   cudaStream_t st = c->st;
   WaveScratch ws;
   u64 maxlen = n + 1;
   u64 nt = wave_tiles(maxlen);
-  ws.C = pool.alloc<u32>(4 * nt + 4);
-  ws.partials = pool.alloc<u32>(scan_partials_len(4 * nt));
-  ws.scan_total = pool.alloc<u32>(1);
   ws.tot_dev = pool.alloc<u32>(4);
   ws.tot_host = c->pinned + 32;
-  const char* mode = getenv("KISS_B200_WAVES");
-  ws.fused = !(mode && std::string(mode) == "classic");
   ws.tail_dev = pool.alloc<u64>(8);
   ws.tail_host = reinterpret_cast<u64*>(c->pinned + 64);
   ws.status = pool.alloc<u64>(4 * nt + 4);
@@ -407,24 +404,25 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
   u64 Lc[4], nL[4], Sc[4];
   for (int s = 0; s < 4; s++) Lc[s] = bk.B[s];
   // L pass (kiss_common.hpp:372-403)
-  induce_wave(SA, CTX, T, 0, 1, false, 0xFu, Lc, ws, tot, st);
+  set_sentinel(SA, CTX, n, st);
+  induce_wave(SA, CTX, T, nullptr, 0, 1, false, 0xFu, Lc, ws, tot, st);
   for (int s = 0; s < 4; s++) Lc[s] += tot[s];
   is->waves_L++;
   for (int cb = 0; cb < 4; cb++) {
     u64 p = bk.B[cb];
     while (p < Lc[cb]) {
       u64 q = Lc[cb];
-      if (ws.fused && q - p <= WAVE_TAIL_LIMIT) {
+      if (q - p <= WAVE_TAIL_LIMIT) {
         is->waves_L += induce_tail(SA, CTX, T, (u32)cb, &p, false, (0xFu << cb) & 0xFu, Lc, ws, st);
         continue;
       }
-      induce_wave(SA, CTX, T, p, q - p, false, (0xFu << cb) & 0xFu, Lc, ws, tot, st);
+      induce_wave(SA, CTX, T, nullptr, p, q - p, false, (0xFu << cb) & 0xFu, Lc, ws, tot, st);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
       p = q;
       is->waves_L++;
     }
     if (bk.lms_count[cb]) {
-      induce_wave(SA, CTX, T, bk.B[cb + 1] - bk.lms_count[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
+      induce_wave(SA, CTX, T, lms, bk.lms_off[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
       is->waves_L++;
     }
@@ -438,17 +436,17 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
     u64 p = bk.B[cb + 1];
     while (Sc[cb] < p) {
       u64 q = Sc[cb];
-      if (ws.fused && p - q <= WAVE_TAIL_LIMIT) {
+      if (p - q <= WAVE_TAIL_LIMIT) {
         is->waves_S += induce_tail(SA, CTX, T, (u32)cb, &p, true, (1u << (cb + 1)) - 1u, Sc, ws, st);
         continue;
       }
-      induce_wave(SA, CTX, T, q, p - q, true, (1u << (cb + 1)) - 1u, Sc, ws, tot, st);
+      induce_wave(SA, CTX, T, nullptr, q, p - q, true, (1u << (cb + 1)) - 1u, Sc, ws, tot, st);
       for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
       p = q;
       is->waves_S++;
     }
     if (cb > 0 && nL[cb]) {
-      induce_wave(SA, CTX, T, bk.B[cb], nL[cb], true, (1u << cb) - 1u, Sc, ws, tot, st);
+      induce_wave(SA, CTX, T, nullptr, bk.B[cb], nL[cb], true, (1u << cb) - 1u, Sc, ws, tot, st);
       for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
       is->waves_S++;
     }
@@ -475,6 +473,14 @@ void do_shorts(kiss_b200_ctx* c, Pool& pool, const u32* shorts_text, u32 ns, con
   out->ins = pool.alloc<u32>(ns);
   shorts_order(shorts_text, ns, sp, rank0, out->shorts, c->st);
   shorts_insertions(out->shorts, ns, longs, nl, sp, out->ins, c->st);
+}
+
+// one list out of the sorted longs and the ordered shorts (the longs themselves when there are no shorts)
+const u32* merged_lms(Pool& pool, const SortedLms& sl, cudaStream_t st) {
+  if (!sl.ns) return sl.longs;
+  u32* out = pool.alloc<u32>((u64)sl.nl + sl.ns);
+  merge_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, out, st);
+  return out;
 }
 
 void do_sort(kiss_b200_ctx* c, Pool& pool, SortedLms* out, SortStats* stats) {
@@ -513,6 +519,7 @@ void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* d
     Pool pool(st, &c->arena);
     SortedLms sl;
     u32* dCTX = nullptr;
+    const u32* lms = nullptr;
     CK(cudaEventRecord(c->ev[3], st));
     do_sort(c, pool, &sl, &ss);
     CK(cudaEventRecord(c->ev[4], st));
@@ -523,13 +530,16 @@ void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* d
       lin.B[1] = P.m1 + 1; lin.lms_count[0] = P.m1; lin.lms_off[0] = 0;
       lin.lms_off[1] = lin.lms_off[2] = lin.lms_off[3] = ~0ull;
       place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, lin, n, dSA, nullptr, st);
+    } else if (stop == STOP_PUT) {
+      CK(cudaMemsetAsync(dSA, 0xFF, (n + 1) * sizeof(u32), st));
+      place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, n, dSA, nullptr, st);
     } else {
-      if (stop == STOP_PUT) CK(cudaMemsetAsync(dSA, 0xFF, (n + 1) * sizeof(u32), st));
-      if (stop == STOP_FULL) dCTX = pool.alloc<u32>(n + 1);
-      place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, n, dSA, dCTX, st);
+      // the full path never places: the L pass scans the sorted list itself (put_lms_suffix is folded into it)
+      dCTX = pool.alloc<u32>(n + 1);
+      lms = merged_lms(pool, sl, st);
     }
     CK(cudaEventRecord(c->ev[5], st));
-    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, dSA, dCTX, &is);
+    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, lms, dSA, dCTX, &is);
     CK(cudaEventRecord(c->ev[6], st));
     CK(cudaEventSynchronize(c->ev[6]));
     CK(cudaEventElapsedTime(&t_sort, c->ev[3], c->ev[4]));
@@ -676,7 +686,6 @@ int kiss_b200_create(kiss_b200_ctx** out, int device) {
     u64 thr = ~0ull;  // keep freed scratch cached in the pool between calls
     CK(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &thr));
     radix_init();
-    if (const char* g = getenv("KISS_B200_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(g));
   } catch (const CudaError& err) {
     g_last_error = err.what();
     delete c;
@@ -796,9 +805,8 @@ int kiss_b200_induce_from_sorted_lms(kiss_b200_ctx* c, const uint8_t* S_host, ui
     u32* dSA = pool.alloc<u32>(n + 1);
     Buckets bk = make_buckets(c->prep.counters, n);
     u32* dCTX = pool.alloc<u32>(n + 1);
-    place_sorted(dsorted + 1, (u32)(m - 1), bk, n, dSA, dCTX, st);
     InduceStats is;
-    do_induce(c, pool, c->prep.T, n, bk, dSA, dCTX, &is);
+    do_induce(c, pool, c->prep.T, n, bk, dsorted + 1, dSA, dCTX, &is);
     CK(cudaMemcpyAsync(SA_host, dSA, (n + 1) * sizeof(u32), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     free_prepared(c);
@@ -903,10 +911,10 @@ int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_lo
     do_shorts(c, pool, P.pos + P.n_long, ns, sorted_long_dev, P.n_long, P.sp, &sl);
     Buckets bk = make_buckets(P.counters, P.n);
     u32* dCTX = pool.alloc<u32>(P.n + 1);
-    place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, P.n, SA_dev, dCTX, st);
+    const u32* lms = merged_lms(pool, sl, st);
     CK(cudaEventRecord(c->ev[5], st));
     InduceStats is;
-    do_induce(c, pool, P.T, P.n, bk, SA_dev, dCTX, &is);
+    do_induce(c, pool, P.T, P.n, bk, lms, SA_dev, dCTX, &is);
     CK(cudaEventRecord(c->ev[6], st));
     CK(cudaEventSynchronize(c->ev[6]));
     if (t) {

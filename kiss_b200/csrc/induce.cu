@@ -14,6 +14,7 @@
 //
 // Algorithmic bytes per scanned entry: 4 (SA read) + 0.25 (packed text) + 4 per induced suffix; the context
 // array adds 4 + 4 of streaming traffic and removes all but ~0.3 n of the random text gathers.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -89,6 +90,7 @@ void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, u32* C
 // suffix v-1 it induces inherits CTX >> 2 — so the packed text is gathered (one random 32-byte sector) only
 // when a context runs out (CTX == 1): once per LMS suffix and once per 15 steps of a chain, instead of once
 // per scanned entry as in the reference's prepare loops (kiss_common.hpp:63-113, 278-325).
+
 #define WAVE_THREADS 256
 #define WAVE_ITEMS 16
 #define WAVE_WARPS 8
@@ -96,6 +98,8 @@ void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, u32* C
 struct WaveArgs {
   u32* SA;
   u32* CTX;
+  const u32* inSA;   // scanned entries: SA itself, or the sorted LMS list (then lo/len index that list)
+  const u32* inCTX;  // nullptr: every scanned entry fetches its context (LMS list)
   const u64* T;
   u64 lo;       // first slot of the wave
   u64 len;      // number of slots
@@ -104,166 +108,32 @@ struct WaveArgs {
   u64 cur[4];   // bucket cursors
 };
 
-// context of suffix v: the 15 bases before it (two adjacent text words).  A one-word variant (context = what
-// the word holding S[v-1] offers) measured 45 % slower overall: short contexts run out in the middle of chains
-// and at their ends, and every exhausted entry costs another random sector in a later wave.
+// context of suffix v: the 15 bases before it (two adjacent text words).  Variants that were measured and lost:
+// a one-word context (what the word holding S[v-1] offers: short contexts run out in the middle of chains, every
+// exhausted entry costs another random access later, 45 % slower overall); a copy of the text in overlapping
+// 32-base windows so that one aligned load suffices (a DRAM miss fetches ~128 B whatever the request size —
+// 107 B per gather against 93 B here, and the copy is twice the text so fewer gathers hit L2);
+// branch-free batched gathers (no gain: the LMS waves are bound by random DRAM accesses, not by latency);
+// fetching the LMS contexts up front in 2-8 sweeps, each restricted to an L2-sized slice of the text
+// (2 sweeps: 3.8 ms + 1.7 ms of gather-free LMS waves against 5.9 ms with the gathers in the waves — a wash).
 __device__ __forceinline__ u32 ctx_gather(const u64* __restrict__ T, u32 v) {
   if (v >= 15) return (1u << 30) | (u32)(word_at(T, (u64)v - 15) >> 34);
   if (v == 0) return 1u;
   return (1u << (2 * v)) | (u32)(__ldg(T) >> (64 - 2 * v));
 }
 
-__device__ __forceinline__ u64 wave_slot(const WaveArgs& a, u64 j) { return a.down ? a.lo + a.len - 1 - j : a.lo + j; }
-
-// context of the entry at `slot`, refreshed from the text (and stored back) when it has run out
-__device__ __forceinline__ u32 wave_ctx_refresh(const WaveArgs& a, u64 slot) {
-  u32 c = a.CTX[slot];
-  if (c == 1u) {
-    u32 v = a.SA[slot];
-    if (v != 0 && v != KISS_EMPTY) {
-      c = ctx_gather(a.T, v);
-      a.CTX[slot] = c;
-    }
-  }
-  return c;
-}
 // symbol (0..3) the entry induces into, or 4
 __device__ __forceinline__ u32 ctx_symbol(u32 c, u32 symmask) {
   u32 cu = c & 3u;
   return (c > 1u && ((symmask >> cu) & 1u)) ? cu : 4u;
 }
 
-__global__ void __launch_bounds__(WAVE_THREADS) k_wave_count(WaveArgs a, u32* __restrict__ C, u32 ntiles) {
-  __shared__ u32 wsum[WAVE_WARPS][4];
-  const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const u64 j0 = (u64)blockIdx.x * WAVE_TILE + w * (32 * WAVE_ITEMS);
-  u32 cnt[4] = {0, 0, 0, 0};
-#pragma unroll
-  for (int r = 0; r < WAVE_ITEMS; r++) {
-    u64 j = j0 + r * 32 + lane;
-    u32 cu = 4;
-    if (j < a.len) cu = ctx_symbol(wave_ctx_refresh(a, wave_slot(a, j)), a.symmask);
-#pragma unroll
-    for (u32 s = 0; s < 4; s++) cnt[s] += __popc(__ballot_sync(0xffffffffu, cu == s));
-  }
-  if (lane == 0) {
-#pragma unroll
-    for (int s = 0; s < 4; s++) wsum[w][s] = cnt[s];
-  }
-  __syncthreads();
-  if (threadIdx.x < 4) {
-    u32 t = 0;
-#pragma unroll
-    for (int ww = 0; ww < WAVE_WARPS; ww++) t += wsum[ww][threadIdx.x];
-    C[(u64)threadIdx.x * ntiles + blockIdx.x] = t;
-  }
-}
-
-// per-symbol totals from the scanned counter matrix
-__global__ void k_wave_totals(const u32* __restrict__ E, u32 ntiles, const u32* __restrict__ grand, u32* __restrict__ tot) {
-  u32 s = threadIdx.x;
-  if (s < 4) {
-    u32 beg = E[(u64)s * ntiles];
-    u32 end = (s < 3) ? E[(u64)(s + 1) * ntiles] : *grand;
-    tot[s] = end - beg;
-  }
-}
-
 struct WaveSmem {
-  u32 wsum[WAVE_WARPS][4];
   u32 sb[5];
   u32 sSA[WAVE_TILE];
   u32 sCTX[WAVE_TILE];
 };
 
-// rank the tile's induced suffixes (contexts must be fresh), stage them in shared memory grouped by symbol,
-// then write each symbol's run with coalesced stores.  Returns nothing; sm.sb[s+1]-sm.sb[s] = tile count of s.
-__device__ __forceinline__ void wave_scatter_tile(const WaveArgs& a, u64 tile, const u32 tile_off[4], WaveSmem& sm) {
-  const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const u64 j0 = tile * WAVE_TILE + w * (32 * WAVE_ITEMS);
-  const u32 lt = (1u << lane) - 1u;
-  u32 sym[WAVE_ITEMS], cx[WAVE_ITEMS], val[WAVE_ITEMS];
-  u32 cnt[4] = {0, 0, 0, 0};
-#pragma unroll
-  for (int r = 0; r < WAVE_ITEMS; r++) {
-    u64 j = j0 + r * 32 + lane;
-    u32 c = 1u, v = 0;
-    if (j < a.len) {
-      u64 slot = wave_slot(a, j);
-      c = a.CTX[slot];
-      v = a.SA[slot];
-    }
-    cx[r] = c;
-    val[r] = v;
-    u32 cu = ctx_symbol(c, a.symmask);
-    sym[r] = cu;
-#pragma unroll
-    for (u32 s = 0; s < 4; s++) cnt[s] += __popc(__ballot_sync(0xffffffffu, cu == s));
-  }
-  if (lane == 0) {
-#pragma unroll
-    for (int s = 0; s < 4; s++) sm.wsum[w][s] = cnt[s];
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    u32 acc = 0;
-    for (int s = 0; s < 4; s++) {
-      sm.sb[s] = acc;
-      for (int ww = 0; ww < WAVE_WARPS; ww++) acc += sm.wsum[ww][s];
-    }
-    sm.sb[4] = acc;
-  }
-  __syncthreads();
-  u32 run[4];
-#pragma unroll
-  for (int s = 0; s < 4; s++) {
-    u32 t = sm.sb[s];
-    for (u32 ww = 0; ww < w; ww++) t += sm.wsum[ww][s];
-    run[s] = t;
-  }
-#pragma unroll
-  for (int r = 0; r < WAVE_ITEMS; r++) {
-    u32 cu = sym[r];
-    u32 b0 = __ballot_sync(0xffffffffu, cu == 0), b1 = __ballot_sync(0xffffffffu, cu == 1);
-    u32 b2 = __ballot_sync(0xffffffffu, cu == 2), b3 = __ballot_sync(0xffffffffu, cu == 3);
-    if (cu < 4) {
-      u32 bm = cu == 0 ? b0 : cu == 1 ? b1 : cu == 2 ? b2 : b3;
-      u32 lp = (cu == 0 ? run[0] : cu == 1 ? run[1] : cu == 2 ? run[2] : run[3]) + __popc(bm & lt);
-      sm.sSA[lp] = val[r] - 1u;
-      sm.sCTX[lp] = cx[r] >> 2;
-    }
-    run[0] += __popc(b0); run[1] += __popc(b1); run[2] += __popc(b2); run[3] += __popc(b3);
-  }
-  __syncthreads();
-  const u32 total = sm.sb[4];
-  for (u32 idx = threadIdx.x; idx < total; idx += WAVE_THREADS) {
-    u32 s = (idx >= sm.sb[1]) + (idx >= sm.sb[2]) + (idx >= sm.sb[3]);
-    u32 toff = s == 0 ? tile_off[0] : s == 1 ? tile_off[1] : s == 2 ? tile_off[2] : tile_off[3];
-    u32 off = toff + (idx - sm.sb[s]);
-    u64 cur = s == 0 ? a.cur[0] : s == 1 ? a.cur[1] : s == 2 ? a.cur[2] : a.cur[3];
-    u64 dst = a.down ? cur - 1 - off : cur + off;
-    a.SA[dst] = sm.sSA[idx];
-    a.CTX[dst] = sm.sCTX[idx];
-  }
-}
-
-__global__ void __launch_bounds__(WAVE_THREADS) k_wave_scatter(WaveArgs a, const u32* __restrict__ E, u32 ntiles) {
-  __shared__ WaveSmem sm;
-  u32 tile_off[4];
-#pragma unroll
-  for (int s = 0; s < 4; s++) tile_off[s] = E[(u64)s * ntiles + blockIdx.x] - E[(u64)s * ntiles];
-  wave_scatter_tile(a, blockIdx.x, tile_off, sm);
-}
-
-// a wave of at most one tile: refresh + scatter in one block, totals written to tot[4]
-__global__ void __launch_bounds__(WAVE_THREADS) k_wave_small(WaveArgs a, u32* __restrict__ tot) {
-  __shared__ WaveSmem sm;
-  for (u32 j = threadIdx.x; j < a.len; j += WAVE_THREADS) wave_ctx_refresh(a, wave_slot(a, j));
-  __syncthreads();
-  u32 tile_off[4] = {0, 0, 0, 0};
-  wave_scatter_tile(a, 0, tile_off, sm);
-  if (threadIdx.x < 4) tot[threadIdx.x] = sm.sb[threadIdx.x + 1] - sm.sb[threadIdx.x];
-}
 
 // ---- single-pass wave: count, decoupled look-back across tiles, scatter — one read of (CTX, SA) per entry.
 // Tiles take their index from an atomic ticket (so a tile never waits on one that has not started), publish
@@ -300,7 +170,9 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
   const u32 w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const u64 hi = a.lo + a.len;
   // logical index q of the aligned wave: up: slot = abase + q; down: slot = atop - 1 - q
-  const u64 abase = a.lo & ~3ull, atop = (hi + 3) & ~3ull;
+  // (cut on 16-byte boundaries of the scanned array: `mis` = its misalignment in entries, 0 for SA itself)
+  const u64 mis = ((u64)(uintptr_t)a.inSA >> 2) & 3ull;
+  const u64 abase = a.lo - ((a.lo + mis) & 3ull), atop = hi + ((4ull - ((hi + mis) & 3ull)) & 3ull);
   const u64 q0 = (u64)tile * WAVE_TILE + (u64)threadIdx.x * WAVE_ITEMS;
   u32 cx[WAVE_ITEMS], val[WAVE_ITEMS];
   {
@@ -314,15 +186,17 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
       u32 c4[4] = {1u, 1u, 1u, 1u}, v4[4] = {0u, 0u, 0u, 0u};
       const s64 s0 = first + 4 * g;
       if (s0 >= slo && s0 + 4 <= shi) {
-        uint4 c = *reinterpret_cast<const uint4*>(a.CTX + s0);
-        uint4 v = *reinterpret_cast<const uint4*>(a.SA + s0);
-        c4[0] = c.x; c4[1] = c.y; c4[2] = c.z; c4[3] = c.w;
+        uint4 v = *reinterpret_cast<const uint4*>(a.inSA + s0);
         v4[0] = v.x; v4[1] = v.y; v4[2] = v.z; v4[3] = v.w;
+        if (a.inCTX) {
+          uint4 c = *reinterpret_cast<const uint4*>(a.inCTX + s0);
+          c4[0] = c.x; c4[1] = c.y; c4[2] = c.z; c4[3] = c.w;
+        }
       } else if (s0 + 4 > slo && s0 < shi) {
 #pragma unroll
         for (int e = 0; e < 4; e++) {
           s64 sl = s0 + e;
-          if (sl >= slo && sl < shi) { c4[e] = a.CTX[sl]; v4[e] = a.SA[sl]; }
+          if (sl >= slo && sl < shi) { c4[e] = a.inCTX ? a.inCTX[sl] : 1u; v4[e] = a.inSA[sl]; }
         }
       }
 #pragma unroll
@@ -489,7 +363,8 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
 u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, u32 symmask, u64 cur[4],
                 WaveScratch ws, cudaStream_t st) {
   WaveArgs a;
-  a.SA = SA; a.CTX = CTX; a.T = T; a.lo = 0; a.len = 0; a.down = down ? 1u : 0u; a.symmask = symmask;
+  a.SA = SA; a.CTX = CTX; a.inSA = SA; a.inCTX = CTX; a.T = T; a.lo = 0; a.len = 0; a.down = down ? 1u : 0u;
+  a.symmask = symmask;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
   {
     ProfScope ps(PK_WAVE_SMALL, st);
@@ -504,47 +379,84 @@ u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, 
   return (u32)ws.tail_host[5];
 }
 
-void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4],
-                 WaveScratch ws, u32 tot[4], cudaStream_t st) {
+void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, u64 lo, u64 len, bool down, u32 symmask,
+                 const u64 cur[4], WaveScratch ws, u32 tot[4], cudaStream_t st) {
   tot[0] = tot[1] = tot[2] = tot[3] = 0;
   if (len == 0) return;
   WaveArgs a;
   a.SA = SA; a.CTX = CTX; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
+  a.inSA = lms_src ? lms_src : SA;
+  a.inCTX = lms_src ? nullptr : CTX;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
-  if (ws.fused) {
-    u64 len_al = down ? (((lo + len + 3) & ~3ull) - lo) : (lo + len - (lo & ~3ull));
-    u32 ntiles = (u32)wave_tiles(len_al);
-    ProfScope ps(len <= WAVE_TILE ? PK_WAVE_SMALL : PK_WAVE_SCATTER, st);
+  const u64 mis = ((u64)(uintptr_t)a.inSA >> 2) & 3ull, hi = lo + len;
+  u64 len_al = down ? (hi + ((4ull - ((hi + mis) & 3ull)) & 3ull) - lo) : (hi - (lo - ((lo + mis) & 3ull)));
+  u32 ntiles = (u32)wave_tiles(len_al);
+  {
+    ProfScope ps(len <= WAVE_TILE ? PK_WAVE_SMALL : (lms_src ? PK_WAVE_LMS : PK_WAVE_SCATTER), st);
     if (down)
       k_wave_fused<true><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ++*ws.epoch, ws.tot_dev);
     else
       k_wave_fused<false><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ++*ws.epoch, ws.tot_dev);
     CK_LAUNCH(); g_launches++;
     *ws.tile_base += ntiles;
-  } else if (len <= WAVE_TILE) {
-    ProfScope ps(PK_WAVE_SMALL, st);
-    k_wave_small<<<1, WAVE_THREADS, 0, st>>>(a, ws.tot_dev);
-    CK_LAUNCH(); g_launches++;
-  } else {
-    u32 ntiles = (u32)wave_tiles(len);
-    {
-      ProfScope ps(PK_WAVE_COUNT, st);
-      k_wave_count<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.C, ntiles);
-      CK_LAUNCH();
-    }
-    scan_excl_u32(ws.C, (u64)4 * ntiles, ws.partials, ws.scan_total, st);
-    k_wave_totals<<<1, 32, 0, st>>>(ws.C, ntiles, ws.scan_total, ws.tot_dev);
-    CK_LAUNCH();
-    {
-      ProfScope ps(PK_WAVE_SCATTER, st);
-      k_wave_scatter<<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.C, ntiles);
-      CK_LAUNCH();
-    }
-    g_launches += 3;
   }
   CK(cudaMemcpyAsync(ws.tot_host, ws.tot_dev, 4 * sizeof(u32), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   for (int s = 0; s < 4; s++) tot[s] = ws.tot_host[s];
+}
+
+__global__ void k_set_sentinel(u32* SA, u32* CTX, u32 n) { SA[0] = n; CTX[0] = 1u; }
+void set_sentinel(u32* SA, u32* CTX, u64 n, cudaStream_t st) {
+  k_set_sentinel<<<1, 1, 0, st>>>(SA, CTX, (u32)n);
+  CK_LAUNCH(); g_launches++;
+}
+
+#define MERGE_TILE 4096u
+// sorted longs + ordered shorts with their insertion points -> one sorted list (same ranks as k_place_lms)
+__global__ void __launch_bounds__(256) k_merge_lms(const u32* __restrict__ longs, u32 nl, const u32* __restrict__ shorts,
+                                                  const u32* __restrict__ ins, u32 ns, u32* __restrict__ out) {
+  __shared__ u32 sins[PLACE_INS_SMEM];
+  const bool cached = ns <= PLACE_INS_SMEM;
+  if (cached)
+    for (u32 t = threadIdx.x; t < ns; t += blockDim.x) sins[t] = ins[t];
+  __syncthreads();
+  const u32* I = cached ? sins : ins;
+  // shorts placed before long i = number of insertion points <= i; almost every block sees one value
+  __shared__ u32 s_edge[2];
+  const u64 b0 = (u64)blockIdx.x * MERGE_TILE;
+  if (threadIdx.x < 2) {
+    u64 q = threadIdx.x ? min(b0 + MERGE_TILE - 1, (u64)nl - 1) : b0;
+    u32 lo = 0, hi = ns;
+    while (lo < hi) {
+      u32 mid = lo + (hi - lo) / 2;
+      if (I[mid] <= (u32)q) lo = mid + 1; else hi = mid;
+    }
+    s_edge[threadIdx.x] = lo;
+  }
+  __syncthreads();
+  const u32 e0 = s_edge[0], e1 = s_edge[1];
+#pragma unroll 4
+  for (u32 t = threadIdx.x; t < MERGE_TILE; t += 256) {
+    u64 i = b0 + t;
+    if (i < nl) {
+      u32 lo = e0, hi = e1;
+      while (lo < hi) {
+        u32 mid = lo + (hi - lo) / 2;
+        if (I[mid] <= (u32)i) lo = mid + 1; else hi = mid;
+      }
+      out[i + lo] = longs[i];
+    } else if (i < (u64)nl + ns) {
+      u32 k = (u32)(i - nl);
+      out[(u64)I[k] + k] = shorts[k];
+    }
+  }
+}
+void merge_lms(const u32* longs, u32 nl, const u32* shorts, const u32* ins, u32 ns, u32* out, cudaStream_t st) {
+  u64 tot = (u64)nl + ns;
+  if (!tot || !ns) return;
+  ProfScope ps(PK_PLACE, st);
+  k_merge_lms<<<(unsigned)((tot + MERGE_TILE - 1) / MERGE_TILE), 256, 0, st>>>(longs, nl, shorts, ins, ns, out);
+  CK_LAUNCH(); g_launches++;
 }
 
 }  // namespace kiss

@@ -27,7 +27,7 @@ extern thread_local u64 g_launches;  // kernels launched by this thread (reporte
 
 // ---- optional per-kernel timing (CUDA events around each launch of a kernel class, on the launching stream)
 enum ProfKernel { PK_PACK, PK_LMS_CLASSIFY, PK_LMS_EMIT, PK_SCAN, PK_RADIX_HIST, PK_RADIX_SCATTER, PK_GROUPS_TINY,
-                  PK_GROUPS_MEDIUM, PK_GROUPS_OTHER, PK_SHORTS, PK_PLACE, PK_WAVE_COUNT, PK_WAVE_SCATTER, PK_WAVE_SMALL,
+                  PK_GROUPS_MEDIUM, PK_GROUPS_OTHER, PK_SHORTS, PK_PLACE, PK_WAVE_LMS, PK_WAVE_SCATTER, PK_WAVE_SMALL,
                   PK_COUNT };
 const char* prof_name(int id);
 struct Profiler {
@@ -144,13 +144,9 @@ void place_lms(const u32* longs, u32 nl, const u32* sorted_shorts, const u32* in
 void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, u32* CTX, cudaStream_t st);
 
 struct WaveScratch {
-  u32* C;      // 4 * tiles counters
-  u32* partials;
-  u32* scan_total;
   u32* tot_dev;   // 4
   u32* tot_host;  // 4, pinned
   // single-pass (decoupled look-back) waves
-  bool fused;
   u64* status;    // 4 words per tile of the largest wave, zeroed once per call
   u32* state;     // [0] tile ticket, [1] watchdog flag; zeroed once per call
   u32* tile_base; // host: tickets handed out so far
@@ -163,9 +159,14 @@ inline u64 wave_tiles(u64 len) { return (len + WAVE_TILE - 1) / WAVE_TILE; }
 // One induction wave over SA[lo, lo+len) (scanned downwards when `down`): every entry v > 0 whose preceding
 // symbol S[v-1] is in `symmask` appends v-1 at cur[S[v-1]] (upwards) or below it (downwards).  Synchronises
 // the stream and returns the per-symbol counts in tot[4].
-// CTX is the per-entry context array (n + 1 words, see induce.cu).
-void induce_wave(u32* SA, u32* CTX, const u64* T, u64 lo, u64 len, bool down, u32 symmask, const u64 cur[4],
-                 WaveScratch ws, u32 tot[4], cudaStream_t st);
+// CTX is the per-entry context array (n + 1 words, see induce.cu).  With `lms_src` the scanned entries are
+// lms_src[lo, lo+len) — the sorted LMS list itself, so the LMS suffixes are never written to SA on this path.
+void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, u64 lo, u64 len, bool down, u32 symmask,
+                 const u64 cur[4], WaveScratch ws, u32 tot[4], cudaStream_t st);
+// SA[0] = n (the sentinel suffix), context not fetched
+void set_sentinel(u32* SA, u32* CTX, u64 n, cudaStream_t st);
+// longs + shorts -> one sorted list `out` (nl + ns entries); no-op when ns == 0 (the longs are the list)
+void merge_lms(const u32* longs, u32 nl, const u32* shorts, const u32* ins, u32 ns, u32* out, cudaStream_t st);
 
 // Run every remaining wave of `bucket` on the device while it fits one tile (see k_wave_tail): the wave starts
 // at *p and ends at cur[bucket].  Returns the number of waves; updates *p and cur[].

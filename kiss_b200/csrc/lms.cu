@@ -42,53 +42,148 @@ __device__ __forceinline__ u32 word_types(u64 x, u64 next_top, u64 j, u64 n, u32
   return cout;
 }
 
+// Passes A and C give one warp 256 consecutive words (8 rows of 32, 4 chunks): every load is one coalesced
+// 256-byte row, all 8 are in flight at once, and the carries inside a row are resolved by ONE 32-bit addition
+// over the warp's (generate, propagate) ballots — the same trick as inside a word, one level up.
+#define CL_ROWS 8
+#define CL_WORDS (32 * CL_ROWS)
+
+struct RowBits { u32 G[CL_ROWS], P[CL_ROWS]; };
+
+// loads the warp's rows; nt[r] = first base of the word after lane's word of row r
+__device__ __forceinline__ void cl_load(const u64* __restrict__ T, u64 w0, u64 nwords, u32 lane, u64 xs[CL_ROWS],
+                                        u64 nt[CL_ROWS]) {
+#pragma unroll
+  for (int r = 0; r < CL_ROWS; r++) {
+    u64 j = w0 + 32 * r + lane;
+    xs[r] = j < nwords + KISS_PAD_WORDS ? __ldg(T + j) : 0ull;
+  }
+  u64 after = w0 + CL_WORDS < nwords + KISS_PAD_WORDS ? __ldg(T + w0 + CL_WORDS) : 0ull;
+#pragma unroll
+  for (int r = 0; r < CL_ROWS; r++) {
+    u64 d = __shfl_down_sync(0xffffffffu, xs[r], 1);
+    u64 nrow = r + 1 < CL_ROWS ? __shfl_sync(0xffffffffu, xs[r + 1 < CL_ROWS ? r + 1 : r], 0) : after;
+    nt[r] = (lane == 31 ? nrow : d) >> 62;
+  }
+}
+
+// word-level (generate, propagate) ballots of every row; lane L holds bit L
+__device__ __forceinline__ void cl_rowbits(const u64 xs[CL_ROWS], const u64 nt[CL_ROWS], u64 w0, u64 n, u32 lane,
+                                           RowBits& rb) {
+#pragma unroll
+  for (int r = 0; r < CL_ROWS; r++) {
+    u64 sb;
+    bool ap;
+    u32 g = word_types(xs[r], nt[r], w0 + 32 * r + lane, n, 0u, sb, ap);
+    rb.G[r] = __ballot_sync(0xffffffffu, g != 0);
+    rb.P[r] = __ballot_sync(0xffffffffu, ap);
+  }
+}
+
+// carries of one row: lane 31 is the rightmost word, so reverse the ballots and add.
+// returns the carry out of the row (into the row to its left); cin_lanes bit L = carry into lane L's word.
+__device__ __forceinline__ u32 cl_row_carry(u32 G, u32 P, u32 cin, u32& cin_lanes) {
+  u32 a = __brev(G | P), b = __brev(G);
+  u64 sum = (u64)a + b + cin;
+  cin_lanes = __brev((u32)sum ^ a ^ b);
+  return (u32)(sum >> 32);
+}
+
 // pass A: (generate, propagate) of every chunk
 __global__ void __launch_bounds__(256) k_lms_summary(const u64* __restrict__ T, u64 n, u64 nwords, u64 nchunks,
                                                     u8* __restrict__ gp) {
-  u64 c = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= nchunks) return;
-  u64 w0 = c * LMS_CHUNK_WORDS, w1 = min(nwords, w0 + LMS_CHUNK_WORDS);
-  u32 carry = 0;
-  bool prop = true;
-  u64 nxt = T[w1];  // padded: always readable
-  for (u64 j = w1; j-- > w0;) {
-    u64 x = T[j];
-    u64 s;
-    bool ap;
-    carry = word_types(x, nxt >> 62, j, n, carry, s, ap);
-    prop = prop && ap;
-    nxt = x;
+  const u32 lane = lane_id();
+  const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const u64 w0 = warp * CL_WORDS;
+  if (w0 >= nwords) return;
+  u64 xs[CL_ROWS], nt[CL_ROWS];
+  cl_load(T, w0, nwords, lane, xs, nt);
+  RowBits rb;
+  cl_rowbits(xs, nt, w0, n, lane, rb);
+  u32 out = 0;
+#pragma unroll
+  for (int c = 0; c < CL_ROWS / 2; c++) {
+    u32 dummy;
+    u32 g_hi = cl_row_carry(rb.G[2 * c + 1], rb.P[2 * c + 1], 0u, dummy);
+    u32 g_lo = cl_row_carry(rb.G[2 * c], rb.P[2 * c], 0u, dummy);
+    u32 p_hi = rb.P[2 * c + 1] == 0xffffffffu, p_lo = rb.P[2 * c] == 0xffffffffu;
+    u32 v = (g_lo | (p_lo & g_hi)) | ((p_lo & p_hi) << 1);
+    if ((int)lane == c) out = v;
   }
-  gp[c] = (u8)(carry | (prop ? 2u : 0u));
+  u64 c = warp * (CL_ROWS / 2) + lane;
+  if (lane < CL_ROWS / 2 && c < nchunks) gp[c] = (u8)out;
 }
 
-// pass B: carry into every chunk (bit 2 of gp[c]); single block
+// pass B: carry into every chunk (bit 2 of gp[c]); single block, 16 chunks per load
+__device__ __forceinline__ void gp_fold(u32 v, u32& g, u32& p) {  // extend a run leftwards by chunk v
+  g = (v & 1u) | (((v >> 1) & 1u) & g);
+  p = p & ((v >> 1) & 1u);
+}
 __global__ void __launch_bounds__(1024) k_lms_carry(u8* __restrict__ gp, u64 nchunks) {
   __shared__ u8 rg[1024], rp[1024], rc[1024];
-  u64 per = (nchunks + 1023) / 1024;
+  u64 per = ((nchunks + 1023) / 1024 + 15) & ~15ull;
   u64 c0 = min(nchunks, (u64)threadIdx.x * per), c1 = min(nchunks, c0 + per);
   u32 g = 0, p = 1;
-  for (u64 c = c1; c-- > c0;) {
-    u32 v = gp[c];
-    g = (v & 1u) | (((v >> 1) & 1u) & g);
-    p = p & ((v >> 1) & 1u);
+  {
+    u64 c = c1;
+    while (c > c0 && (c & 15)) { c--; gp_fold(gp[c], g, p); }
+    while (c >= c0 + 16) {
+      c -= 16;
+      uint4 q = *reinterpret_cast<const uint4*>(gp + c);
+      u32 w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int k = 15; k >= 0; k--) gp_fold((w[k >> 2] >> (8 * (k & 3))) & 3u, g, p);
+    }
+    while (c > c0) { c--; gp_fold(gp[c], g, p); }
   }
   rg[threadIdx.x] = (u8)g;
   rp[threadIdx.x] = (u8)p;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    u32 carry = 0;
-    for (int t = 1023; t >= 0; t--) {
-      rc[t] = (u8)carry;
-      carry = rg[t] | (rp[t] & carry);
+  if (threadIdx.x < 32) {  // 32 runs of 32 thread summaries, then the 32 run summaries by one lane
+    u32 gg = 0, pp = 1;
+    for (int t = 31; t >= 0; t--) {
+      u32 i = threadIdx.x * 32 + t;
+      gg = rg[i] | (rp[i] & gg);
+      pp = pp & rp[i];
+    }
+    u32 G = __ballot_sync(0xffffffffu, gg != 0), P = __ballot_sync(0xffffffffu, pp != 0), cl;
+    cl_row_carry(G, P, 0u, cl);
+    u32 carry = (cl >> threadIdx.x) & 1u;
+    for (int t = 31; t >= 0; t--) {
+      u32 i = threadIdx.x * 32 + t;
+      rc[i] = (u8)carry;
+      carry = rg[i] | (rp[i] & carry);
     }
   }
   __syncthreads();
   u32 carry = rc[threadIdx.x];
-  for (u64 c = c1; c-- > c0;) {
-    u32 v = gp[c];
-    gp[c] = (u8)(v | (carry << 2));
-    carry = (v & 1u) | (((v >> 1) & 1u) & carry);
+  {
+    u64 c = c1;
+    while (c > c0 && (c & 15)) {
+      c--;
+      u32 v = gp[c];
+      gp[c] = (u8)(v | (carry << 2));
+      carry = (v & 1u) | (((v >> 1) & 1u) & carry);
+    }
+    while (c >= c0 + 16) {
+      c -= 16;
+      uint4 q = *reinterpret_cast<const uint4*>(gp + c);
+      u32 w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int k = 15; k >= 0; k--) {
+        u32 sh = 8 * (k & 3);
+        u32 v = (w[k >> 2] >> sh) & 3u;
+        w[k >> 2] |= carry << (sh + 2);
+        carry = (v & 1u) | (((v >> 1) & 1u) & carry);
+      }
+      *reinterpret_cast<uint4*>(gp + c) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    while (c > c0) {
+      c--;
+      u32 v = gp[c];
+      gp[c] = (u8)(v | (carry << 2));
+      carry = (v & 1u) | (((v >> 1) & 1u) & carry);
+    }
   }
 }
 
@@ -96,49 +191,60 @@ __global__ void __launch_bounds__(1024) k_lms_carry(u8* __restrict__ gp, u64 nch
 __global__ void __launch_bounds__(256) k_lms_mask(const u64* __restrict__ T, u64 n, u64 nwords, u64 nchunks,
                                                  const u8* __restrict__ gp, u64* __restrict__ lmsmask,
                                                  u32* __restrict__ chunk_cnt, u64* __restrict__ counters) {
-  u64 c = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  const u32 lane = lane_id();
+  const u64 warp = ((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const u64 w0 = warp * CL_WORDS;
   u32 cnt[4] = {0, 0, 0, 0}, lcnt[4] = {0, 0, 0, 0};
-  if (c < nchunks) {
-    u64 w0 = c * LMS_CHUNK_WORDS, w1 = min(nwords, w0 + LMS_CHUNK_WORDS);
-    u32 carry = (gp[c] >> 2) & 1u;
-    u64 nxt = T[w1];
-    u32 total = 0;
-    for (u64 j = w1; j-- > w0;) {
-      u64 x = T[j];
-      u64 s;
-      bool ap;
-      carry = word_types(x, nxt >> 62, j, n, carry, s, ap);
-      nxt = x;
-      // S[i-1] aligned under S[i]; word 0 has no predecessor: repeat its own first base (never greater)
-      u64 prev_last = (j > 0) ? (T[j - 1] & 3ull) : (x >> 62);
-      u64 z = (x >> 2) | (prev_last << 62);
-      u64 ltp, eqp;
-      field_cmp(x, z, ltp, eqp);  // S[i] < S[i-1]
-      u64 lms = ltp & s;
-      lmsmask[j] = lms;
-      total += (u32)__popcll(lms);
-      u64 first = j * 32;
-      u32 cn = (n > first) ? (u32)min((u64)32, n - first) : 0u;
-      u64 vn = first_fields(cn);
-      u64 xh = (x >> 1) & FIELD_LO, xl = x & FIELD_LO;
-      u64 m3 = xh & xl, m2 = xh & ~xl, m1 = ~xh & xl, m0 = FIELD_LO & ~(xh | xl);
-      cnt[0] += (u32)__popcll(m0 & vn); cnt[1] += (u32)__popcll(m1 & vn);
-      cnt[2] += (u32)__popcll(m2 & vn); cnt[3] += (u32)__popcll(m3 & vn);
-      lcnt[0] += (u32)__popcll(m0 & lms); lcnt[1] += (u32)__popcll(m1 & lms);
-      lcnt[2] += (u32)__popcll(m2 & lms); lcnt[3] += (u32)__popcll(m3 & lms);
+  if (w0 < nwords) {
+    u64 xs[CL_ROWS], nt[CL_ROWS];
+    cl_load(T, w0, nwords, lane, xs, nt);
+    const u64 before = w0 > 0 ? __ldg(T + w0 - 1) : 0ull;
+    RowBits rb;
+    cl_rowbits(xs, nt, w0, n, lane, rb);
+#pragma unroll
+    for (int c = 0; c < CL_ROWS / 2; c++) {
+      const u64 ch = warp * (CL_ROWS / 2) + c;
+      u32 carry = ch < nchunks ? ((u32)gp[ch] >> 2) & 1u : 0u;
+      u32 total = 0;
+#pragma unroll
+      for (int rr = 1; rr >= 0; rr--) {
+        const int r = 2 * c + rr;
+        u32 cl;
+        carry = cl_row_carry(rb.G[r], rb.P[r], carry, cl);
+        const u64 j = w0 + 32 * r + lane, x = xs[r];
+        u64 s;
+        bool ap;
+        word_types(x, nt[r], j, n, (cl >> lane) & 1u, s, ap);
+        // S[i-1] aligned under S[i]; word 0 has no predecessor: repeat its own first base (never greater)
+        u64 up = __shfl_up_sync(0xffffffffu, x, 1);
+        u64 prow = __shfl_sync(0xffffffffu, xs[r > 0 ? r - 1 : 0], 31);
+        u64 prev = lane > 0 ? up : (r > 0 ? prow : before);
+        u64 prev_last = j > 0 ? (prev & 3ull) : (x >> 62);
+        u64 z = (x >> 2) | (prev_last << 62);
+        u64 ltp, eqp;
+        field_cmp(x, z, ltp, eqp);  // S[i] < S[i-1]
+        u64 lms = j < nwords ? (ltp & s) : 0ull;
+        if (j < nwords) lmsmask[j] = lms;
+        total += (u32)__popcll(lms);
+        u64 first = j * 32;
+        u32 cn = (n > first) ? (u32)min((u64)32, n - first) : 0u;
+        u64 vn = first_fields(cn);
+        u64 xh = (x >> 1) & FIELD_LO, xl = x & FIELD_LO;
+        u64 m3 = xh & xl, m2 = xh & ~xl, m1 = ~xh & xl, m0 = FIELD_LO & ~(xh | xl);
+        cnt[0] += (u32)__popcll(m0 & vn); cnt[1] += (u32)__popcll(m1 & vn);
+        cnt[2] += (u32)__popcll(m2 & vn); cnt[3] += (u32)__popcll(m3 & vn);
+        lcnt[0] += (u32)__popcll(m0 & lms); lcnt[1] += (u32)__popcll(m1 & lms);
+        lcnt[2] += (u32)__popcll(m2 & lms); lcnt[3] += (u32)__popcll(m3 & lms);
+      }
+      total = __reduce_add_sync(0xffffffffu, total);
+      if (lane == 0 && ch < nchunks) chunk_cnt[ch] = total;
     }
-    chunk_cnt[c] = total;
   }
   // warp reduce, one atomic per warp and counter
 #pragma unroll
   for (int s = 0; s < 4; s++) {
-    u32 a = cnt[s], b = lcnt[s];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      a += __shfl_xor_sync(0xffffffffu, a, o);
-      b += __shfl_xor_sync(0xffffffffu, b, o);
-    }
-    if (lane_id() == 0) {
+    u32 a = __reduce_add_sync(0xffffffffu, cnt[s]), b = __reduce_add_sync(0xffffffffu, lcnt[s]);
+    if (lane == 0) {
       if (a) atomicAdd(&counters[s], (u64)a);
       if (b) atomicAdd(&counters[4 + s], (u64)b);
     }
@@ -149,7 +255,8 @@ void lms_classify(const u64* T, u64 n, u8* gp, u64* lmsmask, u32* chunk_cnt, u64
   u64 nwords = (n + 31) / 32, nchunks = lms_chunks(n);
   if (nchunks == 0) return;
   ProfScope ps(PK_LMS_CLASSIFY, st);
-  unsigned grid = (unsigned)((nchunks + 255) / 256);
+  u64 nwarps = (nwords + CL_WORDS - 1) / CL_WORDS;
+  unsigned grid = (unsigned)((nwarps + 7) / 8);
   k_lms_summary<<<grid, 256, 0, st>>>(T, n, nwords, nchunks, gp);
   CK_LAUNCH();
   k_lms_carry<<<1, 1024, 0, st>>>(gp, nchunks);

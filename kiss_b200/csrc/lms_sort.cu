@@ -192,44 +192,164 @@ void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, cudaStre
 }
 
 // ------------------------------------------------------------------------------------------- medium groups
-__global__ void __launch_bounds__(256) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med, u32 nmed,
-                                                      SortParams sp, u64 h) {
-  __shared__ u32 s[MED_MAX];
-  for (u32 gi = blockIdx.x; gi < nmed; gi += gridDim.x) {
-    u32 start = med[2 * gi], size = med[2 * gi + 1];
-    u32 P = 16;
-    while (P < size) P <<= 1;
-    for (u32 i = threadIdx.x; i < P; i += blockDim.x) s[i] = i < size ? pos[start + i] : KISS_EMPTY;
-    __syncthreads();
+// One team (a warp for groups <= 64, a block above) refines one group in shared memory by rounds of 32 bases:
+// every element that still shares its segment with another fetches its next word (independent gathers), the
+// group is bitonic-sorted on (segment, word, position) and the segments are split where the words differ.
+// A round whose words are all equal inside their segments skips the sort (long shared prefixes — copies of a
+// repeat — cost one gather per round and nothing else), and the loop ends as soon as every segment is a
+// singleton.  Gathers per element: at most (D - h) / 32, instead of one dependent chain per comparison.
+#define MEDW_MAX 64u
+struct MedView {
+  u64* key;
+  u32* pos;
+  u32* seg;
+};
+
+template <u32 GT>
+__device__ __forceinline__ void team_sync() {
+  if (GT == 32) __syncwarp(); else __syncthreads();
+}
+template <u32 GT>
+__device__ __forceinline__ bool team_or(bool v) {
+  if (GT == 32) return __any_sync(0xffffffffu, v);
+  return __syncthreads_or(v);
+}
+
+// element i before element j at depth `off` (both in the same array; padding has seg = 0xFFFFFFFF)
+__device__ __forceinline__ bool med_less(const MedView& m, u32 i, u32 j, u64 off, u64 n) {
+  u32 si = m.seg[i], sj = m.seg[j];
+  if (si != sj) return si < sj;
+  u32 pi = m.pos[i], pj = m.pos[j];
+  bool ei = (u64)pi + off >= n, ej = (u64)pj + off >= n;  // suffix ended: a prefix of the others, hence first
+  if (ei | ej) return (ei && ej) ? pi > pj : ei;
+  u64 ki = m.key[i], kj = m.key[j];
+  if (ki != kj) return ki < kj;
+  return pi < pj;
+}
+
+template <u32 GT>
+__device__ __forceinline__ void med_refine(const MedView& m, u32 t, u32 size, u32 P, const SortParams& sp, u64 h,
+                                           u32* s_scan) {
+  for (u64 off = h; off < sp.D; off += 32) {
+    const u64 rem = sp.D - off;
+    const u64 mk = rem < 32 ? ~0ull << (64 - 2 * rem) : ~0ull;
+    bool anyact = false;
+    for (u32 i = t; i < size; i += GT) {
+      u32 sg = m.seg[i];
+      bool act = sg != i || (i + 1 < size && m.seg[i + 1] == sg);
+      u64 key = 0;
+      if (act) {
+        anyact = true;
+        u64 p = m.pos[i];
+        if (p + off < sp.n) key = word_at(sp.T, p + off) & mk;
+      }
+      m.key[i] = key;
+    }
+    if (!team_or<GT>(anyact)) break;
+    bool need = false;
+    for (u32 i = t; i < size; i += GT)
+      if (m.seg[i] != i) {  // not a segment head: same segment as i - 1
+        bool e = (u64)m.pos[i] + off >= sp.n || (u64)m.pos[i - 1] + off >= sp.n;
+        need |= e || m.key[i] != m.key[i - 1];
+      }
+    if (!team_or<GT>(need)) continue;
     for (u32 k2 = 2; k2 <= P; k2 <<= 1) {
       for (u32 j = k2 >> 1; j > 0; j >>= 1) {
-        for (u32 i = threadIdx.x; i < P; i += blockDim.x) {
-          u32 ixj = i ^ j;
-          if (ixj > i) {
-            u32 a = s[i], b = s[ixj];
+        for (u32 i = t; i < P; i += GT) {
+          u32 x = i ^ j;
+          if (x > i) {
             bool asc = (i & k2) == 0;
-            // b_before_a: must the pair be swapped for ascending order?
-            bool b_lt_a;
-            if (b == KISS_EMPTY) b_lt_a = false;
-            else if (a == KISS_EMPTY) b_lt_a = true;
-            else b_lt_a = suffix_less(sp, b, a, h);
-            if (b_lt_a == asc) { s[i] = b; s[ixj] = a; }
+            if (med_less(m, x, i, off, sp.n) == asc) {
+              u64 kk = m.key[i]; m.key[i] = m.key[x]; m.key[x] = kk;
+              u32 pp = m.pos[i]; m.pos[i] = m.pos[x]; m.pos[x] = pp;
+              u32 ss = m.seg[i]; m.seg[i] = m.seg[x]; m.seg[x] = ss;
+            }
           }
         }
-        __syncthreads();
+        team_sync<GT>();
       }
     }
-    for (u32 i = threadIdx.x; i < size; i += blockDim.x) pos[start + i] = s[i];
-    __syncthreads();
+    // split the segments: thread t owns E consecutive slots; head index = running maximum
+    const u32 E = P > GT ? P / GT : 1u;
+    const u32 i0 = t * E;
+    u32 heads = 0;
+    for (u32 e = 0; e < E; e++) {
+      u32 i = i0 + e;
+      if (i < size) {
+        bool hd = i == 0 || m.seg[i] != m.seg[i - 1] || m.key[i] != m.key[i - 1] ||
+                  (u64)m.pos[i] + off >= sp.n || (u64)m.pos[i - 1] + off >= sp.n;
+        heads |= (hd ? 1u : 0u) << e;
+      }
+    }
+    u32 v = heads ? i0 + (31u - (u32)__clz((int)heads)) + 1u : 0u;  // last head in my slots, +1
+    u32 incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      u32 u = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)(t & 31u) >= o) incl = max(incl, u);
+    }
+    u32 excl = __shfl_up_sync(0xffffffffu, incl, 1);
+    if ((t & 31u) == 0) excl = 0;
+    if (GT > 32) {
+      if ((t & 31u) == 31u) s_scan[t >> 5] = incl;
+      __syncthreads();
+      for (u32 w = 0; w < (t >> 5); w++) excl = max(excl, s_scan[w]);
+    } else {
+      __syncwarp();
+    }
+    u32 cur = excl;  // head index + 1 of the segment running into my first slot
+    for (u32 e = 0; e < E; e++) {
+      u32 i = i0 + e;
+      if (i < size) {
+        if ((heads >> e) & 1u) cur = i + 1;
+        m.seg[i] = cur - 1;
+      }
+    }
+    team_sync<GT>();
+  }
+}
+
+// GT = 32: one warp per group of <= MEDW_MAX; GT = 256: one block per larger group
+template <u32 GT>
+__global__ void __launch_bounds__(256) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med, u32 nmed,
+                                                      SortParams sp, u64 h) {
+  constexpr u32 CAP = GT == 32 ? MEDW_MAX : MED_MAX;
+  constexpr u32 TEAMS = 256 / GT;
+  __shared__ u64 s_key[TEAMS * CAP];
+  __shared__ u32 s_pos[TEAMS * CAP];
+  __shared__ u32 s_seg[TEAMS * CAP];
+  __shared__ u32 s_scan[8];
+  const u32 team = threadIdx.x / GT, t = threadIdx.x % GT;
+  MedView m{s_key + team * CAP, s_pos + team * CAP, s_seg + team * CAP};
+  for (u32 gi = blockIdx.x * TEAMS + team; gi < nmed; gi += gridDim.x * TEAMS) {
+    const u32 start = med[2 * gi], size = med[2 * gi + 1];
+    const bool mine = GT == 32 ? size <= MEDW_MAX : size > MEDW_MAX;
+    if (!mine) continue;  // (uniform per team)
+    u32 P = 2;
+    while (P < size) P <<= 1;
+    for (u32 i = t; i < P; i += GT) {
+      m.pos[i] = i < size ? pos[start + i] : KISS_EMPTY;
+      m.seg[i] = i < size ? 0u : 0xFFFFFFFFu;
+    }
+    team_sync<GT>();
+    med_refine<GT>(m, t, size, P, sp, h, s_scan);
+    team_sync<GT>();
+    for (u32 i = t; i < size; i += GT) pos[start + i] = m.pos[i];
+    team_sync<GT>();
   }
 }
 
 void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st) {
   if (!nmed || h >= sp.D) return;
   ProfScope ps(PK_GROUPS_MEDIUM, st);
-  u32 grid = nmed < 1048576u ? nmed : 1048576u;
-  k_groups_medium<<<grid, 256, 0, st>>>(pos, med, nmed, sp, h);
-  CK_LAUNCH(); g_launches++;
+  u32 gw = (nmed + 7) / 8, gb = nmed;
+  if (gw > 1048576u) gw = 1048576u;
+  if (gb > 1048576u) gb = 1048576u;
+  k_groups_medium<32><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h);
+  CK_LAUNCH();
+  k_groups_medium<256><<<gb, 256, 0, st>>>(pos, med, nmed, sp, h);
+  CK_LAUNCH();
+  g_launches += 2;
 }
 
 // ------------------------------------------------------------------------------------------- big groups

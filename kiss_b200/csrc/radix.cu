@@ -20,7 +20,7 @@ thread_local Profiler* g_prof = nullptr;
 const char* prof_name(int id) {
   static const char* names[PK_COUNT] = {"k_pack_codes", "k_lms_summary+carry+mask", "k_lms_emit", "k_scan_*", "k_radix_hist",
                                         "k_radix_scatter", "k_groups_tiny", "k_groups_medium", "k_groups_classify+big_*",
-                                        "k_short_*", "k_place_lms", "k_wave_count", "k_wave_scatter", "k_wave_small"};
+                                        "k_short_*", "k_place/merge_lms", "k_wave_fused(lms)", "k_wave_fused", "k_wave_small/tail"};
   return (id >= 0 && id < PK_COUNT) ? names[id] : "?";
 }
 cudaEvent_t Profiler::get() {
@@ -214,14 +214,11 @@ __global__ void __launch_bounds__(RADIX_THREADS, 3) k_radix_scatter(const K* __r
       u32 bal = __ballot_sync(0xffffffffu, bit);
       peers &= bit ? bal : ~bal;
     }
-    u32 leader = (u32)__ffs(peers) - 1u;
-    u32 old = 0;
-    if (lane == leader && valid) {
-      old = wcnt[w * 256 + d];
-      wcnt[w * 256 + d] = old + (u32)__popc(peers);
-    }
-    old = __shfl_sync(0xffffffffu, old, leader);
-    rank[r] = old + (u32)__popc(peers & lt_mask);
+    // every lane reads its digit's running count (a broadcast for equal digits); the lowest peer bumps it
+    const u32 below = peers & lt_mask;
+    const u32 old = wcnt[w * 256 + d];
+    if (valid && below == 0) wcnt[w * 256 + d] = old + (u32)__popc(peers);
+    rank[r] = old + (u32)__popc(below);
     __syncwarp();
   }
   __syncthreads();
@@ -348,14 +345,11 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
         u32 bal = __ballot_sync(0xffffffffu, bit);
         peers &= bit ? bal : ~bal;
       }
-      u32 leader = (u32)__ffs(peers) - 1u;
-      u32 old = 0;
-      if (lane == leader && valid) {
-        old = wcnt[w * 256 + d];
-        wcnt[w * 256 + d] = old + (u32)__popc(peers);
-      }
-      old = __shfl_sync(0xffffffffu, old, leader);
-      rank[r] = old + (u32)__popc(peers & lt_mask);
+      // every lane reads its digit's running count (a broadcast for equal digits); the lowest peer bumps it
+      const u32 below = peers & lt_mask;
+      const u32 old = wcnt[w * 256 + d];
+      if (valid && below == 0) wcnt[w * 256 + d] = old + (u32)__popc(peers);
+      rank[r] = old + (u32)__popc(below);
       __syncwarp();
     }
     __syncthreads();
