@@ -207,8 +207,9 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
       }
     }
   }
-  // symbols + packed per-thread counts (field s = bits 16s..16s+15)
-  u64 symbits = 0, P = 0;
+  // symbols + per-thread counts: 8-bit fields while counting (<= 16 per thread), 16-bit fields for the scans
+  u64 symbits = 0;
+  u32 P8 = 0;
 #pragma unroll
   for (int i = 0; i < WAVE_ITEMS; i++) {
     u32 c = cx[i], v = val[i];
@@ -218,8 +219,9 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
     }
     u32 cu = ctx_symbol(c, a.symmask);
     symbits |= (u64)cu << (4 * i);
-    P += (cu < 4) ? (1ull << (16 * cu)) : 0ull;
+    P8 += (cu < 4) ? (1u << (8 * cu)) : 0u;
   }
+  const u64 P = (u64)(P8 & 0xFFu) | ((u64)(P8 & 0xFF00u) << 8) | ((u64)(P8 & 0xFF0000u) << 16) | ((u64)(P8 >> 24) << 48);
   // exclusive scan of P over the threads of the warp, warp totals to shared memory
   u64 incl = P;
 #pragma unroll
@@ -283,35 +285,40 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
       if (tile == ntiles - 1) tot[s] = excl + mine;
     }
   }
-  // tile-local position of this thread's first induced suffix per symbol (packed): symbol base + earlier warps
-  // + earlier threads of the warp
+  // tile-local position of this thread's first induced suffix per symbol: symbol base + earlier warps + earlier
+  // threads of the warp; inside the thread an 8-bit running count per symbol
   u64 R = incl - P;
   for (u32 ww = 0; ww < w; ww++) R += s_wsum[ww];
-  R += (u64)sm.sb[0] | ((u64)sm.sb[1] << 16) | ((u64)sm.sb[2] << 32) | ((u64)sm.sb[3] << 48);
+  const u32 r0 = ((u32)R & 0xFFFFu) + sm.sb[0], r1 = ((u32)(R >> 16) & 0xFFFFu) + sm.sb[1],
+            r2 = ((u32)(R >> 32) & 0xFFFFu) + sm.sb[2], r3 = (u32)(R >> 48) + sm.sb[3];
+  u32 L8 = 0;
 #pragma unroll
   for (int i = 0; i < WAVE_ITEMS; i++) {
     u32 cu = (u32)(symbits >> (4 * i)) & 7u;
     if (cu < 4) {
-      u32 lp = (u32)(R >> (16 * cu)) & 0xFFFFu;
-      R += 1ull << (16 * cu);
+      u32 lp = (cu == 0 ? r0 : cu == 1 ? r1 : cu == 2 ? r2 : r3) + ((L8 >> (8 * cu)) & 0xFFu);
+      L8 += 1u << (8 * cu);
       sm.sSA[lp] = val[i] - 1u;
       sm.sCTX[lp] = cx[i] >> 2;
     }
   }
   __syncthreads();
-  const u32 total = sm.sb[4];
-  for (u32 idx = threadIdx.x; idx < total; idx += WAVE_THREADS) {
-    u32 s = (idx >= sm.sb[1]) + (idx >= sm.sb[2]) + (idx >= sm.sb[3]);
-    u32 off = s_off[s] + (idx - sm.sb[s]);
-    u64 cur = s == 0 ? a.cur[0] : s == 1 ? a.cur[1] : s == 2 ? a.cur[2] : a.cur[3];
-    u64 dst = DOWN ? cur - 1 - off : cur + off;
-    a.SA[dst] = sm.sSA[idx];
-    a.CTX[dst] = sm.sCTX[idx];
+  // each symbol's run goes out with coalesced stores
+#pragma unroll
+  for (int s = 0; s < 4; s++) {
+    const u32 b = sm.sb[s], e = sm.sb[s + 1];
+    const long long cur = (long long)a.cur[s], off = (long long)s_off[s] - (long long)b;
+    const long long base = DOWN ? cur - 1 - off : cur + off;  // dst = base -/+ idx
+    for (u32 idx = b + threadIdx.x; idx < e; idx += WAVE_THREADS) {
+      const long long dst = DOWN ? base - (long long)idx : base + (long long)idx;
+      a.SA[dst] = sm.sSA[idx];
+      a.CTX[dst] = sm.sCTX[idx];
+    }
   }
 }
 
 template <bool DOWN>
-__global__ void __launch_bounds__(WAVE_THREADS) k_wave_fused(WaveArgs a, u64* __restrict__ status, u32* __restrict__ state,
+__global__ void __launch_bounds__(WAVE_THREADS, 4) k_wave_fused(WaveArgs a, u64* __restrict__ status, u32* __restrict__ state,
                                                             u32 tile_base, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
   __shared__ WaveShared sh;
   if (threadIdx.x == 0) sh.tile = atomicAdd(&state[0], 1u) - tile_base;
@@ -393,10 +400,13 @@ void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, u64 lo, u6
   u32 ntiles = (u32)wave_tiles(len_al);
   {
     ProfScope ps(len <= WAVE_TILE ? PK_WAVE_SMALL : (lms_src ? PK_WAVE_LMS : PK_WAVE_SCATTER), st);
+    // (a persistent variant that requests the next ticket early measured 2x slower: a ticket taken long before
+    // its tile starts makes every later tile wait in the look-back)
+    const u32 ep = ++*ws.epoch;
     if (down)
-      k_wave_fused<true><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ++*ws.epoch, ws.tot_dev);
+      k_wave_fused<true><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_dev);
     else
-      k_wave_fused<false><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ++*ws.epoch, ws.tot_dev);
+      k_wave_fused<false><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_dev);
     CK_LAUNCH(); g_launches++;
     *ws.tile_base += ntiles;
   }

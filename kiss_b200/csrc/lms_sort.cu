@@ -49,9 +49,10 @@ __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict_
   __shared__ K skey[TG_TILE + TINY_MAX + 2];   // keys[base-1 .. base+TG_TILE+TINY_MAX]
   __shared__ u32 spos[TG_TILE + TINY_MAX];
   __shared__ u64 sw[TG_TILE + TINY_MAX];
-  __shared__ u32 s_tied;
+  __shared__ unsigned short sheads[TG_TILE / 2];  // tile-local index of every group head (a group has >= 2 elements)
+  __shared__ u32 s_tied, s_nheads;
   const u32 tid = threadIdx.x;
-  if (tid == 0) s_tied = 0;
+  if (tid == 0) { s_tied = 0; s_nheads = 0; }
   const u64 base = (u64)blockIdx.x * TG_TILE;
   for (u32 j = tid; j < TG_TILE + TINY_MAX + 2; j += TG_THREADS) {
     u64 idx = base + j;  // = element index + 1
@@ -60,8 +61,9 @@ __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict_
   __syncthreads();
   const bool deep = h < sp.D;
   const u64 rem = sp.D - h;
-  if (deep) {
-    // all tied elements of the tile fetch position and next word; loads of one thread are independent
+  {
+    // all tied elements of the tile fetch position and next word; loads of one thread are independent.
+    // Group heads (tied with the next element, not with the previous one) are queued for the second phase.
     u32 p[TG_ITEMS + 1];
     bool tied[TG_ITEMS + 1];
 #pragma unroll
@@ -70,31 +72,41 @@ __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict_
       u64 e = base + t;
       tied[it] = false;
       p[it] = 0;
+      bool head = false;
       if (t < TG_TILE + TINY_MAX && e < N) {
         K k = skey[t + 1];
-        tied[it] = (e > 0 && skey[t] == k) || (e + 1 < N && skey[t + 2] == k);
-        if (tied[it]) p[it] = pos[e];
+        bool prev = e > 0 && skey[t] == k, next = e + 1 < N && skey[t + 2] == k;
+        tied[it] = prev || next;
+        head = next && !prev && t < TG_TILE;
+        if (tied[it] && deep) p[it] = pos[e];
+      }
+      u32 hb = __ballot_sync(0xffffffffu, head);
+      if (hb) {
+        u32 lane = tid & 31u, slot = 0;
+        if (lane == 0) slot = atomicAdd(&s_nheads, (u32)__popc(hb));
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (head) sheads[slot + __popc(hb & ((1u << lane) - 1u))] = (unsigned short)t;
       }
     }
+    if (deep) {
 #pragma unroll
-    for (int it = 0; it <= TG_ITEMS; it++) {
-      if (tied[it]) {
-        u32 t = tid + it * TG_THREADS;
-        u64 wv = word_at(sp.T, (u64)p[it] + h);
-        if (rem < 32) wv &= ~0ull << (64 - 2 * rem);
-        spos[t] = p[it];
-        sw[t] = wv;
+      for (int it = 0; it <= TG_ITEMS; it++) {
+        if (tied[it]) {
+          u32 t = tid + it * TG_THREADS;
+          u64 wv = word_at(sp.T, (u64)p[it] + h);
+          if (rem < 32) wv &= ~0ull << (64 - 2 * rem);
+          spos[t] = p[it];
+          sw[t] = wv;
+        }
       }
     }
   }
   __syncthreads();
-#pragma unroll 1
-  for (int it = 0; it < TG_ITEMS; it++) {
-    const u32 t = tid + it * TG_THREADS;
+  const u32 nheads = s_nheads;
+  for (u32 hi = tid; hi < nheads; hi += TG_THREADS) {
+    const u32 t = sheads[hi];
     const u64 e = base + t;
-    if (e >= N) continue;
     const K k = skey[t + 1];
-    if ((e > 0 && skey[t] == k) || !(e + 1 < N && skey[t + 2] == k)) continue;  // not the head of a group
     u32 g = 2;
     while (g <= TINY_MAX && e + g < N && skey[t + 1 + g] == k) g++;
     if (g > TINY_MAX) {

@@ -280,7 +280,7 @@ __device__ __forceinline__ void tile_fetch(E* sdst, const E* __restrict__ g, u32
   }
 }
 
-template <typename K>
+template <typename K, int NMATCH>
 __global__ void __launch_bounds__(RADIX_THREADS, (sizeof(K) == 4 ? 3 : 2))
 k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __restrict__ kout, u32* __restrict__ vout,
                   u32 N, int shift, u32 mask, const u32* __restrict__ H, u32 ntiles) {
@@ -338,12 +338,19 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
     for (int r = 0; r < RADIX_ITEMS; r++) {
       bool valid = lbase + r * 32 + lane < tile_n;
       u32 d = (u32)(keys[r] >> shift) & mask;
-      u32 peers = __ballot_sync(0xffffffffu, valid);
+      u32 peers;
+      if (r < NMATCH) {
+        // a few rounds go through MATCH.ANY (ADU pipe) so that the ballot rounds (ALU pipe) are not the only load
+        peers = __match_any_sync(0xffffffffu, valid ? d : 256u + lane);
+      } else {
+        peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
-      for (int b = 0; b < 8; b++) {
-        bool bit = (d >> b) & 1u;
-        u32 bal = __ballot_sync(0xffffffffu, bit);
-        peers &= bit ? bal : ~bal;
+        for (int b = 0; b < 8; b++) {
+          const bool bit = (d & (1u << b)) != 0;
+          const u32 bal = __ballot_sync(0xffffffffu, bit);
+          const u32 m = bit ? 0xffffffffu : 0u;
+          peers &= ~(bal ^ m);
+        }
       }
       // every lane reads its digit's running count (a broadcast for equal digits); the lowest peer bumps it
       const u32 below = peers & lt_mask;
@@ -389,7 +396,7 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
 }
 
 template <typename K>
-static size_t radix_smem_p() {
+static size_t radix_smem_p() {  // (same for every NMATCH)
   return 2 * RADIX_TILE * (sizeof(K) + 4) + (RADIX_WARPS * 256 + 256 + 256 + 40) * 4;
 }
 static int g_radix_grid[2] = {0, 0};  // resident blocks of the persistent kernel (u32, u64 keys)
@@ -402,13 +409,15 @@ static size_t radix_smem() {
 void radix_init() {
   CK(cudaFuncSetAttribute(k_radix_scatter<u32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter<u64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem<u64>()));
-  CK(cudaFuncSetAttribute(k_radix_scatter_p<u32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
-  CK(cudaFuncSetAttribute(k_radix_scatter_p<u64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
   int dev = 0, sms = 0, b32 = 0, b64 = 0;
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b32, k_radix_scatter_p<u32>, RADIX_THREADS, radix_smem_p<u32>()));
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b64, k_radix_scatter_p<u64>, RADIX_THREADS, radix_smem_p<u64>()));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b32, k_radix_scatter_p<u32, 0>, RADIX_THREADS, radix_smem_p<u32>()));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b64, k_radix_scatter_p<u64, 0>, RADIX_THREADS, radix_smem_p<u64>()));
   g_radix_grid[0] = sms * (b32 > 0 ? b32 : 1);
   g_radix_grid[1] = sms * (b64 > 0 ? b64 : 1);
 }
@@ -437,8 +446,14 @@ static void radix_sort_impl(K*& keys, u32*& vals, K*& keys_alt, u32*& vals_alt, 
       } else {
         u32 grid = (u32)g_radix_grid[sizeof(K) == 4 ? 0 : 1];
         if (grid > ntiles) grid = ntiles;
-        k_radix_scatter_p<K><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift,
-                                                                            mask, H, ntiles);
+        static const int nmatch = [] { const char* e = getenv("KISS_B200_NMATCH"); return e ? atoi(e) : 0; }();
+        if (sizeof(K) == 4 && nmatch == 4)
+          k_radix_scatter_p<u32, 4><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);
+        else if (sizeof(K) == 4 && nmatch == 8)
+          k_radix_scatter_p<u32, 8><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);
+        else
+          k_radix_scatter_p<K, 0><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift,
+                                                                                 mask, H, ntiles);
       }
       CK_LAUNCH();
     }
