@@ -163,6 +163,10 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------ B200 arm
+# mean DRAM bytes (read + write) per launch at the 1 Gbp workload, ncu --set full (profiles/r1_v6_dram_per_kernel.txt)
+NCU_DRAM_BYTES_PER_LAUNCH = {"k_wave_fused": 0.8955e9, "k_radix_scatter": 5.2185e9, "k_groups_tiny": 6.7629e9}
+
+
 def b200_alg_bytes(n, m):
     """B_alg(n, m) = 18 n + 28 m"""
     return 18 * n + 28 * m
@@ -254,31 +258,44 @@ def run_b200(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         n_long = m - 1
-        alg = {  # bytes per launch (DESIGN.md "Kernels")
+        # one entry per kernel FUNCTION: the three profiler classes of k_wave_fused / k_wave_tail are one kernel (K5)
+        merged = {}
+        for name, (tot_ms, cnt) in prof.items():
+            key = "k_wave_fused" if name.startswith("k_wave") else name
+            a, b = merged.get(key, (0.0, 0))
+            merged[key] = (a + tot_ms, b + cnt)
+        steps = args.steps
+        alg = {  # algorithmic bytes per launch (SURVEY.md 8(d) per-unit figures x units of one launch)
             "k_radix_scatter": 2 * (4 + 4) * n_long,            # read + write of (key32, pos32) per pass
             "k_radix_hist": 4 * n_long,
             "k_groups_tiny": (4 + 4) * n_long,
-            "k_place_lms": (4 + 4 + 4) * n_long,
+            "k_place/merge_lms": (4 + 4) * n_long,
+            "k_pack_codes": n + n // 4,
         }
-        # induction: per scanned entry 4 (SA) + 4 (context), per induced suffix 4 + 4; summed over all waves
-        scanned = (n + 1) + (n // 2 + m)
-        if "k_wave_scatter" in prof:
-            alg["k_wave_scatter"] = (8 * scanned + 8 * n) / prof["k_wave_scatter"][1]
-        if "k_wave_count" in prof:
-            alg["k_wave_count"] = (4 * scanned + 0.25 * n) / prof["k_wave_count"][1]
+        if "k_wave_fused" in merged:
+            # K5 induction (8(d)): 2 x 4(n+1) SA reads + 4n induced writes + 4m + 2 x n/4 packed text, per step,
+            # spread over the launches of one step
+            alg["k_wave_fused"] = (8 * (n + 1) + 4 * n + 4 * m + n // 2) / (merged["k_wave_fused"][1] / steps)
         kernels = {}
-        for name, (tot_ms, cnt) in prof.items():
-            kernels[name] = {"ms_per_step": tot_ms / args.steps, "launches_per_step": cnt / args.steps}
+        for name, (tot_ms, cnt) in merged.items():
+            kernels[name] = {"ms_per_step": tot_ms / steps, "launches_per_step": cnt / steps}
             if name in alg:
                 gbs = alg[name] / (tot_ms / cnt * 1e-3) / 1e9
                 kernels[name].update(alg_bytes_per_launch=alg[name], achieved_gbs=gbs, frac=gbs / peak)
+        for name, (tot_ms, cnt) in prof.items():
+            if name.startswith("k_wave"):
+                kernels["k_wave_fused"].setdefault("classes", {})[name] = {"ms_per_step": tot_ms / steps,
+                                                                          "launches_per_step": cnt / steps}
         line["kernels"] = kernels
         dom = max((k for k in kernels if "achieved_gbs" in kernels[k]), key=lambda k: kernels[k]["ms_per_step"])
-        traffic = {"k_radix_scatter": 4.70e9}.get(dom)  # dram read+write per launch, ncu --set full (profiles/)
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch (mean over the launches of one step) from the
+        # ncu capture under profiles/ (r1_v6_dram_per_kernel.txt); None when the dominant kernel has no capture
+        traffic = NCU_DRAM_BYTES_PER_LAUNCH.get(dom)
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
                             "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": traffic,
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
-                            "share_of_step": kernels[dom]["ms_per_step"] / ms_step}
+                            "share_of_step": kernels[dom]["ms_per_step"] / ms_step,
+                            "launches_per_step": kernels[dom]["launches_per_step"]}
         balg = b200_alg_bytes(n, m)
         dev_s = stage.get("total_device", ms * 1e-3) / args.steps
         line["roofline_whole_path"] = {"alg_bytes": balg, "achieved": balg / dev_s / 1e9, "frac": balg / dev_s / 1e9 / peak,

@@ -89,6 +89,9 @@ struct Pool {
     bytes = (bytes + 255) & ~255ull;
     void* p = ar->take(bytes);
     if (!p) {
+      static const bool dbg = getenv("KISS_B200_DEBUG_ARENA") != nullptr;
+      if (dbg) fprintf(stderr, "[kiss_b200] arena overflow: %llu bytes (cap %llu, top %llu, blocks %zu)\n",
+                       (unsigned long long)bytes, (unsigned long long)ar->cap, (unsigned long long)ar->top(), ar->blks.size());
       CK(cudaMallocAsync(&p, bytes, st));
       ar->live_extra += bytes;
       ar->note();
@@ -173,13 +176,19 @@ void free_prepared(kiss_b200_ctx* c) {
   p = kiss_b200_ctx::Prepared();
 }
 
-// ---- pack + get_lms.  Leaves T, pos, key owned by ctx->prep.
-void do_prepare(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, float* t_pack, float* t_lms) {
+// Drop the previous text and, when nothing else lives in the arena, regrow it to the peak seen so far.
+// Must run before a call allocates anything (run_host allocates the device text first).
+void begin_call(kiss_b200_ctx* c) {
   free_prepared(c);
   if (c->arena.idle() && c->arena.peak > c->arena.cap) {
     cudaStreamSynchronize(c->st);
     c->arena.settle();
   }
+}
+
+// ---- pack + get_lms.  Leaves T, pos, key owned by ctx->prep.
+void do_prepare(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, float* t_pack, float* t_lms) {
+  begin_call(c);
   cudaStream_t st = c->st;
   Pool pool(st, &c->arena);
   Sync sync{c};
@@ -243,6 +252,26 @@ struct SortStats { u64 tied = 0, rounds = 0; };
 template <typename K>
 u32 run_groups(kiss_b200_ctx* c, const K* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl);
 
+// KISS_B200_DEBUG_GROUPS=1: per level, how many groups of each class and the size histogram of the medium ones
+void debug_groups(kiss_b200_ctx* c, const char* tag, u32 N, u64 h, const u32 cn[4], const GroupLists& gl) {
+  static const bool on = getenv("KISS_B200_DEBUG_GROUPS") != nullptr;
+  if (!on) return;
+  std::vector<u32> med(2ull * cn[1]);
+  if (cn[1]) CK(cudaMemcpy(med.data(), gl.med, med.size() * sizeof(u32), cudaMemcpyDeviceToHost));
+  u64 hist[12] = {}, elems = 0;
+  for (u32 g = 0; g < cn[1]; g++) {
+    u32 sz = med[2 * g + 1];
+    elems += sz;
+    int b = 0;
+    while ((1u << (b + 4)) < sz && b < 11) b++;
+    hist[b]++;
+  }
+  fprintf(stderr, "[kiss_b200] groups %s h=%llu N=%u: >tiny %u, medium %u (%llu elements; sizes <=16:%llu <=32:%llu <=64:%llu <=128:%llu <=256:%llu <=512:%llu <=1024:%llu <=2048:%llu), big %u\n",
+          tag, (unsigned long long)h, N, cn[0], cn[1], (unsigned long long)elems, (unsigned long long)hist[0], (unsigned long long)hist[1],
+          (unsigned long long)hist[2], (unsigned long long)hist[3], (unsigned long long)hist[4], (unsigned long long)hist[5],
+          (unsigned long long)hist[6], (unsigned long long)hist[7], cn[2]);
+}
+
 template <>
 u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl) {
   Sync sync{c};
@@ -254,6 +283,7 @@ u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const So
   if (!cn[0] || h >= sp.D) return 0;
   groups_classify_u32(keys, N, cn[0], gl, c->st);
   sync.read(gl.counters, 4, cn);
+  debug_groups(c, "u32", N, h, cn, gl);
   groups_medium(pos, gl.med, cn[1], sp, h, c->st);
   return cn[2];
 }
@@ -268,6 +298,7 @@ u32 run_groups<u64>(kiss_b200_ctx* c, const u64* keys, u32* pos, u32 N, const So
   if (!cn[0] || h >= sp.D) return 0;
   groups_classify_u64(keys, N, cn[0], gl, c->st);
   sync.read(gl.counters, 4, cn);
+  debug_groups(c, "u64", N, h, cn, gl);
   groups_medium(pos, gl.med, cn[1], sp, h, c->st);
   return cn[2];
 }
@@ -597,6 +628,7 @@ double elapsed_s(kiss_b200_ctx* c, int a, int b) {
 void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* out_host, u64 out_count_hint, Stop stop,
               bool ascii, kiss_b200_timings* t, uint64_t* m_out) {
   cudaStream_t st = c->st;
+  begin_call(c);
   Pool pool(st, &c->arena);
   u8* dS = pool.alloc<u8>(n + 16);
   cudaEvent_t e0, e1, e2, e3;
@@ -795,6 +827,7 @@ int kiss_b200_induce_from_sorted_lms(kiss_b200_ctx* c, const uint8_t* S_host, ui
   if (n == 0) { SA_host[0] = 0; return KISS_B200_OK; }
   return guarded(c, [&] {
     cudaStream_t st = c->st;
+    begin_call(c);
     Pool pool(st, &c->arena);
     u8* dS = pool.alloc<u8>(n + 16);
     CK(cudaMemcpyAsync(dS, S_host, n, cudaMemcpyHostToDevice, st));

@@ -37,81 +37,117 @@ __device__ __forceinline__ bool suffix_less(const SortParams& sp, u32 p, u32 q, 
 }
 
 // ------------------------------------------------------------------------------------------- tiny groups
-// One block looks at 256 consecutive sorted keys (+ a halo).  Every element whose key equals a neighbour's
-// fetches its next 32 bases in parallel (independent gathers, no dependent chains); then the first element of
-// each group of <= TINY_MAX orders the group in shared memory by (next word, deeper words, position).
+// One block looks at 2048 consecutive sorted keys (+ a halo of TINY_MAX).  Three dense phases:
+//  1. every thread compares its 8 consecutive keys (two 16-byte loads, neighbours by shuffle) and queues the
+//     tile-local index of every tied element and of every group head in shared memory;
+//  2. the tied elements (14 % on uniform DNA) fetch position and next 32 bases — the queue makes this phase run
+//     with full warps instead of one active lane in seven;
+//  3. one thread per group head orders its group of <= TINY_MAX by (next word, deeper words, position).
 #define TG_THREADS 256
 #define TG_ITEMS 8
 #define TG_TILE (TG_THREADS * TG_ITEMS)
 template <typename K>
 __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict__ keys, u32* __restrict__ pos, u32 N,
                                                            SortParams sp, u64 h, GroupLists gl) {
-  __shared__ K skey[TG_TILE + TINY_MAX + 2];   // keys[base-1 .. base+TG_TILE+TINY_MAX]
   __shared__ u32 spos[TG_TILE + TINY_MAX];
   __shared__ u64 sw[TG_TILE + TINY_MAX];
-  __shared__ unsigned short sheads[TG_TILE / 2];  // tile-local index of every group head (a group has >= 2 elements)
-  __shared__ u32 s_tied, s_nheads;
-  const u32 tid = threadIdx.x;
-  if (tid == 0) { s_tied = 0; s_nheads = 0; }
-  const u64 base = (u64)blockIdx.x * TG_TILE;
-  for (u32 j = tid; j < TG_TILE + TINY_MAX + 2; j += TG_THREADS) {
-    u64 idx = base + j;  // = element index + 1
-    skey[j] = (idx >= 1 && idx - 1 < N) ? keys[idx - 1] : (K)0;
-  }
+  __shared__ unsigned short stied[TG_TILE + TINY_MAX];  // tile-local indices of the tied elements
+  __shared__ unsigned short sheads[TG_TILE / 2];        // ... of the group heads (a group has >= 2 elements)
+  __shared__ u32 s_tied, s_nheads, s_ntied;
+  const u32 tid = threadIdx.x, lane = tid & 31u;
+  if (tid == 0) { s_tied = 0; s_nheads = 0; s_ntied = 0; }
   __syncthreads();
+  const u32 base = blockIdx.x * TG_TILE;  // (N < 2^32)
   const bool deep = h < sp.D;
   const u64 rem = sp.D - h;
   {
-    // all tied elements of the tile fetch position and next word; loads of one thread are independent.
-    // Group heads (tied with the next element, not with the previous one) are queued for the second phase.
-    u32 p[TG_ITEMS + 1];
-    bool tied[TG_ITEMS + 1];
+    // ---- phase 1: k[i + 1] = key of element t0 + i, k[0] / k[9] the neighbours
+    const u32 t0 = tid * TG_ITEMS, e0 = base + t0;
+    K k[TG_ITEMS + 2];
+    if (e0 + TG_ITEMS <= N && ((uintptr_t)keys & 15) == 0) {
+      constexpr int PER = 16 / sizeof(K);
+      const uint4* src = reinterpret_cast<const uint4*>(keys + e0);
 #pragma unroll
-    for (int it = 0; it <= TG_ITEMS; it++) {
-      u32 t = tid + it * TG_THREADS;
-      u64 e = base + t;
-      tied[it] = false;
-      p[it] = 0;
-      bool head = false;
-      if (t < TG_TILE + TINY_MAX && e < N) {
-        K k = skey[t + 1];
-        bool prev = e > 0 && skey[t] == k, next = e + 1 < N && skey[t + 2] == k;
-        tied[it] = prev || next;
-        head = next && !prev && t < TG_TILE;
-        if (tied[it] && deep) p[it] = pos[e];
-      }
-      u32 hb = __ballot_sync(0xffffffffu, head);
-      if (hb) {
-        u32 lane = tid & 31u, slot = 0;
-        if (lane == 0) slot = atomicAdd(&s_nheads, (u32)__popc(hb));
-        slot = __shfl_sync(0xffffffffu, slot, 0);
-        if (head) sheads[slot + __popc(hb & ((1u << lane) - 1u))] = (unsigned short)t;
-      }
-    }
-    if (deep) {
-#pragma unroll
-      for (int it = 0; it <= TG_ITEMS; it++) {
-        if (tied[it]) {
-          u32 t = tid + it * TG_THREADS;
-          u64 wv = word_at(sp.T, (u64)p[it] + h);
-          if (rem < 32) wv &= ~0ull << (64 - 2 * rem);
-          spos[t] = p[it];
-          sw[t] = wv;
+      for (int q = 0; q < TG_ITEMS / PER; q++) {
+        uint4 v = __ldg(src + q);
+        if (sizeof(K) == 4) {
+          k[1 + 4 * q] = (K)v.x; k[2 + 4 * q] = (K)v.y; k[3 + 4 * q] = (K)v.z; k[4 + 4 * q] = (K)v.w;
+        } else {
+          k[1 + 2 * q] = (K)(((u64)v.y << 32) | v.x); k[2 + 2 * q] = (K)(((u64)v.w << 32) | v.z);
         }
       }
+    } else {
+#pragma unroll
+      for (int i = 0; i < TG_ITEMS; i++) k[1 + i] = e0 + i < N ? keys[e0 + i] : (K)0;
+    }
+    K up = __shfl_up_sync(0xffffffffu, k[TG_ITEMS], 1), dn = __shfl_down_sync(0xffffffffu, k[1], 1);
+    k[0] = lane > 0 ? up : (e0 > 0 && e0 <= N ? keys[e0 - 1] : (K)0);
+    k[TG_ITEMS + 1] = lane < 31 ? dn : (e0 + TG_ITEMS < N ? keys[e0 + TG_ITEMS] : (K)0);
+    u32 tmask = 0, hmask = 0;
+#pragma unroll
+    for (int i = 0; i < TG_ITEMS; i++) {
+      const u32 e = e0 + i;
+      const bool prev = e > 0 && k[i] == k[i + 1], next = e + 1 < N && k[i + 2] == k[i + 1];
+      if (e < N && (prev || next)) tmask |= 1u << i;
+      if (e < N && next && !prev) hmask |= 1u << i;
+    }
+    // the halo: elements past the tile that may belong to a group starting inside it
+    bool halo_tied = false;
+    if (tid < TINY_MAX) {
+      const u32 e = base + TG_TILE + tid;
+      if (e < N) {
+        K kk = keys[e];
+        halo_tied = keys[e - 1] == kk || (e + 1 < N && keys[e + 1] == kk);
+      }
+    }
+    // queue slots: one atomic per warp and queue
+    u32 cnt = (u32)__popc(tmask) + (halo_tied ? 1u : 0u) + ((u32)__popc(hmask) << 16);
+    u32 incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      u32 x = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += x;
+    }
+    u32 wbase = 0;
+    if (lane == 31) {
+      u32 a = atomicAdd(&s_ntied, incl & 0xFFFFu), b = atomicAdd(&s_nheads, incl >> 16);
+      wbase = a | (b << 16);
+    }
+    wbase = __shfl_sync(0xffffffffu, wbase, 31);
+    u32 ex = incl - cnt;
+    u32 ot = (wbase & 0xFFFFu) + (ex & 0xFFFFu), oh = (wbase >> 16) + (ex >> 16);
+#pragma unroll
+    for (int i = 0; i < TG_ITEMS; i++) {
+      if ((tmask >> i) & 1u) stied[ot++] = (unsigned short)(t0 + i);
+      if ((hmask >> i) & 1u) sheads[oh++] = (unsigned short)(t0 + i);
+    }
+    if (halo_tied) stied[ot] = (unsigned short)(TG_TILE + tid);
+  }
+  __syncthreads();
+  // ---- phase 2: dense gathers
+  if (deep) {
+    const u32 ntied = s_ntied;
+    for (u32 j = tid; j < ntied; j += TG_THREADS) {
+      const u32 t = stied[j];
+      const u32 pp = pos[base + t];
+      u64 wv = word_at(sp.T, (u64)pp + h);
+      if (rem < 32) wv &= ~0ull << (64 - 2 * rem);
+      spos[t] = pp;
+      sw[t] = wv;
     }
   }
   __syncthreads();
+  // ---- phase 3: one thread per group
   const u32 nheads = s_nheads;
   for (u32 hi = tid; hi < nheads; hi += TG_THREADS) {
     const u32 t = sheads[hi];
-    const u64 e = base + t;
-    const K k = skey[t + 1];
+    const u32 e = base + t;
+    const K kk = keys[e];
     u32 g = 2;
-    while (g <= TINY_MAX && e + g < N && skey[t + 1 + g] == k) g++;
+    while (g <= TINY_MAX && e + g < N && keys[e + g] == kk) g++;
     if (g > TINY_MAX) {
       u32 idx = atomicAdd(&gl.counters[0], 1u);
-      if (idx < gl.gcap) gl.glist[idx] = (u32)e; else gl.counters[3] = 1;
+      if (idx < gl.gcap) gl.glist[idx] = e; else gl.counters[3] = 1;
       continue;
     }
     atomicAdd(&s_tied, g);
@@ -204,164 +240,286 @@ void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, cudaStre
 }
 
 // ------------------------------------------------------------------------------------------- medium groups
-// One team (a warp for groups <= 64, a block above) refines one group in shared memory by rounds of 32 bases:
-// every element that still shares its segment with another fetches its next word (independent gathers), the
-// group is bitonic-sorted on (segment, word, position) and the segments are split where the words differ.
-// A round whose words are all equal inside their segments skips the sort (long shared prefixes — copies of a
-// repeat — cost one gather per round and nothing else), and the loop ends as soon as every segment is a
-// singleton.  Gathers per element: at most (D - h) / 32, instead of one dependent chain per comparison.
-#define MEDW_MAX 64u
-struct MedView {
-  u64* key;
-  u32* pos;
-  u32* seg;
-};
-
-template <u32 GT>
+// One team (a warp up to 256 elements, a block of 8 warps above) refines one group by PIVOT ROUNDS.  In a round
+// every element that still shares its segment with another is compared with the segment's first element (the
+// pivot) from the segment's depth on: it finds the first base q where it differs (word-wise, independent
+// loads), which side of the pivot it falls on, and its own next 14 bases from q.  ONE 64-bit key
+//     [segment:11 | side:2 | q (descending on the greater side):12 | 14 bases:28 | slot:11]
+// then orders the whole segment: before the pivot by ascending q, after it by descending q, equal (q, bases)
+// classes become new segments at depth q + 14, and everything equal to the pivot up to D is final (the slot
+// field keeps equal keys in their current order, which is ascending text position).  So the long common
+// prefixes of repeat copies are skipped in one step — a group of near-identical copies (tandem arrays: a
+// mutation every 100 bases) is done after one or two rounds, where fixed 20/32-base rounds needed (D - h) / 20
+// full sorts — and a group without common prefix is split by 14 bases per round.
+// Unbounded depth (-k -1 / PREFIX_DOUBLING): q needs 32 bits, so the key carries one base instead of 14 and a
+// suffix that ends inside the comparison is smaller than one that goes on (kiss1_core.hpp:134).
+// The keys live in registers — lane l of warp w holds the slots (w R + r) 32 + l, r < R — and are bitonic-sorted
+// with warp shuffles (partner distance < 32), register swaps (< 32 R) and, in the block team only, shared
+// memory (six steps of 66 at 2048 slots).
+template <int NW>
 __device__ __forceinline__ void team_sync() {
-  if (GT == 32) __syncwarp(); else __syncthreads();
+  if (NW == 1) __syncwarp(); else __syncthreads();
 }
-template <u32 GT>
+template <int NW>
 __device__ __forceinline__ bool team_or(bool v) {
-  if (GT == 32) return __any_sync(0xffffffffu, v);
+  if (NW == 1) return __any_sync(0xffffffffu, v);
   return __syncthreads_or(v);
 }
 
-// element i before element j at depth `off` (both in the same array; padding has seg = 0xFFFFFFFF)
-__device__ __forceinline__ bool med_less(const MedView& m, u32 i, u32 j, u64 off, u64 n) {
-  u32 si = m.seg[i], sj = m.seg[j];
-  if (si != sj) return si < sj;
-  u32 pi = m.pos[i], pj = m.pos[j];
-  bool ei = (u64)pi + off >= n, ej = (u64)pj + off >= n;  // suffix ended: a prefix of the others, hence first
-  if (ei | ej) return (ei && ej) ? pi > pj : ei;
-  u64 ki = m.key[i], kj = m.key[j];
-  if (ki != kj) return ki < kj;
-  return pi < pj;
+#define MK_SLOT_BITS 11
+#define MK_SIDE_SHIFT 51
+#define MK_SEG_SHIFT 53
+#define MK_EQUAL 1ull
+// key of an element against its pivot; `d` = depth both are known equal to
+template <bool UNB>
+__device__ __forceinline__ u64 pivot_key(const SortParams& sp, u32 p, u32 ph, u64 d) {
+  u64 q = d, side = MK_EQUAL;
+  if (!UNB) {
+    while (q < sp.D) {
+      u64 wa = word_at(sp.T, (u64)p + q), wb = word_at(sp.T, (u64)ph + q);
+      const u64 rem = sp.D - q;
+      if (rem < 32) { const u64 mk = ~0ull << (64 - 2 * rem); wa &= mk; wb &= mk; }
+      const u64 x = wa ^ wb;
+      if (x) {
+        q += (u64)(__clzll((long long)x) >> 1);
+        side = wa > wb ? 2ull : 0ull;
+        break;
+      }
+      q += 32;
+    }
+    if (side == MK_EQUAL) return MK_EQUAL << MK_SIDE_SHIFT;
+    u64 b14 = word_at(sp.T, (u64)p + q) >> 36;
+    const u64 rem = sp.D - q;
+    if (rem < 14) b14 &= (~0ull << (28 - 2 * rem)) & 0xFFFFFFFull;
+    const u64 qk = side == 2 ? 4095ull - q : q;
+    return (side << MK_SIDE_SHIFT) | (qk << 39) | (b14 << MK_SLOT_BITS);
+  } else {
+    const u64 lp = sp.n - p, lh = sp.n - ph, lim = lp < lh ? lp : lh;  // bases both suffixes have
+    const u64 L = lim < sp.D ? lim : sp.D;
+    while (q < L) {
+      u64 wa = word_at(sp.T, (u64)p + q), wb = word_at(sp.T, (u64)ph + q);
+      const u64 rem = L - q;
+      if (rem < 32) { const u64 mk = ~0ull << (64 - 2 * rem); wa &= mk; wb &= mk; }
+      const u64 x = wa ^ wb;
+      if (x) {
+        q += (u64)(__clzll((long long)x) >> 1);
+        side = wa > wb ? 2ull : 0ull;
+        break;
+      }
+      q += 32;
+    }
+    u64 b = 0;  // 0 = the suffix ended at q
+    if (side == MK_EQUAL) {
+      if (L == sp.D) return MK_EQUAL << MK_SIDE_SHIFT;  // equal on the whole compared depth: position decides
+      q = lim;  // one is a prefix of the other: the shorter first
+      side = lp < lh ? 0ull : 2ull;
+    }
+    if ((u64)p + q < sp.n) b = 1ull + (word_at(sp.T, (u64)p + q) >> 62);
+    const u64 qk = side == 2 ? 0xFFFFFFFFull - q : q;
+    return (side << MK_SIDE_SHIFT) | (qk << 19) | (b << 16);
+  }
+}
+// depth at which the elements of a class (equal keys above the slot field) are known equal
+template <bool UNB>
+__device__ __forceinline__ u64 class_depth(u64 key) {
+  const u64 side = (key >> MK_SIDE_SHIFT) & 3ull;
+  if (!UNB) {
+    const u64 qk = (key >> 39) & 0xFFFull;
+    return (side == 2 ? 4095ull - qk : qk) + 14ull;
+  }
+  const u64 qk = (key >> 19) & 0xFFFFFFFFull;
+  return (side == 2 ? 0xFFFFFFFFull - qk : qk) + 1ull;
 }
 
-template <u32 GT>
-__device__ __forceinline__ void med_refine(const MedView& m, u32 t, u32 size, u32 P, const SortParams& sp, u64 h,
-                                           u32* s_scan) {
-  for (u64 off = h; off < sp.D; off += 32) {
-    const u64 rem = sp.D - off;
-    const u64 mk = rem < 32 ? ~0ull << (64 - 2 * rem) : ~0ull;
-    bool anyact = false;
-    for (u32 i = t; i < size; i += GT) {
-      u32 sg = m.seg[i];
-      bool act = sg != i || (i + 1 < size && m.seg[i + 1] == sg);
-      u64 key = 0;
-      if (act) {
-        anyact = true;
-        u64 p = m.pos[i];
-        if (p + off < sp.n) key = word_at(sp.T, p + off) & mk;
-      }
-      m.key[i] = key;
-    }
-    if (!team_or<GT>(anyact)) break;
-    bool need = false;
-    for (u32 i = t; i < size; i += GT)
-      if (m.seg[i] != i) {  // not a segment head: same segment as i - 1
-        bool e = (u64)m.pos[i] + off >= sp.n || (u64)m.pos[i - 1] + off >= sp.n;
-        need |= e || m.key[i] != m.key[i - 1];
-      }
-    if (!team_or<GT>(need)) continue;
-    for (u32 k2 = 2; k2 <= P; k2 <<= 1) {
-      for (u32 j = k2 >> 1; j > 0; j >>= 1) {
-        for (u32 i = t; i < P; i += GT) {
-          u32 x = i ^ j;
-          if (x > i) {
-            bool asc = (i & k2) == 0;
-            if (med_less(m, x, i, off, sp.n) == asc) {
-              u64 kk = m.key[i]; m.key[i] = m.key[x]; m.key[x] = kk;
-              u32 pp = m.pos[i]; m.pos[i] = m.pos[x]; m.pos[x] = pp;
-              u32 ss = m.seg[i]; m.seg[i] = m.seg[x]; m.seg[x] = ss;
-            }
+// ascending bitonic sort of the team's NW * R * 32 keys (slot order = (w R + r) 32 + lane)
+template <int NW, int R>
+__device__ __forceinline__ void team_sort(u64 (&x)[R], const u32 w, const u32 lane, u64* sx) {
+  constexpr int P = NW * R * 32;
+#pragma unroll
+  for (int k2 = 2; k2 <= P; k2 <<= 1) {
+#pragma unroll
+    for (int j = k2 >> 1; j > 0; j >>= 1) {
+      if (j < 32) {
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+          const u32 i = ((w * R + r) << 5) | lane;
+          const u64 y = __shfl_xor_sync(0xffffffffu, x[r], j);
+          const bool takemin = ((i & k2) == 0) == ((lane & j) == 0);
+          x[r] = takemin ? (x[r] < y ? x[r] : y) : (x[r] < y ? y : x[r]);
+        }
+      } else if (j < 32 * R) {
+        const int jr = j >> 5;
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+          if ((r & jr) == 0) {
+            const int r2 = r | jr;
+            const u32 i = ((w * R + r) << 5) | lane;
+            const bool asc = (i & k2) == 0;
+            const u64 a = x[r], b = x[r2];
+            const u64 lo = a < b ? a : b, hi = a < b ? b : a;
+            x[r] = asc ? lo : hi;
+            x[r2] = asc ? hi : lo;
           }
         }
-        team_sync<GT>();
-      }
-    }
-    // split the segments: thread t owns E consecutive slots; head index = running maximum
-    const u32 E = P > GT ? P / GT : 1u;
-    const u32 i0 = t * E;
-    u32 heads = 0;
-    for (u32 e = 0; e < E; e++) {
-      u32 i = i0 + e;
-      if (i < size) {
-        bool hd = i == 0 || m.seg[i] != m.seg[i - 1] || m.key[i] != m.key[i - 1] ||
-                  (u64)m.pos[i] + off >= sp.n || (u64)m.pos[i - 1] + off >= sp.n;
-        heads |= (hd ? 1u : 0u) << e;
-      }
-    }
-    u32 v = heads ? i0 + (31u - (u32)__clz((int)heads)) + 1u : 0u;  // last head in my slots, +1
-    u32 incl = v;
+      } else {  // partner in another warp of the block
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      u32 u = __shfl_up_sync(0xffffffffu, incl, o);
-      if ((int)(t & 31u) >= o) incl = max(incl, u);
-    }
-    u32 excl = __shfl_up_sync(0xffffffffu, incl, 1);
-    if ((t & 31u) == 0) excl = 0;
-    if (GT > 32) {
-      if ((t & 31u) == 31u) s_scan[t >> 5] = incl;
-      __syncthreads();
-      for (u32 w = 0; w < (t >> 5); w++) excl = max(excl, s_scan[w]);
-    } else {
-      __syncwarp();
-    }
-    u32 cur = excl;  // head index + 1 of the segment running into my first slot
-    for (u32 e = 0; e < E; e++) {
-      u32 i = i0 + e;
-      if (i < size) {
-        if ((heads >> e) & 1u) cur = i + 1;
-        m.seg[i] = cur - 1;
+        for (int r = 0; r < R; r++) sx[((w * R + r) << 5) | lane] = x[r];
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+          const u32 i = ((w * R + r) << 5) | lane;
+          const u64 y = sx[i ^ (u32)j];
+          const bool takemin = ((i & k2) == 0) == ((i & j) == 0);
+          x[r] = takemin ? (x[r] < y ? x[r] : y) : (x[r] < y ? y : x[r]);
+        }
+        __syncthreads();
       }
     }
-    team_sync<GT>();
   }
 }
 
-// GT = 32: one warp per group of <= MEDW_MAX; GT = 256: one block per larger group
-template <u32 GT>
-__global__ void __launch_bounds__(256) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med, u32 nmed,
-                                                      SortParams sp, u64 h) {
-  constexpr u32 CAP = GT == 32 ? MEDW_MAX : MED_MAX;
-  constexpr u32 TEAMS = 256 / GT;
-  __shared__ u64 s_key[TEAMS * CAP];
-  __shared__ u32 s_pos[TEAMS * CAP];
-  __shared__ u32 s_seg[TEAMS * CAP];
+template <int NW, int R, bool UNB>
+__global__ void __launch_bounds__(256, (R >= 8 ? 2 : 4)) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med,
+                                                                        u32 nmed, SortParams sp, u64 h, u32 size_lo,
+                                                                        u32 size_hi) {
+  constexpr u32 P = NW * R * 32;
+  constexpr u32 TEAMS = NW == 1 ? 8 : 1;
+  static_assert(P <= 2048, "slot field is 11 bits");
+  __shared__ u64 s_key[TEAMS * P];
+  __shared__ u32 s_pos[TEAMS * P];
+  __shared__ u32 s_seg[TEAMS * P];
+  __shared__ u32 s_dep[TEAMS * P];  // depth of the segment, kept at its head slot
   __shared__ u32 s_scan[8];
-  const u32 team = threadIdx.x / GT, t = threadIdx.x % GT;
-  MedView m{s_key + team * CAP, s_pos + team * CAP, s_seg + team * CAP};
+  const u32 lane = threadIdx.x & 31u, wb = threadIdx.x >> 5;
+  const u32 team = NW == 1 ? wb : 0u, w = NW == 1 ? 0u : wb;
+  u64* skey = s_key + team * P;
+  u32* spos = s_pos + team * P;
+  u32* sseg = s_seg + team * P;
+  u32* sdep = s_dep + team * P;
   for (u32 gi = blockIdx.x * TEAMS + team; gi < nmed; gi += gridDim.x * TEAMS) {
     const u32 start = med[2 * gi], size = med[2 * gi + 1];
-    const bool mine = GT == 32 ? size <= MEDW_MAX : size > MEDW_MAX;
-    if (!mine) continue;  // (uniform per team)
-    u32 P = 2;
-    while (P < size) P <<= 1;
-    for (u32 i = t; i < P; i += GT) {
-      m.pos[i] = i < size ? pos[start + i] : KISS_EMPTY;
-      m.seg[i] = i < size ? 0u : 0xFFFFFFFFu;
+    if (size <= size_lo || size > size_hi) continue;  // (uniform per team)
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const u32 i = ((w * R + r) << 5) | lane;
+      spos[i] = i < size ? pos[start + i] : KISS_EMPTY;
+      sseg[i] = i < size ? 0u : 0xFFFFFFFFu;
     }
-    team_sync<GT>();
-    med_refine<GT>(m, t, size, P, sp, h, s_scan);
-    team_sync<GT>();
-    for (u32 i = t; i < size; i += GT) pos[start + i] = m.pos[i];
-    team_sync<GT>();
+    if (threadIdx.x % (NW * 32) == 0) sdep[0] = (u32)h;
+    team_sync<NW>();
+    for (;;) {
+      u64 x[R];
+      bool anyact = false, moved = false;
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const u32 i = ((w * R + r) << 5) | lane;
+        u64 key = ~0ull;
+        if (i < size) {
+          const u32 sg = sseg[i];
+          const bool act = sg != i || (i + 1 < size && sseg[i + 1] == sg);
+          key = 0;
+          if (act) {
+            anyact = true;
+            key = MK_EQUAL << MK_SIDE_SHIFT;
+            if (sg != i) key = pivot_key<UNB>(sp, spos[i], spos[sg], sdep[sg]);
+            moved |= ((key >> MK_SIDE_SHIFT) & 3ull) != MK_EQUAL;
+          }
+          key |= ((u64)sg << MK_SEG_SHIFT) | i;
+        }
+        x[r] = key;
+      }
+      if (!team_or<NW>(anyact)) break;
+      if (team_or<NW>(moved)) {
+        team_sort<NW, R>(x, w, lane, skey);
+        u32 pp[R];
+#pragma unroll
+        for (int r = 0; r < R; r++) pp[r] = x[r] != ~0ull ? spos[(u32)x[r] & 0x7FFu] : KISS_EMPTY;
+        team_sync<NW>();
+#pragma unroll
+        for (int r = 0; r < R; r++) spos[((w * R + r) << 5) | lane] = pp[r];
+      }
+#pragma unroll
+      for (int r = 0; r < R; r++) skey[((w * R + r) << 5) | lane] = x[r];
+      team_sync<NW>();
+      // new segment = running maximum of the head slots; everything equal to its pivot is final (own segment)
+      u32 run = 0;  // head slot + 1 carried into the current row
+      u32 sg[R];
+      bool hdv[R];
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const u32 i = ((w * R + r) << 5) | lane;
+        bool hd = false;
+        if (i < size) {
+          const u64 a = x[r] >> MK_SLOT_BITS;
+          hd = i == 0 || a != (skey[i - 1] >> MK_SLOT_BITS) || ((x[r] >> MK_SIDE_SHIFT) & 3ull) == MK_EQUAL;
+        }
+        hdv[r] = hd;
+        u32 v = hd ? i + 1u : 0u;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          u32 u = __shfl_up_sync(0xffffffffu, v, o);
+          if ((int)lane >= o) v = max(v, u);
+        }
+        v = max(v, run);
+        sg[r] = v;
+        run = __shfl_sync(0xffffffffu, v, 31);
+      }
+      u32 before = 0;
+      if constexpr (NW > 1) {
+        if (lane == 0) s_scan[w] = run;
+        __syncthreads();
+        for (u32 ww = 0; ww < w; ww++) before = max(before, s_scan[ww]);
+      }
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const u32 i = ((w * R + r) << 5) | lane;
+        if (i < size) {
+          sseg[i] = max(sg[r], before) - 1u;
+          if (hdv[r]) {
+            const u64 dd = class_depth<UNB>(x[r]);
+            sdep[i] = (u32)(dd < 0xFFFFFFFFull ? dd : 0xFFFFFFFFull);
+          }
+        }
+      }
+      team_sync<NW>();
+    }
+    team_sync<NW>();
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const u32 i = ((w * R + r) << 5) | lane;
+      if (i < size) pos[start + i] = spos[i];
+    }
+    team_sync<NW>();
   }
+}
+
+template <bool UNB>
+static void groups_medium_launch(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st) {
+  u32 gw = (nmed + 7) / 8, gb = nmed;
+  if (gw > 1048576u) gw = 1048576u;
+  if (gb > 1048576u) gb = 1048576u;
+  // every launch walks the whole list and takes the groups of its size class
+  k_groups_medium<1, 1, UNB><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h, 0u, 32u);
+  CK_LAUNCH();
+  k_groups_medium<1, 2, UNB><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h, 32u, 64u);
+  CK_LAUNCH();
+  k_groups_medium<1, 4, UNB><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h, 64u, 128u);
+  CK_LAUNCH();
+  k_groups_medium<1, 8, UNB><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h, 128u, 256u);
+  CK_LAUNCH();
+  k_groups_medium<8, 2, UNB><<<gb, 256, 0, st>>>(pos, med, nmed, sp, h, 256u, 512u);
+  CK_LAUNCH();
+  k_groups_medium<8, 8, UNB><<<gb, 256, 0, st>>>(pos, med, nmed, sp, h, 512u, 2048u);
+  CK_LAUNCH();
+  g_launches += 6;
 }
 
 void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st) {
   if (!nmed || h >= sp.D) return;
   ProfScope ps(PK_GROUPS_MEDIUM, st);
-  u32 gw = (nmed + 7) / 8, gb = nmed;
-  if (gw > 1048576u) gw = 1048576u;
-  if (gb > 1048576u) gb = 1048576u;
-  k_groups_medium<32><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h);
-  CK_LAUNCH();
-  k_groups_medium<256><<<gb, 256, 0, st>>>(pos, med, nmed, sp, h);
-  CK_LAUNCH();
-  g_launches += 2;
+  // the 12-bit q field of the bounded key holds depths up to 4095
+  if (sp.D == KISS_UNBOUNDED || sp.D > 4000) groups_medium_launch<true>(pos, med, nmed, sp, h, st);
+  else groups_medium_launch<false>(pos, med, nmed, sp, h, st);
 }
 
 // ------------------------------------------------------------------------------------------- big groups
