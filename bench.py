@@ -265,10 +265,11 @@ def run_b200(args):
             a, b = merged.get(key, (0.0, 0))
             merged[key] = (a + tot_ms, b + cnt)
         steps = args.steps
+        n_sort = n_long // world  # LMS suffixes one rank sorts (the sort shards, the rest runs on rank 0)
         alg = {  # algorithmic bytes per launch (SURVEY.md 8(d) per-unit figures x units of one launch)
-            "k_radix_scatter": 2 * (4 + 4) * n_long,            # read + write of (key32, pos32) per pass
-            "k_radix_hist": 4 * n_long,
-            "k_groups_tiny": (4 + 4) * n_long,
+            "k_radix_scatter": 2 * (4 + 4) * n_sort,            # read + write of (key32, pos32) per pass
+            "k_radix_hist": 4 * n_sort,
+            "k_groups_tiny": (4 + 4) * n_sort,
             "k_place/merge_lms": (4 + 4) * n_long,
             "k_pack_codes": n + n // 4,
         }
@@ -296,6 +297,10 @@ def run_b200(args):
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                             "share_of_step": kernels[dom]["ms_per_step"] / ms_step,
                             "launches_per_step": kernels[dom]["launches_per_step"]}
+        if "lms_sort" in stage:  # the stage the north star asks to be reported at 2/4/8 GPUs as well
+            sort_s = stage["lms_sort"] / args.steps
+            line["lms_sort_stage"] = {"ms": sort_s * 1e3, "m": m, "value": m / sort_s / 1e9, "unit": "G LMS suffixes/s",
+                                      "alg_bytes": 16 * m, "frac": 16 * m / sort_s / 1e9 / peak}
         balg = b200_alg_bytes(n, m)
         dev_s = stage.get("total_device", ms * 1e-3) / args.steps
         line["roofline_whole_path"] = {"alg_bytes": balg, "achieved": balg / dev_s / 1e9, "frac": balg / dev_s / 1e9 / peak,

@@ -250,7 +250,7 @@ struct SortStats { u64 tied = 0, rounds = 0; };
 
 // one level of group handling; returns the number of big groups (their list in gl.big)
 template <typename K>
-u32 run_groups(kiss_b200_ctx* c, const K* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl);
+u32 run_groups(kiss_b200_ctx* c, const K* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl, int kind = 0);
 
 // KISS_B200_DEBUG_GROUPS=1: per level, how many groups of each class and the size histogram of the medium ones
 void debug_groups(kiss_b200_ctx* c, const char* tag, u32 N, u64 h, const u32 cn[4], const GroupLists& gl) {
@@ -273,7 +273,7 @@ void debug_groups(kiss_b200_ctx* c, const char* tag, u32 N, u64 h, const u32 cn[
 }
 
 template <>
-u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl) {
+u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl, int) {
   Sync sync{c};
   CK(cudaMemsetAsync(gl.counters, 0, 4 * sizeof(u32), c->st));
   groups_tiny_u32(keys, pos, N, sp, h, gl, c->st);
@@ -281,14 +281,14 @@ u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const So
   sync.read(gl.counters, 4, cn);
   if (cn[3]) throw CudaError(-3, "internal: group list overflow");
   if (!cn[0] || h >= sp.D) return 0;
-  groups_classify_u32(keys, N, cn[0], gl, c->st);
+  groups_classify_u32(keys, N, cn[0], gl, (u32)h, c->st);
   sync.read(gl.counters, 4, cn);
   debug_groups(c, "u32", N, h, cn, gl);
   groups_medium(pos, gl.med, cn[1], sp, h, c->st);
   return cn[2];
 }
 template <>
-u32 run_groups<u64>(kiss_b200_ctx* c, const u64* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl) {
+u32 run_groups<u64>(kiss_b200_ctx* c, const u64* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl, int kind) {
   Sync sync{c};
   CK(cudaMemsetAsync(gl.counters, 0, 4 * sizeof(u32), c->st));
   groups_tiny_u64(keys, pos, N, sp, h, gl, c->st);
@@ -296,7 +296,7 @@ u32 run_groups<u64>(kiss_b200_ctx* c, const u64* keys, u32* pos, u32 N, const So
   sync.read(gl.counters, 4, cn);
   if (cn[3]) throw CudaError(-3, "internal: group list overflow");
   if (!cn[0] || h >= sp.D) return 0;
-  groups_classify_u64(keys, N, cn[0], gl, c->st);
+  groups_classify_u64(keys, N, cn[0], gl, kind, (u32)h, c->st);
   sync.read(gl.counters, 4, cn);
   debug_groups(c, "u64", N, h, cn, gl);
   groups_medium(pos, gl.med, cn[1], sp, h, c->st);
@@ -308,7 +308,7 @@ GroupLists alloc_lists(Pool& pool, u32 N, u64* tied) {
   gl.gcap = N / (TINY_MAX + 1) + 1;
   gl.glist = pool.alloc<u32>(gl.gcap);
   gl.med = pool.alloc<u32>(2ull * gl.gcap);
-  gl.big = pool.alloc<u32>(2ull * (N / (MED_MAX + 1) + 1));
+  gl.big = pool.alloc<u32>(3ull * (N / (MED_MAX + 1) + 1));
   gl.counters = pool.alloc<u32>(4);
   gl.tied = tied;
   return gl;
@@ -342,7 +342,9 @@ void sort_long_lms(kiss_b200_ctx* c, Pool& pool, u32* key, u32* pos, u32 N, cons
   GroupLists gl = alloc_lists(pool, N, tied);
   u32 nbig = run_groups<u32>(c, key, pos, N, sp, h, gl);
 
-  // radix rounds over the big groups
+  // pivot rounds over the big groups (lms_sort.cu): h is now only a lower bound of what a group shares
+  const bool unb = sp.D == KISS_UNBOUNDED || sp.D > 4000;  // the bounded key layout holds depths < 4096
+  const int field_bits = unb ? 37 : 42;
   struct Level { u64 *wkey = nullptr, *wkey_alt = nullptr; u32 *wpos = nullptr, *wpos_alt = nullptr, *wslot = nullptr; u32 total = 0; };
   Level prev;
   const u32* pos_prev = pos;
@@ -362,18 +364,18 @@ void sort_long_lms(kiss_b200_ctx* c, Pool& pool, u32* key, u32* pos, u32 N, cons
     cur.wkey = pool.alloc<u64>(total); cur.wkey_alt = pool.alloc<u64>(total);
     cur.wpos = pool.alloc<u32>(total); cur.wpos_alt = pool.alloc<u32>(total);
     cur.wslot = pool.alloc<u32>(total);
-    big_fill(pos_prev, slot_prev, gl_prev.big, boff, nbig, sp, h, cur.wkey, cur.wpos, cur.wslot, st);
+    big_fill(pos_prev, slot_prev, gl_prev.big, boff, nbig, total, sp, unb, cur.wkey, cur.wpos, cur.wslot, st);
     int nb = 0;
     while (nb < 31 && (1u << nb) < nbig) nb++;
     u64 wt = radix_tiles(total);
     u32* H2 = pool.alloc<u32>(256 * wt);
     u32* part2 = pool.alloc<u32>(scan_partials_len(256 * wt));
-    radix_sort_u64(cur.wkey, cur.wpos, cur.wkey_alt, cur.wpos_alt, total, 0, 33 + nb, H2, part2, st);
+    radix_sort_u64(cur.wkey, cur.wpos, cur.wkey_alt, cur.wpos_alt, total, 0, field_bits + nb, H2, part2, st);
     pool.release(H2); pool.release(part2); pool.release(boff); pool.release(bpart); pool.release(btot);
-    h += 16;
+    h += unb ? 1 : 14;  // every class of equal keys shares at least this much
     GroupLists gl_cur = alloc_lists(pool, total, tied);
     u32 nbig_next = 0;
-    if (h < sp.D) nbig_next = run_groups<u64>(c, cur.wkey, cur.wpos, total, sp, h, gl_cur);
+    if (h < sp.D) nbig_next = run_groups<u64>(c, cur.wkey, cur.wpos, total, sp, h, gl_cur, unb ? 2 : 1);
     big_writeback(pos, cur.wslot, cur.wpos, total, st);
     // retire the previous level
     free_lists(pool, gl_prev);

@@ -102,21 +102,23 @@ struct GroupLists {  // device
   u32* glist;        // starts of groups larger than TINY_MAX
   u32 gcap;
   u32* med;          // (start, size) pairs
-  u32* big;          // (start, size) pairs
+  u32* big;          // (start, size, known common depth) triples
   u32* counters;     // [0] = #glist, [1] = #med, [2] = #big, [3] = overflow flag
   u64* tied;         // statistics: elements found in groups
 };
 void groups_tiny_u32(const u32* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st);
 void groups_tiny_u64(const u64* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st);
-void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st);
-void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st);
+void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, u32 h, cudaStream_t st);
+// kind: 1 / 2 = pivot keys of the big path, bounded / unbounded layout (the group depth is decoded from the key)
+void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, int kind, u32 h, cudaStream_t st);
 void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st);
-// sizes[g] = big[2g+1]
+// sizes[g] = big[3g+1]
 void big_sizes(const u32* big, u32 nbig, u32* sizes, cudaStream_t st);
-// worklist of the big groups: wkey = gid << 33 | (1 + next 16 bases at depth h, or 0 when the suffix has
-// ended), wpos = suffix, wslot = slot in the main array
-void big_fill(const u32* pos_prev, const u32* slot_prev, const u32* big, const u32* boff, u32 nbig, SortParams sp,
-              u64 h, u64* wkey, u32* wpos, u32* wslot, cudaStream_t st);
+// worklist of the big groups (one pivot round, see lms_sort.cu): wkey = [group | side | q | bases] against the
+// group's first element, wpos = suffix, wslot = slot in the main array.  Key width below the group id: 42 bits
+// (bounded layout), 37 bits (unbounded layout)
+void big_fill(const u32* pos_prev, const u32* slot_prev, const u32* big, const u32* boff, u32 nbig, u32 total,
+              SortParams sp, bool unbounded_layout, u64* wkey, u32* wpos, u32* wslot, cudaStream_t st);
 void big_writeback(u32* pos_main, const u32* wslot, const u32* wpos, u32 total, cudaStream_t st);
 
 // key[i] = first 16 bases of suffix pos[i]

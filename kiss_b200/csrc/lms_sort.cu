@@ -182,8 +182,24 @@ __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict_
   if (tid == 0 && s_tied) atomicAdd(gl.tied, (u64)s_tied);
 }
 
+// depth (bases) the elements of a group of equal composite keys are known to share; `kind`: 0 = plain keys (the
+// level's depth h), 1 / 2 = pivot keys of the big path in the bounded / unbounded layout (see k_big_fill)
+__device__ __forceinline__ u32 group_depth(u64 key, int kind, u32 h) {
+  if (kind == 1) {
+    const u64 side = (key >> 40) & 3ull, qk = (key >> 28) & 0xFFFull;
+    return (u32)((side == 2 ? 4095ull - qk : qk) + 14ull);
+  }
+  if (kind == 2) {
+    const u64 side = (key >> 35) & 3ull, qk = (key >> 3) & 0xFFFFFFFFull;
+    const u64 d = (side == 2 ? 0xFFFFFFFFull - qk : qk) + 1ull;
+    return (u32)(d < 0xFFFFFFFFull ? d : 0xFFFFFFFFull);
+  }
+  return h;
+}
+
 template <typename K>
-__global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ keys, u32 N, u32 ng, GroupLists gl) {
+__global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ keys, u32 N, u32 ng, GroupLists gl,
+                                                        int kind, u32 h) {
   u32 g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= ng) return;
   u64 start = gl.glist[g];
@@ -209,8 +225,9 @@ __global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ k
     gl.med[2 * j + 1] = size;
   } else {
     u32 j = atomicAdd(&gl.counters[2], 1u);
-    gl.big[2 * j] = (u32)start;
-    gl.big[2 * j + 1] = size;
+    gl.big[3 * j] = (u32)start;
+    gl.big[3 * j + 1] = size;
+    gl.big[3 * j + 2] = group_depth((u64)k, kind, h);
   }
 }
 
@@ -226,16 +243,16 @@ void groups_tiny_u64(const u64* keys, u32* pos, u32 N, SortParams sp, u64 h, Gro
   k_groups_tiny<u64><<<(N + TG_TILE - 1) / TG_TILE, TG_THREADS, 0, st>>>(keys, pos, N, sp, h, gl);
   CK_LAUNCH(); g_launches++;
 }
-void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st) {
+void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, u32 h, cudaStream_t st) {
   if (!ng) return;
   ProfScope ps(PK_GROUPS_OTHER, st);
-  k_groups_classify<u32><<<(ng + 127) / 128, 128, 0, st>>>(keys, N, ng, gl);
+  k_groups_classify<u32><<<(ng + 127) / 128, 128, 0, st>>>(keys, N, ng, gl, 0, h);
   CK_LAUNCH(); g_launches++;
 }
-void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, cudaStream_t st) {
+void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, int kind, u32 h, cudaStream_t st) {
   if (!ng) return;
   ProfScope ps(PK_GROUPS_OTHER, st);
-  k_groups_classify<u64><<<(ng + 127) / 128, 128, 0, st>>>(keys, N, ng, gl);
+  k_groups_classify<u64><<<(ng + 127) / 128, 128, 0, st>>>(keys, N, ng, gl, kind, h);
   CK_LAUNCH(); g_launches++;
 }
 
@@ -523,9 +540,16 @@ void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cud
 }
 
 // ------------------------------------------------------------------------------------------- big groups
+// Groups larger than a block's shared memory go through PIVOT ROUNDS in global memory: every element of a big
+// group is compared with the group's first element from the group's known depth on (pivot_key above: first
+// differing base q, side, next 14 bases), the composite key [group | side | q | bases] is sorted with the stable
+// LSD radix sort, and the classes of equal keys are the groups of the next level (tiny / medium / big again).
+// Elements equal to their pivot up to D get unique keys (their index in the group): they are final and must not
+// group again.  Long common prefixes are skipped in one round; the first version advanced 16 bases per round
+// (23 rounds at k = 256 on repeat-rich text).
 __global__ void k_big_sizes(const u32* __restrict__ big, u32 nbig, u32* __restrict__ sizes) {
   u32 g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g < nbig) sizes[g] = big[2 * g + 1];
+  if (g < nbig) sizes[g] = big[3 * g + 1];
 }
 void big_sizes(const u32* big, u32 nbig, u32* sizes, cudaStream_t st) {
   if (!nbig) return;
@@ -534,36 +558,41 @@ void big_sizes(const u32* big, u32 nbig, u32* sizes, cudaStream_t st) {
   CK_LAUNCH(); g_launches++;
 }
 
+// one thread per element of the work list; boff = exclusive scan of the group sizes
+template <bool UNB>
 __global__ void __launch_bounds__(256) k_big_fill(const u32* __restrict__ pos_prev, const u32* __restrict__ slot_prev,
                                                  const u32* __restrict__ big, const u32* __restrict__ boff, u32 nbig,
-                                                 SortParams sp, u64 h, u64* __restrict__ wkey, u32* __restrict__ wpos,
-                                                 u32* __restrict__ wslot) {
-  for (u32 g = blockIdx.x; g < nbig; g += gridDim.x) {
-    u32 start = big[2 * g], size = big[2 * g + 1], off = boff[g];
-    for (u32 j = threadIdx.x; j < size; j += blockDim.x) {
-      u32 p = pos_prev[start + j];
-      u64 c33;
-      if ((u64)p + h >= sp.n) {
-        c33 = 0;  // the suffix ended: it is a proper prefix of the others in its group, hence first
-      } else {
-        u32 c = (u32)(word_at(sp.T, (u64)p + h) >> 32);
-        u64 rem = sp.D - h;
-        if (rem < 16) c &= ~0u << (32 - 2 * (u32)rem);
-        c33 = 1ull + c;
-      }
-      wkey[off + j] = ((u64)g << 33) | c33;
-      wpos[off + j] = p;
-      wslot[off + j] = slot_prev ? slot_prev[start + j] : start + j;
-    }
+                                                 u32 total, SortParams sp, u64* __restrict__ wkey,
+                                                 u32* __restrict__ wpos, u32* __restrict__ wslot) {
+  constexpr int SIDE_SHIFT = UNB ? 35 : 40, G_SHIFT = UNB ? 37 : 42, DROP = UNB ? 16 : 11;
+  const u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  u32 lo = 0, hi = nbig;  // last group with boff <= t
+  while (hi - lo > 1) {
+    u32 mid = lo + (hi - lo) / 2;
+    if (boff[mid] <= t) lo = mid; else hi = mid;
   }
+  const u32 g = lo, start = big[3 * g], depth = big[3 * g + 2], j = t - boff[g];
+  const u32 p = pos_prev[start + j];
+  u64 f = (MK_EQUAL << SIDE_SHIFT) | j;  // the pivot itself, and everything equal to it: unique, in order
+  if (j) {
+    const u64 key = pivot_key<UNB>(sp, p, pos_prev[start], depth) >> DROP;
+    if (((key >> SIDE_SHIFT) & 3ull) != MK_EQUAL) f = key;
+  }
+  wkey[t] = ((u64)g << G_SHIFT) | f;
+  wpos[t] = p;
+  wslot[t] = slot_prev ? slot_prev[start + j] : start + j;
 }
 
-void big_fill(const u32* pos_prev, const u32* slot_prev, const u32* big, const u32* boff, u32 nbig, SortParams sp,
-              u64 h, u64* wkey, u32* wpos, u32* wslot, cudaStream_t st) {
-  if (!nbig) return;
+void big_fill(const u32* pos_prev, const u32* slot_prev, const u32* big, const u32* boff, u32 nbig, u32 total,
+              SortParams sp, bool unbounded_layout, u64* wkey, u32* wpos, u32* wslot, cudaStream_t st) {
+  if (!nbig || !total) return;
   ProfScope ps(PK_GROUPS_OTHER, st);
-  u32 grid = nbig < 65535u * 16u ? nbig : 65535u * 16u;
-  k_big_fill<<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, sp, h, wkey, wpos, wslot);
+  u32 grid = (total + 255) / 256;
+  if (unbounded_layout)
+    k_big_fill<true><<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, total, sp, wkey, wpos, wslot);
+  else
+    k_big_fill<false><<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, total, sp, wkey, wpos, wslot);
   CK_LAUNCH(); g_launches++;
 }
 

@@ -24,6 +24,9 @@ CONFIGS = {
     "c3small": dict(n=200_000_000, seed=3, kind="chm13", k=256),
     "c3": dict(n=3_117_292_070, seed=3, kind="chm13", k=256),         # README.md:101
     "c3k32": dict(n=500_000_000, seed=3, kind="chm13", k=32),
+    # one 1 Mbp unit x 512 with 0.1 % substitutions per copy, -k -1 -s PREFIX_DOUBLING (full SA)
+    "c4": dict(n=536_870_912, seed=4, kind="replicated", k=0xFFFFFFFF, algo="PREFIX_DOUBLING"),
+    "c4small": dict(n=67_108_864, seed=4, kind="replicated", k=0xFFFFFFFF, algo="PREFIX_DOUBLING"),
 }
 
 
@@ -36,6 +39,13 @@ def text(ctx, cfg):
     torch.cuda.empty_cache()
     if cfg["kind"] == "chm13":
         S = tg.chm13_like(cfg["seed"], n, base=S)
+    if cfg["kind"] == "replicated":
+        unit = 1 << 20
+        rng = np.random.default_rng(cfg["seed"])
+        S = np.tile(S[:unit], n // unit + 1)[:n].copy()
+        kk = rng.binomial(n, 0.001)
+        p = rng.integers(0, n, kk)
+        S[p] = (S[p] + rng.integers(1, 4, kk).astype(np.uint8)) & 3
     return S
 
 
@@ -58,7 +68,9 @@ def main():
         S = text(ctx, cfg)
         n = S.size
         t0 = time.perf_counter()
-        sa = ctx.suffix_array_dna(S, cfg["k"])
+        algo_name = cfg.get("algo", "PARALLEL_SORTING")
+        algo = getattr(kiss_b200, algo_name)
+        sa = ctx.suffix_array_dna(S, cfg["k"], algo=algo)
         t_gpu = time.perf_counter() - t0
         tm = ctx.last_timings
         out = dict(config=name, **cfg, m=tm["m"], gpu_host_call_s=t_gpu, gpu_device_s=tm["total_device"],
@@ -66,14 +78,15 @@ def main():
                    waves=[tm["waves_L"], tm["waves_S"]], sa0_is_n=bool(int(sa[0]) == n), permutation=is_permutation(sa, n))
         if profile:  # second call with CUDA events around every launch (kernel class -> [ms, launches])
             ctx.profile_enable(True)
-            ctx.suffix_array_dna(S, cfg["k"])
+            ctx.suffix_array_dna(S, cfg["k"], algo=algo)
             out["kernels"] = {k: [round(v[0], 3), v[1]] for k, v in ctx.profile().items()}
             out["profiled_stages_s"] = {k: ctx.last_timings[k] for k in ("get_lms", "lms_sort", "put_lms", "induce")}
             ctx.profile_enable(False)
         if ol.have_ref() and "--noref" not in args:
             ref = np.empty(n + 1, np.uint32)
             threads = os.cpu_count()
-            sec = ol.ref().ref_kiss1_suffix_array_dna(S.ctypes.data, n, cfg["k"], threads, ref.ctypes.data)
+            fn = ol.ref().ref_kiss2_suffix_array_dna if algo_name == "PREFIX_DOUBLING" else ol.ref().ref_kiss1_suffix_array_dna
+            sec = fn(S.ctypes.data, n, cfg["k"], threads, ref.ctypes.data)
             out.update(reference_s=sec, reference_threads=threads, bit_exact=bool(np.array_equal(sa, ref)),
                        speedup_host_call=sec / t_gpu, speedup_device=sec / tm["total_device"])
             if not out["bit_exact"]:
