@@ -720,6 +720,7 @@ int kiss_b200_create(kiss_b200_ctx** out, int device) {
     u64 thr = ~0ull;  // keep freed scratch cached in the pool between calls
     CK(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &thr));
     radix_init();
+    wave_init();
   } catch (const CudaError& err) {
     g_last_error = err.what();
     delete c;

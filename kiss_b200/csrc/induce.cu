@@ -91,9 +91,10 @@ void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, u32* C
 // when a context runs out (CTX == 1): once per LMS suffix and once per 15 steps of a chain, instead of once
 // per scanned entry as in the reference's prepare loops (kiss_common.hpp:63-113, 278-325).
 
-#define WAVE_THREADS 256
+#define WAVE_THREADS (WAVE_TILE / 16)
 #define WAVE_ITEMS 16
-#define WAVE_WARPS 8
+#define WAVE_WARPS (WAVE_THREADS / 32)
+#define WAVE_MINB (WAVE_TILE == 4096 ? 4 : WAVE_TILE == 8192 ? 2 : 1)
 
 struct WaveArgs {
   u32* SA;
@@ -116,8 +117,20 @@ struct WaveArgs {
 // branch-free batched gathers (no gain: the LMS waves are bound by random DRAM accesses, not by latency);
 // fetching the LMS contexts up front in 2-8 sweeps, each restricted to an L2-sized slice of the text
 // (2 sweeps: 3.8 ms + 1.7 ms of gather-free LMS waves against 5.9 ms with the gathers in the waves — a wash).
+// (L2 fetch-size hints on the gather loads — ld.global.nc.L2::64B / 128B / 256B — measured no different)
+__device__ __forceinline__ u64 ldg_gather(const u64* p) { return __ldg(p); }
+// the 32 bases from p on, of which the caller uses the first 15: the second word is fetched only when they
+// straddle the word boundary
+__device__ __forceinline__ u64 word_at_gather(const u64* __restrict__ T, u64 p) {
+  u64 i = p >> 5;
+  u32 s = (u32)(p & 31) * 2;
+  u64 a = ldg_gather(T + i);
+  if (s <= 34) return a << s;
+  u64 b = ldg_gather(T + i + 1);
+  return (a << s) | (b >> (64 - s));
+}
 __device__ __forceinline__ u32 ctx_gather(const u64* __restrict__ T, u32 v) {
-  if (v >= 15) return (1u << 30) | (u32)(word_at(T, (u64)v - 15) >> 34);
+  if (v >= 15) return (1u << 30) | (u32)(word_at_gather(T, (u64)v - 15) >> 34);
   if (v == 0) return 1u;
   return (1u << (2 * v)) | (u32)(__ldg(T) >> (64 - 2 * v));
 }
@@ -140,6 +153,7 @@ struct WaveSmem {
 // their per-symbol counts in a 64-bit status word [epoch:30 | flag:2 | count:32] and look back over their
 // predecessors' words for the exclusive prefix.  The epoch (one per wave) makes stale words of earlier waves
 // read as "empty", so the status array is zeroed once per call, not per wave.
+#define WF_LB 1  // look-back window = 32 * WF_LB tiles (4: every lane polling 4 predecessors measured 15 % slower)
 #define WF_AGG 1ull
 #define WF_INCL 2ull
 __device__ __forceinline__ u64 wf_pack(u32 epoch, u64 flag, u32 v) { return ((u64)epoch << 34) | (flag << 32) | v; }
@@ -258,25 +272,39 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
       long long base = (long long)tile - 1;
       u32 spins = 0;
       for (;;) {
-        long long t = base - lane;
-        u64 word = 0;
+        u64 word[WF_LB];
         bool ready;
         do {
-          word = (t >= 0) ? st[(u64)t * 4 + s] : wf_pack(epoch, WF_INCL, 0);
-          ready = (u32)(word >> 34) == epoch && ((word >> 32) & 3ull) != 0;
-          if (++spins > (1u << 24)) { state[1] = 1u; ready = true; word = wf_pack(epoch, WF_INCL, 0); }  // watchdog: never hang
-        } while (!__all_sync(0xffffffffu, ready));
-        u32 inclm = __ballot_sync(0xffffffffu, ((word >> 32) & 3ull) == WF_INCL);
-        u32 v = (u32)word;
-        if (inclm) {
-          u32 first = __ffs(inclm) - 1;  // nearest predecessor holding an inclusive prefix
-          if (lane > first) v = 0;
-        }
+          ready = true;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        excl += v;
-        if (inclm) break;
-        base -= 32;
+          for (int k = 0; k < WF_LB; k++) {
+            const long long t = base - lane - 32 * k;
+            word[k] = (t >= 0) ? st[(u64)t * 4 + s] : wf_pack(epoch, WF_INCL, 0);
+            ready &= (u32)(word[k] >> 34) == epoch && ((word[k] >> 32) & 3ull) != 0;
+          }
+          if (++spins > (1u << 24)) {  // watchdog: never hang
+            state[1] = 1u;
+            ready = true;
+#pragma unroll
+            for (int k = 0; k < WF_LB; k++) word[k] = wf_pack(epoch, WF_INCL, 0);
+          }
+        } while (!__all_sync(0xffffffffu, ready));
+        bool done = false;
+#pragma unroll
+        for (int k = 0; k < WF_LB; k++) {
+          if (!done) {  // (warp-uniform)
+            const u32 inclm = __ballot_sync(0xffffffffu, ((word[k] >> 32) & 3ull) == WF_INCL);
+            u32 v = (u32)word[k];
+            if (inclm) {
+              const u32 first = __ffs(inclm) - 1;  // nearest predecessor holding an inclusive prefix
+              if (lane > first) v = 0;
+              done = true;
+            }
+            excl += __reduce_add_sync(0xffffffffu, v);
+          }
+        }
+        if (done) break;
+        base -= 32 * WF_LB;
       }
       if (lane == 0) st[(u64)tile * 4 + s] = wf_pack(epoch, WF_INCL, excl + mine);
     }
@@ -320,7 +348,8 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
 template <bool DOWN, int MINB>
 __global__ void __launch_bounds__(WAVE_THREADS, MINB) k_wave_fused(WaveArgs a, u64* __restrict__ status, u32* __restrict__ state,
                                                                   u32 tile_base, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
-  __shared__ WaveShared sh;
+  extern __shared__ __align__(16) unsigned char wave_smem[];
+  WaveShared& sh = *reinterpret_cast<WaveShared*>(wave_smem);
   if (threadIdx.x == 0) sh.tile = atomicAdd(&state[0], 1u) - tile_base;
   __syncthreads();
   wave_tile<DOWN, true>(a, sh.tile, sh, status, state, ntiles, epoch, tot);
@@ -334,7 +363,8 @@ __global__ void __launch_bounds__(WAVE_THREADS, MINB) k_wave_fused(WaveArgs a, u
 template <bool DOWN>
 __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 bucket, u64 p0, u32 max_waves,
                                                            u64* __restrict__ out) {
-  __shared__ WaveShared sh;
+  extern __shared__ __align__(16) unsigned char wave_smem[];
+  WaveShared& sh = *reinterpret_cast<WaveShared*>(wave_smem);
   __shared__ u32 s_tot[4];
   if (threadIdx.x == 0) {
     for (int s = 0; s < 4; s++) sh.cur[s] = a0.cur[s];
@@ -375,8 +405,8 @@ u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, 
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
   {
     ProfScope ps(PK_WAVE_SMALL, st);
-    if (down) k_wave_tail<true><<<1, WAVE_THREADS, 0, st>>>(a, bucket, *p, 1u << 20, ws.tail_dev);
-    else k_wave_tail<false><<<1, WAVE_THREADS, 0, st>>>(a, bucket, *p, 1u << 20, ws.tail_dev);
+    if (down) k_wave_tail<true><<<1, WAVE_THREADS, sizeof(WaveShared), st>>>(a, bucket, *p, 1u << 20, ws.tail_dev);
+    else k_wave_tail<false><<<1, WAVE_THREADS, sizeof(WaveShared), st>>>(a, bucket, *p, 1u << 20, ws.tail_dev);
     CK_LAUNCH(); g_launches++;
   }
   CK(cudaMemcpyAsync(ws.tail_host, ws.tail_dev, 6 * sizeof(u64), cudaMemcpyDeviceToHost, st));
@@ -384,6 +414,14 @@ u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, 
   *p = ws.tail_host[0];
   for (int s = 0; s < 4; s++) cur[s] = ws.tail_host[1 + s];
   return (u32)ws.tail_host[5];
+}
+
+void wave_init() {
+  const int bytes = (int)sizeof(WaveShared);
+  CK(cudaFuncSetAttribute(k_wave_fused<true, WAVE_MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  CK(cudaFuncSetAttribute(k_wave_fused<false, WAVE_MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  CK(cudaFuncSetAttribute(k_wave_tail<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  CK(cudaFuncSetAttribute(k_wave_tail<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
 }
 
 void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, u64 lo, u64 len, bool down, u32 symmask,
@@ -404,8 +442,8 @@ void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, u64 lo, u6
     // its tile starts makes every later tile wait in the look-back)
     const u32 ep = ++*ws.epoch;
     // (5 resident blocks per SM, 48 registers with a small spill, measured 1 ms slower than 4)
-    if (down) k_wave_fused<true, 4><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_dev);
-    else k_wave_fused<false, 4><<<ntiles, WAVE_THREADS, 0, st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_dev);
+    if (down) k_wave_fused<true, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_dev);
+    else k_wave_fused<false, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_dev);
     CK_LAUNCH(); g_launches++;
     *ws.tile_base += ntiles;
   }

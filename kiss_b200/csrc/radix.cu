@@ -346,10 +346,10 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
         peers = __ballot_sync(0xffffffffu, valid);
 #pragma unroll
         for (int b = 0; b < 8; b++) {
-          const bool bit = (d & (1u << b)) != 0;
-          const u32 bal = __ballot_sync(0xffffffffu, bit);
-          const u32 m = bit ? 0xffffffffu : 0u;
-          peers &= ~(bal ^ m);
+          int m;  // 0 or -1: bit b of the digit, sign-extended (one bit-field extract)
+          asm("bfe.s32 %0, %1, %2, 1;" : "=r"(m) : "r"(d), "r"(b));
+          const u32 bal = __ballot_sync(0xffffffffu, m != 0);
+          peers &= ~(bal ^ (u32)m);
         }
       }
       // every lane reads its digit's running count (a broadcast for equal digits); the lowest peer bumps it

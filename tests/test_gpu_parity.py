@@ -28,6 +28,14 @@ CASES = [
     ("periodic_CA", lambda: np.concatenate([tg.periodic(5000, [1, 0]), tg.uniform(14, 700)])),
     ("periodic_big", lambda: np.concatenate([tg.periodic(40_000, [2, 0, 1]), tg.uniform(15, 900)])),
     ("homopolymers", lambda: tg.tandem(16, 120_000, arrays=12, max_unit=1, max_len=9000)),
+    # tie groups of near-identical copies: 40 (warp team), 200 (warp team, 8 slots per lane), 1500 (block team),
+    # 5000 (pivot rounds in global memory); sparse and dense mutations, exact copies
+    ("copies40", lambda: tg.near_identical_copies(17, 700, 40, 0.01)),
+    ("copies200", lambda: tg.near_identical_copies(18, 500, 200, 0.004)),
+    ("copies1500", lambda: tg.near_identical_copies(19, 150, 1500, 0.005)),
+    ("copies5000", lambda: tg.near_identical_copies(20, 60, 5000, 0.003)),
+    ("copies5000_dense", lambda: tg.near_identical_copies(21, 90, 5000, 0.08)),
+    ("copies3000_exact", lambda: tg.near_identical_copies(22, 70, 3000, 0.0)),
 ]
 IDS = [c[0] for c in CASES]
 

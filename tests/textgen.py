@@ -160,3 +160,17 @@ def chm13_like(seed, n, base=None, families=64, tandem_arrays=2000, segdups=500,
         p = int(rng.integers(0, lim - L))
         S[p:p + L] = int(rng.integers(0, 4))
     return S
+
+
+def near_identical_copies(seed, unit_len, copies, rate, tail=600):
+    """`copies` copies of one random unit, each base substituted with probability `rate`, then `tail` uniform bases:
+    LMS suffixes at the same offset of every copy share long prefixes (tie groups of size `copies`: a warp team up
+    to 256, a block team up to 2048, the global pivot rounds above) and differ only where a copy was mutated."""
+    rng = np.random.default_rng(seed)
+    unit = rng.integers(0, 4, unit_len).astype(np.uint8)
+    S = np.tile(unit, copies)
+    k = rng.binomial(S.size, rate)
+    if k:
+        p = rng.integers(0, S.size, k)
+        S[p] = (S[p] + rng.integers(1, 4, k).astype(np.uint8)) & 3
+    return np.concatenate([S, uniform(seed + 1, tail)])
