@@ -163,8 +163,8 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------ B200 arm
-# mean DRAM bytes (read + write) per launch at the 1 Gbp workload, ncu --set full (profiles/r1_v6_dram_per_kernel.txt)
-NCU_DRAM_BYTES_PER_LAUNCH = {"k_wave_fused": 0.8955e9, "k_radix_scatter": 5.2185e9, "k_groups_tiny": 6.7629e9}
+# mean DRAM bytes (read + write) per launch at the 1 Gbp workload, ncu --set full (profiles/r1_final_launches_1gbp.txt)
+NCU_DRAM_BYTES_PER_LAUNCH = {"k_wave_fused": 46.658e9 / 58, "k_radix_scatter": 5.4073e9, "k_groups_tiny": 6.7628e9}
 
 
 def b200_alg_bytes(n, m):

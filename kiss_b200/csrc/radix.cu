@@ -136,18 +136,20 @@ void scan_excl_u32(u32* data, u64 N, u32* partials, u32* total_dev, cudaStream_t
 }
 
 // =================================================================================== radix
-#define RADIX_THREADS 256
-#define RADIX_ITEMS 16
+#ifndef RADIX_THREADS
+#define RADIX_THREADS 256  // 512 threads x 8 keys (2 blocks/SM, 32 warps) measured slower: scatter 7.86 vs 7.50 ms, hist 1.24 vs 1.00 ms
+#endif
 #define RADIX_TILE 4096
-#define RADIX_WARPS 8
+#define RADIX_ITEMS (RADIX_TILE / RADIX_THREADS)
+#define RADIX_WARPS (RADIX_THREADS / 32)
+#define RADIX_MINB32 (RADIX_THREADS == 256 ? 3 : 2)
 
 template <typename K>
 __global__ void __launch_bounds__(RADIX_THREADS) k_radix_hist(const K* __restrict__ kin, u32 N, int shift, u32 mask,
                                                              u32* __restrict__ H, u32 ntiles) {
   __shared__ u32 hist[RADIX_WARPS][256];  // one sub-histogram per warp keeps shared-memory atomics uncontended
   const u32 tid = threadIdx.x, tile = blockIdx.x, w = tid >> 5;
-#pragma unroll
-  for (int ww = 0; ww < RADIX_WARPS; ww++) hist[ww][tid] = 0;
+  for (u32 i = tid; i < RADIX_WARPS * 256; i += RADIX_THREADS) (&hist[0][0])[i] = 0;
   __syncthreads();
   const u32 tile_base = tile * RADIX_TILE;
   K keys[RADIX_ITEMS];
@@ -162,14 +164,16 @@ __global__ void __launch_bounds__(RADIX_THREADS) k_radix_hist(const K* __restric
     if (e < N) atomicAdd(&hist[w][(u32)(keys[i] >> shift) & mask], 1u);
   }
   __syncthreads();
-  u32 t = 0;
+  if (tid < 256) {
+    u32 t = 0;
 #pragma unroll
-  for (int ww = 0; ww < RADIX_WARPS; ww++) t += hist[ww][tid];
-  H[(u64)tid * ntiles + tile] = t;
+    for (int ww = 0; ww < RADIX_WARPS; ww++) t += hist[ww][tid];
+    H[(u64)tid * ntiles + tile] = t;
+  }
 }
 
 template <typename K>
-__global__ void __launch_bounds__(RADIX_THREADS, 3) k_radix_scatter(const K* __restrict__ kin, const u32* __restrict__ vin,
+__global__ void __launch_bounds__(RADIX_THREADS, RADIX_MINB32) k_radix_scatter(const K* __restrict__ kin, const u32* __restrict__ vin,
                                                                 K* __restrict__ kout, u32* __restrict__ vout, u32 N,
                                                                 int shift, u32 mask, const u32* __restrict__ H,
                                                                 u32 ntiles) {
@@ -198,7 +202,7 @@ __global__ void __launch_bounds__(RADIX_THREADS, 3) k_radix_scatter(const K* __r
     u32 e = wbase + r * 32 + lane;
     keys[r] = e < N ? kin[e] : (K)0;
   }
-  const u32 hbase = H[(u64)tid * ntiles + tile];
+  const u32 hbase = tid < 256 ? H[(u64)tid * ntiles + tile] : 0u;
 #pragma unroll
   for (int r = 0; r < RADIX_ITEMS; r++) {
     u32 e = wbase + r * 32 + lane;
@@ -224,16 +228,20 @@ __global__ void __launch_bounds__(RADIX_THREADS, 3) k_radix_scatter(const K* __r
   __syncthreads();
   {
     u32 run = 0;
+    if (tid < 256) {
 #pragma unroll
-    for (int ww = 0; ww < RADIX_WARPS; ww++) {
-      u32 c = wcnt[ww * 256 + tid];
-      wcnt[ww * 256 + tid] = run;
-      run += c;
+      for (int ww = 0; ww < RADIX_WARPS; ww++) {
+        u32 c = wcnt[ww * 256 + tid];
+        wcnt[ww * 256 + tid] = run;
+        run += c;
+      }
     }
     u32 tot;
     u32 ex = block_excl_scan(run, ws, tot);
-    texcl[tid] = ex;
-    dbase[tid] = hbase - ex;
+    if (tid < 256) {
+      texcl[tid] = ex;
+      dbase[tid] = hbase - ex;
+    }
   }
   __syncthreads();
 #pragma unroll
@@ -281,7 +289,7 @@ __device__ __forceinline__ void tile_fetch(E* sdst, const E* __restrict__ g, u32
 }
 
 template <typename K, int NMATCH>
-__global__ void __launch_bounds__(RADIX_THREADS, (sizeof(K) == 4 ? 3 : 2))
+__global__ void __launch_bounds__(RADIX_THREADS, (sizeof(K) == 4 ? RADIX_MINB32 : (RADIX_THREADS == 256 ? 2 : 1)))
 k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __restrict__ kout, u32* __restrict__ vout,
                   u32 N, int shift, u32 mask, const u32* __restrict__ H, u32 ntiles) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -304,7 +312,7 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
     tile_fetch<u32>(vbuf0, vin, tb, nv);
     asm volatile("cp.async.commit_group;\n" ::);
   }
-  u32 hb_next = H[(u64)tid * ntiles + tile];
+  u32 hb_next = tid < 256 ? H[(u64)tid * ntiles + tile] : 0u;
   for (u32 it = 0; tile < ntiles; tile += gridDim.x, it++) {
     K* kb = (it & 1) ? kbuf1 : kbuf0;
     u32* vb = (it & 1) ? vbuf1 : vbuf0;
@@ -330,7 +338,7 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
         u32 tb = next * RADIX_TILE, nv = min((u32)RADIX_TILE, N - tb);
         tile_fetch<K>((it & 1) ? kbuf0 : kbuf1, kin, tb, nv);
         tile_fetch<u32>((it & 1) ? vbuf0 : vbuf1, vin, tb, nv);
-        hb_next = H[(u64)tid * ntiles + next];
+        if (tid < 256) hb_next = H[(u64)tid * ntiles + next];
       }
       asm volatile("cp.async.commit_group;\n" ::);
     }
@@ -362,16 +370,20 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
     __syncthreads();
     {
       u32 run = 0;
+      if (tid < 256) {
 #pragma unroll
-      for (int ww = 0; ww < RADIX_WARPS; ww++) {
-        u32 c = wcnt[ww * 256 + tid];
-        wcnt[ww * 256 + tid] = run;
-        run += c;
+        for (int ww = 0; ww < RADIX_WARPS; ww++) {
+          u32 c = wcnt[ww * 256 + tid];
+          wcnt[ww * 256 + tid] = run;
+          run += c;
+        }
       }
       u32 tot;
       u32 ex = block_excl_scan(run, ws, tot);
-      texcl[tid] = ex;
-      dbase[tid] = hbase - ex;
+      if (tid < 256) {
+        texcl[tid] = ex;
+        dbase[tid] = hbase - ex;
+      }
     }
     __syncthreads();
 #pragma unroll
@@ -410,6 +422,7 @@ void radix_init() {
   CK(cudaFuncSetAttribute(k_radix_scatter<u32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter<u64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem<u64>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
@@ -446,8 +459,10 @@ static void radix_sort_impl(K*& keys, u32*& vals, K*& keys_alt, u32*& vals_alt, 
       } else {
         u32 grid = (u32)g_radix_grid[sizeof(K) == 4 ? 0 : 1];
         if (grid > ntiles) grid = ntiles;
-        static const int nmatch = [] { const char* e = getenv("KISS_B200_NMATCH"); return e ? atoi(e) : 4; }();  // 0: 8.16 ms, 4: 7.94 ms, 8: 8.43 ms per 1 Gbp sort
-        if (sizeof(K) == 4 && nmatch == 4)
+        static const int nmatch = [] { const char* e = getenv("KISS_B200_NMATCH"); return e ? atoi(e) : RADIX_ITEMS / 4; }();  // 0: 8.16 ms, 4: 7.94 ms, 8: 8.43 ms per 1 Gbp sort
+        if (sizeof(K) == 4 && nmatch == 2)
+          k_radix_scatter_p<u32, 2><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);
+        else if (sizeof(K) == 4 && nmatch == 4)
           k_radix_scatter_p<u32, 4><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);
         else if (sizeof(K) == 4 && nmatch == 8)
           k_radix_scatter_p<u32, 8><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);
