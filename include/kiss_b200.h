@@ -54,7 +54,8 @@ typedef struct kiss_b200_timings {
   double lms_sort;       /* reference: lms_suffix_direct_sort_dna, kiss1_core.hpp:23-145 */
   double put_lms;        /* reference: put_lms_suffix, kiss_common.hpp:445-481 */
   double induce;         /* reference: induced_sort, kiss_common.hpp:422-442 */
-  double d2h;            /* host variant only: copy of SA back to the host */
+  double d2h;            /* host variant only: copy of SA back to the host; with a pinned destination the copies
+                            of finished regions overlap the S pass and this is only the part left after it */
   double total_device;   /* pack .. induce */
   uint64_t n;            /* text length */
   uint64_t m;            /* LMS count including the sentinel (what get_lms returns, kiss_common.hpp:578) */

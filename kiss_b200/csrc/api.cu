@@ -137,6 +137,7 @@ struct kiss_b200_ctx {
   int device = 0;
   cudaStream_t st = nullptr;
   cudaEvent_t ev[8] = {};
+  cudaStream_t st_copy = nullptr;  // device-to-host copies of finished SA regions, concurrent with the S pass
   u32* pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs (+ 8 u64 for the wave tail)
   Profiler prof;          // optional per-kernel timing
   Arena arena;
@@ -415,9 +416,24 @@ Buckets make_buckets(const u64 counters[8], u64 n) {
 
 struct InduceStats { u64 waves_L = 0, waves_S = 0; };
 
+// Where finished parts of the suffix array go while induction is still running: the L-type part of every bucket
+// is final after the L pass, the S-type part of bucket c after its S pass, and nothing later writes them — so
+// their device-to-host copies run on a second stream under the remaining waves (a pinned destination only:
+// a pageable one would block the host thread that drives the waves).
+struct CopyOut {
+  u32* host = nullptr;
+  cudaStream_t st = nullptr;
+  u64 bytes = 0;
+  void send(const u32* SA, u64 lo, u64 cnt) {
+    if (!host || !cnt) return;
+    CK(cudaMemcpyAsync(host + lo, SA + lo, cnt * sizeof(u32), cudaMemcpyDeviceToHost, st));
+    bytes += cnt * sizeof(u32);
+  }
+};
+
 // `lms` = the sorted LMS suffixes (sentinel excluded), grouped by first symbol: bk.lms_off / bk.lms_count
 void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets& bk, const u32* lms, u32* SA, u32* CTX,
-               InduceStats* is) {
+               InduceStats* is, CopyOut* co = nullptr) {
   cudaStream_t st = c->st;
   WaveScratch ws;
   u64 maxlen = n + 1;
@@ -464,6 +480,10 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
     nL[s] = Lc[s] - bk.B[s];
     Sc[s] = bk.B[s + 1];
   }
+  if (co) {  // (every wave ended with a stream synchronisation: the L-type entries are complete)
+    co->send(SA, 0, 1);
+    for (int s = 0; s < 4; s++) co->send(SA, bk.B[s], nL[s]);
+  }
   // S pass (kiss_common.hpp:192-224); the LMS slots are simply overwritten (induced_clear, :405-420)
   for (int cb = 3; cb >= 0; cb--) {
     u64 p = bk.B[cb + 1];
@@ -478,6 +498,7 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
       p = q;
       is->waves_S++;
     }
+    if (co) co->send(SA, bk.B[cb] + nL[cb], bk.B[cb + 1] - bk.B[cb] - nL[cb]);  // bucket cb's S-type part is final
     if (cb > 0 && nL[cb]) {
       induce_wave(SA, CTX, T, nullptr, bk.B[cb], nL[cb], true, (1u << cb) - 1u, Sc, ws, tot, st);
       for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
@@ -540,7 +561,8 @@ void fill_timings(kiss_b200_timings* t, float pack, float lms, float sort, float
 enum Stop { STOP_LMS, STOP_SORT, STOP_PUT, STOP_FULL };
 
 // the whole path on device-resident data; `stage_out` receives the stage's array when stopping early
-void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* dSA, Stop stop, kiss_b200_timings* t) {
+void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* dSA, Stop stop, kiss_b200_timings* t,
+                  CopyOut* co = nullptr) {
   cudaStream_t st = c->st;
   u64 launches0 = g_launches;
   float t_pack = 0, t_lms = 0, t_sort = 0, t_put = 0, t_ind = 0;
@@ -572,7 +594,7 @@ void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* d
       lms = merged_lms(pool, sl, st);
     }
     CK(cudaEventRecord(c->ev[5], st));
-    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, lms, dSA, dCTX, &is);
+    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, lms, dSA, dCTX, &is, co);
     CK(cudaEventRecord(c->ev[6], st));
     CK(cudaEventSynchronize(c->ev[6]));
     CK(cudaEventElapsedTime(&t_sort, c->ev[3], c->ev[4]));
@@ -604,11 +626,13 @@ int guarded(kiss_b200_ctx* c, F&& f) {
     g_prof = &c->prof;
     f();
     cudaStreamSynchronize(c->st);
+    cudaStreamSynchronize(c->st_copy);
     c->prof.collect();
     c->arena.settle();
     return KISS_B200_OK;
   } catch (const CudaError& e) {
     g_last_error = e.what();
+    cudaStreamSynchronize(c->st_copy);  // no copy into the caller's buffer may outlive the call
     cudaGetLastError();
     return e.code;
   } catch (const std::bad_alloc&) {
@@ -647,7 +671,17 @@ void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* o
   u32* dOut = pool.alloc<u32>(out_n);
   kiss_b200_timings tt;
   memset(&tt, 0, sizeof(tt));
-  run_pipeline(c, dS, n, k, algo, dOut, stop, &tt);
+  CopyOut co;
+  if (stop == STOP_FULL && out_host && n) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, out_host) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+      co.host = out_host;
+      co.st = c->st_copy;
+    } else {
+      cudaGetLastError();
+    }
+  }
+  run_pipeline(c, dS, n, k, algo, dOut, stop, &tt, co.host ? &co : nullptr);
   u64 m = c->prep.m1 + 1;
   u64 cnt = out_n;
   if (stop == STOP_LMS) {
@@ -662,8 +696,14 @@ void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* o
   }
   (void)out_count_hint;
   CK(cudaEventRecord(e2, st));
-  if (out_host) CK(cudaMemcpyAsync(out_host, dOut, cnt * sizeof(u32), cudaMemcpyDeviceToHost, st));
-  CK(cudaEventRecord(e3, st));
+  if (co.host) {
+    // everything was sent region by region; what is left of the copies is the exposed device-to-host time
+    if (co.bytes != cnt * sizeof(u32)) throw CudaError(-3, "internal: overlapped copy-out missed a region");
+    CK(cudaEventRecord(e3, co.st));
+  } else {
+    if (out_host) CK(cudaMemcpyAsync(out_host, dOut, cnt * sizeof(u32), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(e3, st));
+  }
   CK(cudaEventSynchronize(e3));
   float h2d = 0, d2h = 0;
   cudaEventElapsedTime(&h2d, e0, e1);
@@ -713,6 +753,7 @@ int kiss_b200_create(kiss_b200_ctx** out, int device) {
   try {
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->st_copy, cudaStreamNonBlocking));
     for (auto& ev : c->ev) CK(cudaEventCreate(&ev));
     CK(cudaHostAlloc((void**)&c->pinned, 64 * sizeof(u32) + 8 * sizeof(u64), cudaHostAllocDefault));
     cudaMemPool_t mp;
@@ -737,6 +778,7 @@ void kiss_b200_destroy(kiss_b200_ctx* c) {
   if (c->st) cudaStreamSynchronize(c->st);
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
   if (c->pinned) cudaFreeHost(c->pinned);
+  if (c->st_copy) cudaStreamDestroy(c->st_copy);
   if (c->st) cudaStreamDestroy(c->st);
   delete c;
 }

@@ -131,3 +131,16 @@ def test_medium_sizes_bit_exact(ctx, name, n, gen):
     bad = np.nonzero(got != want)[0]
     assert bad.size == 0, f"{bad.size} mismatches, first at {bad[:5]}"
     assert ol.fnv1a(got) == ol.fnv1a(want)
+
+
+@pytest.mark.parametrize("name,gen", [c for c in CASES if c[0] in ("uniform200k", "repeats_mut", "copies1500", "all_T", "uniform7")],
+                         ids=["uniform200k", "repeats_mut", "copies1500", "all_T", "uniform7"])
+def test_full_sa_into_pinned_buffer(ctx, name, gen):
+    """a pinned destination takes the overlapped copy-out: finished SA regions leave on a second stream while
+    the S pass is still running"""
+    import torch
+    S = gen()
+    out = torch.empty(S.size + 1, dtype=torch.int32).pin_memory()
+    out.fill_(-1)
+    sa = ctx.suffix_array_dna(S, 256, out=out.numpy().view(np.uint32))
+    assert np.array_equal(sa, ol.oracle_kiss1(S, k=256))
