@@ -139,7 +139,7 @@ def run_reference_arm(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    sample = args.cpu_sample or 100_000_000
+    sample = min(args.n, args.cpu_sample or 100_000_000)
     times = []
     kind = "reference"
     for i in range(args.warmup + args.steps):

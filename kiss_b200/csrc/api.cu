@@ -438,9 +438,8 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
   WaveScratch ws;
   u64 maxlen = n + 1;
   u64 nt = wave_tiles(maxlen);
-  ws.tot_dev = pool.alloc<u32>(4);
   ws.tot_host = c->pinned + 32;
-  ws.tail_dev = pool.alloc<u64>(8);
+  ws.tot_host[4] = 0;
   ws.tail_host = reinterpret_cast<u64*>(c->pinned + 64);
   ws.status = pool.alloc<u64>(4 * nt + 4);
   ws.state = pool.alloc<u32>(2);
@@ -457,6 +456,7 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
   induce_wave(SA, CTX, T, nullptr, 0, 1, false, 0xFu, Lc, ws, tot, st);
   for (int s = 0; s < 4; s++) Lc[s] += tot[s];
   is->waves_L++;
+  if (co) co->send(SA, 0, 1);
   for (int cb = 0; cb < 4; cb++) {
     u64 p = bk.B[cb];
     while (p < Lc[cb]) {
@@ -470,6 +470,9 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
       p = q;
       is->waves_L++;
     }
+    // bucket cb's L-type part is final (every wave ended with a stream synchronisation; later waves only fill
+    // higher buckets): it can leave now
+    if (co) co->send(SA, bk.B[cb], Lc[cb] - bk.B[cb]);
     if (bk.lms_count[cb]) {
       induce_wave(SA, CTX, T, lms, bk.lms_off[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
@@ -480,10 +483,7 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
     nL[s] = Lc[s] - bk.B[s];
     Sc[s] = bk.B[s + 1];
   }
-  if (co) {  // (every wave ended with a stream synchronisation: the L-type entries are complete)
-    co->send(SA, 0, 1);
-    for (int s = 0; s < 4; s++) co->send(SA, bk.B[s], nL[s]);
-  }
+
   // S pass (kiss_common.hpp:192-224); the LMS slots are simply overwritten (induced_clear, :405-420)
   for (int cb = 3; cb >= 0; cb--) {
     u64 p = bk.B[cb + 1];
@@ -505,9 +505,7 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
       is->waves_S++;
     }
   }
-  u32 wd[2];
-  Sync{c}.read(ws.state, 2, wd);
-  if (wd[1]) throw CudaError(-3, "internal: induction look-back watchdog fired");
+  if (ws.tot_host[4]) throw CudaError(-3, "internal: induction look-back watchdog fired");
   for (int s = 0; s < 4; s++)
     if (Sc[s] != bk.B[s] + nL[s]) throw CudaError(-3, "internal: induction did not fill every bucket");
 }
@@ -755,7 +753,7 @@ int kiss_b200_create(kiss_b200_ctx** out, int device) {
     CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&c->st_copy, cudaStreamNonBlocking));
     for (auto& ev : c->ev) CK(cudaEventCreate(&ev));
-    CK(cudaHostAlloc((void**)&c->pinned, 64 * sizeof(u32) + 8 * sizeof(u64), cudaHostAllocDefault));
+    CK(cudaHostAlloc((void**)&c->pinned, 64 * sizeof(u32) + 8 * sizeof(u64), cudaHostAllocMapped | cudaHostAllocPortable));
     cudaMemPool_t mp;
     CK(cudaDeviceGetDefaultMemPool(&mp, device));
     u64 thr = ~0ull;  // keep freed scratch cached in the pool between calls

@@ -284,6 +284,7 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
           }
           if (++spins > (1u << 24)) {  // watchdog: never hang
             state[1] = 1u;
+            tot[4] = 1u;  // (pinned host memory, read after the last wave)
             ready = true;
 #pragma unroll
             for (int k = 0; k < WF_LB; k++) word[k] = wf_pack(epoch, WF_INCL, 0);
@@ -405,11 +406,10 @@ u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, 
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
   {
     ProfScope ps(PK_WAVE_SMALL, st);
-    if (down) k_wave_tail<true><<<1, WAVE_THREADS, sizeof(WaveShared), st>>>(a, bucket, *p, 1u << 20, ws.tail_dev);
-    else k_wave_tail<false><<<1, WAVE_THREADS, sizeof(WaveShared), st>>>(a, bucket, *p, 1u << 20, ws.tail_dev);
+    if (down) k_wave_tail<true><<<1, WAVE_THREADS, sizeof(WaveShared), st>>>(a, bucket, *p, 1u << 20, ws.tail_host);
+    else k_wave_tail<false><<<1, WAVE_THREADS, sizeof(WaveShared), st>>>(a, bucket, *p, 1u << 20, ws.tail_host);
     CK_LAUNCH(); g_launches++;
   }
-  CK(cudaMemcpyAsync(ws.tail_host, ws.tail_dev, 6 * sizeof(u64), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   *p = ws.tail_host[0];
   for (int s = 0; s < 4; s++) cur[s] = ws.tail_host[1 + s];
@@ -442,12 +442,12 @@ void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, u64 lo, u6
     // its tile starts makes every later tile wait in the look-back)
     const u32 ep = ++*ws.epoch;
     // (5 resident blocks per SM, 48 registers with a small spill, measured 1 ms slower than 4)
-    if (down) k_wave_fused<true, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_dev);
-    else k_wave_fused<false, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_dev);
+    if (down) k_wave_fused<true, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_host);
+    else k_wave_fused<false, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_host);
     CK_LAUNCH(); g_launches++;
     *ws.tile_base += ntiles;
   }
-  CK(cudaMemcpyAsync(ws.tot_host, ws.tot_dev, 4 * sizeof(u32), cudaMemcpyDeviceToHost, st));
+  // (the kernel stored the totals in pinned host memory: no copy engine between the waves and the host)
   CK(cudaStreamSynchronize(st));
   for (int s = 0; s < 4; s++) tot[s] = ws.tot_host[s];
 }

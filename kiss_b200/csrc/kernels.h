@@ -146,15 +146,13 @@ void place_lms(const u32* longs, u32 nl, const u32* sorted_shorts, const u32* in
 void place_sorted(const u32* sorted, u32 cnt, Buckets bk, u64 n, u32* SA, u32* CTX, cudaStream_t st);
 
 struct WaveScratch {
-  u32* tot_dev;   // 4
-  u32* tot_host;  // 4, pinned
+  u32* tot_host;  // pinned host memory the kernels write directly (UVA): [0..3] totals of the wave, [4] watchdog flag
   // single-pass (decoupled look-back) waves
   u64* status;    // 4 words per tile of the largest wave, zeroed once per call
   u32* state;     // [0] tile ticket, [1] watchdog flag; zeroed once per call
   u32* tile_base; // host: tickets handed out so far
   u32* epoch;     // host: wave number
-  u64* tail_dev;  // 6 words: result of the on-device tail loop
-  u64* tail_host; // pinned
+  u64* tail_host; // pinned, written by k_wave_tail: next wave start, 4 cursors, waves run
 };
 #ifndef WAVE_TILE
 #define WAVE_TILE 8192u  // measured per 1 Gbp: 2048: 15.0 ms, 4096: 13.8 ms, 8192: 12.8 ms, 16384: 13.2 ms of waves
