@@ -247,6 +247,10 @@ def run_b200(args):
         "stages_ms": {kk: v / args.steps * 1e3 for kk, v in stage.items()},
         "waves": [last.get("waves_L"), last.get("waves_S")],
     }
+    if "steps_ms" in last:
+        line["sharded_sort_steps_ms"] = last["steps_ms"]
+    if "shard_sizes" in last:
+        line["shard_sizes"] = last["shard_sizes"]
 
     if rank == 0:
         # roofline of the dominant kernel class: algorithmic bytes per launch / its mean launch duration, measured

@@ -84,6 +84,16 @@ def sharded_lms_sort(backend, dist, n_long, rank, world):
     """returns (sorted_long on rank 0 else None, stats).  Collectives: one all_gather of key samples, one
     all_to_all of counts, one all_to_all of positions, one gather-shaped all_to_all of the sorted ranges."""
     torch = backend.torch
+    import os
+    import time
+    marks = []
+
+    def mark(name):  # KISS_B200_MGPU_TIMING=1: synchronised wall-clock marks between the steps (debug aid)
+        if os.environ.get("KISS_B200_MGPU_TIMING"):
+            backend.sync()
+            marks.append((name, time.perf_counter()))
+
+    mark("start")
     lo, hi = slice_bounds(n_long, rank, world)
     # 1. splitters
     mine = backend.sample_keys(lo, hi, SAMPLES_PER_RANK)
@@ -95,6 +105,7 @@ def sharded_lms_sort(backend, dist, n_long, rank, world):
     dist.all_gather(gathered, t)
     samples = np.concatenate([g.cpu().numpy()[1:1 + int(g[0].item())] for g in gathered]).astype(np.uint32)
     splitters = choose_splitters(samples, world)
+    mark("splitters")
     # 2. bucket this rank's slice by destination (stable) and exchange the counts
     send, send_counts = backend.partition(splitters, lo, hi)
     sc = torch.from_numpy(send_counts.astype(np.int64)).to(backend_device(backend))
@@ -102,13 +113,16 @@ def sharded_lms_sort(backend, dist, n_long, rank, world):
     dist.all_to_all_single(rc, sc)
     recv_counts = rc.cpu().numpy()
     total = int(recv_counts.sum())
+    mark("partition")
     # 3. the exchange: LMS positions only
     recv = backend.empty(total)
     backend.sync()
     dist.all_to_all_single(recv, send, output_split_sizes=recv_counts.tolist(), input_split_sizes=send_counts.tolist())
+    mark("exchange")
     # chunks arrive in source-rank order = ascending text order: the stable sort's precondition
     # 4. local sort of this rank's key range
     st = backend.sort_subset(recv, total)
+    mark("local_sort")
     # 5. concatenate the ranges on rank 0 (key ranges are ordered by rank)
     sizes = torch.tensor([total], dtype=torch.int64, device=backend_device(backend))
     all_sizes = [torch.empty_like(sizes) for _ in range(world)]
@@ -119,8 +133,11 @@ def sharded_lms_sort(backend, dist, n_long, rank, world):
     result = backend.empty(sum(out_split))
     backend.sync()
     dist.all_to_all_single(result, recv, output_split_sizes=out_split, input_split_sizes=in_split)
+    mark("concat")
     stats = {"shard_sizes": all_sizes, "imbalance": (max(all_sizes) * world / max(1, sum(all_sizes))),
              "sort": st}
+    if marks:
+        stats["steps_ms"] = {marks[i][0]: round((marks[i][1] - marks[i - 1][1]) * 1e3, 3) for i in range(1, len(marks))}
     return (result if rank == 0 else None), stats
 
 
@@ -144,6 +161,8 @@ def sharded_suffix_array_dev(ctx, S, n, SA, k, dist):
     t2 = time.perf_counter()
     out = {"kernel_launches": 12, "m": be.m, "get_lms": t1 - t0, "lms_sort": t2 - t1, "put_lms": 0.0, "induce": 0.0,
            "pack": 0.0, "shard_sizes": stats["shard_sizes"], "imbalance": stats["imbalance"]}
+    if "steps_ms" in stats:
+        out["steps_ms"] = stats["steps_ms"]
     if rank == 0:
         ft = be.finish(sorted_long, n_long, SA)
         out.update(put_lms=ft["put_lms"], induce=ft["induce"], waves_L=ft["waves_L"], waves_S=ft["waves_S"],
