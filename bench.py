@@ -4,8 +4,10 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--n BASES] [--k K]
 
 One step = one pass of the whole path (pack -> get_lms -> k-ordered LMS sort -> put_lms -> induced_sort)
-over one synthetic text.  At N=1 the workload is BASELINE.json configs[1]: uniform-random ACGT, 1 Gbp, k=256,
-PARALLEL_SORTING.  `value` is device-resident throughput (text and SA in HBM, CUDA events on the library's
+over one synthetic text.  The workload is the one BASELINE.json's metric is quoted on ("k=256 SA build ... on
+3.1 Gbp"): configs[2] = C3 of SURVEY.md 8(d), chm13-sized 3 117 292 070 bp with injected interspersed / tandem /
+segmental repeats (tests/textgen.py chm13_like, seed 3), k=256, PARALLEL_SORTING; it fits one B200 (45 of
+180 GB).  `--workload c2` selects configs[1] (uniform-random 1 Gbp, seed 2).  `value` is device-resident throughput (text and SA in HBM, CUDA events on the library's
 stream); `e2e` is the same call through the host C ABI with pinned host buffers (H2D of the text and D2H of
 the suffix array inside the timed region).  At N>1 the LMS sort is sharded by key range with an NCCL
 all-to-all; induction runs on rank 0.
@@ -27,8 +29,11 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-N_DEFAULT = 1_000_000_000
-SEED = 2
+# C2 = uniform 1 Gbp seed 2; C3 = chm13-sized with repeats, seed 3 (README.md:101 gives the length)
+WORKLOADS = {
+    "c2": dict(n=1_000_000_000, seed=2, kind="uniform", name="uniform-random ACGT"),
+    "c3": dict(n=3_117_292_070, seed=3, kind="chm13", name="chm13-sized ACGT with injected tandem/interspersed/segmental repeats"),
+}
 
 
 def parse():
@@ -37,12 +42,16 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=N_DEFAULT)
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--n", type=int, default=0, help="bases (0 = the workload's own size)")
     ap.add_argument("--k", type=int, default=256)
     ap.add_argument("--cpu-sample", type=int, default=0, help="bases of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    args = ap.parse_args()
+    args.wl = WORKLOADS[args.workload]
+    args.n = args.n or args.wl["n"]
+    return args
 
 
 # ------------------------------------------------------------------------------------------ clocks
@@ -102,12 +111,27 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------ CPU reference
-def cpu_reference_run(n, k, threads):
-    """seconds of the reference's kiss1_suffix_array_dna on n bases of the bench text, with `threads` threads"""
+def host_sample(wl, sample, full=None):
+    """`sample` bases of the workload for the CPU legs: a prefix of the bench text when it is at hand (`full`; its
+    last 4096 bases are replaced by uniform ones so no repeat touches the text end, as in the generator), else the
+    same generator run at the sample size (numpy only: the reference arm never touches the GPU)."""
+    import numpy as np
+    import textgen as tg
+    if full is not None and sample <= full.size:
+        S = np.ascontiguousarray(full[:sample]).copy()
+        if wl["kind"] != "uniform" and sample > 8192:
+            S[-4096:] = tg.uniform(wl["seed"] + 1, 4096)
+        return S, f"first {sample} bases of the bench text"
+    if wl["kind"] == "uniform":
+        return tg.uniform(wl["seed"], sample), f"first {sample} bases of the bench text"
+    return tg.chm13_like(wl["seed"], sample), f"the bench text's generator (chm13_like, seed {wl['seed']}) at {sample} bases"
+
+
+def cpu_reference_run(S, k, threads):
+    """seconds of the reference's kiss1_suffix_array_dna on the text S with `threads` threads"""
     import numpy as np
     import oracle_lib as ol
-    import textgen as tg
-    S = tg.uniform(SEED, n)
+    n = S.size
     if ol.have_ref():
         L = ol.ref()
         SA = np.empty(n + 1, np.uint32)
@@ -122,16 +146,18 @@ def cpu_reference_run(n, k, threads):
     return sec, kind
 
 
-def cpu_baseline(k, sample=0):
+def cpu_baseline(wl, k, sample=0, full=None):
     threads = os.cpu_count() or 1
     if not sample:
-        sec, kind = cpu_reference_run(20_000_000, k, threads)
+        S, _ = host_sample(wl, 20_000_000, full)
+        sec, kind = cpu_reference_run(S, k, threads)
         rate = 20_000_001 / sec
         sample = int(min(400_000_000, max(20_000_000, rate * 12)))
-    sec, kind = cpu_reference_run(sample, k, threads)
+    S, what = host_sample(wl, sample, full)
+    sec, kind = cpu_reference_run(S, k, threads)
     return {"value": (sample + 1) / sec / 1e9, "unit": "Gsuffixes/s", "cores": threads, "kind": kind,
-            "sample": f"uniform ACGT seed {SEED}, first {sample} bases of the bench text, k={k}, "
-                      f"kiss1_suffix_array_dna, {sec:.2f} s", "seconds": sec}
+            "sample": f"{what} ({wl['name']}, seed {wl['seed']}), k={k}, kiss1_suffix_array_dna, {sec:.2f} s",
+            "seconds": sec}
 
 
 def run_reference_arm(args):
@@ -139,11 +165,13 @@ def run_reference_arm(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
+    wl = args.wl
     sample = min(args.n, args.cpu_sample or 100_000_000)
+    S, what = host_sample(wl, sample)
     times = []
     kind = "reference"
     for i in range(args.warmup + args.steps):
-        sec, kind = cpu_reference_run(sample, args.k, threads)
+        sec, kind = cpu_reference_run(S, args.k, threads)
         if i >= args.warmup:
             times.append(sec)
     sec = sum(times) / len(times)
@@ -152,10 +180,10 @@ def run_reference_arm(args):
         "impl": "reference", "metric": "k=256 SA build throughput", "value": val, "unit": "Gsuffixes/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": f"uniform-random ACGT {args.n} bp, k={args.k}, PARALLEL_SORTING "
-                               f"(reference timed on a {sample}-base sample per step)"},
+        "config": {"workload": f"{wl['name']} {args.n} bp (seed {wl['seed']}), k={args.k}, PARALLEL_SORTING "
+                               f"(reference timed on a {sample}-base sample per step: {what})"},
         "cpu_baseline": {"value": val, "unit": "Gsuffixes/s", "cores": threads, "kind": kind,
-                         "sample": f"first {sample} bases of the bench text per step"},
+                         "sample": f"{what}, every step"},
         "e2e": {"value": val, "unit": "Gsuffixes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -163,13 +191,40 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------ B200 arm
-# mean DRAM bytes (read + write) per launch at the 1 Gbp workload, ncu --set full (profiles/r1_final_launches_1gbp.txt)
-NCU_DRAM_BYTES_PER_LAUNCH = {"k_wave_fused": 46.658e9 / 58, "k_radix_scatter": 5.4073e9, "k_groups_tiny": 6.7628e9}
+# mean DRAM bytes (read + write) per launch, ncu dram__bytes_read.sum + dram__bytes_write.sum of one step
+# (profiles/r1_final_launches_1gbp.txt for c2, profiles/r1_c3_launches.txt for c3); None = no capture
+NCU_DRAM_BYTES_PER_LAUNCH = {
+    "c2": {"k_wave_fused": 46.658e9 / 58, "k_radix_scatter": 5.4073e9, "k_groups_tiny": 6.7628e9},
+    "c3": {},
+}
 
 
 def b200_alg_bytes(n, m):
     """B_alg(n, m) = 18 n + 28 m"""
     return 18 * n + 28 * m
+
+
+def make_text(ctx, wl, n, dist, rank, keep_host):
+    """the bench text in HBM (n + 64 bytes); rank 0 builds it and the other ranks receive it.  Returns (S_dev, host
+    copy or None)."""
+    import torch
+    S = torch.empty(n + 64, dtype=torch.uint8, device="cuda")
+    ctx.synth_uniform_dev(S.data_ptr(), n, wl["seed"])
+    torch.cuda.synchronize()
+    host = None
+    if wl["kind"] == "chm13":
+        if rank == 0:
+            import textgen as tg
+            host = S[:n].cpu().numpy()
+            host = tg.chm13_like(wl["seed"], n, base=host)
+            S[:n].copy_(torch.from_numpy(host))
+            torch.cuda.synchronize()
+        if dist is not None:
+            dist.broadcast(S, src=0)
+            torch.cuda.synchronize()
+    elif keep_host and rank == 0:
+        host = S[:n].cpu().numpy()
+    return S, (host if keep_host else None)
 
 
 def run_b200(args):
@@ -183,13 +238,12 @@ def run_b200(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    n, k = args.n, args.k
+    n, k, wl = args.n, args.k, args.wl
     ctx = kiss_b200.Context(local)
     lib_stream = torch.cuda.ExternalStream(kiss_b200.lib().kiss_b200_stream(ctx.handle), device=local)
-    S = torch.empty(n + 64, dtype=torch.uint8, device="cuda")
+    want_host = rank == 0 and not (args.no_e2e and (args.no_cpu_baseline or world > 1))
+    S, host_text = make_text(ctx, wl, n, dist, rank, want_host)
     SA = torch.empty(n + 1, dtype=torch.int32, device="cuda")
-    ctx.synth_uniform_dev(S.data_ptr(), n, SEED)
-    torch.cuda.synchronize()
 
     if world > 1:
         from kiss_b200.multi_gpu import sharded_suffix_array_dev
@@ -226,6 +280,7 @@ def run_b200(args):
     ms = e0.elapsed_time(e1)
     clk = clocks.stop()
     prof = ctx.profile()
+    prof_bytes = ctx.profile_alg_bytes()
     ctx.profile_enable(False)
     if dist is not None:
         tt = torch.tensor([ms], device="cuda")
@@ -239,13 +294,15 @@ def run_b200(args):
         "metric": "k=256 SA build throughput", "value": value, "unit": "Gsuffixes/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": f"uniform-random ACGT {n} bp (seed {SEED}), k={k}, PARALLEL_SORTING, "
+        "config": {"workload": f"{wl['name']} {n} bp (seed {wl['seed']}), k={k}, PARALLEL_SORTING, "
                                f"{'LMS sort sharded over %d GPUs, induction on rank 0' % world if world > 1 else '1 B200'}",
+                   "baseline_config": {"c2": "configs[1]", "c3": "configs[2]"}[args.workload],
                    "n": n, "m": m, "k": k, "l2": "inputs larger than L2 (text n bytes, SA 4(n+1) bytes)"},
         "clocks": clk,
         "gpu_launches": launches,
         "stages_ms": {kk: v / args.steps * 1e3 for kk, v in stage.items()},
         "waves": [last.get("waves_L"), last.get("waves_S")],
+        "lms_sort_tied": last.get("lms_sort_tied"), "lms_sort_rounds": last.get("lms_sort_rounds"),
     }
     if "steps_ms" in last:
         line["sharded_sort_steps_ms"] = last["steps_ms"]
@@ -253,7 +310,7 @@ def run_b200(args):
         line["shard_sizes"] = last["shard_sizes"]
 
     if rank == 0:
-        # roofline of the dominant kernel class: algorithmic bytes per launch / its mean launch duration, measured
+        # roofline of the dominant kernel: algorithmic bytes per launch / its mean launch duration, measured
         # live with CUDA events around every launch (kiss_b200_profile_*), vs the measured copy bandwidth
         peaks = {}
         try:
@@ -262,21 +319,25 @@ def run_b200(args):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         n_long = m - 1
-        # one entry per kernel FUNCTION: the three profiler classes of k_wave_fused / k_wave_tail are one kernel (K5)
-        merged = {}
+        # one entry per kernel FUNCTION: the profiler classes of k_wave_fused / k_wave_tail are one kernel (K5), the
+        # six size classes of k_groups_medium are template instances of one kernel
+        def function_of(name):
+            if name.startswith("k_wave"):
+                return "k_wave_fused"
+            if name.startswith("k_groups_medium"):
+                return "k_groups_medium"
+            return name
+        merged, alg_tot = {}, {}
         for name, (tot_ms, cnt) in prof.items():
-            key = "k_wave_fused" if name.startswith("k_wave") else name
+            key = function_of(name)
             a, b = merged.get(key, (0.0, 0))
             merged[key] = (a + tot_ms, b + cnt)
+            if name in prof_bytes:  # the launcher's own count (radix passes, tie-group classes)
+                alg_tot[key] = alg_tot.get(key, 0) + prof_bytes[name]
         steps = args.steps
-        n_sort = n_long // world  # LMS suffixes one rank sorts (the sort shards, the rest runs on rank 0)
-        alg = {  # algorithmic bytes per launch (SURVEY.md 8(d) per-unit figures x units of one launch)
-            "k_radix_scatter": 2 * (4 + 4) * n_sort,            # read + write of (key32, pos32) per pass
-            "k_radix_hist": 4 * n_sort,
-            "k_groups_tiny": (4 + 4) * n_sort,
-            "k_place/merge_lms": (4 + 4) * n_long,
-            "k_pack_codes": n + n // 4,
-        }
+        alg = {kk: v / merged[kk][1] for kk, v in alg_tot.items()}  # algorithmic bytes per launch
+        alg.setdefault("k_place/merge_lms", (4 + 4) * n_long)
+        alg.setdefault("k_pack_codes", n + n // 4)
         if "k_wave_fused" in merged:
             # K5 induction (8(d)): 2 x 4(n+1) SA reads + 4n induced writes + 4m + 2 x n/4 packed text, per step,
             # spread over the launches of one step
@@ -288,14 +349,18 @@ def run_b200(args):
                 gbs = alg[name] / (tot_ms / cnt * 1e-3) / 1e9
                 kernels[name].update(alg_bytes_per_launch=alg[name], achieved_gbs=gbs, frac=gbs / peak)
         for name, (tot_ms, cnt) in prof.items():
-            if name.startswith("k_wave"):
-                kernels["k_wave_fused"].setdefault("classes", {})[name] = {"ms_per_step": tot_ms / steps,
-                                                                          "launches_per_step": cnt / steps}
+            key = function_of(name)
+            if key != name:
+                cls = {"ms_per_step": tot_ms / steps, "launches_per_step": cnt / steps}
+                if name in prof_bytes:
+                    cls["alg_bytes_per_step"] = prof_bytes[name] / steps
+                    cls["achieved_gbs"] = prof_bytes[name] / (tot_ms * 1e-3) / 1e9
+                kernels[key].setdefault("classes", {})[name] = cls
         line["kernels"] = kernels
-        dom = max((k for k in kernels if "achieved_gbs" in kernels[k]), key=lambda k: kernels[k]["ms_per_step"])
+        dom = max((kk for kk in kernels if "achieved_gbs" in kernels[kk]), key=lambda kk: kernels[kk]["ms_per_step"])
         # dram__bytes_read.sum + dram__bytes_write.sum per launch (mean over the launches of one step) from the
-        # ncu capture under profiles/ (r1_v6_dram_per_kernel.txt); None when the dominant kernel has no capture
-        traffic = NCU_DRAM_BYTES_PER_LAUNCH.get(dom)
+        # ncu capture under profiles/; None when the dominant kernel has no capture at this workload
+        traffic = NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload, {}).get(dom) if n == wl["n"] and world == 1 else None
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
                             "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": traffic,
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
@@ -310,31 +375,64 @@ def run_b200(args):
         line["roofline_whole_path"] = {"alg_bytes": balg, "achieved": balg / dev_s / 1e9, "frac": balg / dev_s / 1e9 / peak,
                                        "note": "B_alg = 18 n + 28 m (SURVEY.md 8(d))"}
 
-    # ---- end to end through the host C ABI (pinned host buffers, H2D + D2H inside the timed region)
-    if world == 1 and not args.no_e2e:
+    # ---- end to end: host buffers in, host suffix array out, copies inside the timed region.  N=1: the C-ABI
+    # host call.  N>1: rank 0 uploads the text, every rank receives it (NCCL broadcast), the sharded sort and the
+    # induction run, rank 0 reads the suffix array back.
+    if not args.no_e2e:
         import numpy as np
-        hS = torch.empty(n, dtype=torch.uint8).pin_memory()
-        hSA = torch.empty(n + 1, dtype=torch.int32).pin_memory()
-        hS.copy_(S[:n])
-        torch.cuda.synchronize()
-        del SA
-        torch.cuda.empty_cache()
-        hS_np = hS.numpy()
-        hSA_np = hSA.numpy().view(np.uint32)
-        ctx.suffix_array_dna(hS_np, k, out=hSA_np)  # warm-up
-        t0 = time.perf_counter()
+        hS = hSA = None
+        if rank == 0:
+            hS = torch.empty(n, dtype=torch.uint8).pin_memory()
+            hSA = torch.empty(n + 1, dtype=torch.int32).pin_memory()
+            if host_text is not None:
+                hS.copy_(torch.from_numpy(host_text))
+            else:
+                hS.copy_(S[:n])
+            torch.cuda.synchronize()
         reps = max(1, min(args.steps, 2))
-        for _ in range(reps):
-            ctx.suffix_array_dna(hS_np, k, out=hSA_np)
-        torch.cuda.synchronize()
-        sec = (time.perf_counter() - t0) / reps
-        assert int(hSA_np[0]) == n
-        line["e2e"] = {"value": (n + 1) / sec / 1e9, "unit": "Gsuffixes/s", "h2d_bytes_per_step": n,
-                       "d2h_bytes_per_step": 4 * (n + 1), "ms_per_step": sec * 1e3,
-                       "h2d_ms": ctx.last_timings["h2d"] * 1e3, "d2h_ms": ctx.last_timings["d2h"] * 1e3}
+        if world == 1:
+            del SA
+            torch.cuda.empty_cache()
+            hS_np = hS.numpy()
+            hSA_np = hSA.numpy().view(np.uint32)
+            ctx.suffix_array_dna(hS_np, k, out=hSA_np)  # warm-up
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                ctx.suffix_array_dna(hS_np, k, out=hSA_np)
+            torch.cuda.synchronize()
+            sec = (time.perf_counter() - t0) / reps
+            assert int(hSA_np[0]) == n
+            line["e2e"] = {"value": (n + 1) / sec / 1e9, "unit": "Gsuffixes/s", "h2d_bytes_per_step": n,
+                           "d2h_bytes_per_step": 4 * (n + 1), "ms_per_step": sec * 1e3,
+                           "h2d_ms": ctx.last_timings["h2d"] * 1e3, "d2h_ms": ctx.last_timings["d2h"] * 1e3}
+        else:
+            def e2e_step():
+                if rank == 0:
+                    S[:n].copy_(hS, non_blocking=True)
+                dist.broadcast(S, src=0)
+                torch.cuda.synchronize()
+                sharded_suffix_array_dev(ctx, S, n, SA, k, dist)
+                if rank == 0:
+                    hSA.copy_(SA, non_blocking=True)
+                torch.cuda.synchronize()
+            e2e_step()  # warm-up
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                e2e_step()
+            barrier()
+            tt = torch.tensor([(time.perf_counter() - t0) / reps], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            sec = float(tt.item())
+            if rank == 0:
+                assert int(hSA[0]) == n
+                line["e2e"] = {"value": (n + 1) / sec / 1e9, "unit": "Gsuffixes/s", "h2d_bytes_per_step": n,
+                               "d2h_bytes_per_step": 4 * (n + 1), "ms_per_step": sec * 1e3,
+                               "note": "rank 0 uploads, NCCL broadcast of the text to the other ranks, rank 0 reads the SA back"}
+        del hS, hSA
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            line["cpu_baseline"] = cpu_baseline(k, args.cpu_sample)
+            line["cpu_baseline"] = cpu_baseline(wl, k, args.cpu_sample, host_text)
         except Exception as e:  # the checker is optional for the number, never for the product
             line["cpu_baseline"] = {"value": None, "unit": "Gsuffixes/s", "cores": os.cpu_count(), "kind": "unavailable",
                                     "sample": f"failed: {e}"}

@@ -152,6 +152,9 @@ int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_
  * profile_read: idx = 0, 1, ... until it returns KISS_B200_ERR_ARG. */
 int kiss_b200_profile_enable(kiss_b200_ctx* ctx, int on);
 int kiss_b200_profile_read(kiss_b200_ctx* ctx, int idx, const char** name, double* ms, uint64_t* launches);
+/* algorithmic bytes of the launches of class idx, where the launcher knows them (radix passes: keys and positions
+ * read + written; tie-group classes: 16 B per LMS suffix in the groups refined); else 0 */
+int kiss_b200_profile_alg_bytes(kiss_b200_ctx* ctx, int idx, uint64_t* bytes);
 
 /* ---- synthetic inputs ---------------------------------------------------------
  * Fill S_dev[0..n) with the counter-hash uniform stream `seed` (identical to tests/textgen.py uniform). */

@@ -254,53 +254,44 @@ template <typename K>
 u32 run_groups(kiss_b200_ctx* c, const K* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl, int kind = 0);
 
 // KISS_B200_DEBUG_GROUPS=1: per level, how many groups of each class and the size histogram of the medium ones
-void debug_groups(kiss_b200_ctx* c, const char* tag, u32 N, u64 h, const u32 cn[4], const GroupLists& gl) {
+void debug_groups(kiss_b200_ctx* c, const char* tag, u32 N, u64 h, const u32* cn, const GroupLists& gl) {
   static const bool on = getenv("KISS_B200_DEBUG_GROUPS") != nullptr;
   if (!on) return;
-  std::vector<u32> med(2ull * cn[1]);
-  if (cn[1]) CK(cudaMemcpy(med.data(), gl.med, med.size() * sizeof(u32), cudaMemcpyDeviceToHost));
-  u64 hist[12] = {}, elems = 0;
-  for (u32 g = 0; g < cn[1]; g++) {
-    u32 sz = med[2 * g + 1];
-    elems += sz;
-    int b = 0;
-    while ((1u << (b + 4)) < sz && b < 11) b++;
-    hist[b]++;
-  }
-  fprintf(stderr, "[kiss_b200] groups %s h=%llu N=%u: >tiny %u, medium %u (%llu elements; sizes <=16:%llu <=32:%llu <=64:%llu <=128:%llu <=256:%llu <=512:%llu <=1024:%llu <=2048:%llu), big %u\n",
-          tag, (unsigned long long)h, N, cn[0], cn[1], (unsigned long long)elems, (unsigned long long)hist[0], (unsigned long long)hist[1],
-          (unsigned long long)hist[2], (unsigned long long)hist[3], (unsigned long long)hist[4], (unsigned long long)hist[5],
-          (unsigned long long)hist[6], (unsigned long long)hist[7], cn[2]);
+  (void)c; (void)gl;
+  fprintf(stderr, "[kiss_b200] groups %s h=%llu N=%u: >tiny %u, medium %u, big %u; medium groups (elements) of size "
+                  "<=32: %u (%u) <=64: %u (%u) <=128: %u (%u) <=256: %u (%u) <=512: %u (%u) <=2048: %u (%u)\n",
+          tag, (unsigned long long)h, N, cn[0], cn[1], cn[2], cn[4], cn[10], cn[5], cn[11], cn[6], cn[12], cn[7], cn[13],
+          cn[8], cn[14], cn[9], cn[15]);
 }
 
 template <>
 u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl, int) {
   Sync sync{c};
-  CK(cudaMemsetAsync(gl.counters, 0, 4 * sizeof(u32), c->st));
+  CK(cudaMemsetAsync(gl.counters, 0, GL_COUNTERS * sizeof(u32), c->st));
   groups_tiny_u32(keys, pos, N, sp, h, gl, c->st);
-  u32 cn[4];
+  u32 cn[GL_COUNTERS];
   sync.read(gl.counters, 4, cn);
   if (cn[3]) throw CudaError(-3, "internal: group list overflow");
   if (!cn[0] || h >= sp.D) return 0;
   groups_classify_u32(keys, N, cn[0], gl, (u32)h, c->st);
-  sync.read(gl.counters, 4, cn);
+  sync.read(gl.counters, GL_COUNTERS, cn);
   debug_groups(c, "u32", N, h, cn, gl);
-  groups_medium(pos, gl.med, cn[1], sp, h, c->st);
+  groups_medium(pos, gl.med, gl.medN, cn + 4, cn + 10, sp, h, c->st);
   return cn[2];
 }
 template <>
 u32 run_groups<u64>(kiss_b200_ctx* c, const u64* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl, int kind) {
   Sync sync{c};
-  CK(cudaMemsetAsync(gl.counters, 0, 4 * sizeof(u32), c->st));
+  CK(cudaMemsetAsync(gl.counters, 0, GL_COUNTERS * sizeof(u32), c->st));
   groups_tiny_u64(keys, pos, N, sp, h, gl, c->st);
-  u32 cn[4];
+  u32 cn[GL_COUNTERS];
   sync.read(gl.counters, 4, cn);
   if (cn[3]) throw CudaError(-3, "internal: group list overflow");
   if (!cn[0] || h >= sp.D) return 0;
   groups_classify_u64(keys, N, cn[0], gl, kind, (u32)h, c->st);
-  sync.read(gl.counters, 4, cn);
+  sync.read(gl.counters, GL_COUNTERS, cn);
   debug_groups(c, "u64", N, h, cn, gl);
-  groups_medium(pos, gl.med, cn[1], sp, h, c->st);
+  groups_medium(pos, gl.med, gl.medN, cn + 4, cn + 10, sp, h, c->st);
   return cn[2];
 }
 
@@ -308,9 +299,10 @@ GroupLists alloc_lists(Pool& pool, u32 N, u64* tied) {
   GroupLists gl;
   gl.gcap = N / (TINY_MAX + 1) + 1;
   gl.glist = pool.alloc<u32>(gl.gcap);
-  gl.med = pool.alloc<u32>(2ull * gl.gcap);
+  gl.medN = N;
+  gl.med = pool.alloc<u32>(2ull * med_class_off(N, MED_CLASSES));
   gl.big = pool.alloc<u32>(3ull * (N / (MED_MAX + 1) + 1));
-  gl.counters = pool.alloc<u32>(4);
+  gl.counters = pool.alloc<u32>(GL_COUNTERS);
   gl.tied = tied;
   return gl;
 }
@@ -1017,6 +1009,12 @@ int kiss_b200_profile_read(kiss_b200_ctx* c, int idx, const char** name, double*
   if (name) *name = prof_name(idx);
   if (ms) *ms = c->prof.ms[idx];
   if (launches) *launches = c->prof.launches[idx];
+  return KISS_B200_OK;
+}
+
+int kiss_b200_profile_alg_bytes(kiss_b200_ctx* c, int idx, uint64_t* bytes) {
+  if (!c || !bytes || idx < 0 || idx >= PK_COUNT) return KISS_B200_ERR_ARG;
+  *bytes = c->prof.bytes[idx];
   return KISS_B200_OK;
 }
 

@@ -377,6 +377,51 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
     const u64 cc = sh.cur[bucket], p = sh.p;
     const u64 len = DOWN ? p - cc : cc - p;
     if (len == 0 || len > WAVE_TAIL_MAX || sh.nwaves >= max_waves) break;
+    if (len <= 32) {
+      // Waves of at most one warp's width (the chains of homopolymer / tandem runs: one wave per base, thousands
+      // per bucket on repeat-rich text): warp 0 runs them alone — one entry per lane, ballot ranks, no block
+      // barrier, cursors in registers.  A wave never grows inside a bucket, so this normally ends the tail.
+      __syncthreads();  // (every thread has read sh.cur / sh.p before warp 0 rewrites them)
+      if (threadIdx.x < 32) {
+        const u32 lane = threadIdx.x;
+        u64 c0 = sh.cur[0], c1 = sh.cur[1], c2 = sh.cur[2], c3 = sh.cur[3], pp = p;
+        u32 nw = sh.nwaves;
+        for (;;) {
+          const u64 cb = bucket == 0 ? c0 : bucket == 1 ? c1 : bucket == 2 ? c2 : c3;
+          const u64 ln = DOWN ? pp - cb : cb - pp;
+          if (ln == 0 || ln > 32 || nw >= max_waves) break;
+          u32 v = 0, c = 1u;
+          if (lane < ln) {
+            const u64 slot = DOWN ? pp - 1 - lane : pp + lane;
+            v = a0.SA[slot];
+            c = a0.CTX[slot];
+            if (c == 1u && v != 0 && v != KISS_EMPTY) c = ctx_gather(a0.T, v);
+          }
+          const u32 cu = ctx_symbol(c, a0.symmask);
+          const u32 m0 = __ballot_sync(0xffffffffu, cu == 0), m1 = __ballot_sync(0xffffffffu, cu == 1),
+                    m2 = __ballot_sync(0xffffffffu, cu == 2), m3 = __ballot_sync(0xffffffffu, cu == 3);
+          if (cu < 4) {
+            const u32 mm = cu == 0 ? m0 : cu == 1 ? m1 : cu == 2 ? m2 : m3;
+            const u64 cs = cu == 0 ? c0 : cu == 1 ? c1 : cu == 2 ? c2 : c3;
+            const u32 r = __popc(mm & ((1u << lane) - 1u));
+            const u64 dst = DOWN ? cs - 1 - r : cs + r;
+            a0.SA[dst] = v - 1u;
+            a0.CTX[dst] = c >> 2;
+          }
+          pp = cb;
+          if (DOWN) { c0 -= __popc(m0); c1 -= __popc(m1); c2 -= __popc(m2); c3 -= __popc(m3); }
+          else { c0 += __popc(m0); c1 += __popc(m1); c2 += __popc(m2); c3 += __popc(m3); }
+          nw++;
+          __syncwarp();  // (orders this wave's stores before the next wave's loads)
+        }
+        if (lane == 0) {
+          sh.cur[0] = c0; sh.cur[1] = c1; sh.cur[2] = c2; sh.cur[3] = c3;
+          sh.p = pp;
+          sh.nwaves = nw;
+        }
+      }
+      continue;
+    }
     WaveArgs a = a0;
     a.lo = DOWN ? cc : p;
     a.len = len;

@@ -27,7 +27,8 @@ extern thread_local u64 g_launches;  // kernels launched by this thread (reporte
 
 // ---- optional per-kernel timing (CUDA events around each launch of a kernel class, on the launching stream)
 enum ProfKernel { PK_PACK, PK_LMS_CLASSIFY, PK_LMS_EMIT, PK_SCAN, PK_RADIX_HIST, PK_RADIX_SCATTER, PK_GROUPS_TINY,
-                  PK_GROUPS_MEDIUM, PK_GROUPS_OTHER, PK_SHORTS, PK_PLACE, PK_WAVE_LMS, PK_WAVE_SCATTER, PK_WAVE_SMALL,
+                  PK_GROUPS_MEDIUM, PK_GROUPS_MEDIUM_64, PK_GROUPS_MEDIUM_128, PK_GROUPS_MEDIUM_256, PK_GROUPS_MEDIUM_512,
+                  PK_GROUPS_MEDIUM_2048, PK_GROUPS_OTHER, PK_SHORTS, PK_PLACE, PK_WAVE_LMS, PK_WAVE_SCATTER, PK_WAVE_SMALL,
                   PK_COUNT };
 const char* prof_name(int id);
 struct Profiler {
@@ -37,6 +38,7 @@ struct Profiler {
   std::vector<cudaEvent_t> pool;
   double ms[PK_COUNT] = {};
   u64 launches[PK_COUNT] = {};
+  u64 bytes[PK_COUNT] = {};  // algorithmic bytes of the launches of a class, where the launcher knows them
   cudaEvent_t get();
   void collect();   // call after the stream has been synchronised
   void reset();
@@ -101,9 +103,11 @@ struct SortParams {
 struct GroupLists {  // device
   u32* glist;        // starts of groups larger than TINY_MAX
   u32 gcap;
-  u32* med;          // (start, size) pairs
+  u32* med;          // (start, size) pairs, one list per size class: class c starts at pair med_class_off(medN, c)
+  u32 medN;          // the N the class offsets are computed from (length of the sorted array)
   u32* big;          // (start, size, known common depth) triples
-  u32* counters;     // [0] = #glist, [1] = #med, [2] = #big, [3] = overflow flag
+  u32* counters;     // [0] = #glist, [1] = #med, [2] = #big, [3] = overflow flag, [4..9] = groups per medium class,
+                     // [10..15] = elements per medium class
   u64* tied;         // statistics: elements found in groups
 };
 void groups_tiny_u32(const u32* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st);
@@ -111,7 +115,26 @@ void groups_tiny_u64(const u64* keys, u32* pos, u32 N, SortParams sp, u64 h, Gro
 void groups_classify_u32(const u32* keys, u32 N, u32 ng, GroupLists gl, u32 h, cudaStream_t st);
 // kind: 1 / 2 = pivot keys of the big path, bounded / unbounded layout (the group depth is decoded from the key)
 void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, int kind, u32 h, cudaStream_t st);
-void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st);
+#define GL_COUNTERS 16
+#define MED_CLASSES 6
+// medium size classes: TINY_MAX < size <= 32, 64, 128, 256, 512, 2048.  A class holding groups larger than `lo` has at
+// most N / (lo + 1) of them: its list starts at this pair index of `med`
+__host__ __device__ inline u64 med_class_off(u32 N, u32 cls) {
+  u64 off = 0;
+  if (cls > 0) off += N / (TINY_MAX + 1) + 1;
+  if (cls > 1) off += N / 33 + 1;
+  if (cls > 2) off += N / 65 + 1;
+  if (cls > 3) off += N / 129 + 1;
+  if (cls > 4) off += N / 257 + 1;
+  if (cls > 5) off += N / 513 + 1;
+  return off;
+}
+__host__ __device__ inline u32 med_class_of(u32 size) {
+  return size <= 32 ? 0u : size <= 64 ? 1u : size <= 128 ? 2u : size <= 256 ? 3u : size <= 512 ? 4u : 5u;
+}
+// class_groups[6] / class_elems[6]: groups and elements per size class (a class without groups is not launched)
+void groups_medium(u32* pos, const u32* med, u32 medN, const u32* class_groups, const u32* class_elems, SortParams sp,
+                   u64 h, cudaStream_t st);
 // sizes[g] = big[3g+1]
 void big_sizes(const u32* big, u32 nbig, u32* sizes, cudaStream_t st);
 // worklist of the big groups (one pivot round, see lms_sort.cu): wkey = [group | side | q | bases] against the

@@ -220,9 +220,12 @@ __global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ k
   u32 size = (u32)(hi - start);
   atomicAdd(gl.tied, (u64)size);
   if (size <= MED_MAX) {
-    u32 j = atomicAdd(&gl.counters[1], 1u);
+    const u32 cls = med_class_of(size);
+    atomicAdd(&gl.counters[1], 1u);
+    const u64 j = med_class_off(gl.medN, cls) + atomicAdd(&gl.counters[4 + cls], 1u);
     gl.med[2 * j] = (u32)start;
     gl.med[2 * j + 1] = size;
+    atomicAdd(&gl.counters[10 + cls], size);
   } else {
     u32 j = atomicAdd(&gl.counters[2], 1u);
     gl.big[3 * j] = (u32)start;
@@ -234,12 +237,14 @@ __global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ k
 void groups_tiny_u32(const u32* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st) {
   if (!N) return;
   ProfScope ps(PK_GROUPS_TINY, st);
+  if (ps.p) ps.p->bytes[PK_GROUPS_TINY] += 8ull * N;  // key + position
   k_groups_tiny<u32><<<(N + TG_TILE - 1) / TG_TILE, TG_THREADS, 0, st>>>(keys, pos, N, sp, h, gl);
   CK_LAUNCH(); g_launches++;
 }
 void groups_tiny_u64(const u64* keys, u32* pos, u32 N, SortParams sp, u64 h, GroupLists gl, cudaStream_t st) {
   if (!N) return;
   ProfScope ps(PK_GROUPS_TINY, st);
+  if (ps.p) ps.p->bytes[PK_GROUPS_TINY] += 12ull * N;
   k_groups_tiny<u64><<<(N + TG_TILE - 1) / TG_TILE, TG_THREADS, 0, st>>>(keys, pos, N, sp, h, gl);
   CK_LAUNCH(); g_launches++;
 }
@@ -397,8 +402,7 @@ __device__ __forceinline__ void team_sort(u64 (&x)[R], const u32 w, const u32 la
 
 template <int NW, int R, bool UNB>
 __global__ void __launch_bounds__(256, (R >= 8 ? 2 : 4)) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med,
-                                                                        u32 nmed, SortParams sp, u64 h, u32 size_lo,
-                                                                        u32 size_hi) {
+                                                                        u32 nmed, SortParams sp, u64 h) {
   constexpr u32 P = NW * R * 32;
   constexpr u32 TEAMS = NW == 1 ? 8 : 1;
   static_assert(P <= 2048, "slot field is 11 bits");
@@ -415,7 +419,6 @@ __global__ void __launch_bounds__(256, (R >= 8 ? 2 : 4)) k_groups_medium(u32* __
   u32* sdep = s_dep + team * P;
   for (u32 gi = blockIdx.x * TEAMS + team; gi < nmed; gi += gridDim.x * TEAMS) {
     const u32 start = med[2 * gi], size = med[2 * gi + 1];
-    if (size <= size_lo || size > size_hi) continue;  // (uniform per team)
 #pragma unroll
     for (int r = 0; r < R; r++) {
       const u32 i = ((w * R + r) << 5) | lane;
@@ -510,33 +513,35 @@ __global__ void __launch_bounds__(256, (R >= 8 ? 2 : 4)) k_groups_medium(u32* __
   }
 }
 
+template <int NW, int R, bool UNB>
+static void groups_medium_class(int pk, u32 cls, u32* pos, const u32* med, u32 medN, const u32* cg, const u32* ce,
+                                SortParams sp, u64 h, cudaStream_t st) {
+  const u32 ngroups = cg[cls];
+  if (!ngroups) return;
+  ProfScope ps(pk, st);
+  if (ps.p) ps.p->bytes[pk] += 16ull * ce[cls];  // position read + write, one 8-byte key word
+  u32 grid = NW == 1 ? (ngroups + 7) / 8 : ngroups;
+  if (grid > 1048576u) grid = 1048576u;
+  k_groups_medium<NW, R, UNB><<<grid, 256, 0, st>>>(pos, med + 2 * med_class_off(medN, cls), ngroups, sp, h);
+  CK_LAUNCH(); g_launches++;
+}
 template <bool UNB>
-static void groups_medium_launch(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st) {
-  u32 gw = (nmed + 7) / 8, gb = nmed;
-  if (gw > 1048576u) gw = 1048576u;
-  if (gb > 1048576u) gb = 1048576u;
-  // every launch walks the whole list and takes the groups of its size class
-  k_groups_medium<1, 1, UNB><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h, 0u, 32u);
-  CK_LAUNCH();
-  k_groups_medium<1, 2, UNB><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h, 32u, 64u);
-  CK_LAUNCH();
-  k_groups_medium<1, 4, UNB><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h, 64u, 128u);
-  CK_LAUNCH();
-  k_groups_medium<1, 8, UNB><<<gw, 256, 0, st>>>(pos, med, nmed, sp, h, 128u, 256u);
-  CK_LAUNCH();
-  k_groups_medium<8, 2, UNB><<<gb, 256, 0, st>>>(pos, med, nmed, sp, h, 256u, 512u);
-  CK_LAUNCH();
-  k_groups_medium<8, 8, UNB><<<gb, 256, 0, st>>>(pos, med, nmed, sp, h, 512u, 2048u);
-  CK_LAUNCH();
-  g_launches += 6;
+static void groups_medium_launch(u32* pos, const u32* med, u32 medN, const u32* cg, const u32* ce, SortParams sp, u64 h,
+                                 cudaStream_t st) {
+  groups_medium_class<1, 1, UNB>(PK_GROUPS_MEDIUM, 0, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<1, 2, UNB>(PK_GROUPS_MEDIUM_64, 1, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<1, 4, UNB>(PK_GROUPS_MEDIUM_128, 2, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<1, 8, UNB>(PK_GROUPS_MEDIUM_256, 3, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<8, 2, UNB>(PK_GROUPS_MEDIUM_512, 4, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<8, 8, UNB>(PK_GROUPS_MEDIUM_2048, 5, pos, med, medN, cg, ce, sp, h, st);
 }
 
-void groups_medium(u32* pos, const u32* med, u32 nmed, SortParams sp, u64 h, cudaStream_t st) {
-  if (!nmed || h >= sp.D) return;
-  ProfScope ps(PK_GROUPS_MEDIUM, st);
+void groups_medium(u32* pos, const u32* med, u32 medN, const u32* class_groups, const u32* class_elems, SortParams sp,
+                   u64 h, cudaStream_t st) {
+  if (h >= sp.D) return;
   // the 12-bit q field of the bounded key holds depths up to 4095
-  if (sp.D == KISS_UNBOUNDED || sp.D > 4000) groups_medium_launch<true>(pos, med, nmed, sp, h, st);
-  else groups_medium_launch<false>(pos, med, nmed, sp, h, st);
+  if (sp.D == KISS_UNBOUNDED || sp.D > 4000) groups_medium_launch<true>(pos, med, medN, class_groups, class_elems, sp, h, st);
+  else groups_medium_launch<false>(pos, med, medN, class_groups, class_elems, sp, h, st);
 }
 
 // ------------------------------------------------------------------------------------------- big groups

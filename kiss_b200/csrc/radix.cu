@@ -19,7 +19,9 @@ thread_local Profiler* g_prof = nullptr;
 
 const char* prof_name(int id) {
   static const char* names[PK_COUNT] = {"k_pack_codes", "k_lms_summary+carry+mask", "k_lms_emit", "k_scan_*", "k_radix_hist",
-                                        "k_radix_scatter", "k_groups_tiny", "k_groups_medium", "k_groups_classify+big_*",
+                                        "k_radix_scatter", "k_groups_tiny", "k_groups_medium<=32", "k_groups_medium<=64",
+                                        "k_groups_medium<=128", "k_groups_medium<=256", "k_groups_medium<=512",
+                                        "k_groups_medium<=2048", "k_groups_classify+big_*",
                                         "k_short_*", "k_place/merge_lms", "k_wave_fused(lms)", "k_wave_fused", "k_wave_small/tail"};
   return (id >= 0 && id < PK_COUNT) ? names[id] : "?";
 }
@@ -38,7 +40,7 @@ void Profiler::collect() {
   recs.clear();
 }
 void Profiler::reset() {
-  for (int i = 0; i < PK_COUNT; i++) { ms[i] = 0; launches[i] = 0; }
+  for (int i = 0; i < PK_COUNT; i++) { ms[i] = 0; launches[i] = 0; bytes[i] = 0; }
 }
 Profiler::~Profiler() {
   collect();
@@ -445,12 +447,14 @@ static void radix_sort_impl(K*& keys, u32*& vals, K*& keys_alt, u32*& vals_alt, 
     u32 mask = (1u << bits) - 1u;
     {
       ProfScope ps(PK_RADIX_HIST, st);
+      if (ps.p) ps.p->bytes[PK_RADIX_HIST] += sizeof(K) * (u64)N;
       k_radix_hist<K><<<ntiles, RADIX_THREADS, 0, st>>>(keys, N, shift, mask, H, ntiles);
       CK_LAUNCH();
     }
     scan_excl_u32(H, (u64)256 * ntiles, partials, nullptr, st);
     {
       ProfScope ps(PK_RADIX_SCATTER, st);
+      if (ps.p) ps.p->bytes[PK_RADIX_SCATTER] += 2 * (sizeof(K) + 4) * (u64)N;  // read + write of (key, position)
       static const bool classic = getenv("KISS_B200_RADIX") && std::string(getenv("KISS_B200_RADIX")) == "classic";
       bool aligned = (((uintptr_t)keys | (uintptr_t)vals) & 15) == 0;
       if (classic || !aligned) {

@@ -155,6 +155,17 @@ class Context:
             i += 1
         return out
 
+    def profile_alg_bytes(self):
+        """{kernel class: algorithmic bytes of its launches} for the classes whose launcher knows them"""
+        out, i = {}, 0
+        name, ms, cnt, units = C.c_char_p(), C.c_double(), C.c_uint64(), C.c_uint64()
+        while lib().kiss_b200_profile_read(self._h, i, C.byref(name), C.byref(ms), C.byref(cnt)) == 0:
+            check(lib().kiss_b200_profile_alg_bytes(self._h, i, C.byref(units)))
+            if units.value:
+                out[name.value.decode()] = units.value
+            i += 1
+        return out
+
     def synth_uniform_dev(self, S_ptr, n, seed):
         check(lib().kiss_b200_synth_uniform_dev(self._h, S_ptr, n, seed))
 
