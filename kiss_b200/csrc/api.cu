@@ -275,6 +275,7 @@ u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const So
   if (!cn[0] || h >= sp.D) return 0;
   groups_classify_u32(keys, N, cn[0], gl, (u32)h, c->st);
   sync.read(gl.counters, GL_COUNTERS, cn);
+  cn[1] = cn[4] + cn[5] + cn[6] + cn[7] + cn[8] + cn[9];
   debug_groups(c, "u32", N, h, cn, gl);
   groups_medium(pos, gl.med, gl.medN, cn + 4, cn + 10, sp, h, c->st);
   return cn[2];
@@ -290,6 +291,7 @@ u32 run_groups<u64>(kiss_b200_ctx* c, const u64* keys, u32* pos, u32 N, const So
   if (!cn[0] || h >= sp.D) return 0;
   groups_classify_u64(keys, N, cn[0], gl, kind, (u32)h, c->st);
   sync.read(gl.counters, GL_COUNTERS, cn);
+  cn[1] = cn[4] + cn[5] + cn[6] + cn[7] + cn[8] + cn[9];
   debug_groups(c, "u64", N, h, cn, gl);
   groups_medium(pos, gl.med, gl.medN, cn + 4, cn + 10, sp, h, c->st);
   return cn[2];
@@ -752,6 +754,7 @@ int kiss_b200_create(kiss_b200_ctx** out, int device) {
     CK(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &thr));
     radix_init();
     wave_init();
+    // (cudaLimitMaxL2FetchGranularity 32 / 128 instead of the default measured no different on either workload)
   } catch (const CudaError& err) {
     g_last_error = err.what();
     delete c;

@@ -377,6 +377,73 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
     const u64 cc = sh.cur[bucket], p = sh.p;
     const u64 len = DOWN ? p - cc : cc - p;
     if (len == 0 || len > WAVE_TAIL_MAX || sh.nwaves >= max_waves) break;
+    if (len > 32 && len <= WAVE_THREADS) {
+      // Waves of at most one entry per thread (repeat-rich text: thousands per bucket, shrinking from a few
+      // hundred entries to a handful): ballot ranks, one packed count per warp, two block barriers per wave,
+      // cursors replicated in registers — and, as in the warp path below, the entries appended to this bucket are
+      // handed to the next wave through shared memory instead of a global-memory round trip.  (The full tile
+      // machinery — 16 slots per thread, staging, coalesced copy-out — costs ~2 us per wave whatever its size.)
+      __syncthreads();  // (every thread has read sh.cur / sh.p)
+      const u32 t = threadIdx.x, lane = t & 31u, w = t >> 5;
+      u32* nbv = sh.sm.sSA;   // next wave's entries, in rank order
+      u32* nbc = sh.sm.sCTX;
+      u64 c0 = sh.cur[0], c1 = sh.cur[1], c2 = sh.cur[2], c3 = sh.cur[3], pp = p;
+      u32 nw = sh.nwaves;
+      bool have = false;
+      for (;;) {
+        const u64 cb = bucket == 0 ? c0 : bucket == 1 ? c1 : bucket == 2 ? c2 : c3;
+        const u64 ln = DOWN ? pp - cb : cb - pp;
+        if (ln <= 32 || ln > WAVE_THREADS || nw >= max_waves) break;  // (uniform: every thread holds the same cursors)
+        u32 v = 0, c = 1u;
+        if (t < ln) {
+          if (have) {
+            v = nbv[t];
+            c = nbc[t];
+          } else {
+            const u64 slot = DOWN ? pp - 1 - t : pp + t;
+            v = a0.SA[slot];
+            c = a0.CTX[slot];
+          }
+        }
+        if (c == 1u && v != 0 && v != KISS_EMPTY) c = ctx_gather(a0.T, v);
+        const u32 cu = ctx_symbol(c, a0.symmask);
+        const u32 m0 = __ballot_sync(0xffffffffu, cu == 0), m1 = __ballot_sync(0xffffffffu, cu == 1),
+                  m2 = __ballot_sync(0xffffffffu, cu == 2), m3 = __ballot_sync(0xffffffffu, cu == 3);
+        if (lane == 0)
+          sh.wsum[w] = (u64)__popc(m0) | ((u64)__popc(m1) << 16) | ((u64)__popc(m2) << 32) | ((u64)__popc(m3) << 48);
+        __syncthreads();  // counts published; every thread has read its entry from the hand-over buffer
+        u64 before = 0, total = 0;
+#pragma unroll
+        for (u32 ww = 0; ww < WAVE_WARPS; ww++) {
+          const u64 x = sh.wsum[ww];
+          total += x;
+          if (ww < w) before += x;
+        }
+        if (cu < 4) {
+          const u32 mm = cu == 0 ? m0 : cu == 1 ? m1 : cu == 2 ? m2 : m3;
+          const u64 cs = cu == 0 ? c0 : cu == 1 ? c1 : cu == 2 ? c2 : c3;
+          const u32 r = ((u32)(before >> (16 * cu)) & 0xFFFFu) + __popc(mm & ((1u << lane) - 1u));
+          const u64 dst = DOWN ? cs - 1 - r : cs + r;
+          a0.SA[dst] = v - 1u;
+          a0.CTX[dst] = c >> 2;
+          if (cu == bucket) { nbv[r] = v - 1u; nbc[r] = c >> 2; }
+        }
+        const u32 t0 = (u32)total & 0xFFFFu, t1 = (u32)(total >> 16) & 0xFFFFu, t2 = (u32)(total >> 32) & 0xFFFFu,
+                  t3 = (u32)(total >> 48);
+        pp = cb;
+        if (DOWN) { c0 -= t0; c1 -= t1; c2 -= t2; c3 -= t3; }
+        else { c0 += t0; c1 += t1; c2 += t2; c3 += t3; }
+        nw++;
+        have = true;
+        __syncthreads();  // hand-over buffer complete; the counts may be rewritten
+      }
+      if (t == 0) {
+        sh.cur[0] = c0; sh.cur[1] = c1; sh.cur[2] = c2; sh.cur[3] = c3;
+        sh.p = pp;
+        sh.nwaves = nw;
+      }
+      continue;
+    }
     if (len <= 32) {
       // Waves of at most one warp's width (the chains of homopolymer / tandem runs: one wave per base, thousands
       // per bucket on repeat-rich text): warp 0 runs them alone — one entry per lane, ballot ranks, no block
@@ -386,34 +453,49 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
         const u32 lane = threadIdx.x;
         u64 c0 = sh.cur[0], c1 = sh.cur[1], c2 = sh.cur[2], c3 = sh.cur[3], pp = p;
         u32 nw = sh.nwaves;
+        // The entries a wave appends to its own bucket ARE the next wave, in rank order: they are handed on in
+        // registers (lane r of the next wave takes them from the lane that ranked r), so the chain of waves
+        // never waits on a global-memory round trip; only the first wave is loaded.
+        bool have = false;
+        u32 v = 0, c = 1u;
         for (;;) {
           const u64 cb = bucket == 0 ? c0 : bucket == 1 ? c1 : bucket == 2 ? c2 : c3;
           const u64 ln = DOWN ? pp - cb : cb - pp;
           if (ln == 0 || ln > 32 || nw >= max_waves) break;
-          u32 v = 0, c = 1u;
-          if (lane < ln) {
-            const u64 slot = DOWN ? pp - 1 - lane : pp + lane;
-            v = a0.SA[slot];
-            c = a0.CTX[slot];
-            if (c == 1u && v != 0 && v != KISS_EMPTY) c = ctx_gather(a0.T, v);
+          if (!have) {
+            v = 0; c = 1u;
+            if (lane < ln) {
+              const u64 slot = DOWN ? pp - 1 - lane : pp + lane;
+              v = a0.SA[slot];
+              c = a0.CTX[slot];
+            }
           }
+          if (c == 1u && v != 0 && v != KISS_EMPTY) c = ctx_gather(a0.T, v);
           const u32 cu = ctx_symbol(c, a0.symmask);
           const u32 m0 = __ballot_sync(0xffffffffu, cu == 0), m1 = __ballot_sync(0xffffffffu, cu == 1),
                     m2 = __ballot_sync(0xffffffffu, cu == 2), m3 = __ballot_sync(0xffffffffu, cu == 3);
+          const u32 nv = v - 1u, nc = c >> 2;
           if (cu < 4) {
             const u32 mm = cu == 0 ? m0 : cu == 1 ? m1 : cu == 2 ? m2 : m3;
             const u64 cs = cu == 0 ? c0 : cu == 1 ? c1 : cu == 2 ? c2 : c3;
             const u32 r = __popc(mm & ((1u << lane) - 1u));
             const u64 dst = DOWN ? cs - 1 - r : cs + r;
-            a0.SA[dst] = v - 1u;
-            a0.CTX[dst] = c >> 2;
+            a0.SA[dst] = nv;
+            a0.CTX[dst] = nc;
           }
+          // next wave: lane r <- the lane whose entry ranked r in this bucket
+          const u32 mb = bucket == 0 ? m0 : bucket == 1 ? m1 : bucket == 2 ? m2 : m3;
+          const u32 src = __fns(mb, 0, lane + 1);  // lane of the (lane+1)-th set bit, 0xffffffff if none
+          const u32 tv = __shfl_sync(0xffffffffu, nv, src & 31u), tc = __shfl_sync(0xffffffffu, nc, src & 31u);
+          v = src < 32u ? tv : 0u;
+          c = src < 32u ? tc : 1u;
+          have = true;
           pp = cb;
           if (DOWN) { c0 -= __popc(m0); c1 -= __popc(m1); c2 -= __popc(m2); c3 -= __popc(m3); }
           else { c0 += __popc(m0); c1 += __popc(m1); c2 += __popc(m2); c3 += __popc(m3); }
           nw++;
-          __syncwarp();  // (orders this wave's stores before the next wave's loads)
         }
+        __syncwarp();
         if (lane == 0) {
           sh.cur[0] = c0; sh.cur[1] = c1; sh.cur[2] = c2; sh.cur[3] = c3;
           sh.p = pp;

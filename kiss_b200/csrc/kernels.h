@@ -106,7 +106,7 @@ struct GroupLists {  // device
   u32* med;          // (start, size) pairs, one list per size class: class c starts at pair med_class_off(medN, c)
   u32 medN;          // the N the class offsets are computed from (length of the sorted array)
   u32* big;          // (start, size, known common depth) triples
-  u32* counters;     // [0] = #glist, [1] = #med, [2] = #big, [3] = overflow flag, [4..9] = groups per medium class,
+  u32* counters;     // [0] = #glist, [1] = (host: #med), [2] = #big, [3] = overflow flag, [4..9] = groups per medium class,
                      // [10..15] = elements per medium class
   u64* tied;         // statistics: elements found in groups
 };

@@ -13,6 +13,7 @@
 //   big               radix rounds: composite key (group id, next 16 bases) sorted with the LSD sort, the
 //                     resulting sub-groups go through the same three cases at the next depth
 // All paths are stable with respect to text position, which is the reference's final tie-break (:131-133).
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -90,6 +91,15 @@ __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict_
       const bool prev = e > 0 && k[i] == k[i + 1], next = e + 1 < N && k[i + 2] == k[i + 1];
       if (e < N && (prev || next)) tmask |= 1u << i;
       if (e < N && next && !prev) hmask |= 1u << i;
+    }
+    // a thread whose 8 keys and both neighbours are all equal sits inside a run of >= 10 > TINY_MAX: that group is
+    // not handled here (phase 3 hands it on by its head), so its elements need no position / text gathers
+    // (repeat-rich text: most tied elements are in such runs)
+    if (e0 > 0 && e0 + TG_ITEMS < N && k[0] == k[1] && k[TG_ITEMS + 1] == k[TG_ITEMS]) {
+      bool alleq = true;
+#pragma unroll
+      for (int i = 1; i < TG_ITEMS; i++) alleq &= k[i] == k[i + 1];
+      if (alleq) tmask = 0;
     }
     // the halo: elements past the tile that may belong to a group starting inside it
     bool halo_tied = false;
@@ -200,33 +210,51 @@ __device__ __forceinline__ u32 group_depth(u64 key, int kind, u32 h) {
 template <typename K>
 __global__ void __launch_bounds__(128) k_groups_classify(const K* __restrict__ keys, u32 N, u32 ng, GroupLists gl,
                                                         int kind, u32 h) {
-  u32 g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= ng) return;
-  u64 start = gl.glist[g];
-  K k = keys[start];
-  // keys[start + TINY_MAX] == k is known; gallop, then bisect for the first index whose key differs
-  u64 lo = start + TINY_MAX, hi, step = TINY_MAX;
-  for (;;) {
-    u64 nx = lo + step;
-    if (nx >= N) { hi = N; break; }
-    if (keys[nx] != k) { hi = nx; break; }
-    lo = nx;
-    step <<= 1;
+  const u32 g = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
+  const bool valid = g < ng;
+  u64 start = 0;
+  u32 size = 0;
+  K k = 0;
+  if (valid) {
+    start = gl.glist[g];
+    k = keys[start];
+    // keys[start + TINY_MAX] == k is known; gallop, then bisect for the first index whose key differs
+    u64 lo = start + TINY_MAX, hi, step = TINY_MAX;
+    for (;;) {
+      u64 nx = lo + step;
+      if (nx >= N) { hi = N; break; }
+      if (keys[nx] != k) { hi = nx; break; }
+      lo = nx;
+      step <<= 1;
+    }
+    while (hi - lo > 1) {
+      u64 mid = lo + (hi - lo) / 2;
+      if (keys[mid] == k) lo = mid; else hi = mid;
+    }
+    size = (u32)(hi - start);
   }
-  while (hi - lo > 1) {
-    u64 mid = lo + (hi - lo) / 2;
-    if (keys[mid] == k) lo = mid; else hi = mid;
+  // statistics and list slots: one atomic per warp and class (millions of groups on repeat-rich text)
+  const u32 wsum = __reduce_add_sync(0xffffffffu, size);
+  if (lane == 0 && wsum) atomicAdd(gl.tied, (u64)wsum);
+  const u32 cls = !valid ? 7u : size <= MED_MAX ? med_class_of(size) : 6u;
+#pragma unroll
+  for (u32 c = 0; c < MED_CLASSES; c++) {
+    const u32 mask = __ballot_sync(0xffffffffu, cls == c);
+    if (cls == c) {
+      const u32 leader = __ffs(mask) - 1u;
+      const u32 esum = __reduce_add_sync(mask, size);
+      u32 base = 0;
+      if (lane == leader) {
+        base = atomicAdd(&gl.counters[4 + c], (u32)__popc(mask));
+        atomicAdd(&gl.counters[10 + c], esum);
+      }
+      base = __shfl_sync(mask, base, leader);
+      const u64 j = med_class_off(gl.medN, c) + base + __popc(mask & ((1u << lane) - 1u));
+      gl.med[2 * j] = (u32)start;
+      gl.med[2 * j + 1] = size;
+    }
   }
-  u32 size = (u32)(hi - start);
-  atomicAdd(gl.tied, (u64)size);
-  if (size <= MED_MAX) {
-    const u32 cls = med_class_of(size);
-    atomicAdd(&gl.counters[1], 1u);
-    const u64 j = med_class_off(gl.medN, cls) + atomicAdd(&gl.counters[4 + cls], 1u);
-    gl.med[2 * j] = (u32)start;
-    gl.med[2 * j + 1] = size;
-    atomicAdd(&gl.counters[10 + cls], size);
-  } else {
+  if (cls == 6u) {
     u32 j = atomicAdd(&gl.counters[2], 1u);
     gl.big[3 * j] = (u32)start;
     gl.big[3 * j + 1] = size;
@@ -353,55 +381,68 @@ __device__ __forceinline__ u64 class_depth(u64 key) {
   return (side == 2 ? 0xFFFFFFFFull - qk : qk) + 1ull;
 }
 
-// ascending bitonic sort of the team's NW * R * 32 keys (slot order = (w R + r) 32 + lane)
+// ascending bitonic sort of the team's NW * R * 32 keys (slot order = (w R + r) 32 + lane).  The stage (k2) and
+// shuffle / shared-memory step (j) loops stay ROLLED: one body per kind of step — a fully unrolled network is 66
+// steps x R at 2048 slots, 44 k instructions that miss the instruction cache (12 % of the stall samples) and made
+// ptxas keep x[] in local memory (10 % of all instructions were LDL / STL, profiles/r1_c3_medium2048_v0.txt).
+// Only the register steps (partner = another register of the same lane) need a compile-time distance.
+template <int NW, int R, int JR>
+__device__ __forceinline__ void sort_step_reg(u64 (&x)[R], const u32 w, const u32 lane, const u32 k2) {
+#pragma unroll
+  for (int r = 0; r < R; r++) {
+    if ((r & JR) == 0) {
+      const u32 i = ((w * R + r) << 5) | lane;
+      const bool asc = (i & k2) == 0;
+      const u64 a = x[r], b = x[r | JR];
+      const u64 lo = a < b ? a : b, hi = a < b ? b : a;
+      x[r] = asc ? lo : hi;
+      x[r | JR] = asc ? hi : lo;
+    }
+  }
+}
 template <int NW, int R>
 __device__ __forceinline__ void team_sort(u64 (&x)[R], const u32 w, const u32 lane, u64* sx) {
-  constexpr int P = NW * R * 32;
-#pragma unroll
-  for (int k2 = 2; k2 <= P; k2 <<= 1) {
-#pragma unroll
-    for (int j = k2 >> 1; j > 0; j >>= 1) {
-      if (j < 32) {
-#pragma unroll
-        for (int r = 0; r < R; r++) {
-          const u32 i = ((w * R + r) << 5) | lane;
-          const u64 y = __shfl_xor_sync(0xffffffffu, x[r], j);
-          const bool takemin = ((i & k2) == 0) == ((lane & j) == 0);
-          x[r] = takemin ? (x[r] < y ? x[r] : y) : (x[r] < y ? y : x[r]);
-        }
-      } else if (j < 32 * R) {
-        const int jr = j >> 5;
-#pragma unroll
-        for (int r = 0; r < R; r++) {
-          if ((r & jr) == 0) {
-            const int r2 = r | jr;
-            const u32 i = ((w * R + r) << 5) | lane;
-            const bool asc = (i & k2) == 0;
-            const u64 a = x[r], b = x[r2];
-            const u64 lo = a < b ? a : b, hi = a < b ? b : a;
-            x[r] = asc ? lo : hi;
-            x[r2] = asc ? hi : lo;
-          }
-        }
-      } else {  // partner in another warp of the block
+  constexpr u32 P = NW * R * 32;
+  constexpr int UNROLL = P <= 64 ? 16 : 1;  // the small warp teams keep the unrolled network (measured faster there)
+#pragma unroll UNROLL
+  for (u32 k2 = 2; k2 <= P; k2 <<= 1) {
+    if constexpr (NW > 1) {  // partner in another warp of the block
+#pragma unroll 1
+      for (u32 j = k2 >> 1; j >= 32u * R; j >>= 1) {
 #pragma unroll
         for (int r = 0; r < R; r++) sx[((w * R + r) << 5) | lane] = x[r];
         __syncthreads();
 #pragma unroll
         for (int r = 0; r < R; r++) {
           const u32 i = ((w * R + r) << 5) | lane;
-          const u64 y = sx[i ^ (u32)j];
+          const u64 y = sx[i ^ j];
           const bool takemin = ((i & k2) == 0) == ((i & j) == 0);
           x[r] = takemin ? (x[r] < y ? x[r] : y) : (x[r] < y ? y : x[r]);
         }
         __syncthreads();
       }
     }
+    if constexpr (R > 16) { if (k2 > 32u * 16) sort_step_reg<NW, R, 16>(x, w, lane, k2); }
+    if constexpr (R > 8) { if (k2 > 32u * 8) sort_step_reg<NW, R, 8>(x, w, lane, k2); }
+    if constexpr (R > 4) { if (k2 > 32u * 4) sort_step_reg<NW, R, 4>(x, w, lane, k2); }
+    if constexpr (R > 2) { if (k2 > 32u * 2) sort_step_reg<NW, R, 2>(x, w, lane, k2); }
+    if constexpr (R > 1) { if (k2 > 32u) sort_step_reg<NW, R, 1>(x, w, lane, k2); }
+#pragma unroll UNROLL
+    for (u32 j = k2 > 32u ? 16u : (k2 >> 1); j > 0; j >>= 1) {
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const u32 i = ((w * R + r) << 5) | lane;
+        const u64 y = __shfl_xor_sync(0xffffffffu, x[r], j);
+        const bool takemin = ((i & k2) == 0) == ((lane & j) == 0);
+        x[r] = takemin ? (x[r] < y ? x[r] : y) : (x[r] < y ? y : x[r]);
+      }
+    }
   }
 }
 
+#define MED_THREADS(NW) ((NW) == 1 ? 256 : (NW) * 32)
 template <int NW, int R, bool UNB>
-__global__ void __launch_bounds__(256, (R >= 8 ? 2 : 4)) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med,
+__global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4))) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med,
                                                                         u32 nmed, SortParams sp, u64 h) {
   constexpr u32 P = NW * R * 32;
   constexpr u32 TEAMS = NW == 1 ? 8 : 1;
@@ -410,7 +451,7 @@ __global__ void __launch_bounds__(256, (R >= 8 ? 2 : 4)) k_groups_medium(u32* __
   __shared__ u32 s_pos[TEAMS * P];
   __shared__ u32 s_seg[TEAMS * P];
   __shared__ u32 s_dep[TEAMS * P];  // depth of the segment, kept at its head slot
-  __shared__ u32 s_scan[8];
+  __shared__ u32 s_scan[NW];
   const u32 lane = threadIdx.x & 31u, wb = threadIdx.x >> 5;
   const u32 team = NW == 1 ? wb : 0u, w = NW == 1 ? 0u : wb;
   u64* skey = s_key + team * P;
@@ -522,7 +563,7 @@ static void groups_medium_class(int pk, u32 cls, u32* pos, const u32* med, u32 m
   if (ps.p) ps.p->bytes[pk] += 16ull * ce[cls];  // position read + write, one 8-byte key word
   u32 grid = NW == 1 ? (ngroups + 7) / 8 : ngroups;
   if (grid > 1048576u) grid = 1048576u;
-  k_groups_medium<NW, R, UNB><<<grid, 256, 0, st>>>(pos, med + 2 * med_class_off(medN, cls), ngroups, sp, h);
+  k_groups_medium<NW, R, UNB><<<grid, MED_THREADS(NW), 0, st>>>(pos, med + 2 * med_class_off(medN, cls), ngroups, sp, h);
   CK_LAUNCH(); g_launches++;
 }
 template <bool UNB>
@@ -533,7 +574,10 @@ static void groups_medium_launch(u32* pos, const u32* med, u32 medN, const u32* 
   groups_medium_class<1, 4, UNB>(PK_GROUPS_MEDIUM_128, 2, pos, med, medN, cg, ce, sp, h, st);
   groups_medium_class<1, 8, UNB>(PK_GROUPS_MEDIUM_256, 3, pos, med, medN, cg, ce, sp, h, st);
   groups_medium_class<8, 2, UNB>(PK_GROUPS_MEDIUM_512, 4, pos, med, medN, cg, ce, sp, h, st);
-  groups_medium_class<8, 8, UNB>(PK_GROUPS_MEDIUM_2048, 5, pos, med, medN, cg, ce, sp, h, st);
+  // 16 warps x 4 keys per thread (2 blocks = 32 warps per SM): 36.6 ms against 40.6 ms for 8 warps x 8 keys on C3
+  static const bool narrow = getenv("KISS_B200_MED_NARROW") != nullptr;
+  if (!narrow) groups_medium_class<16, 4, UNB>(PK_GROUPS_MEDIUM_2048, 5, pos, med, medN, cg, ce, sp, h, st);
+  else groups_medium_class<8, 8, UNB>(PK_GROUPS_MEDIUM_2048, 5, pos, med, medN, cg, ce, sp, h, st);
 }
 
 void groups_medium(u32* pos, const u32* med, u32 medN, const u32* class_groups, const u32* class_elems, SortParams sp,
