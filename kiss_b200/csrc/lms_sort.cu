@@ -466,11 +466,20 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
       spos[i] = i < size ? pos[start + i] : KISS_EMPTY;
       sseg[i] = i < size ? 0u : 0xFFFFFFFFu;
     }
-    if (threadIdx.x % (NW * 32) == 0) sdep[0] = (u32)h;
+    if (threadIdx.x % (NW * 32) == 0) { sdep[0] = (u32)h; sdep[1] = size; }
     team_sync<NW>();
+    // Two ways to order the segments of a round.  The bitonic network costs the same whatever the segments look
+    // like (LOGP (LOGP + 1) / 2 steps of ~12 instructions per key); counting, for every element, the smaller keys
+    // of its own segment costs ~4 instructions per segment member.  After the first round or two the segments are
+    // short, so the later rounds rank (ncu, C3: the network was ~90 % of the 25 G warp instructions of the
+    // largest class, issue slots 65 % busy, profiles/r1_c3_medium2048_v1.txt).
+    constexpr u32 LOGP = P == 32 ? 5 : P == 64 ? 6 : P == 128 ? 7 : P == 256 ? 8 : P == 512 ? 9 : P == 1024 ? 10 : 11;
+    constexpr u32 RANK_MAX = 2 * LOGP * (LOGP + 1);  // longest segment for which ranking is the cheaper way
+    u32 maxlen = size;                               // longest segment with >= 2 elements (team-uniform)
     for (;;) {
       u64 x[R];
       bool anyact = false, moved = false;
+      u32 actm = 0;
 #pragma unroll
       for (int r = 0; r < R; r++) {
         const u32 i = ((w * R + r) << 5) | lane;
@@ -481,6 +490,7 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
           key = 0;
           if (act) {
             anyact = true;
+            actm |= 1u << r;
             key = MK_EQUAL << MK_SIDE_SHIFT;
             if (sg != i) key = pivot_key<UNB>(sp, spos[i], spos[sg], sdep[sg]);
             moved |= ((key >> MK_SIDE_SHIFT) & 3ull) != MK_EQUAL;
@@ -491,13 +501,43 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
       }
       if (!team_or<NW>(anyact)) break;
       if (team_or<NW>(moved)) {
-        team_sort<NW, R>(x, w, lane, skey);
-        u32 pp[R];
+        if (maxlen > RANK_MAX) {
+          team_sort<NW, R>(x, w, lane, skey);
+          u32 pp[R];
 #pragma unroll
-        for (int r = 0; r < R; r++) pp[r] = x[r] != ~0ull ? spos[(u32)x[r] & 0x7FFu] : KISS_EMPTY;
-        team_sync<NW>();
+          for (int r = 0; r < R; r++) pp[r] = x[r] != ~0ull ? spos[(u32)x[r] & 0x7FFu] : KISS_EMPTY;
+          team_sync<NW>();
 #pragma unroll
-        for (int r = 0; r < R; r++) spos[((w * R + r) << 5) | lane] = pp[r];
+          for (int r = 0; r < R; r++) spos[((w * R + r) << 5) | lane] = pp[r];
+        } else {
+#pragma unroll
+          for (int r = 0; r < R; r++) skey[((w * R + r) << 5) | lane] = x[r];
+          team_sync<NW>();
+          u32 pp[R], dst[R];
+#pragma unroll
+          for (int r = 0; r < R; r++) {
+            const u32 i = ((w * R + r) << 5) | lane;
+            pp[r] = spos[i];
+            dst[r] = i;
+            if ((actm >> r) & 1u) {
+              const u32 sg = (u32)(x[r] >> MK_SEG_SHIFT);  // head slot of the segment; its end is kept at sdep[head + 1]
+              const u32 end = sdep[sg + 1];
+              u32 rank = 0;
+              for (u32 j = sg; j < end; j++) rank += skey[j] < x[r] ? 1u : 0u;
+              dst[r] = sg + rank;
+            }
+          }
+          team_sync<NW>();
+#pragma unroll
+          for (int r = 0; r < R; r++) {
+            skey[dst[r]] = x[r];
+            spos[dst[r]] = pp[r];
+          }
+          team_sync<NW>();
+#pragma unroll
+          for (int r = 0; r < R; r++) x[r] = skey[((w * R + r) << 5) | lane];
+          team_sync<NW>();
+        }
       }
 #pragma unroll
       for (int r = 0; r < R; r++) skey[((w * R + r) << 5) | lane] = x[r];
@@ -542,6 +582,30 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
           }
         }
       }
+      team_sync<NW>();
+      // segment ends (kept in the slot after the head: a segment that is still refined has >= 2 elements) and the
+      // longest segment
+      u32 ml = 0;
+#pragma unroll
+      for (int r = 0; r < R; r++) {
+        const u32 i = ((w * R + r) << 5) | lane;
+        if (i < size) {
+          const u32 hd = sseg[i];
+          if (hd != i && (i + 1 == size || sseg[i + 1] != hd)) {
+            sdep[hd + 1] = i + 1u;
+            ml = max(ml, i + 1u - hd);
+          }
+        }
+      }
+      ml = __reduce_max_sync(0xffffffffu, ml);
+      if constexpr (NW > 1) {
+        __syncthreads();  // (s_scan was read above)
+        if (lane == 0) s_scan[w] = ml;
+        __syncthreads();
+#pragma unroll
+        for (u32 ww = 0; ww < NW; ww++) ml = max(ml, s_scan[ww]);
+      }
+      maxlen = ml;
       team_sync<NW>();
     }
     team_sync<NW>();
