@@ -443,7 +443,7 @@ __device__ __forceinline__ void team_sort(u64 (&x)[R], const u32 w, const u32 la
 #define MED_THREADS(NW) ((NW) == 1 ? 256 : (NW) * 32)
 template <int NW, int R, bool UNB>
 __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4))) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med,
-                                                                        u32 nmed, SortParams sp, u64 h) {
+                                                                        u32 nmed, SortParams sp, u64 h, u32 rank_scale) {
   constexpr u32 P = NW * R * 32;
   constexpr u32 TEAMS = NW == 1 ? 8 : 1;
   static_assert(P <= 2048, "slot field is 11 bits");
@@ -474,7 +474,7 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
     // short, so the later rounds rank (ncu, C3: the network was ~90 % of the 25 G warp instructions of the
     // largest class, issue slots 65 % busy, profiles/r1_c3_medium2048_v1.txt).
     constexpr u32 LOGP = P == 32 ? 5 : P == 64 ? 6 : P == 128 ? 7 : P == 256 ? 8 : P == 512 ? 9 : P == 1024 ? 10 : 11;
-    constexpr u32 RANK_MAX = 2 * LOGP * (LOGP + 1);  // longest segment for which ranking is the cheaper way
+    const u32 RANK_MAX = rank_scale * LOGP * (LOGP + 1) / 2;  // longest segment for which ranking is the cheaper way
     u32 maxlen = size;                               // longest segment with >= 2 elements (team-uniform)
     for (;;) {
       u64 x[R];
@@ -627,7 +627,9 @@ static void groups_medium_class(int pk, u32 cls, u32* pos, const u32* med, u32 m
   if (ps.p) ps.p->bytes[pk] += 16ull * ce[cls];  // position read + write, one 8-byte key word
   u32 grid = NW == 1 ? (ngroups + 7) / 8 : ngroups;
   if (grid > 1048576u) grid = 1048576u;
-  k_groups_medium<NW, R, UNB><<<grid, MED_THREADS(NW), 0, st>>>(pos, med + 2 * med_class_off(medN, cls), ngroups, sp, h);
+  static const u32 rank_scale = [] { const char* e = getenv("KISS_B200_RANK_SCALE"); return e ? (u32)atoi(e) : 6u; }();  // C3: 2: 22.2 ms, 4: 20.5, 8: 19.8, 16: 21.7, 64: 41 (largest class)
+  k_groups_medium<NW, R, UNB><<<grid, MED_THREADS(NW), 0, st>>>(pos, med + 2 * med_class_off(medN, cls), ngroups, sp, h,
+                                                                rank_scale);
   CK_LAUNCH(); g_launches++;
 }
 template <bool UNB>

@@ -36,6 +36,10 @@ CASES = [
     ("copies5000", lambda: tg.near_identical_copies(20, 60, 5000, 0.003)),
     ("copies5000_dense", lambda: tg.near_identical_copies(21, 90, 5000, 0.08)),
     ("copies3000_exact", lambda: tg.near_identical_copies(22, 70, 3000, 0.0)),
+    # hundreds / thousands of parallel homopolymer runs: waves of 33..512 entries (one entry per thread in the
+    # on-device tail) and the hand-over from the tile path above 512 entries down to the single-warp path
+    ("runs300", lambda: tg.many_runs(23, 200_000, 300, 20, 300)),
+    ("runs3000", lambda: tg.many_runs(24, 600_000, 3000, 5, 120)),
 ]
 IDS = [c[0] for c in CASES]
 

@@ -83,6 +83,19 @@ def tandem(seed, n, arrays=20, max_unit=50, max_len=20000, tail=512):
     return S
 
 
+def many_runs(seed, n, runs, min_len, max_len, tail=512):
+    """uniform background with `runs` homopolymer runs (all four symbols) of min_len..max_len bases: the induction
+    chains inside a bucket then shrink from ~runs entries per wave to a handful (the on-device tail of the wave
+    kernels: tile path above 512 entries, one entry per thread up to 512, one warp up to 32)"""
+    S = uniform(seed, n).copy()
+    r = _Rng(seed)
+    for _ in range(runs):
+        L = r.between(min_len, max_len)
+        p = r.below(n - tail - L)
+        S[p:p + L] = r.below(4)
+    return S
+
+
 def low_entropy(seed, n, alphabet=2):
     """text over the first `alphabet` symbols only (long ties everywhere)"""
     return (uniform(seed, n) % alphabet).astype(np.uint8)

@@ -21,3 +21,7 @@ if [ "${SKIP_NCU:-0}" != "1" ]; then
   head -30 $OUT/${TAG}_launches.txt
 fi
 ls -la $OUT/${TAG}_*
+if [ "${SKIP_REF:-0}" != "1" ]; then
+  python bench.py --impl reference --steps 3 --warmup 1 > $OUT/${TAG}_bench_reference.json 2> $OUT/${TAG}_bench_reference.err
+  tail -c 400 $OUT/${TAG}_bench_reference.json
+fi
