@@ -192,10 +192,12 @@ def run_reference_arm(args):
 
 # ------------------------------------------------------------------------------------------ B200 arm
 # mean DRAM bytes (read + write) per launch, ncu dram__bytes_read.sum + dram__bytes_write.sum of one step
-# (profiles/r1_final_launches_1gbp.txt for c2, profiles/r1_c3_launches.txt for c3); None = no capture
+# (profiles/r1_final_launches_1gbp.txt for c2, profiles/r1_c3_final_launches.txt for c3); None = no capture
 NCU_DRAM_BYTES_PER_LAUNCH = {
     "c2": {"k_wave_fused": 46.658e9 / 58, "k_radix_scatter": 5.4073e9, "k_groups_tiny": 6.7628e9},
-    "c3": {},
+    # 2 steps under ncu: k_wave_fused + k_wave_tail 331.7 GB / 150 launches, k_groups_medium 32.8 GB / 78
+    "c3": {"k_wave_fused": 331.70e9 / 150, "k_groups_medium": 32.80e9 / 78, "k_radix_scatter": 1.7273e9,
+           "k_groups_tiny": 5.0004e9},
 }
 
 

@@ -14,6 +14,7 @@
 //
 // Algorithmic bytes per scanned entry: 4 (SA read) + 0.25 (packed text) + 4 per induced suffix; the context
 // array adds 4 + 4 of streaming traffic and removes all but ~0.3 n of the random text gathers.
+#include <cstdio>
 #include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
@@ -172,6 +173,7 @@ struct WaveShared {
   u64 cur[4];
   u64 p;
   u32 nwaves;
+  u32 ntile, nmid;  // statistics: waves that took the tile path / the one-entry-per-thread path
 };
 
 // one tile of a wave.  LOOKBACK = false: the wave is this single tile (no status traffic); tot[] gets the counts.
@@ -371,6 +373,8 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
     for (int s = 0; s < 4; s++) sh.cur[s] = a0.cur[s];
     sh.p = p0;
     sh.nwaves = 0;
+    sh.ntile = 0;
+    sh.nmid = 0;
   }
   for (;;) {
     __syncthreads();
@@ -440,6 +444,7 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
       if (t == 0) {
         sh.cur[0] = c0; sh.cur[1] = c1; sh.cur[2] = c2; sh.cur[3] = c3;
         sh.p = pp;
+        sh.nmid += nw - sh.nwaves;
         sh.nwaves = nw;
       }
       continue;
@@ -515,12 +520,15 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
       sh.p = cc;
       for (int s = 0; s < 4; s++) sh.cur[s] = DOWN ? sh.cur[s] - s_tot[s] : sh.cur[s] + s_tot[s];
       sh.nwaves++;
+      sh.ntile++;
     }
   }
   if (threadIdx.x == 0) {
     out[0] = sh.p;
     for (int s = 0; s < 4; s++) out[1 + s] = sh.cur[s];
     out[5] = sh.nwaves;
+    out[6] = sh.ntile;
+    out[7] = sh.nmid;
   }
 }
 
@@ -540,6 +548,12 @@ u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, 
   CK(cudaStreamSynchronize(st));
   *p = ws.tail_host[0];
   for (int s = 0; s < 4; s++) cur[s] = ws.tail_host[1 + s];
+  static const bool dbg = getenv("KISS_B200_DEBUG_WAVES") != nullptr;
+  if (dbg)
+    fprintf(stderr, "[kiss_b200] tail bucket %u %s: %llu waves (tile path %llu, one entry per thread %llu, one warp %llu)\n",
+            bucket, down ? "S" : "L", (unsigned long long)ws.tail_host[5], (unsigned long long)ws.tail_host[6],
+            (unsigned long long)ws.tail_host[7],
+            (unsigned long long)(ws.tail_host[5] - ws.tail_host[6] - ws.tail_host[7]));
   return (u32)ws.tail_host[5];
 }
 

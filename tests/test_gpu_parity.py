@@ -148,3 +148,25 @@ def test_full_sa_into_pinned_buffer(ctx, name, gen):
     out.fill_(-1)
     sa = ctx.suffix_array_dna(S, 256, out=out.numpy().view(np.uint32))
     assert np.array_equal(sa, ol.oracle_kiss1(S, k=256))
+
+
+def test_kernel_profile_counts_time_and_algorithmic_bytes(ctx):
+    """the per-kernel profiler (bench.py's roofline source): CUDA-event time per kernel class and the launchers'
+    own algorithmic byte counts for the radix passes and the tie-group classes; results unchanged when it is on"""
+    S = tg.near_identical_copies(19, 150, 1500, 0.005)
+    want = ol.oracle_kiss1(S, k=256)
+    ctx.profile_enable(True)
+    try:
+        got = ctx.suffix_array_dna(S, 256)
+        prof, alg = ctx.profile(), ctx.profile_alg_bytes()
+    finally:
+        ctx.profile_enable(False)
+    assert np.array_equal(got, want)
+    m1 = ctx.last_timings["m"] - 1
+    assert prof["k_radix_scatter"][1] >= 4 and prof["k_radix_scatter"][0] > 0
+    assert alg["k_radix_scatter"] >= 4 * 16 * (m1 - 400)       # four passes over (key32, pos32), read + write
+    assert alg["k_radix_hist"] >= 4 * 4 * (m1 - 400)
+    med = {k: v for k, v in alg.items() if k.startswith("k_groups_medium")}
+    assert med and all(v % 16 == 0 for v in med.values())     # 16 B per LMS suffix in a refined group
+    assert sum(med.values()) >= 16 * 1400                     # the 1500-copy groups went through the block team
+    assert set(med) <= set(prof)
