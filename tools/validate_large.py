@@ -28,9 +28,52 @@ CONFIGS = {
     "c4": dict(n=536_870_912, seed=4, kind="replicated", k=0xFFFFFFFF, algo="PREFIX_DOUBLING"),
     "c4small": dict(n=67_108_864, seed=4, kind="replicated", k=0xFFFFFFFF, algo="PREFIX_DOUBLING"),
 }
+# the C3 text, k in {32, 64, 128, 256} x {PARALLEL_SORTING, PREFIX_DOUBLING}.  PARALLEL_SORTING is
+# compared bit by bit with the reference; bounded-k PREFIX_DOUBLING (whose reference output depends on the thread count,
+# SURVEY 0.3) is checked as a k-order (sampled neighbours) and against this implementation's PARALLEL_SORTING array
+for _k in (32, 64, 128, 256):
+    CONFIGS[f"c5k{_k}"] = dict(n=3_117_292_070, seed=3, kind="chm13", k=_k)
+    CONFIGS[f"c5k{_k}pd"] = dict(n=3_117_292_070, seed=3, kind="chm13", k=_k, algo="PREFIX_DOUBLING", property_only=True)
+    CONFIGS[f"c5sk{_k}"] = dict(n=200_000_000, seed=3, kind="chm13", k=_k)
+    CONFIGS[f"c5sk{_k}pd"] = dict(n=200_000_000, seed=3, kind="chm13", k=_k, algo="PREFIX_DOUBLING", property_only=True)
+
+_text_cache = {}
 
 
 def text(ctx, cfg):
+    key = (cfg["n"], cfg["seed"], cfg["kind"])
+    if key not in _text_cache:
+        _text_cache.clear()
+        _text_cache[key] = _text(ctx, cfg)
+    return _text_cache[key]
+
+
+def k_order_violations(S, sa, k, samples=2_000_000, seed=1):
+    """number of sampled neighbours SA[i], SA[i+1] whose first k bases are in the wrong order (a shorter suffix that is
+    a prefix of the other sorts first)"""
+    n = S.size
+    rng = np.random.default_rng(seed)
+    idx = rng.integers(0, n, samples)
+    a, b = sa[idx].astype(np.int64), sa[idx + 1].astype(np.int64)
+    undecided = np.ones(samples, bool)
+    bad = np.zeros(samples, bool)
+    Sp = np.concatenate([S, np.zeros(1, np.uint8)])
+    for j in range(k):
+        act = np.nonzero(undecided)[0]
+        if act.size == 0:
+            break
+        pa, pb = a[act] + j, b[act] + j
+        enda, endb = pa >= n, pb >= n
+        ca, cb = Sp[np.minimum(pa, n)], Sp[np.minimum(pb, n)]
+        # a ended: fine (prefix first); b ended but a not: wrong
+        wrong = (~enda & endb) | (~enda & ~endb & (ca > cb))
+        right = enda | (~endb & (ca < cb))
+        bad[act[wrong]] = True
+        undecided[act[wrong | right]] = False
+    return int(bad.sum())
+
+
+def _text(ctx, cfg):
     n = cfg["n"]
     d = torch.empty(n + 64, dtype=torch.uint8, device="cuda")
     ctx.synth_uniform_dev(d.data_ptr(), n, cfg["seed"])
@@ -64,7 +107,7 @@ def main():
     names = [a for a in args if not a.startswith("--")] or ["c1"]
     ctx = kiss_b200.Context(0)
     for name in names:
-        cfg = CONFIGS[name]
+        cfg = dict(CONFIGS[name])
         S = text(ctx, cfg)
         n = S.size
         t0 = time.perf_counter()
@@ -73,7 +116,7 @@ def main():
         sa = ctx.suffix_array_dna(S, cfg["k"], algo=algo)
         t_gpu = time.perf_counter() - t0
         tm = ctx.last_timings
-        out = dict(config=name, **cfg, m=tm["m"], gpu_host_call_s=t_gpu, gpu_device_s=tm["total_device"],
+        out = dict(config=name, **{kk: vv for kk, vv in cfg.items() if kk != "property_only"}, m=tm["m"], gpu_host_call_s=t_gpu, gpu_device_s=tm["total_device"],
                    lms_sort_s=tm["lms_sort"], induce_s=tm["induce"], tied=tm["lms_sort_tied"], rounds=tm["lms_sort_rounds"],
                    waves=[tm["waves_L"], tm["waves_S"]], sa0_is_n=bool(int(sa[0]) == n), permutation=is_permutation(sa, n))
         if profile:  # second call with CUDA events around every launch (kernel class -> [ms, launches])
@@ -82,7 +125,13 @@ def main():
             out["kernels"] = {k: [round(v[0], 3), v[1]] for k, v in ctx.profile().items()}
             out["profiled_stages_s"] = {k: ctx.last_timings[k] for k in ("get_lms", "lms_sort", "put_lms", "induce")}
             ctx.profile_enable(False)
-        if ol.have_ref() and "--noref" not in args:
+        if cfg.get("property_only"):
+            out["k_order_violations_in_2M_samples"] = k_order_violations(S, sa, cfg["k"])
+            ps = ctx.suffix_array_dna(S, cfg["k"], algo=kiss_b200.PARALLEL_SORTING)
+            out["equals_own_parallel_sorting"] = bool(np.array_equal(sa, ps))
+            out["k_order_violations_parallel_sorting"] = k_order_violations(S, ps, cfg["k"])
+            del ps
+        elif ol.have_ref() and "--noref" not in args:
             ref = np.empty(n + 1, np.uint32)
             threads = os.cpu_count()
             fn = ol.ref().ref_kiss2_suffix_array_dna if algo_name == "PREFIX_DOUBLING" else ol.ref().ref_kiss1_suffix_array_dna
@@ -95,7 +144,7 @@ def main():
                 out["first_bad"] = [int(x) for x in bad[:5]]
             del ref
         print(json.dumps(out), flush=True)
-        del sa, S
+        del sa
     ctx.close()
 
 
