@@ -29,7 +29,10 @@ extern "C" {
 
 #define KISS_B200_EMPTY 0xFFFFFFFFu
 
-/* -s / --sorting-algorithm (reference: include/utils/options.hpp:67-81 SortingAlgorithm) */
+/* -s / --sorting-algorithm (reference: include/utils/options.hpp:67-81 SortingAlgorithm).
+ * PREFIX_DOUBLING with k = 0xFFFFFFFF is the unique suffix array; with a bounded k the LMS suffixes are ordered by their
+ * first max(4096, 16 * 2^ceil(log2 k)) bases (an upper bound of the depth kISS-2's doubling reaches,
+ * kiss2_core.hpp:764-766), then by position — the reference's own order of deeper ties depends on its thread count. */
 #define KISS_B200_PARALLEL_SORTING 0
 #define KISS_B200_PREFIX_DOUBLING 1
 
@@ -145,6 +148,14 @@ int kiss_b200_partition_lms_dev(kiss_b200_ctx* ctx, const uint32_t* splitters_ho
  * short-suffix insertion, placement and induction into SA_dev (n + 1). */
 int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_long_dev, uint64_t n_long,
                                      uint32_t* SA_dev, kiss_b200_timings* t);
+/* Multi-GPU: the rank that sorted a key range also fetches the induction contexts of its suffixes (the 15 bases
+ * before each position, one random 128-byte DRAM fetch per LMS suffix — the part of induced_L's first touch of an LMS
+ * suffix, kiss_common.hpp:226-246, that does shard), and rank 0 finishes from (position, context) pairs.
+ * lms_contexts: ctx_out_dev[i] for the suffixes pos_dev[0..count) of the prepared text.
+ * finish_from_sorted_ctx: as finish_from_sorted_dev; ctx_long_dev (nullable) is aligned like sorted_long_dev mod 16. */
+int kiss_b200_lms_contexts_dev(kiss_b200_ctx* ctx, const uint32_t* pos_dev, uint64_t count, uint32_t* ctx_out_dev);
+int kiss_b200_finish_from_sorted_ctx_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_long_dev, const uint32_t* ctx_long_dev,
+                                         uint64_t n_long, uint32_t* SA_dev, kiss_b200_timings* t);
 
 /* ---- per-kernel timing ---------------------------------------------------------------------------
  * When enabled, every launch of the main kernel classes is bracketed by CUDA events on the context's stream and

@@ -218,11 +218,24 @@ void do_prepare(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, float* t
   lms_emit(T, n, lmsmask, chunk_cnt /* now exclusive offsets */, pos, key, st);
 
   // depth and the long / short split
+  // PREFIX_DOUBLING with a bounded k: kISS-2 doubles over word indices for offset = 1, 2, 4, ... < k
+  // (kiss2_core.hpp:764-766), i.e. it orders by the first 2^ceil(log2 k) words of at most 16 bases each, and leaves
+  // deeper ties in an order that depends on its thread count.  Sorting to pd_depth(k) =
+  // max(4096, 16 * 2^ceil(log2 k)) bases — an upper bound of that depth — and then by position is therefore equal
+  // to the reference wherever the reference is tie-free, a valid k-order everywhere, and far cheaper than the full
+  // order on repeat-rich text (exact 100 kb duplications: 1.02 s of LMS sort on the 3.1 Gbp chm13-like text).
+  // The suffix-end rule of the unbounded comparison (the shorter first) applies: no "short" suffixes.
+  u64 pd_depth = KISS_UNBOUNDED;
+  if (algo == KISS_B200_PREFIX_DOUBLING && k != 0xFFFFFFFFu) {
+    u64 w = 1;
+    while (w < (u64)k) w <<= 1;
+    pd_depth = 16ull * w < 4096ull ? 4096ull : 16ull * w;
+  }
   bool unbounded = (algo == KISS_B200_PREFIX_DOUBLING) || ((u64)k >= n);
   P.sp.T = T; P.sp.n = n; P.sp.k = k;
   u32 n_long;
   if (unbounded) {
-    P.sp.D = KISS_UNBOUNDED;
+    P.sp.D = (algo == KISS_B200_PREFIX_DOUBLING && pd_depth < n) ? pd_depth : KISS_UNBOUNDED;
     n_long = m1;
     CK(cudaStreamSynchronize(st));
   } else {
@@ -427,7 +440,7 @@ struct CopyOut {
 
 // `lms` = the sorted LMS suffixes (sentinel excluded), grouped by first symbol: bk.lms_off / bk.lms_count
 void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets& bk, const u32* lms, u32* SA, u32* CTX,
-               InduceStats* is, CopyOut* co = nullptr) {
+               InduceStats* is, CopyOut* co = nullptr, const u32* lms_ctx = nullptr) {
   cudaStream_t st = c->st;
   WaveScratch ws;
   u64 maxlen = n + 1;
@@ -447,7 +460,7 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
   for (int s = 0; s < 4; s++) Lc[s] = bk.B[s];
   // L pass (kiss_common.hpp:372-403)
   set_sentinel(SA, CTX, n, st);
-  induce_wave(SA, CTX, T, nullptr, 0, 1, false, 0xFu, Lc, ws, tot, st);
+  induce_wave(SA, CTX, T, nullptr, nullptr, 0, 1, false, 0xFu, Lc, ws, tot, st);
   for (int s = 0; s < 4; s++) Lc[s] += tot[s];
   is->waves_L++;
   if (co) co->send(SA, 0, 1);
@@ -459,7 +472,7 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
         is->waves_L += induce_tail(SA, CTX, T, (u32)cb, &p, false, (0xFu << cb) & 0xFu, Lc, ws, st);
         continue;
       }
-      induce_wave(SA, CTX, T, nullptr, p, q - p, false, (0xFu << cb) & 0xFu, Lc, ws, tot, st);
+      induce_wave(SA, CTX, T, nullptr, nullptr, p, q - p, false, (0xFu << cb) & 0xFu, Lc, ws, tot, st);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
       p = q;
       is->waves_L++;
@@ -468,7 +481,7 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
     // higher buckets): it can leave now
     if (co) co->send(SA, bk.B[cb], Lc[cb] - bk.B[cb]);
     if (bk.lms_count[cb]) {
-      induce_wave(SA, CTX, T, lms, bk.lms_off[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
+      induce_wave(SA, CTX, T, lms, lms_ctx, bk.lms_off[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
       is->waves_L++;
     }
@@ -487,14 +500,14 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
         is->waves_S += induce_tail(SA, CTX, T, (u32)cb, &p, true, (1u << (cb + 1)) - 1u, Sc, ws, st);
         continue;
       }
-      induce_wave(SA, CTX, T, nullptr, q, p - q, true, (1u << (cb + 1)) - 1u, Sc, ws, tot, st);
+      induce_wave(SA, CTX, T, nullptr, nullptr, q, p - q, true, (1u << (cb + 1)) - 1u, Sc, ws, tot, st);
       for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
       p = q;
       is->waves_S++;
     }
     if (co) co->send(SA, bk.B[cb] + nL[cb], bk.B[cb + 1] - bk.B[cb] - nL[cb]);  // bucket cb's S-type part is final
     if (cb > 0 && nL[cb]) {
-      induce_wave(SA, CTX, T, nullptr, bk.B[cb], nL[cb], true, (1u << cb) - 1u, Sc, ws, tot, st);
+      induce_wave(SA, CTX, T, nullptr, nullptr, bk.B[cb], nL[cb], true, (1u << cb) - 1u, Sc, ws, tot, st);
       for (int s = 0; s < 4; s++) Sc[s] -= tot[s];
       is->waves_S++;
     }
@@ -964,8 +977,8 @@ int kiss_b200_sort_lms_subset_dev(kiss_b200_ctx* c, uint32_t* pos_dev, uint64_t 
   });
 }
 
-int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_long_dev, uint64_t n_long,
-                                     uint32_t* SA_dev, kiss_b200_timings* t) {
+static int finish_from_sorted(kiss_b200_ctx* c, const uint32_t* sorted_long_dev, const uint32_t* ctx_long_dev,
+                              uint64_t n_long, uint32_t* SA_dev, kiss_b200_timings* t) {
   if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
   if (!SA_dev || (n_long && !sorted_long_dev) || n_long != c->prep.n_long || ((uintptr_t)SA_dev & 15)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   return guarded(c, [&] {
@@ -983,9 +996,18 @@ int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_lo
     Buckets bk = make_buckets(P.counters, P.n);
     u32* dCTX = pool.alloc<u32>(P.n + 1);
     const u32* lms = merged_lms(pool, sl, st);
+    // contexts fetched by the ranks that sorted the ranges; the few short suffixes keep "not fetched" (1)
+    const u32* lms_ctx = ctx_long_dev;
+    if (ctx_long_dev && sl.ns) {
+      u32* ones = pool.alloc<u32>(sl.ns);
+      fill_u32(ones, sl.ns, 1u, st);
+      u32* merged = pool.alloc<u32>((u64)sl.nl + sl.ns);
+      merge_lms(ctx_long_dev, sl.nl, ones, sl.ins, sl.ns, merged, st);
+      lms_ctx = merged;
+    }
     CK(cudaEventRecord(c->ev[5], st));
     InduceStats is;
-    do_induce(c, pool, P.T, P.n, bk, lms, SA_dev, dCTX, &is);
+    do_induce(c, pool, P.T, P.n, bk, lms, SA_dev, dCTX, &is, nullptr, lms_ctx);
     CK(cudaEventRecord(c->ev[6], st));
     CK(cudaEventSynchronize(c->ev[6]));
     if (t) {
@@ -997,6 +1019,25 @@ int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_lo
       t->waves_L = is.waves_L; t->waves_S = is.waves_S;
       t->kernel_launches = g_launches - l0;
     }
+  });
+}
+
+int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* c, const uint32_t* sorted_long_dev, uint64_t n_long,
+                                     uint32_t* SA_dev, kiss_b200_timings* t) {
+  return finish_from_sorted(c, sorted_long_dev, nullptr, n_long, SA_dev, t);
+}
+
+int kiss_b200_finish_from_sorted_ctx_dev(kiss_b200_ctx* c, const uint32_t* sorted_long_dev, const uint32_t* ctx_long_dev,
+                                         uint64_t n_long, uint32_t* SA_dev, kiss_b200_timings* t) {
+  return finish_from_sorted(c, sorted_long_dev, ctx_long_dev, n_long, SA_dev, t);
+}
+
+int kiss_b200_lms_contexts_dev(kiss_b200_ctx* c, const uint32_t* pos_dev, uint64_t count, uint32_t* ctx_out_dev) {
+  if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
+  if (count && (!pos_dev || !ctx_out_dev)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  return guarded(c, [&] {
+    lms_contexts(c->prep.T, pos_dev, count, ctx_out_dev, c->st);
+    CK(cudaStreamSynchronize(c->st));
   });
 }
 

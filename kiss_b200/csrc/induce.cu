@@ -565,14 +565,38 @@ void wave_init() {
   CK(cudaFuncSetAttribute(k_wave_tail<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
 }
 
-void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, u64 lo, u64 len, bool down, u32 symmask,
-                 const u64 cur[4], WaveScratch ws, u32 tot[4], cudaStream_t st) {
+// contexts of a list of suffixes (what the LMS waves would gather themselves): at N > 1 every rank fetches them for
+// the key range it sorted, so the 128-byte DRAM fetch per LMS suffix is spread over the GPUs and rank 0's LMS
+// waves stream (position, context) pairs
+__global__ void __launch_bounds__(256) k_lms_contexts(const u64* __restrict__ T, const u32* __restrict__ pos, u64 cnt,
+                                                     u32* __restrict__ out) {
+  const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < cnt) out[i] = ctx_gather(T, pos[i]);
+}
+void lms_contexts(const u64* T, const u32* pos, u64 cnt, u32* out, cudaStream_t st) {
+  if (!cnt) return;
+  k_lms_contexts<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(T, pos, cnt, out);
+  CK_LAUNCH(); g_launches++;
+}
+__global__ void __launch_bounds__(256) k_fill_u32(u32* __restrict__ p, u64 cnt, u32 v) {
+  const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < cnt) p[i] = v;
+}
+void fill_u32(u32* p, u64 cnt, u32 v, cudaStream_t st) {
+  if (!cnt) return;
+  k_fill_u32<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(p, cnt, v);
+  CK_LAUNCH(); g_launches++;
+}
+
+void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, const u32* lms_ctx, u64 lo, u64 len, bool down,
+                 u32 symmask, const u64 cur[4], WaveScratch ws, u32 tot[4], cudaStream_t st) {
   tot[0] = tot[1] = tot[2] = tot[3] = 0;
   if (len == 0) return;
   WaveArgs a;
   a.SA = SA; a.CTX = CTX; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
   a.inSA = lms_src ? lms_src : SA;
-  a.inCTX = lms_src ? nullptr : CTX;
+  // (the 16-byte loads of the two scanned arrays share their cut points: a context list must be aligned like its list)
+  a.inCTX = lms_src ? ((lms_ctx && (((uintptr_t)lms_ctx ^ (uintptr_t)lms_src) & 15) == 0) ? lms_ctx : nullptr) : CTX;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
   const u64 mis = ((u64)(uintptr_t)a.inSA >> 2) & 3ull, hi = lo + len;
   u64 len_al = down ? (hi + ((4ull - ((hi + mis) & 3ull)) & 3ull) - lo) : (hi - (lo - ((lo + mis) & 3ull)));

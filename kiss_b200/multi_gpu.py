@@ -65,9 +65,18 @@ class GpuBackend:
         self.torch.cuda.synchronize()
         return self.ctx.sort_lms_subset_dev(buf.data_ptr(), count)
 
-    def finish(self, sorted_long, n_long, SA):
+    def contexts(self, buf, count):
+        """induction contexts of the sorted suffixes buf[0..count) (one random text fetch each: this is the part of
+        the induction's first touch of an LMS suffix that shards with the sort)"""
+        out = self.empty(count)
         self.torch.cuda.synchronize()
-        return self.ctx.finish_from_sorted_dev(sorted_long.data_ptr(), n_long, SA.data_ptr())
+        self.ctx.lms_contexts_dev(buf.data_ptr(), count, out.data_ptr())
+        return out
+
+    def finish(self, sorted_long, n_long, SA, ctx_long=None):
+        self.torch.cuda.synchronize()
+        return self.ctx.finish_from_sorted_dev(sorted_long.data_ptr(), n_long, SA.data_ptr(),
+                                               ctx_long.data_ptr() if ctx_long is not None and n_long else None)
 
     def sync(self):
         self.torch.cuda.synchronize()
@@ -123,6 +132,9 @@ def sharded_lms_sort(backend, dist, n_long, rank, world):
     # 4. local sort of this rank's key range
     st = backend.sort_subset(recv, total)
     mark("local_sort")
+    # 4b. (GPU backend) the contexts induction needs for these suffixes, fetched here so that rank 0's LMS waves stream
+    ctx_local = backend.contexts(recv, total) if hasattr(backend, "contexts") else None
+    mark("contexts")
     # 5. concatenate the ranges on rank 0 (key ranges are ordered by rank)
     sizes = torch.tensor([total], dtype=torch.int64, device=backend_device(backend))
     all_sizes = [torch.empty_like(sizes) for _ in range(world)]
@@ -133,9 +145,13 @@ def sharded_lms_sort(backend, dist, n_long, rank, world):
     result = backend.empty(sum(out_split))
     backend.sync()
     dist.all_to_all_single(result, recv, output_split_sizes=out_split, input_split_sizes=in_split)
+    ctx_result = None
+    if ctx_local is not None:
+        ctx_result = backend.empty(sum(out_split))
+        dist.all_to_all_single(ctx_result, ctx_local, output_split_sizes=out_split, input_split_sizes=in_split)
     mark("concat")
     stats = {"shard_sizes": all_sizes, "imbalance": (max(all_sizes) * world / max(1, sum(all_sizes))),
-             "sort": st}
+             "sort": st, "ctx": ctx_result if rank == 0 else None}
     if marks:
         stats["steps_ms"] = {marks[i][0]: round((marks[i][1] - marks[i - 1][1]) * 1e3, 3) for i in range(1, len(marks))}
     return (result if rank == 0 else None), stats
@@ -164,7 +180,7 @@ def sharded_suffix_array_dev(ctx, S, n, SA, k, dist):
     if "steps_ms" in stats:
         out["steps_ms"] = stats["steps_ms"]
     if rank == 0:
-        ft = be.finish(sorted_long, n_long, SA)
+        ft = be.finish(sorted_long, n_long, SA, stats.get("ctx"))
         out.update(put_lms=ft["put_lms"], induce=ft["induce"], waves_L=ft["waves_L"], waves_S=ft["waves_S"],
                    kernel_launches=out["kernel_launches"] + ft["kernel_launches"])
     out["kernel_launches"] += stats["sort"]["kernel_launches"]

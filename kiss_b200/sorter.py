@@ -137,10 +137,16 @@ class Context:
         check(lib().kiss_b200_sort_lms_subset_dev(self._h, pos_ptr, count, C.byref(t)))
         return t.as_dict()
 
-    def finish_from_sorted_dev(self, sorted_ptr, n_long, SA_ptr):
+    def finish_from_sorted_dev(self, sorted_ptr, n_long, SA_ptr, ctx_ptr=None):
         t = Timings()
-        check(lib().kiss_b200_finish_from_sorted_dev(self._h, sorted_ptr, n_long, SA_ptr, C.byref(t)))
+        if ctx_ptr:
+            check(lib().kiss_b200_finish_from_sorted_ctx_dev(self._h, sorted_ptr, ctx_ptr, n_long, SA_ptr, C.byref(t)))
+        else:
+            check(lib().kiss_b200_finish_from_sorted_dev(self._h, sorted_ptr, n_long, SA_ptr, C.byref(t)))
         return t.as_dict()
+
+    def lms_contexts_dev(self, pos_ptr, count, out_ptr):
+        check(lib().kiss_b200_lms_contexts_dev(self._h, pos_ptr, count, out_ptr))
 
     def profile_enable(self, on=True):
         check(lib().kiss_b200_profile_enable(self._h, 1 if on else 0))

@@ -170,3 +170,46 @@ def test_kernel_profile_counts_time_and_algorithmic_bytes(ctx):
     assert med and all(v % 16 == 0 for v in med.values())     # 16 B per LMS suffix in a refined group
     assert sum(med.values()) >= 16 * 1400                     # the 1500-copy groups went through the block team
     assert set(med) <= set(prof)
+
+
+def _check_depth_then_position(S, sa, depth, position_rule=True):
+    """every neighbour pair of the suffix list `sa` is ordered by the first `depth` bases (a suffix that ends first
+    sorts first) and, with position_rule, by position when those are equal; returns the number of such ties"""
+    n = S.size
+    a, b = sa[:-1].astype(np.int64), sa[1:].astype(np.int64)
+    Sp = np.concatenate([S, np.zeros(1, np.uint8)])
+    act = np.arange(a.size)
+    for j in range(depth):
+        if act.size == 0:
+            break
+        pa, pb = a[act] + j, b[act] + j
+        enda, endb = pa >= n, pb >= n
+        ca, cb = Sp[np.minimum(pa, n)], Sp[np.minimum(pb, n)]
+        wrong = (~enda & endb) | (~enda & ~endb & (ca > cb))
+        assert not wrong.any(), f"order violated at depth {j}: list index {act[np.nonzero(wrong)[0][:3]]}"
+        decided = enda | (~endb & (ca < cb))
+        act = act[~decided]
+    if position_rule:
+        assert (a[act] < b[act]).all(), "suffixes equal on the whole depth must keep text order"
+    return act.size
+
+
+@pytest.mark.parametrize("k", [32, 256, 300])
+def test_prefix_doubling_bounded_k_contract(ctx, k):
+    """-s PREFIX_DOUBLING with a bounded k: the LMS suffixes are ordered by their first max(4096, 16 * 2^ceil(log2 k))
+    bases (an upper bound of the depth kISS-2's doubling reaches, kiss2_core.hpp:764-766), then by position; the induced
+    suffix array is a permutation and a k-order; and it is the unique suffix array when no two suffixes share that
+    many bases"""
+    import kiss_b200
+    depth = max(4096, 16 * (1 << (k - 1).bit_length()))
+    S = tg.planted_repeats(61, 120_000, unit_len=9000, copies=6)          # exact copies longer than the depth
+    lms = ctx.sorted_lms(S, k, kiss_b200.PREFIX_DOUBLING)
+    assert int(lms[0]) == S.size                                          # the sentinel first (kiss_common.hpp:578)
+    tied = _check_depth_then_position(S, lms[1:], depth)
+    assert tied > 0                                                       # the case really exercises the position rule
+    sa = ctx.suffix_array_dna(S, k, kiss_b200.PREFIX_DOUBLING)
+    assert int(sa[0]) == S.size and np.array_equal(np.sort(sa), np.arange(S.size + 1, dtype=np.uint32))
+    _check_depth_then_position(S, sa, k, position_rule=False)
+    S2 = tg.planted_repeats(62, 120_000, unit_len=1500, copies=20)        # every LCP below the depth
+    got = ctx.suffix_array_dna(S2, k, kiss_b200.PREFIX_DOUBLING)
+    assert np.array_equal(got, ol.oracle_kiss1(S2, k=0xFFFFFFFF))
