@@ -310,6 +310,7 @@ def run_b200(args):
         line["sharded_sort_steps_ms"] = last["steps_ms"]
     if "shard_sizes" in last:
         line["shard_sizes"] = last["shard_sizes"]
+        line["sharded_concat"] = last.get("concat")
 
     if rank == 0:
         # roofline of the dominant kernel: algorithmic bytes per launch / its mean launch duration, measured

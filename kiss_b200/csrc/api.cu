@@ -1036,8 +1036,7 @@ int kiss_b200_lms_contexts_dev(kiss_b200_ctx* c, const uint32_t* pos_dev, uint64
   if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
   if (count && (!pos_dev || !ctx_out_dev)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   return guarded(c, [&] {
-    lms_contexts(c->prep.T, pos_dev, count, ctx_out_dev, c->st);
-    CK(cudaStreamSynchronize(c->st));
+    lms_contexts(c->prep.T, pos_dev, count, ctx_out_dev, c->st);  // enqueued only: see the header
   });
 }
 

@@ -70,8 +70,12 @@ class GpuBackend:
         the induction's first touch of an LMS suffix that shards with the sort)"""
         out = self.empty(count)
         self.torch.cuda.synchronize()
-        self.ctx.lms_contexts_dev(buf.data_ptr(), count, out.data_ptr())
+        self.ctx.lms_contexts_dev(buf.data_ptr(), count, out.data_ptr())  # enqueued on the library's stream
         return out
+
+    def contexts_wait(self):
+        import kiss_b200
+        self.torch.cuda.ExternalStream(kiss_b200.lib().kiss_b200_stream(self.ctx.handle)).synchronize()
 
     def finish(self, sorted_long, n_long, SA, ctx_long=None):
         self.torch.cuda.synchronize()
@@ -80,6 +84,43 @@ class GpuBackend:
 
     def sync(self):
         self.torch.cuda.synchronize()
+
+
+class PeerBuffers:
+    """(position, context) buffers of n_long words in symmetric memory: every rank's copy is mapped into every process
+    (CUDA peer memory over NVLink / NVSwitch), so a kernel or a copy on rank r stores straight into rank 0's buffer.
+    Creation is collective; `ok` is False on every rank when any rank could not map the buffers."""
+
+    def __init__(self, torch, dist, n_long):
+        self.cap, self.ok = n_long, False
+        flag = 1
+        try:
+            import torch.distributed._symmetric_memory as symm
+            dev = torch.device("cuda", torch.cuda.current_device())
+            self.pos = symm.empty(max(n_long, 4), dtype=torch.int32, device=dev)
+            self.ctx = symm.empty(max(n_long, 4), dtype=torch.int32, device=dev)
+            self.hpos = symm.rendezvous(self.pos, dist.group.WORLD)
+            self.hctx = symm.rendezvous(self.ctx, dist.group.WORLD)
+            self.pos0 = self.hpos.get_buffer(0, (max(n_long, 4),), torch.int32)
+            self.ctx0 = self.hctx.get_buffer(0, (max(n_long, 4),), torch.int32)
+        except Exception as e:  # no peer access / symmetric memory on this system: the NCCL concatenation is used
+            self.err = repr(e)
+            flag = 0
+        t = torch.tensor([flag], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        self.ok = bool(int(t.item()))
+
+
+def peer_buffers(backend, dist, n_long):
+    """cached on the library context (bench steps repeat the same text length)"""
+    import os
+    if os.environ.get("KISS_B200_NO_PEER"):
+        return None
+    pb = getattr(backend.ctx, "_peer_buffers", None)
+    if pb is None or pb.cap != n_long:
+        pb = PeerBuffers(backend.torch, dist, n_long)
+        backend.ctx._peer_buffers = pb
+    return pb if pb.ok else None
 
 
 def _as_tensor(torch, ptr, count):
@@ -132,26 +173,46 @@ def sharded_lms_sort(backend, dist, n_long, rank, world):
     # 4. local sort of this rank's key range
     st = backend.sort_subset(recv, total)
     mark("local_sort")
-    # 4b. (GPU backend) the contexts induction needs for these suffixes, fetched here so that rank 0's LMS waves stream
-    ctx_local = backend.contexts(recv, total) if hasattr(backend, "contexts") else None
-    mark("contexts")
     # 5. concatenate the ranges on rank 0 (key ranges are ordered by rank)
     sizes = torch.tensor([total], dtype=torch.int64, device=backend_device(backend))
     all_sizes = [torch.empty_like(sizes) for _ in range(world)]
     dist.all_gather(all_sizes, sizes)
     all_sizes = [int(x.item()) for x in all_sizes]
+    pb = peer_buffers(backend, dist, n_long) if hasattr(backend, "contexts") else None
+    if pb is not None:
+        # 5a. peer memory: the context kernel of rank r — one random text fetch per sorted suffix, the part of the
+        # induction's first touch of an LMS suffix that shards with the sort — stores its results straight into rank
+        # 0's context buffer over NVLink, and the sorted positions follow with one device-to-device copy into rank
+        # 0's position buffer, both at this rank's offset in the global order.  No staging, no NCCL on this step.
+        off = sum(all_sizes[:rank])
+        backend.sync()
+        if total:
+            backend.ctx.lms_contexts_dev(recv.data_ptr(), total, pb.ctx0.data_ptr() + 4 * off)  # library stream
+            pb.pos0[off:off + total].copy_(recv)                                                # torch stream
+        backend.sync()   # both streams: this rank's stores have left
+        dist.barrier()   # ... and everybody else's have landed
+        mark("concat_peer")
+        stats = {"shard_sizes": all_sizes, "imbalance": (max(all_sizes) * world / max(1, sum(all_sizes))), "sort": st,
+                 "ctx": pb.ctx[:n_long] if rank == 0 else None, "concat": "peer memory"}
+        if marks:
+            stats["steps_ms"] = {marks[i][0]: round((marks[i][1] - marks[i - 1][1]) * 1e3, 3) for i in range(1, len(marks))}
+        return (pb.pos[:n_long] if rank == 0 else None), stats
+    # 5b. NCCL: contexts fetched next to the exchange of the positions, then a second gather-shaped all_to_all
+    ctx_local = backend.contexts(recv, total) if hasattr(backend, "contexts") else None
+    mark("contexts_enqueued")
     out_split = all_sizes if rank == 0 else [0] * world
     in_split = [total] + [0] * (world - 1)
     result = backend.empty(sum(out_split))
     backend.sync()
     dist.all_to_all_single(result, recv, output_split_sizes=out_split, input_split_sizes=in_split)
     ctx_result = None
-    if ctx_local is not None:
+    if ctx_local is not None:  # (the context kernel ran next to the exchange of the positions)
+        backend.contexts_wait()
         ctx_result = backend.empty(sum(out_split))
         dist.all_to_all_single(ctx_result, ctx_local, output_split_sizes=out_split, input_split_sizes=in_split)
     mark("concat")
     stats = {"shard_sizes": all_sizes, "imbalance": (max(all_sizes) * world / max(1, sum(all_sizes))),
-             "sort": st, "ctx": ctx_result if rank == 0 else None}
+             "sort": st, "ctx": ctx_result if rank == 0 else None, "concat": "nccl"}
     if marks:
         stats["steps_ms"] = {marks[i][0]: round((marks[i][1] - marks[i - 1][1]) * 1e3, 3) for i in range(1, len(marks))}
     return (result if rank == 0 else None), stats
@@ -179,6 +240,7 @@ def sharded_suffix_array_dev(ctx, S, n, SA, k, dist):
            "pack": 0.0, "shard_sizes": stats["shard_sizes"], "imbalance": stats["imbalance"]}
     if "steps_ms" in stats:
         out["steps_ms"] = stats["steps_ms"]
+    out["concat"] = stats.get("concat")
     if rank == 0:
         ft = be.finish(sorted_long, n_long, SA, stats.get("ctx"))
         out.update(put_lms=ft["put_lms"], induce=ft["induce"], waves_L=ft["waves_L"], waves_S=ft["waves_S"],
