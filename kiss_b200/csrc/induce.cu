@@ -142,6 +142,46 @@ __device__ __forceinline__ u32 ctx_symbol(u32 c, u32 symmask) {
   return (c > 1u && ((symmask >> cu) & 1u)) ? cu : 4u;
 }
 
+// ---- runs of the bucket's own symbol (the on-device tail, below)
+// Inside a bucket a wave's successor is made of the entries whose preceding base is the bucket's symbol, so a run of r
+// such bases before a suffix is a chain of r waves — a 10^6-base homopolymer run (or a run of N, which the reference
+// maps to A) is 10^6 waves of one entry each.  When EVERY entry of a wave has at least K such bases before it, the next
+// K waves are known without scanning them: wave k holds the suffixes v_j - k in the order of the current wave, nothing
+// goes to another bucket.  They are written in one burst and the tail continues at wave K.
+// bases of the bucket's symbol right before suffix v, as far as its context word shows (exact up to the context length)
+__device__ __forceinline__ u32 ctx_len(u32 c) { return c > 1u ? (31u - (u32)__clz(c)) >> 1 : 0u; }
+__device__ __forceinline__ u32 ctx_run(u32 c, u32 sym) {
+  if (c <= 1u) return 0u;
+  const u32 x = c ^ (sym * 0x55555555u);
+  const u32 tz = x ? ((u32)(__ffs((int)x) - 1) >> 1) : 16u;
+  return min(tz, ctx_len(c));
+}
+// the same from the text: the exact run when it is shorter than cap, else a lower bound in [cap, cap + 32)
+#define RUN_CAP 4096u
+#define BURST_MIN 3u
+__device__ __noinline__ u32 text_run(const u64* __restrict__ T, u32 v, u32 sym, u32 cap) {
+  const u64 pat = (u64)sym * 0x5555555555555555ull;
+  u32 cnt = 0;
+  u64 pos = v;
+  while (cnt < cap && pos >= 32) {
+    const u64 x = word_at(T, pos - 32) ^ pat;  // bases pos-32 .. pos-1, the last one in the lowest bits
+    const u32 tz = x ? ((u32)(__ffsll((long long)x) - 1) >> 1) : 32u;
+    cnt += tz;
+    pos -= tz;
+    if (tz < 32) return cnt;
+  }
+  while (cnt < cap && pos > 0 && base_at(T, pos - 1) == sym) { cnt++; pos--; }  // (the head of the text)
+  return cnt;
+}
+// lower bound of the run before suffix v: what the previous wave handed over, what the context shows, and — when the
+// context is all the bucket's symbol and nothing was handed over — what the text shows
+__device__ __forceinline__ u32 run_bound(const u64* __restrict__ T, u32 v, u32 c, u32 handed, u32 sym) {
+  const u32 cr = ctx_run(c, sym);
+  u32 rr = max(handed, cr);
+  if (handed == 0 && cr != 0 && cr == ctx_len(c)) rr = max(rr, text_run(T, v, sym, RUN_CAP));
+  return rr;
+}
+
 struct WaveSmem {
   u32 sb[5];
   u32 sSA[WAVE_TILE];
@@ -174,6 +214,7 @@ struct WaveShared {
   u64 p;
   u32 nwaves;
   u32 ntile, nmid;  // statistics: waves that took the tile path / the one-entry-per-thread path
+  u32 wmin[WAVE_WARPS];  // per-warp minimum of the run bounds (burst decision of the one-entry-per-thread path)
 };
 
 // one tile of a wave.  LOOKBACK = false: the wave is this single tile (no status traffic); tot[] gets the counts.
@@ -391,6 +432,8 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
       const u32 t = threadIdx.x, lane = t & 31u, w = t >> 5;
       u32* nbv = sh.sm.sSA;   // next wave's entries, in rank order
       u32* nbc = sh.sm.sCTX;
+      u32* nbr = sh.sm.sSA + 2048;   // ... and what is left of their run bounds
+      u32* sv = sh.sm.sSA + 1024;    // the current wave's suffixes by entry index (bursts)
       u64 c0 = sh.cur[0], c1 = sh.cur[1], c2 = sh.cur[2], c3 = sh.cur[3], pp = p;
       u32 nw = sh.nwaves;
       bool have = false;
@@ -398,11 +441,12 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
         const u64 cb = bucket == 0 ? c0 : bucket == 1 ? c1 : bucket == 2 ? c2 : c3;
         const u64 ln = DOWN ? pp - cb : cb - pp;
         if (ln <= 32 || ln > WAVE_THREADS || nw >= max_waves) break;  // (uniform: every thread holds the same cursors)
-        u32 v = 0, c = 1u;
+        u32 v = 0, c = 1u, rr = 0;
         if (t < ln) {
           if (have) {
             v = nbv[t];
             c = nbc[t];
+            rr = nbr[t];
           } else {
             const u64 slot = DOWN ? pp - 1 - t : pp + t;
             v = a0.SA[slot];
@@ -411,17 +455,51 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
         }
         if (c == 1u && v != 0 && v != KISS_EMPTY) c = ctx_gather(a0.T, v);
         const u32 cu = ctx_symbol(c, a0.symmask);
+        if (t < ln) rr = (cu == bucket && v != KISS_EMPTY) ? run_bound(a0.T, v, c, rr, bucket) : 0u;
+        const u32 wm = __reduce_min_sync(0xffffffffu, t < ln ? rr : 0xFFFFFFFFu);
         const u32 m0 = __ballot_sync(0xffffffffu, cu == 0), m1 = __ballot_sync(0xffffffffu, cu == 1),
                   m2 = __ballot_sync(0xffffffffu, cu == 2), m3 = __ballot_sync(0xffffffffu, cu == 3);
-        if (lane == 0)
+        if (lane == 0) {
           sh.wsum[w] = (u64)__popc(m0) | ((u64)__popc(m1) << 16) | ((u64)__popc(m2) << 32) | ((u64)__popc(m3) << 48);
+          sh.wmin[w] = wm;
+        }
+        sv[t] = v;
         __syncthreads();  // counts published; every thread has read its entry from the hand-over buffer
         u64 before = 0, total = 0;
+        u32 K = 0xFFFFFFFFu;
 #pragma unroll
         for (u32 ww = 0; ww < WAVE_WARPS; ww++) {
           const u64 x = sh.wsum[ww];
           total += x;
           if (ww < w) before += x;
+          K = min(K, sh.wmin[ww]);
+        }
+        if (K >= BURST_MIN) {
+          // every entry has >= K bases of the bucket's symbol before it: waves 1..K are the suffixes v_j - k in the
+          // order j of this wave (consecutive threads take consecutive k of one j: adjacent text positions)
+          const u32 n32 = (u32)ln, cnt = K * n32;
+          for (u32 tt = t; tt < cnt; tt += WAVE_THREADS) {
+            const u32 j = tt / K, k = tt - j * K + 1u;
+            const u32 val = sv[j] - k;
+            const u64 idx = (u64)(k - 1u) * n32 + j;
+            const u64 dst = DOWN ? cb - 1 - idx : cb + idx;
+            a0.SA[dst] = val;
+            a0.CTX[dst] = ctx_gather(a0.T, val);
+          }
+          if (t < ln) {
+            v -= K;
+            nbv[t] = v;
+            nbc[t] = ctx_gather(a0.T, v);
+            nbr[t] = rr - K;
+          }
+          const u64 adv = (u64)K * n32, last = (u64)(K - 1u) * n32;
+          pp = DOWN ? cb - last : cb + last;
+          if (DOWN) { c0 -= bucket == 0 ? adv : 0; c1 -= bucket == 1 ? adv : 0; c2 -= bucket == 2 ? adv : 0; c3 -= bucket == 3 ? adv : 0; }
+          else { c0 += bucket == 0 ? adv : 0; c1 += bucket == 1 ? adv : 0; c2 += bucket == 2 ? adv : 0; c3 += bucket == 3 ? adv : 0; }
+          nw += K;
+          have = true;
+          __syncthreads();
+          continue;
         }
         if (cu < 4) {
           const u32 mm = cu == 0 ? m0 : cu == 1 ? m1 : cu == 2 ? m2 : m3;
@@ -430,7 +508,7 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
           const u64 dst = DOWN ? cs - 1 - r : cs + r;
           a0.SA[dst] = v - 1u;
           a0.CTX[dst] = c >> 2;
-          if (cu == bucket) { nbv[r] = v - 1u; nbc[r] = c >> 2; }
+          if (cu == bucket) { nbv[r] = v - 1u; nbc[r] = c >> 2; nbr[r] = rr ? rr - 1u : 0u; }
         }
         const u32 t0 = (u32)total & 0xFFFFu, t1 = (u32)(total >> 16) & 0xFFFFu, t2 = (u32)(total >> 32) & 0xFFFFu,
                   t3 = (u32)(total >> 48);
@@ -462,13 +540,13 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
         // registers (lane r of the next wave takes them from the lane that ranked r), so the chain of waves
         // never waits on a global-memory round trip; only the first wave is loaded.
         bool have = false;
-        u32 v = 0, c = 1u;
+        u32 v = 0, c = 1u, rr = 0;
         for (;;) {
           const u64 cb = bucket == 0 ? c0 : bucket == 1 ? c1 : bucket == 2 ? c2 : c3;
           const u64 ln = DOWN ? pp - cb : cb - pp;
           if (ln == 0 || ln > 32 || nw >= max_waves) break;
           if (!have) {
-            v = 0; c = 1u;
+            v = 0; c = 1u; rr = 0;
             if (lane < ln) {
               const u64 slot = DOWN ? pp - 1 - lane : pp + lane;
               v = a0.SA[slot];
@@ -477,6 +555,35 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
           }
           if (c == 1u && v != 0 && v != KISS_EMPTY) c = ctx_gather(a0.T, v);
           const u32 cu = ctx_symbol(c, a0.symmask);
+          rr = (lane < ln && cu == bucket && v != KISS_EMPTY) ? run_bound(a0.T, v, c, rr, bucket) : 0u;
+          const u32 K = __reduce_min_sync(0xffffffffu, lane < ln ? rr : 0xFFFFFFFFu);
+          if (K >= BURST_MIN) {
+            // (see the one-entry-per-thread path) waves 1..K in one burst; lanes take consecutive k of one entry j
+            const u32 n32 = (u32)ln, cnt = K * n32;
+            for (u32 t0 = 0; t0 < cnt; t0 += 32) {
+              const u32 tt = t0 + lane, j = tt / K, k = tt - j * K + 1u;
+              const u32 vj = __shfl_sync(0xffffffffu, v, j & 31u);
+              if (tt < cnt) {
+                const u32 val = vj - k;
+                const u64 idx = (u64)(k - 1u) * n32 + j;
+                const u64 dst = DOWN ? cb - 1 - idx : cb + idx;
+                a0.SA[dst] = val;
+                a0.CTX[dst] = ctx_gather(a0.T, val);
+              }
+            }
+            if (lane < ln) {
+              v -= K;
+              rr -= K;
+              c = ctx_gather(a0.T, v);
+            }
+            const u64 adv = (u64)K * n32, last = (u64)(K - 1u) * n32;
+            pp = DOWN ? cb - last : cb + last;
+            if (DOWN) { c0 -= bucket == 0 ? adv : 0; c1 -= bucket == 1 ? adv : 0; c2 -= bucket == 2 ? adv : 0; c3 -= bucket == 3 ? adv : 0; }
+            else { c0 += bucket == 0 ? adv : 0; c1 += bucket == 1 ? adv : 0; c2 += bucket == 2 ? adv : 0; c3 += bucket == 3 ? adv : 0; }
+            nw += K;
+            have = true;
+            continue;
+          }
           const u32 m0 = __ballot_sync(0xffffffffu, cu == 0), m1 = __ballot_sync(0xffffffffu, cu == 1),
                     m2 = __ballot_sync(0xffffffffu, cu == 2), m3 = __ballot_sync(0xffffffffu, cu == 3);
           const u32 nv = v - 1u, nc = c >> 2;
@@ -492,8 +599,10 @@ __global__ void __launch_bounds__(WAVE_THREADS) k_wave_tail(WaveArgs a0, u32 buc
           const u32 mb = bucket == 0 ? m0 : bucket == 1 ? m1 : bucket == 2 ? m2 : m3;
           const u32 src = __fns(mb, 0, lane + 1);  // lane of the (lane+1)-th set bit, 0xffffffff if none
           const u32 tv = __shfl_sync(0xffffffffu, nv, src & 31u), tc = __shfl_sync(0xffffffffu, nc, src & 31u);
+          const u32 tr = __shfl_sync(0xffffffffu, rr ? rr - 1u : 0u, src & 31u);
           v = src < 32u ? tv : 0u;
           c = src < 32u ? tc : 1u;
+          rr = src < 32u ? tr : 0u;
           have = true;
           pp = cb;
           if (DOWN) { c0 -= __popc(m0); c1 -= __popc(m1); c2 -= __popc(m2); c3 -= __popc(m3); }

@@ -127,7 +127,10 @@ def test_ascii_front_end(ctx):
     ("uniform_5M", 5_000_000, lambda n: tg.uniform(51, n)),
     ("repeats_5M", 5_000_000, lambda n: tg.planted_repeats(52, n, unit_len=5000, copies=100)),
     ("mixed_3M", 3_000_000, lambda n: tg.mixed(53, n)),
-], ids=["uniform_5M", "repeats_5M", "mixed_3M"])
+    # long homopolymer runs (what a run of N becomes): chains of tens of thousands of waves, written in bursts
+    ("long_runs_4M", 4_000_000, lambda n: tg.many_runs(54, n, 60, 5_000, 60_000)),
+    ("long_runs_few_2M", 2_000_000, lambda n: tg.many_runs(55, n, 7, 50_000, 200_000)),
+], ids=["uniform_5M", "repeats_5M", "mixed_3M", "long_runs_4M", "long_runs_few_2M"])
 def test_medium_sizes_bit_exact(ctx, name, n, gen):
     S = gen(n)
     want = ol.oracle_kiss1(S, k=256)
@@ -213,3 +216,33 @@ def test_prefix_doubling_bounded_k_contract(ctx, k):
     S2 = tg.planted_repeats(62, 120_000, unit_len=1500, copies=20)        # every LCP below the depth
     got = ctx.suffix_array_dna(S2, k, kiss_b200.PREFIX_DOUBLING)
     assert np.array_equal(got, ol.oracle_kiss1(S2, k=0xFFFFFFFF))
+
+
+@pytest.mark.parametrize("with_ctx", [False, True], ids=["gather_in_waves", "contexts_prefetched"])
+@pytest.mark.parametrize("name,gen", [c for c in CASES if c[0] in ("uniform200k", "mixed", "copies1500", "runs300", "uniform7")],
+                         ids=["uniform200k", "mixed", "copies1500", "runs300", "uniform7"])
+def test_sharded_building_blocks_on_one_gpu(ctx, name, gen, with_ctx):
+    """the stage entries of the multi-GPU path as a single shard: prepare -> partition (no splitters) -> subset sort ->
+    contexts of the sorted suffixes -> finish from (position, context) pairs = the full suffix array"""
+    import torch
+    S = gen()
+    n = S.size
+    dS = torch.zeros(n + 64, dtype=torch.uint8, device="cuda")
+    dS[:n] = torch.from_numpy(S).cuda()
+    SA = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ctx.prepare_dev(dS.data_ptr(), n, 256)
+    _, _, n_long = ctx.lms_keys_dev()
+    buf = torch.empty(max(n_long, 1), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    counts = ctx.partition_lms_dev(np.zeros(0, np.uint32), 0, n_long, buf.data_ptr())
+    assert int(counts[0]) == n_long
+    ctx.sort_lms_subset_dev(buf.data_ptr(), n_long)
+    cbuf = None
+    if with_ctx:
+        cbuf = torch.empty(max(n_long, 1), dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        ctx.lms_contexts_dev(buf.data_ptr(), n_long, cbuf.data_ptr())   # enqueued; the next call on the context waits
+    ctx.finish_from_sorted_dev(buf.data_ptr(), n_long, SA.data_ptr(), cbuf.data_ptr() if cbuf is not None else None)
+    got = SA.cpu().numpy().view(np.uint32)
+    assert np.array_equal(got, ol.oracle_kiss1(S, k=256))

@@ -37,6 +37,10 @@ for _k in (32, 64, 128, 256):
     CONFIGS[f"c5sk{_k}"] = dict(n=200_000_000, seed=3, kind="chm13", k=_k)
     CONFIGS[f"c5sk{_k}pd"] = dict(n=200_000_000, seed=3, kind="chm13", k=_k, algo="PREFIX_DOUBLING", property_only=True)
 
+# the chm13-like text plus 100 runs of 10^4..10^6 identical bases (the induction chain: one wave per
+# base of the longest run, all of them on the device in k_wave_tail)
+CONFIGS["c3h"] = dict(n=500_000_000, seed=5, kind="chm13h", k=256)
+
 _text_cache = {}
 
 
@@ -80,8 +84,14 @@ def _text(ctx, cfg):
     S = d[:n].cpu().numpy()
     del d
     torch.cuda.empty_cache()
-    if cfg["kind"] == "chm13":
+    if cfg["kind"] in ("chm13", "chm13h"):
         S = tg.chm13_like(cfg["seed"], n, base=S)
+    if cfg["kind"] == "chm13h":
+        rng = np.random.default_rng(cfg["seed"] + 100)
+        for _ in range(100):
+            L = int(np.exp(rng.uniform(np.log(1e4), np.log(1e6))))
+            p = int(rng.integers(0, n - 4096 - L))
+            S[p:p + L] = int(rng.integers(0, 4))
     if cfg["kind"] == "replicated":
         unit = 1 << 20
         rng = np.random.default_rng(cfg["seed"])
