@@ -159,6 +159,21 @@ int kiss_b200_lms_contexts_dev(kiss_b200_ctx* ctx, const uint32_t* pos_dev, uint
 int kiss_b200_finish_from_sorted_ctx_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_long_dev, const uint32_t* ctx_long_dev,
                                          uint64_t n_long, uint32_t* SA_dev, kiss_b200_timings* t);
 
+/* ---- ingest: the step before the path ------------------------------------
+ * The bytes of a FASTA or plain-text file -> base codes, on the device, with the semantics of the reference's
+ * read_sequence (include/utils/io.hpp:6-18; FASTA extraction include/biovoltron/file_io/fasta.hpp:116-151; Codec::to_int
+ * + `% 4`, istring.hpp:27-46, include/command/suffix_sort.hpp:33): FASTA mode iff the first byte is '>', header lines
+ * (first byte '>') dropped whole, '\n' dropped, everything else kept — a/A c/C g/G t/T -> 0..3, any other byte (N,
+ * IUPAC codes, the '\r' of a CRLF file) -> 0 — and all records concatenated.  The reference does this with serial
+ * getline + push_back; here it is a stream compaction in three kernels.
+ * suffix_sort_file: file bytes on the host in, suffix array out; *n_out = text length; SA_host holds SA_capacity
+ *   entries (file size + 1 always suffices); KISS_B200_ERR_ARG when the text turns out longer than SA_capacity - 1.
+ * ingest_dev: file_dev[0..nbytes) -> codes_dev (room for nbytes bytes), *n_out = text length; fasta = first byte is '>'. */
+int kiss_b200_suffix_sort_file_u32(kiss_b200_ctx* ctx, const uint8_t* file_host, uint64_t nbytes, uint32_t k, int algo,
+                                   uint32_t* SA_host, uint64_t SA_capacity, uint64_t* n_out, kiss_b200_timings* t);
+int kiss_b200_ingest_dev(kiss_b200_ctx* ctx, const uint8_t* file_dev, uint64_t nbytes, int fasta, uint8_t* codes_dev,
+                         uint64_t* n_out);
+
 /* ---- per-kernel timing ---------------------------------------------------------------------------
  * When enabled, every launch of the main kernel classes is bracketed by CUDA events on the context's stream and
  * the durations are accumulated per class (bench.py's roofline numbers).  enable() also clears the totals.

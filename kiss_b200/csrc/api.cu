@@ -656,8 +656,32 @@ double elapsed_s(kiss_b200_ctx* c, int a, int b) {
 }
 
 // host text -> device, run, device SA -> host
+enum Input { IN_CODES = 0, IN_ASCII = 1, IN_FILE = 2 };
+
+// file bytes on the device -> codes on the device (ingest.cu); returns n
+u64 do_ingest(kiss_b200_ctx* c, Pool& pool, const u8* dRaw, u64 nbytes, bool fasta, u8* dCodes) {
+  cudaStream_t st = c->st;
+  const u64 nch = ingest_chunks(nbytes);
+  if (!nch) return 0;
+  u32* lead = pool.alloc<u32>(nch);
+  u32* rest = pool.alloc<u32>(nch);
+  u64* last_ls = pool.alloc<u64>(nch);
+  u8* hflag = pool.alloc<u8>(nch);
+  u32* partials = pool.alloc<u32>(scan_partials_len(nch));
+  u64* total = pool.alloc<u64>(1);
+  ingest(dRaw, nbytes, dCodes, lead, rest, last_ls, hflag, partials, total, fasta, st);
+  u64 n = 0;
+  CK(cudaMemcpyAsync(&n, total, sizeof(u64), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  pool.release(lead); pool.release(rest); pool.release(last_ls); pool.release(hflag); pool.release(partials);
+  pool.release(total);
+  return n;
+}
+
+// `input`: what S_host holds — codes 0..3, the bare sequence in ASCII, or the bytes of a FASTA / text file (then n is
+// the file size, the text length goes to *n_text and out_host must hold out_count_hint >= text length + 1 entries)
 void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* out_host, u64 out_count_hint, Stop stop,
-              bool ascii, kiss_b200_timings* t, uint64_t* m_out) {
+              int input, kiss_b200_timings* t, uint64_t* m_out, uint64_t* n_text = nullptr) {
   cudaStream_t st = c->st;
   begin_call(c);
   Pool pool(st, &c->arena);
@@ -666,10 +690,26 @@ void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* o
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2)); CK(cudaEventCreate(&e3));
   CK(cudaEventRecord(e0, st));
   if (n) CK(cudaMemcpyAsync(dS, S_host, n, cudaMemcpyHostToDevice, st));
-  if (ascii) {
+  if (input == IN_ASCII) {
     u8* dC = pool.alloc<u8>(n + 16);
     ascii_to_codes(dS, n, dC, st);
     dS = dC;
+  } else if (input == IN_FILE) {
+    u8* dC = pool.alloc<u8>(n + 16);
+    const bool fasta = n && S_host[0] == '>';  // io.hpp:8
+    const u64 nt = do_ingest(c, pool, dS, n, fasta, dC);
+    pool.release(dS);
+    dS = dC;
+    n = nt;
+    if (n_text) *n_text = n;
+    if (n + 1 >= 0xFFFFFFFFull) throw CudaError(KISS_B200_ERR_TOO_LARGE, "text too large for 32-bit suffix indices");
+    if (n + 1 > out_count_hint) throw CudaError(KISS_B200_ERR_ARG, "suffix array buffer smaller than text length + 1");
+    if (n == 0) {  // headers / empty lines only: SA = {0} (kiss1_core.hpp:237-238)
+      if (out_host) out_host[0] = 0;
+      if (t) memset(t, 0, sizeof(*t));
+      cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
+      return;
+    }
   }
   CK(cudaEventRecord(e1, st));
   u64 out_n = (stop == STOP_LMS || stop == STOP_SORT) ? n / 2 + 2 : n + 1;
@@ -802,7 +842,7 @@ int kiss_b200_suffix_sort_dna_u32(kiss_b200_ctx* c, const uint8_t* S_host, uint6
   if (!SA_host || (n && !S_host) || (algo != 0 && algo != 1)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   if (int r = check_n(n)) return r;
   if (n == 0) return c ? trivial_n0(SA_host, t) : KISS_B200_ERR_ARG;
-  return guarded(c, [&] { run_host(c, S_host, n, k, algo, SA_host, n + 1, STOP_FULL, false, t, nullptr); });
+  return guarded(c, [&] { run_host(c, S_host, n, k, algo, SA_host, n + 1, STOP_FULL, IN_CODES, t, nullptr); });
 }
 
 int kiss_b200_suffix_sort_ascii_u32(kiss_b200_ctx* c, const char* seq_host, uint64_t n, uint32_t k, int algo,
@@ -810,7 +850,29 @@ int kiss_b200_suffix_sort_ascii_u32(kiss_b200_ctx* c, const char* seq_host, uint
   if (!SA_host || (n && !seq_host) || (algo != 0 && algo != 1)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   if (int r = check_n(n)) return r;
   if (n == 0) return c ? trivial_n0(SA_host, t) : KISS_B200_ERR_ARG;
-  return guarded(c, [&] { run_host(c, (const u8*)seq_host, n, k, algo, SA_host, n + 1, STOP_FULL, true, t, nullptr); });
+  return guarded(c, [&] { run_host(c, (const u8*)seq_host, n, k, algo, SA_host, n + 1, STOP_FULL, IN_ASCII, t, nullptr); });
+}
+
+int kiss_b200_suffix_sort_file_u32(kiss_b200_ctx* c, const uint8_t* file_host, uint64_t nbytes, uint32_t k, int algo,
+                                   uint32_t* SA_host, uint64_t SA_capacity, uint64_t* n_out, kiss_b200_timings* t) {
+  if (!c || !SA_host || !SA_capacity || !n_out || (nbytes && !file_host) || (algo != 0 && algo != 1)) {
+    g_last_error = "bad argument";
+    return KISS_B200_ERR_ARG;
+  }
+  *n_out = 0;
+  if (nbytes == 0) return trivial_n0(SA_host, t);
+  return guarded(c, [&] { run_host(c, file_host, nbytes, k, algo, SA_host, SA_capacity, STOP_FULL, IN_FILE, t, nullptr, n_out); });
+}
+
+int kiss_b200_ingest_dev(kiss_b200_ctx* c, const uint8_t* file_dev, uint64_t nbytes, int fasta, uint8_t* codes_dev,
+                         uint64_t* n_out) {
+  if (!c || !n_out || (nbytes && (!file_dev || !codes_dev))) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  *n_out = 0;
+  if (nbytes == 0) return KISS_B200_OK;
+  return guarded(c, [&] {
+    Pool pool(c->st, &c->arena);
+    *n_out = do_ingest(c, pool, file_dev, nbytes, fasta != 0, codes_dev);
+  });
 }
 
 int kiss_b200_suffix_sort_dna_u32_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, uint32_t k, int algo,

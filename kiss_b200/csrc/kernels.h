@@ -78,6 +78,12 @@ void pack_codes(const u8* S, u64 n, u64* T, cudaStream_t st);
 void ascii_to_codes(const u8* ascii, u64 n, u8* S, cudaStream_t st);
 void synth_uniform(u8* S, u64 n, u64 seed, cudaStream_t st);
 
+// ---------------------------------------------------------------- ingest.cu
+// file bytes -> codes with the reference's read_sequence semantics (FASTA headers and newlines dropped, see ingest.cu)
+u64 ingest_chunks(u64 nbytes);
+void ingest(const u8* raw_dev, u64 nbytes, u8* codes_dev, u32* lead, u32* rest, u64* last_ls, u8* hflag, u32* partials,
+            u64* total_dev, bool fasta, cudaStream_t st);
+
 // ---------------------------------------------------------------- lms.cu
 #define LMS_CHUNK_WORDS 64ull
 inline u64 lms_chunks(u64 n) { return ((n + 31) / 32 + LMS_CHUNK_WORDS - 1) / LMS_CHUNK_WORDS; }

@@ -136,14 +136,28 @@ __global__ void __launch_bounds__(TG_THREADS) k_groups_tiny(const K* __restrict_
   __syncthreads();
   // ---- phase 2: dense gathers
   if (deep) {
+    // (four elements per thread and step: the four position loads, then the eight text loads, are in flight together —
+    // one element per step left two dependent DRAM latencies exposed between the barriers)
     const u32 ntied = s_ntied;
-    for (u32 j = tid; j < ntied; j += TG_THREADS) {
-      const u32 t = stied[j];
-      const u32 pp = pos[base + t];
-      u64 wv = word_at(sp.T, (u64)pp + h);
-      if (rem < 32) wv &= ~0ull << (64 - 2 * rem);
-      spos[t] = pp;
-      sw[t] = wv;
+    for (u32 j0 = 0; j0 < ntied; j0 += 4 * TG_THREADS) {
+      u32 t[4], pp[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const u32 j = j0 + q * TG_THREADS + tid;
+        t[q] = j < ntied ? stied[j] : 0xFFFFFFFFu;
+        pp[q] = j < ntied ? pos[base + t[q]] : 0u;
+      }
+      u64 wv[4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) wv[q] = t[q] != 0xFFFFFFFFu ? word_at(sp.T, (u64)pp[q] + h) : 0ull;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        if (t[q] != 0xFFFFFFFFu) {
+          if (rem < 32) wv[q] &= ~0ull << (64 - 2 * rem);
+          spos[t[q]] = pp[q];
+          sw[t[q]] = wv[q];
+        }
+      }
     }
   }
   __syncthreads();

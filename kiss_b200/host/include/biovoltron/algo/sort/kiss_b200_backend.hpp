@@ -69,6 +69,19 @@ inline void suffix_array_dna(const vector<std::uint8_t>& S, vector<std::uint32_t
   raise(kiss_b200_suffix_sort_dna_u32(context(), S.data(), S.size(), k, algo, SA.data(), &last_timings()));
 }
 
+// read_sequence (include/utils/io.hpp:6-18) + `% 4` + the sorter in one call: `file` holds the bytes of a FASTA or
+// plain-text file, header / newline stripping and base encoding run on the device (kiss_b200_suffix_sort_file_u32).
+// Returns the text length n; SA has n + 1 entries.
+inline std::uint64_t suffix_array_file(const std::vector<std::uint8_t>& file, vector<std::uint32_t>& SA, std::uint32_t k,
+                                       int algo) {
+  SA.resize(file.size() + 1);
+  std::uint64_t n = 0;
+  raise(kiss_b200_suffix_sort_file_u32(context(), file.data(), file.size(), k, algo, SA.data(), SA.size(), &n,
+                                       &last_timings()));
+  SA.resize(n + 1);
+  return n;
+}
+
 }  // namespace b200
 
 template<typename char_type, typename size_type>

@@ -36,7 +36,8 @@ void usage(std::ostream& os) {
         "  -g [ --generic ]          (Under construction) input contains bases other than ATCG\n"
         "  -t [ --num_threads ] NUM  number of thread (accepted, unused: the GPU path has no host threads)\n"
         "  --verbose                 print more information\n"
-        "  --gpu IDX                 CUDA device (default 0)\n\n"
+        "  --gpu IDX                 CUDA device (default 0)\n"
+        "  --host-ingest             parse the file on the host (the reference's serial getline loop) instead of on the device\n\n"
         "./kISS suffix_sort [--option ...] <FASTA filename/Text filename>\n\n"
         "Options:\n"
         "  -k [ --kordered ] NUM (=256)          a k-ordered value, where each suffix is sorted based on the\n"
@@ -87,7 +88,7 @@ std::vector<std::uint8_t> read_sequence(std::istream& fin) {
 }
 
 struct Args {
-  bool help = false, version = false, generic = false, verbose = false;
+  bool help = false, version = false, generic = false, verbose = false, host_ingest = false;
   std::size_t threads = std::thread::hardware_concurrency();
   int gpu = 0;
   std::string command, file, out;
@@ -133,6 +134,7 @@ Args parse(int argc, char** argv) {
     else if (flag == "-t" || flag == "--num_threads") a.threads = parse_size(value(flag));
     else if (flag == "--gpu") a.gpu = (int)parse_size(value(flag));
     else if (flag == "--out") a.out = value(flag);
+    else if (flag == "--host-ingest") a.host_ingest = true;
     else if (flag == "-k" || flag == "--kordered") a.k = parse_size(value(flag));
     else if (flag == "-s" || flag == "--sorting-algorithm") {
       std::string v = upper(value(flag));  // options.hpp:67-81
@@ -155,15 +157,33 @@ int suffix_sort_main(const Args& a) {
   if (a.file.empty()) throw std::invalid_argument("the option '--fasta' is required but missing");
   std::ifstream fa(a.file, std::ios::binary);
   if (!fa) throw std::invalid_argument("cannot open " + a.file);
-  auto seq = read_sequence(fa);
   biovoltron::kiss::b200::device_index() = a.gpu;
   auto k32 = (std::uint32_t)a.k;  // narrows at the call like suffix_sort.hpp:59
-  auto t0 = std::chrono::steady_clock::now();
   biovoltron::kiss::vector<std::uint32_t> sa;
-  if (a.algo == KISS_B200_PARALLEL_SORTING) sa = biovoltron::KISS1Sorter<std::uint32_t>::get_suffix_array_dna(seq, k32, a.threads);
-  else sa = biovoltron::KISS2Sorter<std::uint32_t>::get_suffix_array_dna(seq, k32, a.threads);
-  double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-  if (a.verbose && !seq.empty()) {  // the reference's per-stage DEBUG lines (kiss1_core.hpp:244-267; README.md:95-100)
+  std::uint64_t n_text = 0;
+  double sec = 0;
+  if (a.host_ingest) {
+    // the reference's way: parse on the host (serial getline), then the sorter facade on the codes
+    auto seq = read_sequence(fa);
+    n_text = seq.size();
+    auto t0 = std::chrono::steady_clock::now();
+    if (a.algo == KISS_B200_PARALLEL_SORTING) sa = biovoltron::KISS1Sorter<std::uint32_t>::get_suffix_array_dna(seq, k32, a.threads);
+    else sa = biovoltron::KISS2Sorter<std::uint32_t>::get_suffix_array_dna(seq, k32, a.threads);
+    sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  } else {
+    // default: the file's bytes go to the device as they are; header / newline stripping and base encoding run
+    // there (read_sequence semantics, ingest.cu) — no per-character host loop
+    fa.seekg(0, std::ios::end);
+    const std::streamoff bytes = fa.tellg();
+    fa.seekg(0, std::ios::beg);
+    std::vector<std::uint8_t> file((std::size_t)(bytes > 0 ? bytes : 0));
+    if (!file.empty()) fa.read(reinterpret_cast<char*>(file.data()), (std::streamsize)file.size());
+    if (!fa && !file.empty()) throw std::runtime_error("cannot read " + a.file);
+    auto t0 = std::chrono::steady_clock::now();
+    n_text = biovoltron::kiss::b200::suffix_array_file(file, sa, k32, a.algo);
+    sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  }
+  if (a.verbose && n_text) {  // the reference's per-stage DEBUG lines (kiss1_core.hpp:244-267; README.md:95-100)
     const auto& t = biovoltron::kiss::b200::last_timings();
     const char* w = "kiss_b200";
     log_line("debug", w, "host to device elapsed " + std::to_string(t.h2d));
@@ -175,7 +195,7 @@ int suffix_sort_main(const Args& a) {
     log_line("debug", w, "device to host elapsed " + std::to_string(t.d2h));
   }
   log_line("info", "suffix_sort.hpp:61",
-           "n = " + std::to_string(seq.size()) + ", k = " + std::to_string(a.k) + ", suffix sorting elapsed " + std::to_string(sec));
+           "n = " + std::to_string(n_text) + ", k = " + std::to_string(a.k) + ", suffix sorting elapsed " + std::to_string(sec));
   if (!a.out.empty()) {
     std::ofstream os(a.out, std::ios::binary);
     os.write(reinterpret_cast<const char*>(sa.data()), (std::streamsize)(sa.size() * sizeof(std::uint32_t)));

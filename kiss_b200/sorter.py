@@ -74,6 +74,23 @@ class Context:
         self.last_timings = t.as_dict()
         return SA
 
+    def suffix_array_file(self, data, k=256, algo=PARALLEL_SORTING):
+        """`data` = the bytes of a FASTA / plain-text file (read_sequence semantics, include/utils/io.hpp:6-18):
+        returns (suffix array, text length)"""
+        b = np.frombuffer(data, dtype=np.uint8) if isinstance(data, (bytes, bytearray, memoryview)) else data
+        b = np.ascontiguousarray(b, dtype=np.uint8)
+        SA = np.empty(b.size + 1, np.uint32)
+        n, t = C.c_uint64(), Timings()
+        check(lib().kiss_b200_suffix_sort_file_u32(self._h, b.ctypes.data, b.size, k & 0xFFFFFFFF, algo, SA.ctypes.data,
+                                                   SA.size, C.byref(n), C.byref(t)))
+        self.last_timings = t.as_dict()
+        return SA[:n.value + 1].copy(), n.value
+
+    def ingest_dev(self, file_ptr, nbytes, fasta, codes_ptr):
+        n = C.c_uint64()
+        check(lib().kiss_b200_ingest_dev(self._h, file_ptr, nbytes, 1 if fasta else 0, codes_ptr, C.byref(n)))
+        return n.value
+
     def suffix_array_dna_dev(self, S_ptr, n, SA_ptr, k=256, algo=PARALLEL_SORTING):
         """device-resident variant: S_ptr / SA_ptr are device addresses (e.g. torch tensor.data_ptr())"""
         t = Timings()

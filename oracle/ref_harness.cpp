@@ -13,6 +13,9 @@
 #define SPDLOG_ACTIVE_LEVEL SPDLOG_LEVEL_OFF
 #include <biovoltron/algo/sort/kiss1_sorter.hpp>
 #include <biovoltron/algo/sort/kiss2_sorter.hpp>
+#include <biovoltron/file_io/fasta.hpp>
+#include <utils/io.hpp>
+#include <sstream>
 
 #include <chrono>
 #include <cstdint>
@@ -123,6 +126,16 @@ void ref_induce_from_sorted_lms(const uint8_t* S_, uint64_t n_, uint64_t threads
   kiss::put_lms_suffix(S, SA, SA1, states);
   kiss::induced_sort(S, SA, states);
   std::memcpy(sa_out, SA.data(), sizeof(uint32_t) * ((size_t)n + 1));
+}
+
+// the reference's own ingest: read_sequence (include/utils/io.hpp:6-18) on the bytes of a file, then the `% 4` of
+// suffix_sort_main (include/command/suffix_sort.hpp:33).  Returns the text length; out needs room for nbytes codes.
+uint64_t ref_read_sequence(const uint8_t* file, uint64_t nbytes, uint8_t* out) {
+  std::istringstream fin(std::string(reinterpret_cast<const char*>(file), nbytes));
+  auto seq = read_sequence(fin);
+  uint64_t n = seq.size();
+  for (uint64_t i = 0; i < n; i++) out[i] = (uint8_t)(seq[i] % 4);
+  return n;
 }
 
 int ref_abi_version() { return 1; }

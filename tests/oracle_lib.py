@@ -75,6 +75,9 @@ def ref():
         L.ref_kiss1_stages.argtypes = [_vp, _u64, _u32, _u64, _vp, _vp, _vp, _vp, _vp, _vp]
         L.ref_induce_from_sorted_lms.restype = None
         L.ref_induce_from_sorted_lms.argtypes = [_vp, _u64, _u64, _vp, _vp]
+        if hasattr(L, "ref_read_sequence"):
+            L.ref_read_sequence.restype = _u64
+            L.ref_read_sequence.argtypes = [_vp, _u64, _vp]
         _ref = L
     return _ref
 
@@ -164,3 +167,17 @@ def naive_suffix_array(S):
     S = bytes(_codes(S).tolist())
     n = len(S)
     return np.array([n] + sorted(range(n), key=lambda i: S[i:]), np.uint32)
+
+
+def ref_read_sequence(data):
+    """the reference's own read_sequence (include/utils/io.hpp:6-18) + `% 4` on the bytes of a file"""
+    data = bytes(data)
+    buf = np.frombuffer(data, dtype=np.uint8) if data else np.zeros(0, np.uint8)
+    out = np.zeros(max(len(data), 1), np.uint8)
+    n = ref().ref_read_sequence(buf.ctypes.data if buf.size else None, len(data), out.ctypes.data)
+    return out[:n].copy()
+
+
+def sha_bytes(a):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a, dtype=np.uint8).tobytes()).hexdigest()

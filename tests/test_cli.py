@@ -80,3 +80,23 @@ def test_empty_file(tmp_path):
     r = run("suffix_sort", str(f), "--out", str(out))
     assert r.returncode == 0 and "n = 0" in r.stderr
     assert np.fromfile(out, dtype=np.uint32).tolist() == [0]     # kiss1_core.hpp:237-238
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["fasta_80_crlf", "blank_lines", "gt_inside_line", "long_header", "text_mode_gt_line"])
+def test_device_ingest_equals_host_ingest(tmp_path, name):
+    """default = the file's bytes are stripped / encoded on the device (read_sequence semantics, io.hpp:6-18);
+    --host-ingest = the serial getline loop on the host: same n, same suffix array"""
+    import ingest_cases as ic
+    data = dict(ic.CASES, **ic.big_cases())[name]
+    f = tmp_path / "x.fa"
+    f.write_bytes(data)
+    outs = []
+    for extra in ([], ["--host-ingest"]):
+        out = tmp_path / ("sa%d.bin" % len(outs))
+        r = run("suffix_sort", str(f), "--out", str(out), *extra)
+        assert r.returncode == 0, r.stderr
+        n = int(re.search(r"n = (\d+),", r.stderr).group(1))
+        outs.append((n, np.fromfile(out, dtype=np.uint32)))
+    assert outs[0][0] == outs[1][0] and np.array_equal(outs[0][1], outs[1][1])
+    assert outs[0][1].size == outs[0][0] + 1
