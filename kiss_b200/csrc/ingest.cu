@@ -205,12 +205,32 @@ __global__ void __launch_bounds__(ING_THREADS) k_ingest_emit(const u8* __restric
   }
   if (lane == 31) ws2[w] = incl;
   __syncthreads();
-  u32 before = 0;
-  for (u32 ww = 0; ww < w; ww++) before += ws2[ww];
-  u64 dst = base_off_hi + offset[blockIdx.x] + before + incl - cnt;
+  u32 before = 0, total = 0;
+  for (u32 ww = 0; ww < ING_THREADS / 32; ww++) {
+    if (ww < w) before += ws2[ww];
+    total += ws2[ww];
+  }
+  // staged in shared memory, then written with consecutive threads on consecutive bytes (a thread's own 16 codes
+  // start at an arbitrary byte: storing them directly costs a partial sector per byte store)
+  __shared__ u8 sout[ING_CHUNK];
+  u32 lp = before + incl - cnt;
 #pragma unroll
   for (int k = 0; k < ING_PER; k++)
-    if ((keep >> k) & 1u) codes[dst++] = (u8)ingest_code(it.b[k]);
+    if ((keep >> k) & 1u) sout[lp++] = (u8)ingest_code(it.b[k]);
+  __syncthreads();
+  u8* dst = codes + base_off_hi + offset[blockIdx.x];
+  const u32 head = min(total, (u32)((16 - ((uintptr_t)dst & 15)) & 15));  // bytes before the first 16-byte boundary
+  if (threadIdx.x < head) dst[threadIdx.x] = sout[threadIdx.x];
+  const u32 nvec = (total - head) / 16;
+  for (u32 v = threadIdx.x; v < nvec; v += ING_THREADS) {
+    const u8* sp = sout + head + 16 * v;
+    u32 w4[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) w4[q] = (u32)sp[4 * q] | ((u32)sp[4 * q + 1] << 8) | ((u32)sp[4 * q + 2] << 16) | ((u32)sp[4 * q + 3] << 24);
+    *reinterpret_cast<uint4*>(dst + head + 16 * v) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+  }
+  const u32 tail0 = head + 16 * nvec;
+  if (tail0 + threadIdx.x < total) dst[tail0 + threadIdx.x] = sout[tail0 + threadIdx.x];
 }
 
 u64 ingest_chunks(u64 nbytes) { return (nbytes + ING_CHUNK - 1) / ING_CHUNK; }
