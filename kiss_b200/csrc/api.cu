@@ -666,14 +666,16 @@ u64 do_ingest(kiss_b200_ctx* c, Pool& pool, const u8* dRaw, u64 nbytes, bool fas
   u32* lead = pool.alloc<u32>(nch);
   u32* rest = pool.alloc<u32>(nch);
   u64* last_ls = pool.alloc<u64>(nch);
+  u64* bmax = pool.alloc<u64>(nch / 1024 + 2);
   u8* hflag = pool.alloc<u8>(nch);
   u32* partials = pool.alloc<u32>(scan_partials_len(nch));
   u64* total = pool.alloc<u64>(1);
-  ingest(dRaw, nbytes, dCodes, lead, rest, last_ls, hflag, partials, total, fasta, st);
+  ingest(dRaw, nbytes, dCodes, lead, rest, last_ls, bmax, hflag, partials, total, fasta, st);
   u64 n = 0;
   CK(cudaMemcpyAsync(&n, total, sizeof(u64), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  pool.release(lead); pool.release(rest); pool.release(last_ls); pool.release(hflag); pool.release(partials);
+  pool.release(lead); pool.release(rest); pool.release(last_ls); pool.release(bmax); pool.release(hflag);
+  pool.release(partials);
   pool.release(total);
   return n;
 }
