@@ -339,7 +339,6 @@ def run_b200(args):
                 alg_tot[key] = alg_tot.get(key, 0) + prof_bytes[name]
         steps = args.steps
         alg = {kk: v / merged[kk][1] for kk, v in alg_tot.items()}  # algorithmic bytes per launch
-        alg.setdefault("k_place/merge_lms", (4 + 4) * n_long)
         alg.setdefault("k_pack_codes", n + n // 4)
         if "k_wave_fused" in merged:
             # K5 induction (8(d)): 2 x 4(n+1) SA reads + 4n induced writes + 4m + 2 x n/4 packed text, per step,

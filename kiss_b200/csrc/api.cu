@@ -440,7 +440,8 @@ struct CopyOut {
 
 // `lms` = the sorted LMS suffixes (sentinel excluded), grouped by first symbol: bk.lms_off / bk.lms_count
 void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets& bk, const u32* lms, u32* SA, u32* CTX,
-               InduceStats* is, CopyOut* co = nullptr, const u32* lms_ctx = nullptr) {
+               InduceStats* is, CopyOut* co = nullptr, const u32* lms_ctx = nullptr, const u32* shorts = nullptr,
+               const u32* ins = nullptr, u32 ns = 0) {
   cudaStream_t st = c->st;
   WaveScratch ws;
   u64 maxlen = n + 1;
@@ -481,7 +482,7 @@ void do_induce(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const Buckets&
     // higher buckets): it can leave now
     if (co) co->send(SA, bk.B[cb], Lc[cb] - bk.B[cb]);
     if (bk.lms_count[cb]) {
-      induce_wave(SA, CTX, T, lms, lms_ctx, bk.lms_off[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st);
+      induce_wave(SA, CTX, T, lms, lms_ctx, bk.lms_off[cb], bk.lms_count[cb], false, 0xFu, Lc, ws, tot, st, shorts, ins, ns);
       for (int s = 0; s < 4; s++) Lc[s] += tot[s];
       is->waves_L++;
     }
@@ -532,14 +533,6 @@ void do_shorts(kiss_b200_ctx* c, Pool& pool, const u32* shorts_text, u32 ns, con
   out->ins = pool.alloc<u32>(ns);
   shorts_order(shorts_text, ns, sp, rank0, out->shorts, c->st);
   shorts_insertions(out->shorts, ns, longs, nl, sp, out->ins, c->st);
-}
-
-// one list out of the sorted longs and the ordered shorts (the longs themselves when there are no shorts)
-const u32* merged_lms(Pool& pool, const SortedLms& sl, cudaStream_t st) {
-  if (!sl.ns) return sl.longs;
-  u32* out = pool.alloc<u32>((u64)sl.nl + sl.ns);
-  merge_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, out, st);
-  return out;
 }
 
 void do_sort(kiss_b200_ctx* c, Pool& pool, SortedLms* out, SortStats* stats) {
@@ -596,10 +589,10 @@ void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* d
     } else {
       // the full path never places: the L pass scans the sorted list itself (put_lms_suffix is folded into it)
       dCTX = pool.alloc<u32>(n + 1);
-      lms = merged_lms(pool, sl, st);
+      lms = sl.longs;  // the LMS waves read the merged list on the fly (induce_wave, VIRT): no merge pass
     }
     CK(cudaEventRecord(c->ev[5], st));
-    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, lms, dSA, dCTX, &is, co);
+    if (stop == STOP_FULL) do_induce(c, pool, P.T, n, bk, lms, dSA, dCTX, &is, co, nullptr, sl.shorts, sl.ins, sl.ns);
     CK(cudaEventRecord(c->ev[6], st));
     CK(cudaEventSynchronize(c->ev[6]));
     CK(cudaEventElapsedTime(&t_sort, c->ev[3], c->ev[4]));
@@ -1059,19 +1052,13 @@ static int finish_from_sorted(kiss_b200_ctx* c, const uint32_t* sorted_long_dev,
     do_shorts(c, pool, P.pos + P.n_long, ns, sorted_long_dev, P.n_long, P.sp, &sl);
     Buckets bk = make_buckets(P.counters, P.n);
     u32* dCTX = pool.alloc<u32>(P.n + 1);
-    const u32* lms = merged_lms(pool, sl, st);
-    // contexts fetched by the ranks that sorted the ranges; the few short suffixes keep "not fetched" (1)
+    // the LMS waves read (long suffixes, short ones inserted on the fly): neither the positions nor the contexts
+    // fetched by the ranks that sorted the ranges are merged into new arrays
+    const u32* lms = sl.longs;
     const u32* lms_ctx = ctx_long_dev;
-    if (ctx_long_dev && sl.ns) {
-      u32* ones = pool.alloc<u32>(sl.ns);
-      fill_u32(ones, sl.ns, 1u, st);
-      u32* merged = pool.alloc<u32>((u64)sl.nl + sl.ns);
-      merge_lms(ctx_long_dev, sl.nl, ones, sl.ins, sl.ns, merged, st);
-      lms_ctx = merged;
-    }
     CK(cudaEventRecord(c->ev[5], st));
     InduceStats is;
-    do_induce(c, pool, P.T, P.n, bk, lms, SA_dev, dCTX, &is, nullptr, lms_ctx);
+    do_induce(c, pool, P.T, P.n, bk, lms, SA_dev, dCTX, &is, nullptr, lms_ctx, sl.shorts, sl.ins, sl.ns);
     CK(cudaEventRecord(c->ev[6], st));
     CK(cudaEventSynchronize(c->ev[6]));
     if (t) {

@@ -108,6 +108,11 @@ struct WaveArgs {
   u32 down;     // scan from the top slot downwards
   u32 symmask;  // symbols that may be induced
   u64 cur[4];   // bucket cursors
+  // the scanned list as the sorted long suffixes with the few short ones inserted on the fly (VIRT instances of the
+  // wave kernel): slot L holds shorts[t] when ins[t] + t == L, else inSA[L - (number of shorts placed before L)]
+  const u32* shorts;
+  const u32* ins;
+  u32 ns;
 };
 
 // context of suffix v: the 15 bases before it (two adjacent text words).  Variants that were measured and lost:
@@ -218,7 +223,7 @@ struct WaveShared {
 };
 
 // one tile of a wave.  LOOKBACK = false: the wave is this single tile (no status traffic); tot[] gets the counts.
-template <bool DOWN, bool LOOKBACK>
+template <bool DOWN, bool LOOKBACK, bool VIRT = false>
 __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, WaveShared& sh, u64* __restrict__ status,
                                           u32* __restrict__ state, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
   WaveSmem& sm = sh.sm;
@@ -228,11 +233,41 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
   const u64 hi = a.lo + a.len;
   // logical index q of the aligned wave: up: slot = abase + q; down: slot = atop - 1 - q
   // (cut on 16-byte boundaries of the scanned array: `mis` = its misalignment in entries, 0 for SA itself)
-  const u64 mis = ((u64)(uintptr_t)a.inSA >> 2) & 3ull;
+  const u64 mis = VIRT ? 0ull : ((u64)(uintptr_t)a.inSA >> 2) & 3ull;
   const u64 abase = a.lo - ((a.lo + mis) & 3ull), atop = hi + ((4ull - ((hi + mis) & 3ull)) & 3ull);
   const u64 q0 = (u64)tile * WAVE_TILE + (u64)threadIdx.x * WAVE_ITEMS;
   u32 cx[WAVE_ITEMS], val[WAVE_ITEMS];
-  {
+  if constexpr (VIRT) {
+    // (upward only) the thread's 16 logical slots of the merged list; t = short suffixes placed before the slot
+    typedef long long s64;
+    const s64 first = (s64)abase + (s64)q0, slo = (s64)a.lo, shi = (s64)hi;
+    const s64 L0 = first > slo ? first : slo;
+    u32 t = 0;
+    {
+      u32 lo_ = 0, hi_ = a.ns;  // first short whose slot ins[s] + s is >= L0
+      while (lo_ < hi_) {
+        const u32 mid = lo_ + (hi_ - lo_) / 2;
+        if ((s64)a.ins[mid] + mid < L0) lo_ = mid + 1; else hi_ = mid;
+      }
+      t = lo_;
+    }
+#pragma unroll
+    for (int i = 0; i < WAVE_ITEMS; i++) {
+      const s64 L = first + i;
+      u32 c = 1u, v = 0u;
+      if (L >= slo && L < shi) {
+        if (t < a.ns && (s64)a.ins[t] + t == L) {
+          v = a.shorts[t];
+          t++;
+        } else {
+          v = a.inSA[L - t];
+          if (a.inCTX) c = a.inCTX[L - t];
+        }
+      }
+      cx[i] = c;
+      val[i] = v;
+    }
+  } else {
     // address-ascending block of 16 slots owned by this thread (signed: the last tile of a downward wave may
     // reach below slot 0)
     typedef long long s64;
@@ -389,14 +424,14 @@ __device__ __forceinline__ void wave_tile(const WaveArgs& a, const u32 tile, Wav
   }
 }
 
-template <bool DOWN, int MINB>
+template <bool DOWN, int MINB, bool VIRT = false>
 __global__ void __launch_bounds__(WAVE_THREADS, MINB) k_wave_fused(WaveArgs a, u64* __restrict__ status, u32* __restrict__ state,
                                                                   u32 tile_base, u32 ntiles, u32 epoch, u32* __restrict__ tot) {
   extern __shared__ __align__(16) unsigned char wave_smem[];
   WaveShared& sh = *reinterpret_cast<WaveShared*>(wave_smem);
   if (threadIdx.x == 0) sh.tile = atomicAdd(&state[0], 1u) - tile_base;
   __syncthreads();
-  wave_tile<DOWN, true>(a, sh.tile, sh, status, state, ntiles, epoch, tot);
+  wave_tile<DOWN, true, VIRT>(a, sh.tile, sh, status, state, ntiles, epoch, tot);
 }
 
 // The tail of a bucket: once a wave fits one tile every later wave of the bucket does too (wave sizes never
@@ -646,6 +681,7 @@ u32 induce_tail(u32* SA, u32* CTX, const u64* T, u32 bucket, u64* p, bool down, 
                 WaveScratch ws, cudaStream_t st) {
   WaveArgs a;
   a.SA = SA; a.CTX = CTX; a.inSA = SA; a.inCTX = CTX; a.T = T; a.lo = 0; a.len = 0; a.down = down ? 1u : 0u;
+  a.shorts = nullptr; a.ins = nullptr; a.ns = 0;
   a.symmask = symmask;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
   {
@@ -670,6 +706,7 @@ void wave_init() {
   const int bytes = (int)sizeof(WaveShared);
   CK(cudaFuncSetAttribute(k_wave_fused<true, WAVE_MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
   CK(cudaFuncSetAttribute(k_wave_fused<false, WAVE_MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  CK(cudaFuncSetAttribute(k_wave_fused<false, WAVE_MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
   CK(cudaFuncSetAttribute(k_wave_tail<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
   CK(cudaFuncSetAttribute(k_wave_tail<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
 }
@@ -687,27 +724,22 @@ void lms_contexts(const u64* T, const u32* pos, u64 cnt, u32* out, cudaStream_t 
   k_lms_contexts<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(T, pos, cnt, out);
   CK_LAUNCH(); g_launches++;
 }
-__global__ void __launch_bounds__(256) k_fill_u32(u32* __restrict__ p, u64 cnt, u32 v) {
-  const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < cnt) p[i] = v;
-}
-void fill_u32(u32* p, u64 cnt, u32 v, cudaStream_t st) {
-  if (!cnt) return;
-  k_fill_u32<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(p, cnt, v);
-  CK_LAUNCH(); g_launches++;
-}
-
 void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, const u32* lms_ctx, u64 lo, u64 len, bool down,
-                 u32 symmask, const u64 cur[4], WaveScratch ws, u32 tot[4], cudaStream_t st) {
+                 u32 symmask, const u64 cur[4], WaveScratch ws, u32 tot[4], cudaStream_t st, const u32* shorts,
+                 const u32* ins, u32 ns) {
   tot[0] = tot[1] = tot[2] = tot[3] = 0;
   if (len == 0) return;
   WaveArgs a;
   a.SA = SA; a.CTX = CTX; a.T = T; a.lo = lo; a.len = len; a.down = down ? 1u : 0u; a.symmask = symmask;
   a.inSA = lms_src ? lms_src : SA;
   // (the 16-byte loads of the two scanned arrays share their cut points: a context list must be aligned like its list)
-  a.inCTX = lms_src ? ((lms_ctx && (((uintptr_t)lms_ctx ^ (uintptr_t)lms_src) & 15) == 0) ? lms_ctx : nullptr) : CTX;
+  const bool virt = lms_src && ns && !down;  // the list is (long suffixes, short ones inserted on the fly)
+  a.inCTX = lms_src ? ((lms_ctx && (virt || (((uintptr_t)lms_ctx ^ (uintptr_t)lms_src) & 15) == 0)) ? lms_ctx : nullptr) : CTX;
+  a.shorts = virt ? shorts : nullptr;
+  a.ins = virt ? ins : nullptr;
+  a.ns = virt ? ns : 0u;
   for (int s = 0; s < 4; s++) a.cur[s] = cur[s];
-  const u64 mis = ((u64)(uintptr_t)a.inSA >> 2) & 3ull, hi = lo + len;
+  const u64 mis = virt ? 0ull : ((u64)(uintptr_t)a.inSA >> 2) & 3ull, hi = lo + len;
   u64 len_al = down ? (hi + ((4ull - ((hi + mis) & 3ull)) & 3ull) - lo) : (hi - (lo - ((lo + mis) & 3ull)));
   u32 ntiles = (u32)wave_tiles(len_al);
   {
@@ -716,7 +748,8 @@ void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, const u32*
     // its tile starts makes every later tile wait in the look-back)
     const u32 ep = ++*ws.epoch;
     // (5 resident blocks per SM, 48 registers with a small spill, measured 1 ms slower than 4)
-    if (down) k_wave_fused<true, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_host);
+    if (virt) k_wave_fused<false, WAVE_MINB, true><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_host);
+    else if (down) k_wave_fused<true, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_host);
     else k_wave_fused<false, WAVE_MINB><<<ntiles, WAVE_THREADS, sizeof(WaveShared), st>>>(a, ws.status, ws.state, *ws.tile_base, ntiles, ep, ws.tot_host);
     CK_LAUNCH(); g_launches++;
     *ws.tile_base += ntiles;
@@ -729,54 +762,6 @@ void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, const u32*
 __global__ void k_set_sentinel(u32* SA, u32* CTX, u32 n) { SA[0] = n; CTX[0] = 1u; }
 void set_sentinel(u32* SA, u32* CTX, u64 n, cudaStream_t st) {
   k_set_sentinel<<<1, 1, 0, st>>>(SA, CTX, (u32)n);
-  CK_LAUNCH(); g_launches++;
-}
-
-#define MERGE_TILE 4096u
-// sorted longs + ordered shorts with their insertion points -> one sorted list (same ranks as k_place_lms)
-__global__ void __launch_bounds__(256) k_merge_lms(const u32* __restrict__ longs, u32 nl, const u32* __restrict__ shorts,
-                                                  const u32* __restrict__ ins, u32 ns, u32* __restrict__ out) {
-  __shared__ u32 sins[PLACE_INS_SMEM];
-  const bool cached = ns <= PLACE_INS_SMEM;
-  if (cached)
-    for (u32 t = threadIdx.x; t < ns; t += blockDim.x) sins[t] = ins[t];
-  __syncthreads();
-  const u32* I = cached ? sins : ins;
-  // shorts placed before long i = number of insertion points <= i; almost every block sees one value
-  __shared__ u32 s_edge[2];
-  const u64 b0 = (u64)blockIdx.x * MERGE_TILE;
-  if (threadIdx.x < 2) {
-    u64 q = threadIdx.x ? min(b0 + MERGE_TILE - 1, (u64)nl - 1) : b0;
-    u32 lo = 0, hi = ns;
-    while (lo < hi) {
-      u32 mid = lo + (hi - lo) / 2;
-      if (I[mid] <= (u32)q) lo = mid + 1; else hi = mid;
-    }
-    s_edge[threadIdx.x] = lo;
-  }
-  __syncthreads();
-  const u32 e0 = s_edge[0], e1 = s_edge[1];
-#pragma unroll 4
-  for (u32 t = threadIdx.x; t < MERGE_TILE; t += 256) {
-    u64 i = b0 + t;
-    if (i < nl) {
-      u32 lo = e0, hi = e1;
-      while (lo < hi) {
-        u32 mid = lo + (hi - lo) / 2;
-        if (I[mid] <= (u32)i) lo = mid + 1; else hi = mid;
-      }
-      out[i + lo] = longs[i];
-    } else if (i < (u64)nl + ns) {
-      u32 k = (u32)(i - nl);
-      out[(u64)I[k] + k] = shorts[k];
-    }
-  }
-}
-void merge_lms(const u32* longs, u32 nl, const u32* shorts, const u32* ins, u32 ns, u32* out, cudaStream_t st) {
-  u64 tot = (u64)nl + ns;
-  if (!tot || !ns) return;
-  ProfScope ps(PK_PLACE, st);
-  k_merge_lms<<<(unsigned)((tot + MERGE_TILE - 1) / MERGE_TILE), 256, 0, st>>>(longs, nl, shorts, ins, ns, out);
   CK_LAUNCH(); g_launches++;
 }
 

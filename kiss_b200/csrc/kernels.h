@@ -194,15 +194,15 @@ inline u64 wave_tiles(u64 len) { return (len + WAVE_TILE - 1) / WAVE_TILE; }
 // CTX is the per-entry context array (n + 1 words, see induce.cu).  With `lms_src` the scanned entries are
 // lms_src[lo, lo+len) — the sorted LMS list itself, so the LMS suffixes are never written to SA on this path.
 // `lms_ctx` (nullable, aligned like lms_src): contexts of the list entries, fetched beforehand (lms_contexts)
+// `shorts`, `ins`, `ns` (with lms_src): lms_src holds only the sorted LONG suffixes and the wave reads the merged list
+// (short suffix s sits at slot ins[s] + s) without it ever being materialised; lo / len index the merged list
 void induce_wave(u32* SA, u32* CTX, const u64* T, const u32* lms_src, const u32* lms_ctx, u64 lo, u64 len, bool down,
-                 u32 symmask, const u64 cur[4], WaveScratch ws, u32 tot[4], cudaStream_t st);
+                 u32 symmask, const u64 cur[4], WaveScratch ws, u32 tot[4], cudaStream_t st, const u32* shorts = nullptr,
+                 const u32* ins = nullptr, u32 ns = 0);
 // out[i] = context word of suffix pos[i] (the 15 bases before it, see induce.cu)
 void lms_contexts(const u64* T, const u32* pos, u64 cnt, u32* out, cudaStream_t st);
-void fill_u32(u32* p, u64 cnt, u32 v, cudaStream_t st);
 // SA[0] = n (the sentinel suffix), context not fetched
 void set_sentinel(u32* SA, u32* CTX, u64 n, cudaStream_t st);
-// longs + shorts -> one sorted list `out` (nl + ns entries); no-op when ns == 0 (the longs are the list)
-void merge_lms(const u32* longs, u32 nl, const u32* shorts, const u32* ins, u32 ns, u32* out, cudaStream_t st);
 
 // Run every remaining wave of `bucket` on the device while it fits one tile (see k_wave_tail): the wave starts
 // at *p and ends at cur[bucket].  Returns the number of waves; updates *p and cur[].

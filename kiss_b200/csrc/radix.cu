@@ -22,7 +22,7 @@ const char* prof_name(int id) {
                                         "k_radix_scatter", "k_groups_tiny", "k_groups_medium<=32", "k_groups_medium<=64",
                                         "k_groups_medium<=128", "k_groups_medium<=256", "k_groups_medium<=512",
                                         "k_groups_medium<=2048", "k_groups_classify+big_*",
-                                        "k_short_*", "k_place/merge_lms", "k_wave_fused(lms)", "k_wave_fused", "k_wave_small/tail"};
+                                        "k_short_*", "k_place_lms", "k_wave_fused(lms)", "k_wave_fused", "k_wave_small/tail"};
   return (id >= 0 && id < PK_COUNT) ? names[id] : "?";
 }
 cudaEvent_t Profiler::get() {
