@@ -333,6 +333,10 @@ void sort_long_lms(kiss_b200_ctx* c, Pool& pool, u32* key, u32* pos, u32 N, cons
   Sync sync{c};
   *out_pos = pos;
   if (N == 0) return;
+  if (getenv("KISS_B200_DEBUG_GROUPS") && !g_med_dbg) {
+    CK(cudaMalloc(&g_med_dbg, 6 * 64 * sizeof(u64)));
+    CK(cudaMemset(g_med_dbg, 0, 6 * 64 * sizeof(u64)));
+  }
   u32* key_alt = pool.alloc<u32>(N);
   u32* pos_alt = pool.alloc<u32>(N);
   u64 ntiles = radix_tiles(N);
@@ -401,6 +405,22 @@ void sort_long_lms(kiss_b200_ctx* c, Pool& pool, u32* key, u32* pos, u32 N, cons
   CK(cudaMemcpyAsync(&tied_h, tied, sizeof(u64), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   stats->tied = tied_h;
+  if (g_med_dbg) {
+    u64 d[6 * 64];
+    CK(cudaMemcpy(d, g_med_dbg, sizeof(d), cudaMemcpyDeviceToHost));
+    CK(cudaMemset(g_med_dbg, 0, sizeof(d)));
+    for (int c = 0; c < 6; c++) {
+      const u64* x = d + 64 * c;
+      if (!x[0]) continue;
+      fprintf(stderr, "[kiss_b200] medium class %d: %llu team-rounds (%llu network, %llu ranking); per round (groups, active elements, mean longest segment):",
+              c, (unsigned long long)x[0], (unsigned long long)x[1], (unsigned long long)x[2]);
+      for (int r = 0; r < 16 && x[48 + r]; r++)
+        fprintf(stderr, " [%d: %llu, %llu, %.0f]", r, (unsigned long long)x[48 + r], (unsigned long long)x[16 + r],
+                (double)x[32 + r] / (double)x[48 + r]);
+      fprintf(stderr, "; first round by buckets %llu, by the network %llu (%llu with a crowded pivot bucket), elements equal to the pivot %llu, longest bucket %llu\n",
+              (unsigned long long)x[3], (unsigned long long)x[4], (unsigned long long)x[5], (unsigned long long)x[6], (unsigned long long)x[8]);
+    }
+  }
 }
 
 Buckets make_buckets(const u64 counters[8], u64 n) {

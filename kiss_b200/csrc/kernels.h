@@ -141,6 +141,7 @@ __host__ __device__ inline u32 med_class_of(u32 size) {
 // class_groups[6] / class_elems[6]: groups and elements per size class (a class without groups is not launched)
 void groups_medium(u32* pos, const u32* med, u32 medN, const u32* class_groups, const u32* class_elems, SortParams sp,
                    u64 h, cudaStream_t st);
+extern u64* g_med_dbg;  // debug statistics of the medium teams (null = off)
 // sizes[g] = big[3g+1]
 void big_sizes(const u32* big, u32 nbig, u32* sizes, cudaStream_t st);
 // worklist of the big groups (one pivot round, see lms_sort.cu): wkey = [group | side | q | bases] against the

@@ -304,22 +304,28 @@ void groups_classify_u64(const u64* keys, u32 N, u32 ng, GroupLists gl, int kind
 }
 
 // ------------------------------------------------------------------------------------------- medium groups
-// One team (a warp up to 256 elements, a block of 8 warps above) refines one group by PIVOT ROUNDS.  In a round
-// every element that still shares its segment with another is compared with the segment's first element (the
-// pivot) from the segment's depth on: it finds the first base q where it differs (word-wise, independent
-// loads), which side of the pivot it falls on, and its own next 14 bases from q.  ONE 64-bit key
-//     [segment:11 | side:2 | q (descending on the greater side):12 | 14 bases:28 | slot:11]
-// then orders the whole segment: before the pivot by ascending q, after it by descending q, equal (q, bases)
-// classes become new segments at depth q + 14, and everything equal to the pivot up to D is final (the slot
-// field keeps equal keys in their current order, which is ascending text position).  So the long common
-// prefixes of repeat copies are skipped in one step — a group of near-identical copies (tandem arrays: a
-// mutation every 100 bases) is done after one or two rounds, where fixed 20/32-base rounds needed (D - h) / 20
-// full sorts — and a group without common prefix is split by 14 bases per round.
-// Unbounded depth (-k -1 / PREFIX_DOUBLING): q needs 32 bits, so the key carries one base instead of 14 and a
-// suffix that ends inside the comparison is smaller than one that goes on (kiss1_core.hpp:134).
+// One team (a warp up to 256 elements, a block above) refines one group by PIVOT ROUNDS.  In a round every element
+// that still shares its segment with another is compared with the segment's pivot from the segment's depth on: it
+// finds the first base q where it differs (word-wise, independent loads), which side of the pivot it falls on, and
+// its own next bases from q.  Its key
+//     hi = [segment:11 | side:2 | q (descending on the greater side):12 | 14 bases:28 | slot:11]   lo = the next 32 bases
+// then orders the whole segment: before the pivot by ascending q, after it by descending q, equal (q, bases) classes
+// become new segments at depth q + 46, and everything equal to the pivot up to D is final (the slot field keeps equal
+// keys in their current order, which is ascending text position).  Long common prefixes of repeat copies are skipped
+// in one step, and a group without common prefix is split by 46 bases per round (the first version carried 14 bases
+// in a single word: copies that diverge by 5-15 % needed ~7 rounds of the sorting network per group, 7700 thread
+// instructions per element in the largest class; profiles/r2_a_bench_*.json).
+// The pivot of a block team is VIRTUAL: the base-wise majority of three suffixes of the segment.  Any string works as a
+// pivot; a real element carries its own mutations — every other copy differs from it THERE, so the main lineage of a
+// group of near-identical copies advanced only to the pivot's next mutation per round — while two of three copies agree
+// almost everywhere, so nearly every element is split off by its OWN first mutation.  (Two of the three agreeing fixes
+// both bits of a base; where all three differ the field is arbitrary, which is as good as any.  The three loads are
+// the same for every thread of a segment.)  Warp teams keep the segment's first element: their groups are small and
+// the extra loads cost more than the rounds they save.
+// Unbounded depth (-k -1 / PREFIX_DOUBLING): q needs 32 bits, so the key is one word carrying one base, and a suffix
+// that ends inside the comparison is smaller than one that goes on (kiss1_core.hpp:134).
 // The keys live in registers — lane l of warp w holds the slots (w R + r) 32 + l, r < R — and are bitonic-sorted
-// with warp shuffles (partner distance < 32), register swaps (< 32 R) and, in the block team only, shared
-// memory (six steps of 66 at 2048 slots).
+// with warp shuffles (partner distance < 32), register swaps (< 32 R) and, in the block team only, shared memory.
 template <int NW>
 __device__ __forceinline__ void team_sync() {
   if (NW == 1) __syncwarp(); else __syncthreads();
@@ -334,65 +340,98 @@ __device__ __forceinline__ bool team_or(bool v) {
 #define MK_SIDE_SHIFT 51
 #define MK_SEG_SHIFT 53
 #define MK_EQUAL 1ull
-// key of an element against its pivot; `d` = depth both are known equal to
-template <bool UNB>
-__device__ __forceinline__ u64 pivot_key(const SortParams& sp, u32 p, u32 ph, u64 d) {
-  u64 q = d, side = MK_EQUAL;
-  if (!UNB) {
-    while (q < sp.D) {
-      u64 wa = word_at(sp.T, (u64)p + q), wb = word_at(sp.T, (u64)ph + q);
-      const u64 rem = sp.D - q;
-      if (rem < 32) { const u64 mk = ~0ull << (64 - 2 * rem); wa &= mk; wb &= mk; }
-      const u64 x = wa ^ wb;
-      if (x) {
-        q += (u64)(__clzll((long long)x) >> 1);
-        side = wa > wb ? 2ull : 0ull;
-        break;
-      }
-      q += 32;
-    }
-    if (side == MK_EQUAL) return MK_EQUAL << MK_SIDE_SHIFT;
-    u64 b14 = word_at(sp.T, (u64)p + q) >> 36;
-    const u64 rem = sp.D - q;
-    if (rem < 14) b14 &= (~0ull << (28 - 2 * rem)) & 0xFFFFFFFull;
-    const u64 qk = side == 2 ? 4095ull - q : q;
-    return (side << MK_SIDE_SHIFT) | (qk << 39) | (b14 << MK_SLOT_BITS);
-  } else {
-    const u64 lp = sp.n - p, lh = sp.n - ph, lim = lp < lh ? lp : lh;  // bases both suffixes have
-    const u64 L = lim < sp.D ? lim : sp.D;
-    while (q < L) {
-      u64 wa = word_at(sp.T, (u64)p + q), wb = word_at(sp.T, (u64)ph + q);
-      const u64 rem = L - q;
-      if (rem < 32) { const u64 mk = ~0ull << (64 - 2 * rem); wa &= mk; wb &= mk; }
-      const u64 x = wa ^ wb;
-      if (x) {
-        q += (u64)(__clzll((long long)x) >> 1);
-        side = wa > wb ? 2ull : 0ull;
-        break;
-      }
-      q += 32;
-    }
-    u64 b = 0;  // 0 = the suffix ended at q
-    if (side == MK_EQUAL) {
-      if (L == sp.D) return MK_EQUAL << MK_SIDE_SHIFT;  // equal on the whole compared depth: position decides
-      q = lim;  // one is a prefix of the other: the shorter first
-      side = lp < lh ? 0ull : 2ull;
-    }
-    if ((u64)p + q < sp.n) b = 1ull + (word_at(sp.T, (u64)p + q) >> 62);
-    const u64 qk = side == 2 ? 0xFFFFFFFFull - q : q;
-    return (side << MK_SIDE_SHIFT) | (qk << 19) | (b << 16);
-  }
+#define MK_WIDE_BASES 46ull  // bases of its own an element of the bounded layout carries from q on (14 in hi, 32 in lo)
+__device__ __forceinline__ u64 maj3(u64 a, u64 b, u64 c) { return (a & b) | ((a | b) & c); }
+// bit-wise majority of five (a bit-sliced adder: sum = s1 + 2 (c0 + c1) >= 3)
+__device__ __forceinline__ u64 maj5(u64 a, u64 b, u64 c, u64 d, u64 e) {
+  const u64 s0 = a ^ b ^ c, c0 = maj3(a, b, c), s1 = s0 ^ d ^ e, c1 = maj3(s0, d, e);
+  return (c0 & c1) | ((c0 ^ c1) & s1);
 }
-// depth at which the elements of a class (equal keys above the slot field) are known equal
+
+// bounded layout: key of suffix p against the pivot, whose 32 bases from depth q on are pivot_word(q) (q runs over
+// d, d + 32, ...); `d` = depth all are known equal to.  Returns hi (without segment and slot); lo = the 32 bases after
+// the 14 in hi, cut at D.
+template <typename PW>
+__device__ __forceinline__ u64 pivot_key_pw(const SortParams& sp, u32 p, u64 d, u64& lo, PW pivot_word) {
+  lo = 0;
+  u64 q = d;
+  while (q < sp.D) {
+    u64 wa = word_at(sp.T, (u64)p + q), wb = pivot_word(q);
+    const u64 rem = sp.D - q;
+    if (rem < 32) { const u64 mk = ~0ull << (64 - 2 * rem); wa &= mk; wb &= mk; }
+    const u64 x = wa ^ wb;
+    if (x) {
+      q += (u64)(__clzll((long long)x) >> 1);
+      const u64 side = wa > wb ? 2ull : 0ull;
+      const u64 w0 = word_at(sp.T, (u64)p + q), w1 = word_at(sp.T, (u64)p + q + 32);
+      u64 b14 = w0 >> 36;
+      const u64 rem2 = sp.D - q;  // >= 1
+      if (rem2 < 14) b14 &= (~0ull << (28 - 2 * rem2)) & 0xFFFFFFFull;
+      if (rem2 > 14) {
+        lo = (w0 << 28) | (w1 >> 36);
+        if (rem2 < MK_WIDE_BASES) lo &= ~0ull << (64 - 2 * (rem2 - 14));
+      }
+      const u64 qk = side == 2 ? 4095ull - q : q;
+      return (side << MK_SIDE_SHIFT) | (qk << 39) | (b14 << MK_SLOT_BITS);
+    }
+    q += 32;
+  }
+  return MK_EQUAL << MK_SIDE_SHIFT;
+}
+// ... against p1 alone, or against the majority of p1, p2, p3
+__device__ __forceinline__ u64 pivot_key_b(const SortParams& sp, u32 p, u32 p1, u32 p2, u32 p3, bool maj, u64 d, u64& lo) {
+  return pivot_key_pw(sp, p, d, lo, [&](u64 q) {
+    u64 wb = word_at(sp.T, (u64)p1 + q);
+    if (maj) wb = maj3(wb, word_at(sp.T, (u64)p2 + q), word_at(sp.T, (u64)p3 + q));
+    return wb;
+  });
+}
+// unbounded layout: key of suffix p against the real pivot ph
+__device__ __forceinline__ u64 pivot_key_u(const SortParams& sp, u32 p, u32 ph, u64 d) {
+  u64 q = d, side = MK_EQUAL;
+  const u64 lp = sp.n - p, lh = sp.n - ph, lim = lp < lh ? lp : lh;  // bases both suffixes have
+  const u64 L = lim < sp.D ? lim : sp.D;
+  while (q < L) {
+    u64 wa = word_at(sp.T, (u64)p + q), wb = word_at(sp.T, (u64)ph + q);
+    const u64 rem = L - q;
+    if (rem < 32) { const u64 mk = ~0ull << (64 - 2 * rem); wa &= mk; wb &= mk; }
+    const u64 x = wa ^ wb;
+    if (x) {
+      q += (u64)(__clzll((long long)x) >> 1);
+      side = wa > wb ? 2ull : 0ull;
+      break;
+    }
+    q += 32;
+  }
+  u64 b = 0;  // 0 = the suffix ended at q
+  if (side == MK_EQUAL) {
+    if (L == sp.D) return MK_EQUAL << MK_SIDE_SHIFT;  // equal on the whole compared depth: position decides
+    q = lim;  // one is a prefix of the other: the shorter first
+    side = lp < lh ? 0ull : 2ull;
+  }
+  if ((u64)p + q < sp.n) b = 1ull + (word_at(sp.T, (u64)p + q) >> 62);
+  const u64 qk = side == 2 ? 0xFFFFFFFFull - q : q;
+  return (side << MK_SIDE_SHIFT) | (qk << 19) | (b << 16);
+}
+// depth at which the elements of a class (equal keys above the slot field) are known equal; `own` = bases of its own
+// the key carries from q on (14 for the one-word keys of the big path, MK_WIDE_BASES in the teams)
 template <bool UNB>
-__device__ __forceinline__ u64 class_depth(u64 key) {
+__device__ __forceinline__ u64 class_depth(u64 key, u64 own) {
   const u64 side = (key >> MK_SIDE_SHIFT) & 3ull;
   if (!UNB) {
     const u64 qk = (key >> 39) & 0xFFFull;
-    return (side == 2 ? 4095ull - qk : qk) + 14ull;
+    return (side == 2 ? 4095ull - qk : qk) + own;
   }
   const u64 qk = (key >> 19) & 0xFFFFFFFFull;
   return (side == 2 ? 0xFFFFFFFFull - qk : qk) + 1ull;
+}
+
+// order of two keys (never equal: the slot field is unique)
+template <bool WIDE>
+__device__ __forceinline__ bool mk_less(u64 ah, u64 al, u64 bh, u64 bl) {
+  if constexpr (!WIDE) return ah < bh;
+  const u64 ka = ah >> MK_SLOT_BITS, kb = bh >> MK_SLOT_BITS;
+  return ka != kb ? ka < kb : (al != bl ? al < bl : ah < bh);
 }
 
 // ascending bitonic sort of the team's NW * R * 32 keys (slot order = (w R + r) 32 + lane).  The stage (k2) and
@@ -400,22 +439,27 @@ __device__ __forceinline__ u64 class_depth(u64 key) {
 // steps x R at 2048 slots, 44 k instructions that miss the instruction cache (12 % of the stall samples) and made
 // ptxas keep x[] in local memory (10 % of all instructions were LDL / STL, profiles/r1_c3_medium2048_v0.txt).
 // Only the register steps (partner = another register of the same lane) need a compile-time distance.
-template <int NW, int R, int JR>
-__device__ __forceinline__ void sort_step_reg(u64 (&x)[R], const u32 w, const u32 lane, const u32 k2) {
+template <int NW, int R, int JR, bool WIDE>
+__device__ __forceinline__ void sort_step_reg(u64 (&xh)[R], u64 (&xl)[R], const u32 w, const u32 lane, const u32 k2) {
 #pragma unroll
   for (int r = 0; r < R; r++) {
     if ((r & JR) == 0) {
       const u32 i = ((w * R + r) << 5) | lane;
       const bool asc = (i & k2) == 0;
-      const u64 a = x[r], b = x[r | JR];
-      const u64 lo = a < b ? a : b, hi = a < b ? b : a;
-      x[r] = asc ? lo : hi;
-      x[r | JR] = asc ? hi : lo;
+      const bool swap = mk_less<WIDE>(xh[r], xl[r], xh[r | JR], xl[r | JR]) != asc;
+      const u64 ah = xh[r], bh = xh[r | JR];
+      xh[r] = swap ? bh : ah;
+      xh[r | JR] = swap ? ah : bh;
+      if constexpr (WIDE) {
+        const u64 al = xl[r], bl = xl[r | JR];
+        xl[r] = swap ? bl : al;
+        xl[r | JR] = swap ? al : bl;
+      }
     }
   }
 }
-template <int NW, int R>
-__device__ __forceinline__ void team_sort(u64 (&x)[R], const u32 w, const u32 lane, u64* sx) {
+template <int NW, int R, bool WIDE>
+__device__ __forceinline__ void team_sort(u64 (&xh)[R], u64 (&xl)[R], const u32 w, const u32 lane, u64* sxh, u64* sxl) {
   constexpr u32 P = NW * R * 32;
   constexpr int UNROLL = P <= 64 ? 16 : 1;  // the small warp teams keep the unrolled network (measured faster there)
 #pragma unroll UNROLL
@@ -424,54 +468,79 @@ __device__ __forceinline__ void team_sort(u64 (&x)[R], const u32 w, const u32 la
 #pragma unroll 1
       for (u32 j = k2 >> 1; j >= 32u * R; j >>= 1) {
 #pragma unroll
-        for (int r = 0; r < R; r++) sx[((w * R + r) << 5) | lane] = x[r];
+        for (int r = 0; r < R; r++) {
+          sxh[((w * R + r) << 5) | lane] = xh[r];
+          if constexpr (WIDE) sxl[((w * R + r) << 5) | lane] = xl[r];
+        }
         __syncthreads();
 #pragma unroll
         for (int r = 0; r < R; r++) {
           const u32 i = ((w * R + r) << 5) | lane;
-          const u64 y = sx[i ^ j];
+          const u64 yh = sxh[i ^ j];
+          u64 yl = 0;
+          if constexpr (WIDE) yl = sxl[i ^ j];
           const bool takemin = ((i & k2) == 0) == ((i & j) == 0);
-          x[r] = takemin ? (x[r] < y ? x[r] : y) : (x[r] < y ? y : x[r]);
+          const bool keep = mk_less<WIDE>(xh[r], xl[r], yh, yl) == takemin;
+          xh[r] = keep ? xh[r] : yh;
+          if constexpr (WIDE) xl[r] = keep ? xl[r] : yl;
         }
         __syncthreads();
       }
     }
-    if constexpr (R > 16) { if (k2 > 32u * 16) sort_step_reg<NW, R, 16>(x, w, lane, k2); }
-    if constexpr (R > 8) { if (k2 > 32u * 8) sort_step_reg<NW, R, 8>(x, w, lane, k2); }
-    if constexpr (R > 4) { if (k2 > 32u * 4) sort_step_reg<NW, R, 4>(x, w, lane, k2); }
-    if constexpr (R > 2) { if (k2 > 32u * 2) sort_step_reg<NW, R, 2>(x, w, lane, k2); }
-    if constexpr (R > 1) { if (k2 > 32u) sort_step_reg<NW, R, 1>(x, w, lane, k2); }
+    if constexpr (R > 16) { if (k2 > 32u * 16) sort_step_reg<NW, R, 16, WIDE>(xh, xl, w, lane, k2); }
+    if constexpr (R > 8) { if (k2 > 32u * 8) sort_step_reg<NW, R, 8, WIDE>(xh, xl, w, lane, k2); }
+    if constexpr (R > 4) { if (k2 > 32u * 4) sort_step_reg<NW, R, 4, WIDE>(xh, xl, w, lane, k2); }
+    if constexpr (R > 2) { if (k2 > 32u * 2) sort_step_reg<NW, R, 2, WIDE>(xh, xl, w, lane, k2); }
+    if constexpr (R > 1) { if (k2 > 32u) sort_step_reg<NW, R, 1, WIDE>(xh, xl, w, lane, k2); }
 #pragma unroll UNROLL
     for (u32 j = k2 > 32u ? 16u : (k2 >> 1); j > 0; j >>= 1) {
 #pragma unroll
       for (int r = 0; r < R; r++) {
         const u32 i = ((w * R + r) << 5) | lane;
-        const u64 y = __shfl_xor_sync(0xffffffffu, x[r], j);
+        const u64 yh = __shfl_xor_sync(0xffffffffu, xh[r], j);
+        u64 yl = 0;
+        if constexpr (WIDE) yl = __shfl_xor_sync(0xffffffffu, xl[r], j);
         const bool takemin = ((i & k2) == 0) == ((lane & j) == 0);
-        x[r] = takemin ? (x[r] < y ? x[r] : y) : (x[r] < y ? y : x[r]);
+        const bool keep = mk_less<WIDE>(xh[r], xl[r], yh, yl) == takemin;
+        xh[r] = keep ? xh[r] : yh;
+        if constexpr (WIDE) xl[r] = keep ? xl[r] : yl;
       }
     }
   }
 }
 
 #define MED_THREADS(NW) ((NW) == 1 ? 256 : (NW) * 32)
-template <int NW, int R, bool UNB>
+#define MED_NBK 4096u      // bucket counters of the first round of a block team
+#define MED_VCACHE 64u     // words of the virtual pivot kept in shared memory in the first round
+template <int NW, int R, bool UNB, bool WIDE>
 __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4))) k_groups_medium(u32* __restrict__ pos, const u32* __restrict__ med,
-                                                                        u32 nmed, SortParams sp, u64 h, u32 rank_scale) {
+                                                                        u32 nmed, SortParams sp, u64 h, u32 rank_scale, u32 vpivot,
+                                                                        u32 bucket_cost, u32 fin_max, u64* __restrict__ dbg) {
+  static_assert(!(UNB && WIDE), "the unbounded layout has one-word keys");
   constexpr u32 P = NW * R * 32;
   constexpr u32 TEAMS = NW == 1 ? 8 : 1;
   static_assert(P <= 2048, "slot field is 11 bits");
-  __shared__ u64 s_key[TEAMS * P];
-  __shared__ u32 s_pos[TEAMS * P];
-  __shared__ u32 s_seg[TEAMS * P];
-  __shared__ u32 s_dep[TEAMS * P];  // depth of the segment, kept at its head slot
+  // dynamic shared memory: key words (hi, and lo when WIDE), positions, segment heads, depths; block teams: bucket
+  // counters and the cached pivot words of the first round
+  extern __shared__ __align__(16) unsigned char med_smem[];
+  u64* s_keyh = reinterpret_cast<u64*>(med_smem);
+  u64* s_keyl = s_keyh + TEAMS * P;  // (WIDE only)
+  u32* s_pos = reinterpret_cast<u32*>(s_keyh + (WIDE ? 2 : 1) * TEAMS * P);
+  u32* s_seg = s_pos + TEAMS * P;
+  u32* s_dep = s_seg + TEAMS * P;  // depth of the segment, kept at its head slot
+  u64* s_vp = reinterpret_cast<u64*>(s_dep + TEAMS * P);  // (NW > 1) [MED_VCACHE]
+  u32* s_cnt = reinterpret_cast<u32*>(s_vp + MED_VCACHE);  // (NW > 1) [MED_NBK]
+  __shared__ u32 s_ws[33];
   __shared__ u32 s_scan[NW];
+  __shared__ u32 s_qn[TEAMS];  // small segments queued for their finishing threads
   const u32 lane = threadIdx.x & 31u, wb = threadIdx.x >> 5;
   const u32 team = NW == 1 ? wb : 0u, w = NW == 1 ? 0u : wb;
-  u64* skey = s_key + team * P;
+  u64* skh = s_keyh + team * P;
+  u64* skl = s_keyl + team * P;
   u32* spos = s_pos + team * P;
   u32* sseg = s_seg + team * P;
   u32* sdep = s_dep + team * P;
+  const bool maj = !UNB && vpivot != 0;
   for (u32 gi = blockIdx.x * TEAMS + team; gi < nmed; gi += gridDim.x * TEAMS) {
     const u32 start = med[2 * gi], size = med[2 * gi + 1];
 #pragma unroll
@@ -480,52 +549,217 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
       spos[i] = i < size ? pos[start + i] : KISS_EMPTY;
       sseg[i] = i < size ? 0u : 0xFFFFFFFFu;
     }
-    if (threadIdx.x % (NW * 32) == 0) { sdep[0] = (u32)h; sdep[1] = size; }
+    if (threadIdx.x % (NW * 32) == 0) { sdep[0] = (u32)h; sdep[1] = size; s_qn[team] = 0; }
     team_sync<NW>();
     // Two ways to order the segments of a round.  The bitonic network costs the same whatever the segments look
     // like (LOGP (LOGP + 1) / 2 steps of ~12 instructions per key); counting, for every element, the smaller keys
-    // of its own segment costs ~4 instructions per segment member.  After the first round or two the segments are
-    // short, so the later rounds rank (ncu, C3: the network was ~90 % of the 25 G warp instructions of the
-    // largest class, issue slots 65 % busy, profiles/r1_c3_medium2048_v1.txt).
+    // of its own segment costs ~4 instructions per segment member.  After the first round the segments are short,
+    // so the later rounds rank.
     constexpr u32 LOGP = P == 32 ? 5 : P == 64 ? 6 : P == 128 ? 7 : P == 256 ? 8 : P == 512 ? 9 : P == 1024 ? 10 : 11;
     const u32 RANK_MAX = rank_scale * LOGP * (LOGP + 1) / 2;  // longest segment for which ranking is the cheaper way
     u32 maxlen = size;                               // longest segment with >= 2 elements (team-uniform)
+    u32 dbg_round = 0;
+    bool first = true;
+    // first round of a block team: the virtual pivot's words over [h, D) are computed once per group
+    u32 nvp = 0;
+    if constexpr (NW > 1 && !UNB) {
+      if (maj) {
+        const u64 span = sp.D > h ? sp.D - h : 0;
+        nvp = (u32)min((u64)MED_VCACHE, (span + 31) / 32);
+        if (threadIdx.x < nvp) {
+          const u64 q = h + 32ull * threadIdx.x;
+          // (computed once per group, so five samples cost nothing: the majority is then off the consensus — which sends
+          // the whole group into ONE bucket at that base — where three of five copies share a mutation, not two of three)
+          s_vp[threadIdx.x] = maj5(word_at(sp.T, (u64)spos[0] + q), word_at(sp.T, (u64)spos[size >> 2] + q),
+                                   word_at(sp.T, (u64)spos[size >> 1] + q), word_at(sp.T, (u64)spos[size - 1 - (size >> 2)] + q),
+                                   word_at(sp.T, (u64)spos[size - 1] + q));
+        }
+        __syncthreads();
+      }
+    }
     for (;;) {
-      u64 x[R];
+      u64 xh[R], xl[R];
       bool anyact = false, moved = false;
       u32 actm = 0;
 #pragma unroll
       for (int r = 0; r < R; r++) {
         const u32 i = ((w * R + r) << 5) | lane;
-        u64 key = ~0ull;
+        u64 key = ~0ull, klo = ~0ull;
         if (i < size) {
           const u32 sg = sseg[i];
           const bool act = sg != i || (i + 1 < size && sseg[i + 1] == sg);
           key = 0;
+          klo = 0;
           if (act) {
             anyact = true;
             actm |= 1u << r;
             key = MK_EQUAL << MK_SIDE_SHIFT;
-            if (sg != i) key = pivot_key<UNB>(sp, spos[i], spos[sg], sdep[sg]);
+            if constexpr (UNB) {
+              if (sg != i) key = pivot_key_u(sp, spos[i], spos[sg], sdep[sg]);
+            } else if (maj) {
+              const u32 end = sdep[sg + 1];  // (a segment that is still refined keeps its end in the slot after its head)
+              const u32 p1 = spos[sg], p2 = spos[sg + ((end - sg) >> 1)], p3 = spos[end - 1];
+              if (NW > 1 && first) {
+                key = pivot_key_pw(sp, spos[i], h, klo, [&](u64 q) {
+                  const u64 k = (q - h) >> 5;
+                  if (k < nvp) return s_vp[k];
+                  return maj5(word_at(sp.T, (u64)p1 + q), word_at(sp.T, (u64)spos[size >> 2] + q), word_at(sp.T, (u64)p2 + q),
+                              word_at(sp.T, (u64)spos[size - 1 - (size >> 2)] + q), word_at(sp.T, (u64)p3 + q));
+                });
+              } else {
+                key = pivot_key_b(sp, spos[i], p1, p2, p3, true, sdep[sg], klo);
+              }
+            } else if (sg != i) {
+              key = pivot_key_b(sp, spos[i], spos[sg], 0u, 0u, false, sdep[sg], klo);
+            }
             moved |= ((key >> MK_SIDE_SHIFT) & 3ull) != MK_EQUAL;
           }
           key |= ((u64)sg << MK_SEG_SHIFT) | i;
         }
-        x[r] = key;
+        xh[r] = key;
+        xl[r] = klo;
       }
       if (!team_or<NW>(anyact)) break;
+      if (dbg) {  // KISS_B200_DEBUG_GROUPS: rounds, active elements and longest segment per round
+        const u32 na = __reduce_add_sync(0xffffffffu, (u32)__popc(actm));
+        if (lane == 0) atomicAdd(&dbg[16 + min(dbg_round, 15u)], (u64)na);
+        if (threadIdx.x % (NW * 32) == 0) {
+          atomicAdd(&dbg[0], 1ull);
+          atomicAdd(&dbg[maxlen > RANK_MAX ? 1 : 2], 1ull);
+          atomicAdd(&dbg[32 + min(dbg_round, 15u)], (u64)maxlen);
+          atomicAdd(&dbg[48 + min(dbg_round, 15u)], 1ull);
+        }
+        dbg_round++;
+      }
       if (team_or<NW>(moved)) {
-        if (maxlen > RANK_MAX) {
-          team_sort<NW, R>(x, w, lane, skey);
+        bool sorted = false;
+        if constexpr (NW > 1 && !UNB) {
+          if (first && bucket_cost && maxlen > RANK_MAX) {
+            // First round of a block team (one segment = the whole group): the (side, q, first base) part of the key
+            // alone spreads the elements over up to MED_NBK buckets — a counting sort with shared-memory atomics,
+            // unordered inside a bucket — and every element then counts the smaller keys of its own bucket.  ~12
+            // instructions per bucket member against ~1750 per element for the network (66 steps at 2048 slots on
+            // two-word keys: 58 % of this kernel's instructions, profiles/r2_medium2048_wide.txt).  A group that
+            // crowds one bucket (exact copies, a shared mutation) takes the network instead.
+            const u32 span = (u32)(sp.D - h);  // bucket index: monotone in (side, q, base), quantised to fit
+            u32 qs = 0;
+            while (((4u * (2u * span + 1u)) >> qs) > MED_NBK) qs++;
+            auto bucket_of = [&](u64 kh) {
+              const u32 side = (u32)(kh >> MK_SIDE_SHIFT) & 3u, qk = (u32)(kh >> 39) & 0xFFFu, c = (u32)(kh >> 37) & 3u;
+              const u32 q = side == 2 ? 4095u - qk : qk;
+              const u32 i0 = side == 0 ? q - (u32)h : side == 1 ? span : span + 1u + ((u32)sp.D - 1u - q);
+              return (4u * i0 + (side == 1 ? 0u : c)) >> qs;
+            };
+            for (u32 t = threadIdx.x; t < MED_NBK; t += NW * 32) s_cnt[t] = 0;
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < R; r++)
+              if ((((w * R + r) << 5) | lane) < size) atomicAdd(&s_cnt[bucket_of(xh[r])], 1u);
+            __syncthreads();
+            {
+              constexpr u32 PER = MED_NBK / (NW * 32);
+              u32 c[PER], sum = 0, mx = 0, sq = 0;
+#pragma unroll
+              for (u32 e = 0; e < PER; e++) {
+                c[e] = s_cnt[threadIdx.x * PER + e];
+                mx = max(mx, c[e]);
+                sum += c[e];
+                sq += c[e] * c[e];
+              }
+              u32 tot;
+              u32 ex = block_excl_scan(sum, s_ws, tot);
+#pragma unroll
+              for (u32 e = 0; e < PER; e++) {
+                s_cnt[threadIdx.x * PER + e] = ex;
+                ex += c[e];
+              }
+              // ranking costs one step per (element, member of its bucket) pair: sum of squares against size x the
+              // network's ~bucket_cost steps per element
+              sq = __reduce_add_sync(0xffffffffu, sq);
+              if (lane == 0) s_scan[w] = sq;
+              __syncthreads();
+              u32 sqt = 0;
+#pragma unroll
+              for (u32 ww = 0; ww < NW; ww++) sqt += s_scan[ww];
+              sorted = sqt <= bucket_cost * size;
+              __syncthreads();  // (s_scan is reused below)
+              if (dbg) {
+                const u32 eqb = (4u * span) >> qs;  // the bucket of the elements equal to the pivot
+                const u32 eqc = (eqb + 1 < MED_NBK ? s_cnt[eqb + 1] : size) - s_cnt[eqb];
+                const u32 bmx = __reduce_max_sync(0xffffffffu, mx);
+                if (lane == 0) atomicMax(&dbg[8], (u64)bmx);
+                if (threadIdx.x == 0) {
+                  atomicAdd(&dbg[sorted ? 3 : 4], 1ull);
+                  if (!sorted && eqc * eqc > bucket_cost * size / 2) atomicAdd(&dbg[5], 1ull);
+                  atomicAdd(&dbg[6], (u64)eqc);
+                }
+              }
+            }
+            if (sorted) {
+#pragma unroll
+              for (int r = 0; r < R; r++) {
+                if ((((w * R + r) << 5) | lane) < size) {
+                  const u32 t = atomicAdd(&s_cnt[bucket_of(xh[r])], 1u);
+                  skh[t] = xh[r];
+                  if constexpr (WIDE) skl[t] = xl[r];
+                }
+              }
+              __syncthreads();  // s_cnt[b] is now the END of bucket b
+              u32 pp[R], dst[R];
+#pragma unroll
+              for (int r = 0; r < R; r++) {
+                const u32 t = ((w * R + r) << 5) | lane;
+                pp[r] = KISS_EMPTY;
+                dst[r] = t;
+                xh[r] = ~0ull;
+                xl[r] = ~0ull;
+                if (t < size) {
+                  xh[r] = skh[t];
+                  if constexpr (WIDE) xl[r] = skl[t];
+                  const u32 b = bucket_of(xh[r]);
+                  const u32 lo_ = b ? s_cnt[b - 1] : 0u, hi_ = s_cnt[b];
+                  u32 rank = 0;
+                  for (u32 j = lo_; j < hi_; j++) {
+                    u64 yl = 0;
+                    if constexpr (WIDE) yl = skl[j];
+                    rank += mk_less<WIDE>(skh[j], yl, xh[r], xl[r]) ? 1u : 0u;
+                  }
+                  dst[r] = lo_ + rank;
+                  pp[r] = spos[(u32)xh[r] & 0x7FFu];
+                }
+              }
+              __syncthreads();
+#pragma unroll
+              for (int r = 0; r < R; r++) {
+                skh[dst[r]] = xh[r];
+                if constexpr (WIDE) skl[dst[r]] = xl[r];
+                spos[dst[r]] = pp[r];
+              }
+              __syncthreads();
+#pragma unroll
+              for (int r = 0; r < R; r++) {
+                xh[r] = skh[((w * R + r) << 5) | lane];
+                if constexpr (WIDE) xl[r] = skl[((w * R + r) << 5) | lane];
+              }
+              __syncthreads();
+            }
+          }
+        }
+        if (sorted) {
+        } else if (maxlen > RANK_MAX) {
+          team_sort<NW, R, WIDE>(xh, xl, w, lane, skh, skl);
           u32 pp[R];
 #pragma unroll
-          for (int r = 0; r < R; r++) pp[r] = x[r] != ~0ull ? spos[(u32)x[r] & 0x7FFu] : KISS_EMPTY;
+          for (int r = 0; r < R; r++) pp[r] = xh[r] != ~0ull ? spos[(u32)xh[r] & 0x7FFu] : KISS_EMPTY;
           team_sync<NW>();
 #pragma unroll
           for (int r = 0; r < R; r++) spos[((w * R + r) << 5) | lane] = pp[r];
         } else {
 #pragma unroll
-          for (int r = 0; r < R; r++) skey[((w * R + r) << 5) | lane] = x[r];
+          for (int r = 0; r < R; r++) {
+            skh[((w * R + r) << 5) | lane] = xh[r];
+            if constexpr (WIDE) skl[((w * R + r) << 5) | lane] = xl[r];
+          }
           team_sync<NW>();
           u32 pp[R], dst[R];
 #pragma unroll
@@ -534,27 +768,38 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
             pp[r] = spos[i];
             dst[r] = i;
             if ((actm >> r) & 1u) {
-              const u32 sg = (u32)(x[r] >> MK_SEG_SHIFT);  // head slot of the segment; its end is kept at sdep[head + 1]
+              const u32 sg = (u32)(xh[r] >> MK_SEG_SHIFT);  // head slot of the segment; its end is kept at sdep[head + 1]
               const u32 end = sdep[sg + 1];
               u32 rank = 0;
-              for (u32 j = sg; j < end; j++) rank += skey[j] < x[r] ? 1u : 0u;
+              for (u32 j = sg; j < end; j++) {
+                u64 yl = 0;
+                if constexpr (WIDE) yl = skl[j];
+                rank += mk_less<WIDE>(skh[j], yl, xh[r], xl[r]) ? 1u : 0u;
+              }
               dst[r] = sg + rank;
             }
           }
           team_sync<NW>();
 #pragma unroll
           for (int r = 0; r < R; r++) {
-            skey[dst[r]] = x[r];
+            skh[dst[r]] = xh[r];
+            if constexpr (WIDE) skl[dst[r]] = xl[r];
             spos[dst[r]] = pp[r];
           }
           team_sync<NW>();
 #pragma unroll
-          for (int r = 0; r < R; r++) x[r] = skey[((w * R + r) << 5) | lane];
+          for (int r = 0; r < R; r++) {
+            xh[r] = skh[((w * R + r) << 5) | lane];
+            if constexpr (WIDE) xl[r] = skl[((w * R + r) << 5) | lane];
+          }
           team_sync<NW>();
         }
       }
 #pragma unroll
-      for (int r = 0; r < R; r++) skey[((w * R + r) << 5) | lane] = x[r];
+      for (int r = 0; r < R; r++) {
+        skh[((w * R + r) << 5) | lane] = xh[r];
+        if constexpr (WIDE) skl[((w * R + r) << 5) | lane] = xl[r];
+      }
       team_sync<NW>();
       // new segment = running maximum of the head slots; everything equal to its pivot is final (own segment)
       u32 run = 0;  // head slot + 1 carried into the current row
@@ -565,8 +810,9 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
         const u32 i = ((w * R + r) << 5) | lane;
         bool hd = false;
         if (i < size) {
-          const u64 a = x[r] >> MK_SLOT_BITS;
-          hd = i == 0 || a != (skey[i - 1] >> MK_SLOT_BITS) || ((x[r] >> MK_SIDE_SHIFT) & 3ull) == MK_EQUAL;
+          const u64 a = xh[r] >> MK_SLOT_BITS;
+          hd = i == 0 || a != (skh[i - 1] >> MK_SLOT_BITS) || ((xh[r] >> MK_SIDE_SHIFT) & 3ull) == MK_EQUAL;
+          if constexpr (WIDE) { if (!hd) hd = xl[r] != skl[i - 1]; }
         }
         hdv[r] = hd;
         u32 v = hd ? i + 1u : 0u;
@@ -591,7 +837,7 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
         if (i < size) {
           sseg[i] = max(sg[r], before) - 1u;
           if (hdv[r]) {
-            const u64 dd = class_depth<UNB>(x[r]);
+            const u64 dd = class_depth<UNB>(xh[r], WIDE ? MK_WIDE_BASES : 14ull);
             sdep[i] = (u32)(dd < 0xFFFFFFFFull ? dd : 0xFFFFFFFFull);
           }
         }
@@ -599,6 +845,13 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
       team_sync<NW>();
       // segment ends (kept in the slot after the head: a segment that is still refined has >= 2 elements) and the
       // longest segment
+      // Segments of at most fin_max elements are FINISHED here by one thread each: an insertion sort with the word-wise
+      // suffix comparison from the segment's depth on (stable: equal to D keeps text order).  After the first round
+      // nearly all that is left are such crumbs (C3, largest class: 20 % of the elements, in segments of a handful),
+      // and a team round costs the same barriers, scans and a full pass of the key loop whether 1400 or 14 elements
+      // are still active (half of this kernel's instructions were key loops of later rounds with a few lanes alive,
+      // profiles/r2_medium2048_narrow.txt).
+      u32* queue = reinterpret_cast<u32*>(skh);  // (the key words are free until the next round)
       u32 ml = 0;
 #pragma unroll
       for (int r = 0; r < R; r++) {
@@ -606,10 +859,37 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
         if (i < size) {
           const u32 hd = sseg[i];
           if (hd != i && (i + 1 == size || sseg[i + 1] != hd)) {
-            sdep[hd + 1] = i + 1u;
-            ml = max(ml, i + 1u - hd);
+            const u32 len = i + 1u - hd;
+            if (len <= fin_max) {
+              queue[atomicAdd(&s_qn[team], 1u)] = hd | (len << 16);
+            } else {
+              sdep[hd + 1] = i + 1u;
+              ml = max(ml, len);
+            }
           }
         }
+      }
+      team_sync<NW>();
+      {
+        const u32 nq = s_qn[team];
+        for (u32 e = threadIdx.x % (NW * 32); e < nq; e += NW * 32) {
+          const u32 hd = queue[e] & 0xFFFFu, len = queue[e] >> 16;
+          const u64 dep = sdep[hd];
+          for (u32 a = 1; a < len; a++) {
+            const u32 x = spos[hd + a];
+            u32 b = a;
+            while (b > 0) {
+              const u32 y = spos[hd + b - 1];
+              if (!suffix_less(sp, x, y, dep)) break;
+              spos[hd + b] = y;
+              b--;
+            }
+            spos[hd + b] = x;
+          }
+          for (u32 a = 0; a < len; a++) sseg[hd + a] = hd + a;
+        }
+        team_sync<NW>();
+        if (threadIdx.x % (NW * 32) == 0) s_qn[team] = 0;
       }
       ml = __reduce_max_sync(0xffffffffu, ml);
       if constexpr (NW > 1) {
@@ -620,6 +900,7 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
         for (u32 ww = 0; ww < NW; ww++) ml = max(ml, s_scan[ww]);
       }
       maxlen = ml;
+      first = false;
       team_sync<NW>();
     }
     team_sync<NW>();
@@ -632,40 +913,61 @@ __global__ void __launch_bounds__(MED_THREADS(NW), (R >= 8 ? 2 : (NW > 8 ? 2 : 4
   }
 }
 
-template <int NW, int R, bool UNB>
+u64* g_med_dbg = nullptr;  // KISS_B200_DEBUG_GROUPS: 6 classes x 64 counters (device), owned by api.cu
+
+// KISS_B200_REAL_PIVOT=1: the first element of a segment as the pivot everywhere (the round-1 scheme, kept for A/B timing)
+static bool virtual_pivot() {
+  static const bool real = getenv("KISS_B200_REAL_PIVOT") != nullptr;
+  return !real;
+}
+
+template <int NW, int R, bool WIDE>
+static size_t med_smem_bytes() {
+  const size_t slots = (size_t)(NW == 1 ? 8 : 1) * NW * R * 32;
+  return slots * ((WIDE ? 16 : 8) + 12) + (NW > 1 ? MED_VCACHE * 8 + MED_NBK * 4 : 0);
+}
+template <int NW, int R, bool UNB, bool WIDE>
 static void groups_medium_class(int pk, u32 cls, u32* pos, const u32* med, u32 medN, const u32* cg, const u32* ce,
                                 SortParams sp, u64 h, cudaStream_t st) {
   const u32 ngroups = cg[cls];
   if (!ngroups) return;
+  // (per launch: the attribute belongs to the current device, and a process may drive several)
+  CK(cudaFuncSetAttribute(k_groups_medium<NW, R, UNB, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                          (int)med_smem_bytes<NW, R, WIDE>()));
   ProfScope ps(pk, st);
   if (ps.p) ps.p->bytes[pk] += 16ull * ce[cls];  // position read + write, one 8-byte key word
   u32 grid = NW == 1 ? (ngroups + 7) / 8 : ngroups;
   if (grid > 1048576u) grid = 1048576u;
   static const u32 rank_scale = [] { const char* e = getenv("KISS_B200_RANK_SCALE"); return e ? (u32)atoi(e) : 6u; }();  // C3: 2: 22.2 ms, 4: 20.5, 8: 19.8, 16: 21.7, 64: 41 (largest class)
-  k_groups_medium<NW, R, UNB><<<grid, MED_THREADS(NW), 0, st>>>(pos, med + 2 * med_class_off(medN, cls), ngroups, sp, h,
-                                                                rank_scale);
+  static const u32 bucket_cost = [] { const char* e = getenv("KISS_B200_BUCKET_COST"); return e ? (u32)atoi(e) : 128u; }();  // 0: the network in every first round
+  static const u32 fin_max = [] { const char* e = getenv("KISS_B200_FIN_MAX"); return e ? (u32)atoi(e) : 4u; }();  // 0: off; C3 medium classes in all: 0: 27.1 ms, 4: 24.8, 8: 26.5, 16: 33.3
+  k_groups_medium<NW, R, UNB, WIDE><<<grid, MED_THREADS(NW), med_smem_bytes<NW, R, WIDE>(), st>>>(
+      pos, med + 2 * med_class_off(medN, cls), ngroups, sp, h, rank_scale, (NW > 1 && virtual_pivot()) ? 1u : 0u,
+      bucket_cost, fin_max, g_med_dbg ? g_med_dbg + 64 * cls : nullptr);
   CK_LAUNCH(); g_launches++;
 }
-template <bool UNB>
+template <bool UNB, bool WIDE>
 static void groups_medium_launch(u32* pos, const u32* med, u32 medN, const u32* cg, const u32* ce, SortParams sp, u64 h,
                                  cudaStream_t st) {
-  groups_medium_class<1, 1, UNB>(PK_GROUPS_MEDIUM, 0, pos, med, medN, cg, ce, sp, h, st);
-  groups_medium_class<1, 2, UNB>(PK_GROUPS_MEDIUM_64, 1, pos, med, medN, cg, ce, sp, h, st);
-  groups_medium_class<1, 4, UNB>(PK_GROUPS_MEDIUM_128, 2, pos, med, medN, cg, ce, sp, h, st);
-  groups_medium_class<1, 8, UNB>(PK_GROUPS_MEDIUM_256, 3, pos, med, medN, cg, ce, sp, h, st);
-  groups_medium_class<8, 2, UNB>(PK_GROUPS_MEDIUM_512, 4, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<1, 1, UNB, WIDE>(PK_GROUPS_MEDIUM, 0, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<1, 2, UNB, WIDE>(PK_GROUPS_MEDIUM_64, 1, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<1, 4, UNB, WIDE>(PK_GROUPS_MEDIUM_128, 2, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<1, 8, UNB, WIDE>(PK_GROUPS_MEDIUM_256, 3, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<8, 2, UNB, WIDE>(PK_GROUPS_MEDIUM_512, 4, pos, med, medN, cg, ce, sp, h, st);
   // 16 warps x 4 keys per thread (2 blocks = 32 warps per SM): 36.6 ms against 40.6 ms for 8 warps x 8 keys on C3
-  static const bool narrow = getenv("KISS_B200_MED_NARROW") != nullptr;
-  if (!narrow) groups_medium_class<16, 4, UNB>(PK_GROUPS_MEDIUM_2048, 5, pos, med, medN, cg, ce, sp, h, st);
-  else groups_medium_class<8, 8, UNB>(PK_GROUPS_MEDIUM_2048, 5, pos, med, medN, cg, ce, sp, h, st);
+  groups_medium_class<16, 4, UNB, WIDE>(PK_GROUPS_MEDIUM_2048, 5, pos, med, medN, cg, ce, sp, h, st);
 }
 
 void groups_medium(u32* pos, const u32* med, u32 medN, const u32* class_groups, const u32* class_elems, SortParams sp,
                    u64 h, cudaStream_t st) {
   if (h >= sp.D) return;
+  // two-word keys (46 own bases per round, KISS_B200_WIDE_KEYS=1) measured slower on C3: 18.9 ms against 15.0 ms in the
+  // largest class (a third fewer element-rounds, but every step of sorting and ranking costs 1.6x)
+  static const bool narrow = getenv("KISS_B200_WIDE_KEYS") == nullptr;
   // the 12-bit q field of the bounded key holds depths up to 4095
-  if (sp.D == KISS_UNBOUNDED || sp.D > 4000) groups_medium_launch<true>(pos, med, medN, class_groups, class_elems, sp, h, st);
-  else groups_medium_launch<false>(pos, med, medN, class_groups, class_elems, sp, h, st);
+  if (sp.D == KISS_UNBOUNDED || sp.D > 4000) groups_medium_launch<true, false>(pos, med, medN, class_groups, class_elems, sp, h, st);
+  else if (narrow) groups_medium_launch<false, false>(pos, med, medN, class_groups, class_elems, sp, h, st);
+  else groups_medium_launch<false, true>(pos, med, medN, class_groups, class_elems, sp, h, st);
 }
 
 // ------------------------------------------------------------------------------------------- big groups
@@ -692,7 +994,7 @@ template <bool UNB>
 __global__ void __launch_bounds__(256) k_big_fill(const u32* __restrict__ pos_prev, const u32* __restrict__ slot_prev,
                                                  const u32* __restrict__ big, const u32* __restrict__ boff, u32 nbig,
                                                  u32 total, SortParams sp, u64* __restrict__ wkey,
-                                                 u32* __restrict__ wpos, u32* __restrict__ wslot) {
+                                                 u32* __restrict__ wpos, u32* __restrict__ wslot, u32 vpivot) {
   constexpr int SIDE_SHIFT = UNB ? 35 : 40, G_SHIFT = UNB ? 37 : 42, DROP = UNB ? 16 : 11;
   const u32 t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= total) return;
@@ -701,11 +1003,19 @@ __global__ void __launch_bounds__(256) k_big_fill(const u32* __restrict__ pos_pr
     u32 mid = lo + (hi - lo) / 2;
     if (boff[mid] <= t) lo = mid; else hi = mid;
   }
-  const u32 g = lo, start = big[3 * g], depth = big[3 * g + 2], j = t - boff[g];
+  const u32 g = lo, start = big[3 * g], size = big[3 * g + 1], depth = big[3 * g + 2], j = t - boff[g];
   const u32 p = pos_prev[start + j];
   u64 f = (MK_EQUAL << SIDE_SHIFT) | j;  // the pivot itself, and everything equal to it: unique, in order
-  if (j) {
-    const u64 key = pivot_key<UNB>(sp, p, pos_prev[start], depth) >> DROP;
+  if (UNB) {
+    if (j) {
+      const u64 key = pivot_key_u(sp, p, pos_prev[start], depth) >> DROP;
+      if (((key >> SIDE_SHIFT) & 3ull) != MK_EQUAL) f = key;
+    }
+  } else if (vpivot || j) {
+    // (one-word keys here: the 14 bases after q; the radix passes of the round grow with the key width)
+    u64 lo;
+    const u64 key = pivot_key_b(sp, p, pos_prev[start], pos_prev[start + (size >> 1)], pos_prev[start + size - 1],
+                                vpivot != 0, depth, lo) >> DROP;
     if (((key >> SIDE_SHIFT) & 3ull) != MK_EQUAL) f = key;
   }
   wkey[t] = ((u64)g << G_SHIFT) | f;
@@ -719,9 +1029,10 @@ void big_fill(const u32* pos_prev, const u32* slot_prev, const u32* big, const u
   ProfScope ps(PK_GROUPS_OTHER, st);
   u32 grid = (total + 255) / 256;
   if (unbounded_layout)
-    k_big_fill<true><<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, total, sp, wkey, wpos, wslot);
+    k_big_fill<true><<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, total, sp, wkey, wpos, wslot, 0u);
   else
-    k_big_fill<false><<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, total, sp, wkey, wpos, wslot);
+    k_big_fill<false><<<grid, 256, 0, st>>>(pos_prev, slot_prev, big, boff, nbig, total, sp, wkey, wpos, wslot,
+                                            virtual_pivot() ? 1u : 0u);
   CK_LAUNCH(); g_launches++;
 }
 
