@@ -129,7 +129,7 @@ int kiss_b200_induce_from_sorted_lms(kiss_b200_ctx* ctx, const uint8_t* S_host, 
 
 /* ---- device-resident stage API for the sharded LMS sort (one process per GPU) --------------------
  * kiss_b200_prepare_dev: pack + get_lms on this GPU for the whole text; keeps packed text and the
- * text-ordered LMS list in the context.  *m_out includes the sentinel. */
+ * text-ordered LMS list in the context.  *m_out includes the sentinel.  S_dev must be 16-byte aligned. */
 int kiss_b200_prepare_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, uint32_t k, uint64_t* m_out);
 /* Sort by the reference's LMS order an arbitrary subset of the long LMS suffixes given as device
  * positions in ascending text order (the shard a rank received); result in place. */
@@ -151,9 +151,8 @@ int kiss_b200_finish_from_sorted_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_
 /* Multi-GPU: the rank that sorted a key range also fetches the induction contexts of its suffixes (the 15 bases
  * before each position, one random 128-byte DRAM fetch per LMS suffix — the part of induced_L's first touch of an LMS
  * suffix, kiss_common.hpp:226-246, that does shard), and rank 0 finishes from (position, context) pairs.
- * lms_contexts: ctx_out_dev[i] for the suffixes pos_dev[0..count) of the prepared text; the kernel is only ENQUEUED on
- * the context's stream (kiss_b200_stream) so that the caller can run its exchange of the positions next to it — wait on
- * that stream, or make any other call on the context, before reading ctx_out_dev.
+ * lms_contexts: ctx_out_dev[i] for the suffixes pos_dev[0..count) of the prepared text; the call returns when the
+ * kernel has finished.
  * finish_from_sorted_ctx: as finish_from_sorted_dev; ctx_long_dev (nullable) is aligned like sorted_long_dev mod 16. */
 int kiss_b200_lms_contexts_dev(kiss_b200_ctx* ctx, const uint32_t* pos_dev, uint64_t count, uint32_t* ctx_out_dev);
 int kiss_b200_finish_from_sorted_ctx_dev(kiss_b200_ctx* ctx, const uint32_t* sorted_long_dev, const uint32_t* ctx_long_dev,

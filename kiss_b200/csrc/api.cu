@@ -676,18 +676,18 @@ u64 do_ingest(kiss_b200_ctx* c, Pool& pool, const u8* dRaw, u64 nbytes, bool fas
   cudaStream_t st = c->st;
   const u64 nch = ingest_chunks(nbytes);
   if (!nch) return 0;
-  u32* lead = pool.alloc<u32>(nch);
-  u32* rest = pool.alloc<u32>(nch);
-  u64* last_ls = pool.alloc<u64>(nch);
-  u64* bmax = pool.alloc<u64>(nch / 1024 + 2);
+  u32* kept0 = pool.alloc<u32>(nch);
+  u32* kept1 = pool.alloc<u32>(nch);
+  u8* fn = pool.alloc<u8>(nch);
+  u8* bfn = pool.alloc<u8>(nch / 1024 + 2);
   u8* hflag = pool.alloc<u8>(nch);
   u32* partials = pool.alloc<u32>(scan_partials_len(nch));
   u64* total = pool.alloc<u64>(1);
-  ingest(dRaw, nbytes, dCodes, lead, rest, last_ls, bmax, hflag, partials, total, fasta, st);
+  ingest(dRaw, nbytes, dCodes, kept0, kept1, fn, bfn, hflag, partials, total, fasta, st);
   u64 n = 0;
   CK(cudaMemcpyAsync(&n, total, sizeof(u64), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  pool.release(lead); pool.release(rest); pool.release(last_ls); pool.release(bmax); pool.release(hflag);
+  pool.release(kept0); pool.release(kept1); pool.release(fn); pool.release(bfn); pool.release(hflag);
   pool.release(partials);
   pool.release(total);
   return n;
@@ -701,8 +701,12 @@ void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* o
   begin_call(c);
   Pool pool(st, &c->arena);
   u8* dS = pool.alloc<u8>(n + 16);
-  cudaEvent_t e0, e1, e2, e3;
-  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2)); CK(cudaEventCreate(&e3));
+  struct Events {  // (destroyed on every exit path, exceptions included)
+    cudaEvent_t e[4] = {};
+    Events() { for (auto& x : e) CK(cudaEventCreate(&x)); }
+    ~Events() { for (auto& x : e) if (x) cudaEventDestroy(x); }
+  } evs;
+  cudaEvent_t e0 = evs.e[0], e1 = evs.e[1], e2 = evs.e[2], e3 = evs.e[3];
   CK(cudaEventRecord(e0, st));
   if (n) CK(cudaMemcpyAsync(dS, S_host, n, cudaMemcpyHostToDevice, st));
   if (input == IN_ASCII) {
@@ -721,8 +725,8 @@ void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* o
     if (n + 1 > out_count_hint) throw CudaError(KISS_B200_ERR_ARG, "suffix array buffer smaller than text length + 1");
     if (n == 0) {  // headers / empty lines only: SA = {0} (kiss1_core.hpp:237-238)
       if (out_host) out_host[0] = 0;
-      if (t) memset(t, 0, sizeof(*t));
-      cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
+      if (t) { memset(t, 0, sizeof(*t)); t->m = 1; }  // (as trivial_n0: the sentinel is the only LMS entry)
+      if (m_out) *m_out = 1;
       return;
     }
   }
@@ -768,7 +772,6 @@ void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* o
   float h2d = 0, d2h = 0;
   cudaEventElapsedTime(&h2d, e0, e1);
   cudaEventElapsedTime(&d2h, e2, e3);
-  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
   tt.h2d = h2d * 1e-3; tt.d2h = d2h * 1e-3;
   if (t) *t = tt;
   if (m_out) *m_out = m;
@@ -976,6 +979,7 @@ int kiss_b200_induce_from_sorted_lms(kiss_b200_ctx* c, const uint8_t* S_host, ui
 
 int kiss_b200_prepare_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, uint32_t k, uint64_t* m_out) {
   if (!S_dev || n == 0) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if ((uintptr_t)S_dev & 15) { g_last_error = "S_dev must be 16-byte aligned"; return KISS_B200_ERR_ARG; }
   if (int r = check_n(n)) return r;
   return guarded(c, [&] {
     do_prepare(c, S_dev, n, k, 0, nullptr, nullptr);
@@ -1107,7 +1111,7 @@ int kiss_b200_lms_contexts_dev(kiss_b200_ctx* c, const uint32_t* pos_dev, uint64
   if (!c || !c->prep.valid) { g_last_error = "no prepared text"; return KISS_B200_ERR_ARG; }
   if (count && (!pos_dev || !ctx_out_dev)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   return guarded(c, [&] {
-    lms_contexts(c->prep.T, pos_dev, count, ctx_out_dev, c->st);  // enqueued only: see the header
+    lms_contexts(c->prep.T, pos_dev, count, ctx_out_dev, c->st);  // (guarded() waits for the stream before returning)
   });
 }
 

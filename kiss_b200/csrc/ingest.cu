@@ -6,15 +6,17 @@
 //   * FASTA mode iff the first byte of the file is '>' (io.hpp:8); otherwise text mode: every line is sequence;
 //   * lines are what std::getline returns: split at '\n', the '\n' itself dropped, a '\r' before it KEPT
 //     (it then encodes like any non-ACGT byte: 4 % 4 = 0 = 'A');
-//   * in FASTA mode a line whose FIRST byte is '>' is a header and is dropped whole (fasta.hpp:127, :137-138);
-//     a '>' anywhere else is sequence; all records are concatenated without separators (io.hpp:10-11);
+//   * in FASTA mode a line whose FIRST byte is '>' is a header and is dropped whole (fasta.hpp:127, :137-138) — unless
+//     the line before it was a header: the line after a header is sequence whatever it starts with (:129-133), so
+//     header-looking lines in a row alternate; a '>' anywhere else is sequence; all records are concatenated without
+//     separators (io.hpp:10-11);
 //   * a/A c/C g/G t/T -> 0..3, every other byte -> 0.
 // The reference does this with serial getline + per-character push_back; here a byte is kept iff it is not '\n' and
 // the line it belongs to is not a header, which is a stream compaction:
-//   k_ingest_summary  per 4096-byte chunk: kept bytes of the lines that START in the chunk, non-newline bytes of
-//                     the leading partial line (kept or not depends on where that line started), last line start
-//   k_ingest_bmax / bscan / carry   running maximum of the line starts over the chunks (two levels) -> is the leading
-//                     partial line of chunk c a header? -> kept bytes per chunk
+//   k_ingest_summary  per 4096-byte chunk: what the chunk does to the one-bit state "the current line is a header"
+//                     (one of four functions) and the bytes it keeps under either incoming state
+//   k_ingest_bfn / bscan / carry   scan of those functions over the chunks (two levels) -> state at every chunk's
+//                     first byte -> kept bytes per chunk
 //   (exclusive scan of the kept counts, scan.cu)
 //   k_ingest_emit     per chunk: flags again, block scan, codes written at the chunk's offset
 // Algorithmic bytes: 2 reads of the file + n written.
@@ -82,142 +84,132 @@ __device__ __forceinline__ void ingest_load(const u8* __restrict__ raw, u64 nbyt
   it.last_ls = it.lsmask ? threadIdx.x * ING_PER + (32u - (u32)__clz(it.lsmask)) : 0u;
 }
 
-// exclusive running maximum over the threads of the block (0 = none before)
-__device__ __forceinline__ u32 block_excl_max(u32 v, u32* ws) {
-  const u32 lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
-  u32 incl = v;
+// ---- header state.  "Is the current line a header" is a one-bit state that every line start updates:
+// new = (the line starts with '>') && !old — the line after a header is sequence whatever it starts with
+// (fasta.hpp:129-133), so header-looking lines in a row alternate.  The effect of any stretch of the file on that bit
+// is one of the four functions {0,1} -> {0,1}, kept as two bits (bit s = image of s), and stretches compose
+// associatively: the state at every thread, chunk and block of chunks comes from scans of such functions.
+#define ING_ID 2u  // identity: 0 -> 0, 1 -> 1
+__device__ __forceinline__ u32 fn_apply(u32 f, u32 s) { return (f >> s) & 1u; }
+__device__ __forceinline__ u32 fn_then(u32 earlier, u32 later) {  // later o earlier
+  return fn_apply(later, fn_apply(earlier, 0u)) | (fn_apply(later, fn_apply(earlier, 1u)) << 1);
+}
+// the thread's 16 bytes under incoming state s: mask of the bytes that belong to header lines, and the state after them
+__device__ __forceinline__ u32 ingest_walk(const IngestThread& it, bool fasta, u32 s, u32& drop) {
+  u32 L = it.lsmask, prev = 0;
+  drop = 0;
+  while (L) {
+    const u32 k = (u32)__ffs((int)L) - 1u;
+    L &= L - 1u;
+    if (s) drop |= ((1u << k) - 1u) & ~((1u << prev) - 1u);
+    s = (fasta && ((it.gtmask >> k) & 1u) && !s) ? 1u : 0u;
+    prev = k;
+  }
+  if (s) drop |= 0xFFFFu & ~((1u << prev) - 1u);
+  drop &= it.vmask;
+  return s;
+}
+__device__ __forceinline__ u32 ingest_fn(const IngestThread& it, bool fasta) {
+  if (!it.lsmask) return ING_ID;
+  u32 d;
+  return ingest_walk(it, fasta, 0u, d) | (ingest_walk(it, fasta, 1u, d) << 1);
+}
+// exclusive scan of the threads' functions over the block (thread 0 gets the identity); *total = the whole block's
+__device__ __forceinline__ u32 block_excl_fn(u32 f, u32* ws, u32* total) {
+  const u32 lane = threadIdx.x & 31u, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  u32 incl = f;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const u32 x = __shfl_up_sync(0xffffffffu, incl, o);
-    if ((int)lane >= o) incl = max(incl, x);
+    if ((int)lane >= o) incl = fn_then(x, incl);
   }
   if (lane == 31) ws[w] = incl;
   __syncthreads();
-  u32 before = 0;
-  for (u32 ww = 0; ww < w; ww++) before = max(before, ws[ww]);
-  u32 ex = __shfl_up_sync(0xffffffffu, incl, 1);
-  if (lane == 0) ex = 0;
-  __syncthreads();
-  return max(before, ex);
-}
-
-// Masks of the thread's bytes that belong to a header line (drop) and to the line that started before this chunk
-// (lead: kept or not is decided by k_ingest_carry).  Bit-parallel: a header region runs from a header start ('>' at a
-// line start) up to the next line start; adding the header-start bits to the word that has a 1 at every header start
-// and every byte that does not start a line lets the carry run through exactly those bytes.
-__device__ __forceinline__ void ingest_classes(const u8* __restrict__ raw, u64 chunk0, const IngestThread& it, u32 ls_before,
-                                               bool fasta, u32& drop, u32& lead) {
-  const u32 L = it.lsmask, Hs = fasta ? (L & it.gtmask) : 0u;
-  const u32 A = ((~L) | Hs) & 0xFFFFu;
-  const u32 S = A + Hs;
-  drop = (((S ^ A) | Hs) & A) & it.vmask;
-  // the bytes below the first line start of this thread inherit the class of the line they continue
-  const u32 P = (L ? ((L & (0u - L)) - 1u) : 0xFFFFu) & it.vmask;
-  lead = 0;
-  if (P) {
-    if (!ls_before) lead = P;
-    else if (fasta && raw[chunk0 + ls_before - 1] == '>') drop |= P;
+  u32 before = ING_ID, all = ING_ID;
+  for (u32 ww = 0; ww < nw; ww++) {
+    if (ww < w) before = fn_then(before, ws[ww]);
+    all = fn_then(all, ws[ww]);
   }
+  u32 ex = __shfl_up_sync(0xffffffffu, incl, 1);
+  if (lane == 0) ex = ING_ID;
+  __syncthreads();
+  if (total) *total = all;
+  return fn_then(before, ex);
 }
 
+// per chunk: its function and the bytes it keeps under either incoming state
 __global__ void __launch_bounds__(ING_THREADS) k_ingest_summary(const u8* __restrict__ raw, u64 nbytes, bool fasta,
-                                                               u32* __restrict__ lead, u32* __restrict__ rest,
-                                                               u64* __restrict__ last_ls) {
+                                                               u32* __restrict__ kept0, u32* __restrict__ kept1,
+                                                               u8* __restrict__ fn) {
   __shared__ u32 ws[ING_THREADS / 32];
-  __shared__ u32 s_lead, s_rest, s_last;
-  if (threadIdx.x == 0) { s_lead = 0; s_rest = 0; s_last = 0; }
+  __shared__ u32 s_k0, s_k1;
+  if (threadIdx.x == 0) { s_k0 = 0; s_k1 = 0; }
   const u64 chunk0 = (u64)blockIdx.x * ING_CHUNK;
   IngestThread it;
   ingest_load(raw, nbytes, chunk0, it);
-  const u32 ls_before = block_excl_max(it.last_ls, ws);  // (its barriers also order the zeroing above)
-  u32 drop, leadm;
-  ingest_classes(raw, chunk0, it, ls_before, fasta, drop, leadm);
+  u32 all;
+  const u32 ex = block_excl_fn(ingest_fn(it, fasta), ws, &all);  // (its barriers also order the zeroing above)
   const u32 body = it.vmask & ~it.nlmask;
-  u32 nlead = (u32)__popc(body & leadm), nkeep = (u32)__popc(body & ~leadm & ~drop);
-  nlead = __reduce_add_sync(0xffffffffu, nlead);
-  nkeep = __reduce_add_sync(0xffffffffu, nkeep);
-  const u32 lmax = __reduce_max_sync(0xffffffffu, it.last_ls);
+  u32 d0, d1;
+  ingest_walk(it, fasta, fn_apply(ex, 0u), d0);
+  if (fn_apply(ex, 1u) == fn_apply(ex, 0u)) d1 = d0; else ingest_walk(it, fasta, fn_apply(ex, 1u), d1);
+  const u32 n0 = __reduce_add_sync(0xffffffffu, (u32)__popc(body & ~d0));
+  const u32 n1 = __reduce_add_sync(0xffffffffu, (u32)__popc(body & ~d1));
   if ((threadIdx.x & 31u) == 0) {
-    if (nlead) atomicAdd(&s_lead, nlead);
-    if (nkeep) atomicAdd(&s_rest, nkeep);
-    if (lmax) atomicMax(&s_last, lmax);
+    if (n0) atomicAdd(&s_k0, n0);
+    if (n1) atomicAdd(&s_k1, n1);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    lead[blockIdx.x] = s_lead;
-    rest[blockIdx.x] = s_rest;
-    last_ls[blockIdx.x] = s_last ? chunk0 + s_last : 0ull;  // file index + 1
+    kept0[blockIdx.x] = s_k0;
+    kept1[blockIdx.x] = s_k1;
+    fn[blockIdx.x] = (u8)all;
   }
 }
 
-// Header flag of every chunk's leading partial line and kept bytes per chunk (into `rest`): the line containing a
-// chunk's first byte starts at the running maximum of the line starts of the chunks before it.  Two levels: blocks of
-// 1024 chunks publish their maximum (k_ingest_bmax), one block scans those (k_ingest_bscan), every block then scans
-// its own 1024 chunks (k_ingest_carry).  (One block walking all chunks took 0.9 ms per GB of file.)
-__device__ __forceinline__ u64 block_excl_max64(u64 v, u64* ws, u64* total) {
-  const u32 lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
-  u64 incl = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const u64 x = __shfl_up_sync(0xffffffffu, incl, o);
-    if ((int)lane >= o) incl = max(incl, x);
-  }
-  if (lane == 31) ws[w] = incl;
-  __syncthreads();
-  u64 before = 0, all = 0;
-  for (u32 ww = 0; ww < 32; ww++) {
-    const u64 x = ws[ww];
-    if (ww < w) before = max(before, x);
-    all = max(all, x);
-  }
-  u64 ex = __shfl_up_sync(0xffffffffu, incl, 1);
-  if (lane == 0) ex = 0;
-  __syncthreads();
-  if (total) *total = all;
-  return max(before, ex);
-}
-
-__global__ void __launch_bounds__(1024) k_ingest_bmax(const u64* __restrict__ last_ls, u64 nchunks, u64* __restrict__ bmax) {
-  __shared__ u64 ws[32];
+// State at the start of every chunk, two levels: blocks of 1024 chunks publish their function (k_ingest_bfn), one block
+// scans those (k_ingest_bscan), every block then scans its own 1024 chunks and picks the kept count of each
+// (k_ingest_carry).  (One block walking all chunks took 0.9 ms per GB of file.)
+__global__ void __launch_bounds__(1024) k_ingest_bfn(const u8* __restrict__ fn, u64 nchunks, u8* __restrict__ bfn) {
+  __shared__ u32 ws[32];
   const u64 c = (u64)blockIdx.x * 1024 + threadIdx.x;
-  u64 all;
-  block_excl_max64(c < nchunks ? last_ls[c] : 0ull, ws, &all);
-  if (threadIdx.x == 0) bmax[blockIdx.x] = all;
+  u32 all;
+  block_excl_fn(c < nchunks ? (u32)fn[c] : ING_ID, ws, &all);
+  if (threadIdx.x == 0) bfn[blockIdx.x] = (u8)all;
 }
 
-// in place: bmax[b] <- maximum over the blocks before b; *total zeroed for the kept-byte sum
-__global__ void __launch_bounds__(1024) k_ingest_bscan(u64* __restrict__ bmax, u64 nblocks, u64* __restrict__ total) {
-  __shared__ u64 ws[32];
-  __shared__ u64 s_carry;
-  if (threadIdx.x == 0) { s_carry = 0; *total = 0; }
+// in place: bfn[b] <- state at the start of block b (the file starts outside a header); *total zeroed
+__global__ void __launch_bounds__(1024) k_ingest_bscan(u8* __restrict__ bfn, u64 nblocks, u64* __restrict__ total) {
+  __shared__ u32 ws[32];
+  __shared__ u32 s_carry;
+  if (threadIdx.x == 0) { s_carry = ING_ID; *total = 0; }
   __syncthreads();
   for (u64 base = 0; base < nblocks; base += 1024) {
     const u64 i = base + threadIdx.x;
-    u64 all;
-    const u64 ex = block_excl_max64(i < nblocks ? bmax[i] : 0ull, ws, &all);
-    const u64 carry = s_carry;
-    if (i < nblocks) bmax[i] = max(carry, ex);
+    u32 all;
+    const u32 ex = block_excl_fn(i < nblocks ? (u32)bfn[i] : ING_ID, ws, &all);
+    const u32 carry = s_carry;
+    if (i < nblocks) bfn[i] = (u8)fn_apply(fn_then(carry, ex), 0u);
     __syncthreads();
-    if (threadIdx.x == 0) s_carry = max(carry, all);
+    if (threadIdx.x == 0) s_carry = fn_then(carry, all);
     __syncthreads();
   }
 }
 
-__global__ void __launch_bounds__(1024) k_ingest_carry(const u8* __restrict__ raw, bool fasta, u64 nchunks,
-                                                      const u32* __restrict__ lead, u32* __restrict__ rest,
-                                                      const u64* __restrict__ last_ls, const u64* __restrict__ bmax,
+__global__ void __launch_bounds__(1024) k_ingest_carry(u64 nchunks, u32* __restrict__ kept0, const u32* __restrict__ kept1,
+                                                      const u8* __restrict__ fn, const u8* __restrict__ bstate,
                                                       u8* __restrict__ hflag, u64* __restrict__ total) {
-  __shared__ u64 ws[32];
+  __shared__ u32 ws[32];
   __shared__ unsigned long long s_total;
   if (threadIdx.x == 0) s_total = 0ull;
   const u64 c = (u64)blockIdx.x * 1024 + threadIdx.x;
-  const u64 run = max(bmax[blockIdx.x], block_excl_max64(c < nchunks ? last_ls[c] : 0ull, ws, nullptr));
+  const u32 ex = block_excl_fn(c < nchunks ? (u32)fn[c] : ING_ID, ws, nullptr);
   u32 kept = 0;
   if (c < nchunks) {
-    const bool h = fasta && run != 0 && raw[run - 1] == '>';
-    kept = rest[c] + (h ? 0u : lead[c]);
-    hflag[c] = h ? 1 : 0;
-    rest[c] = kept;
+    const u32 s = fn_apply(ex, (u32)bstate[blockIdx.x]);
+    kept = s ? kept1[c] : kept0[c];
+    hflag[c] = (u8)s;
+    kept0[c] = kept;
   }
   kept = __reduce_add_sync(0xffffffffu, kept);
   if ((threadIdx.x & 31u) == 0 && kept) atomicAdd(&s_total, (unsigned long long)kept);
@@ -233,10 +225,9 @@ __global__ void __launch_bounds__(ING_THREADS) k_ingest_emit(const u8* __restric
   const u64 chunk0 = (u64)blockIdx.x * ING_CHUNK;
   IngestThread it;
   ingest_load(raw, nbytes, chunk0, it);
-  const u32 ls_before = block_excl_max(it.last_ls, ws);
-  u32 drop, leadm;
-  ingest_classes(raw, chunk0, it, ls_before, fasta, drop, leadm);
-  if (hflag[blockIdx.x]) drop |= leadm;
+  const u32 ex = block_excl_fn(ingest_fn(it, fasta), ws, nullptr);
+  u32 drop;
+  ingest_walk(it, fasta, fn_apply(ex, (u32)hflag[blockIdx.x]), drop);  // hflag = state at the chunk's first byte
   const u32 keep = it.vmask & ~it.nlmask & ~drop;
   // exclusive scan of the per-thread counts
   const u32 cnt = (u32)__popc(keep), lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
@@ -290,21 +281,22 @@ __global__ void __launch_bounds__(ING_THREADS) k_ingest_emit(const u8* __restric
 
 u64 ingest_chunks(u64 nbytes) { return (nbytes + ING_CHUNK - 1) / ING_CHUNK; }
 
-// codes_dev needs room for nbytes bytes.  lead / rest: nchunks u32, last_ls: nchunks u64, bmax: nchunks / 1024 + 1 u64,
-// hflag: nchunks bytes,
-// partials: scan_partials_len(nchunks), total_dev: one u64.  Everything is enqueued on st; *total_dev holds n afterwards.
-void ingest(const u8* raw_dev, u64 nbytes, u8* codes_dev, u32* lead, u32* rest, u64* last_ls, u64* bmax, u8* hflag,
+// codes_dev needs room for nbytes bytes.  kept0 / kept1: nchunks u32, fn / hflag: nchunks bytes, bfn: nchunks / 1024 + 1
+// bytes, partials: scan_partials_len(nchunks), total_dev: one u64.  Everything is enqueued on st; *total_dev holds n
+// afterwards.
+void ingest(const u8* raw_dev, u64 nbytes, u8* codes_dev, u32* kept0, u32* kept1, u8* fn, u8* bfn, u8* hflag,
             u32* partials, u64* total_dev, bool fasta, cudaStream_t st) {
   const u64 nch = ingest_chunks(nbytes);
   if (!nch) return;
-  k_ingest_summary<<<(unsigned)nch, ING_THREADS, 0, st>>>(raw_dev, nbytes, fasta, lead, rest, last_ls);
+  u32* rest = kept0;
+  k_ingest_summary<<<(unsigned)nch, ING_THREADS, 0, st>>>(raw_dev, nbytes, fasta, kept0, kept1, fn);
   CK_LAUNCH();
   const u64 nb = (nch + 1023) / 1024;
-  k_ingest_bmax<<<(unsigned)nb, 1024, 0, st>>>(last_ls, nch, bmax);
+  k_ingest_bfn<<<(unsigned)nb, 1024, 0, st>>>(fn, nch, bfn);
   CK_LAUNCH();
-  k_ingest_bscan<<<1, 1024, 0, st>>>(bmax, nb, total_dev);
+  k_ingest_bscan<<<1, 1024, 0, st>>>(bfn, nb, total_dev);
   CK_LAUNCH();
-  k_ingest_carry<<<(unsigned)nb, 1024, 0, st>>>(raw_dev, fasta, nch, lead, rest, last_ls, bmax, hflag, total_dev);
+  k_ingest_carry<<<(unsigned)nb, 1024, 0, st>>>(nch, kept0, kept1, fn, bfn, hflag, total_dev);
   CK_LAUNCH();
   scan_excl_u32(rest, nch, partials, nullptr, st);
   k_ingest_emit<<<(unsigned)nch, ING_THREADS, 0, st>>>(raw_dev, nbytes, fasta, rest, hflag, 0ull, codes_dev);

@@ -81,7 +81,7 @@ void synth_uniform(u8* S, u64 n, u64 seed, cudaStream_t st);
 // ---------------------------------------------------------------- ingest.cu
 // file bytes -> codes with the reference's read_sequence semantics (FASTA headers and newlines dropped, see ingest.cu)
 u64 ingest_chunks(u64 nbytes);
-void ingest(const u8* raw_dev, u64 nbytes, u8* codes_dev, u32* lead, u32* rest, u64* last_ls, u64* bmax, u8* hflag,
+void ingest(const u8* raw_dev, u64 nbytes, u8* codes_dev, u32* kept0, u32* kept1, u8* fn, u8* bfn, u8* hflag,
             u32* partials, u64* total_dev, bool fasta, cudaStream_t st);
 
 // ---------------------------------------------------------------- lms.cu

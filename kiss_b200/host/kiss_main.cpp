@@ -75,13 +75,16 @@ inline std::uint8_t code_of(unsigned char c) {
 
 // read_sequence (include/utils/io.hpp:6-18): FASTA mode iff the first byte is '>' — header lines dropped, all
 // records concatenated without separators; text mode: every line is sequence.  '\r', N and IUPAC codes all
-// become A, as in the reference.
+// become A, as in the reference.  The line after a header is sequence whatever it starts with
+// (include/biovoltron/file_io/fasta.hpp:129-133), so a '>' line is a header only when the line before it was not one.
 std::vector<std::uint8_t> read_sequence(std::istream& fin) {
   std::vector<std::uint8_t> seq;
-  bool fasta = fin.peek() == '>';
+  bool fasta = fin.peek() == '>', prev_header = false;
   std::string line;
   while (std::getline(fin, line)) {
-    if (fasta && !line.empty() && line[0] == '>') continue;
+    const bool header = fasta && !line.empty() && line[0] == '>' && !prev_header;
+    prev_header = header;
+    if (header) continue;
     for (unsigned char c : line) seq.push_back(code_of(c));
   }
   return seq;

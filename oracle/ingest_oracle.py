@@ -29,11 +29,16 @@ def read_sequence(data):
     data = bytes(data)
     fasta = data[:1] == b">"
     keep = []
+    prev_header = False
     for line in _getlines(data):
-        # fasta.hpp:127 (the header line of a record) and :137-138 (a line that starts with '>' begins the next
-        # record): in FASTA mode every line whose first byte is '>' is a header.  io.hpp:13-15: text mode keeps all.
-        if fasta and line[:1] == b">":
-            continue
-        keep.append(line)                # '\r' of a CRLF file stays in the line (getline only strips '\n')
+        # fasta.hpp:116-151: a record = its header line (:127), then lines are appended to the sequence
+        # UNCONDITIONALLY (:129-133) until the byte after a line is '>' (:137-138).  So a line whose first byte is '>'
+        # is a header only when the line before it was not one: of two header-looking lines in a row the second is
+        # SEQUENCE ('>' and the letters encode like any byte), of three the third is a header again.
+        # io.hpp:13-15: text mode keeps every line.
+        header = fasta and line[:1] == b">" and not prev_header
+        prev_header = header
+        if not header:
+            keep.append(line)            # '\r' of a CRLF file stays in the line (getline only strips '\n')
     seq = np.frombuffer(b"".join(keep), dtype=np.uint8)
     return _LUT[seq]

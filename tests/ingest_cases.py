@@ -41,6 +41,20 @@ CASES = {
     "spaces_and_tabs": b">a\nAC GT\n\tACGT \n",
     "long_header": b">" + b"x" * 9000 + b"\nACGTACGT\n>" + b"y" * 5000 + b"\nGGGG\n",
     "line_4096": b">a\n" + b"ACGT" * 1024 + b"\n" + b"TTGA" * 1024 + b"\n",
+    # header-looking lines in a row: the line after a header is always sequence (fasta.hpp:129-133), so they alternate
+    "two_headers_in_a_row": b">a\n>b\nACGT\n",
+    "empty_record_in_the_middle": b">a\nAC\n>b\n>c\nGG\n",
+    "three_headers_in_a_row": b">a\n>b\n>c\nACGT\n",
+    "five_headers_in_a_row": b">a\n>bb\n>ccc\n>dddd\n>eeeee\nACGT\n>f\nTT\n",
+    "headers_only_run": b">a\n>b\n>c\n>d",
+    "blank_line_between_headers": b">a\n\n>b\n>c\nAC\n",
+    "header_run_after_sequence": b">a\nACGT\n>b\n>c\n>d\n>e\nGG\n>f\n>g\n",
+    "gt_only_lines": b">\n>\n>\n>\nA\n>\n>\n",
+    # runs of header-looking lines across the 16-byte thread and 4096-byte chunk boundaries of the device kernels
+    "header_run_across_threads": b">a\n" + b"".join(b">h%02d\n" % i for i in range(40)) + b"ACGT\n",
+    "header_run_across_chunks": b">a\nAC\n" + b"".join(b">" + b"x" * (37 + i % 11) + b"\n" for i in range(400)) + b"GGTT\n",
+    "long_header_run_odd": b">" + b"x" * 5000 + b"\n>" + b"y" * 5000 + b"\n>" + b"z" * 3000 + b"\nACGT\n>q\nTT\n",
+    "long_header_run_even": b">" + b"x" * 5000 + b"\n>" + b"y" * 4100 + b"\nACGT\n>q\n>r\nTT\n",
     # (bytes >= 0x80 index the reference's 128-entry table out of range — undefined there, 0 here: no fixture)
 }
 
