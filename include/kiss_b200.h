@@ -173,6 +173,19 @@ int kiss_b200_suffix_sort_file_u32(kiss_b200_ctx* ctx, const uint8_t* file_host,
 int kiss_b200_ingest_dev(kiss_b200_ctx* ctx, const uint8_t* file_dev, uint64_t nbytes, int fasta, uint8_t* codes_dev,
                          uint64_t* n_out);
 
+/* ---- allocation-free ingest ---------------------------------------------------------------------
+ * kiss_b200_ingest_noalloc_dev has NO COUNTERPART IN THE REFERENCE: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments, kernels and result as kiss_b200_ingest_dev, but the per-chunk scratch lives in a file-scope
+ * __device__ array of the library (about 0.66 MB on every GPU that loads it, held until the process exits) instead of
+ * the context's arena: the call makes no cudaMalloc / cudaFree / allocating library call.  Limit: nbytes <=
+ * KISS_B200_NOALLOC_MAX_BYTES, else KISS_B200_ERR_TOO_LARGE (kiss_b200_last_error says so).  Every call on a GPU shares
+ * the one array — it keeps the last call's contents; nothing in it has to be cleared by the caller — so calls that
+ * overlap on one GPU (two contexts, two host threads) race: serialise them. */
+#define KISS_B200_NOALLOC_MAX_BYTES (256ull << 20)
+int kiss_b200_ingest_noalloc_dev(kiss_b200_ctx* ctx, const uint8_t* file_dev, uint64_t nbytes, int fasta,
+                                 uint8_t* codes_dev, uint64_t* n_out);
+
 /* ---- per-kernel timing ---------------------------------------------------------------------------
  * When enabled, every launch of the main kernel classes is bracketed by CUDA events on the context's stream and
  * the durations are accumulated per class (bench.py's roofline numbers).  enable() also clears the totals.

@@ -10,6 +10,7 @@ PARALLEL_SORTING = 0
 PREFIX_DOUBLING = 1
 EMPTY = 0xFFFFFFFF
 UNBOUNDED_K = 0xFFFFFFFF
+NOALLOC_MAX_BYTES = 256 << 20  # KISS_B200_NOALLOC_MAX_BYTES
 
 
 class Timings(C.Structure):
@@ -55,6 +56,7 @@ SIGNATURES = {
     "kiss_b200_lms_contexts_dev": (_int, [_vp, _vp, _u64, _vp]),
     "kiss_b200_suffix_sort_file_u32": (_int, [_vp, _vp, _u64, _u32, _int, _vp, _u64, C.POINTER(_u64), C.POINTER(Timings)]),
     "kiss_b200_ingest_dev": (_int, [_vp, _vp, _u64, _int, _vp, C.POINTER(_u64)]),
+    "kiss_b200_ingest_noalloc_dev": (_int, [_vp, _vp, _u64, _int, _vp, C.POINTER(_u64)]),
     "kiss_b200_profile_enable": (_int, [_vp, _int]),
     "kiss_b200_profile_read": (_int, [_vp, _int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(_u64)]),
     "kiss_b200_profile_alg_bytes": (_int, [_vp, _int, C.POINTER(_u64)]),

@@ -779,6 +779,12 @@ void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* o
 
 }  // namespace
 
+// ---- accessors for the entry points that live in other files (noalloc.cu)
+namespace kiss {
+void api_set_last_error(const std::string& msg) { g_last_error = msg; }
+int api_ctx_device(const kiss_b200_ctx* c) { return c->device; }
+}  // namespace kiss
+
 // ======================================================================================= extern "C"
 extern "C" {
 

@@ -12,7 +12,13 @@ typedef unsigned long long u64;
 typedef unsigned int u32;
 typedef unsigned char u8;
 
+struct kiss_b200_ctx;
+
 namespace kiss {
+
+// api.cu, for the entry points defined in other files
+void api_set_last_error(const std::string& msg);
+int api_ctx_device(const kiss_b200_ctx* c);
 
 struct CudaError : std::runtime_error {
   int code;

@@ -91,6 +91,12 @@ class Context:
         check(lib().kiss_b200_ingest_dev(self._h, file_ptr, nbytes, 1 if fasta else 0, codes_ptr, C.byref(n)))
         return n.value
 
+    def ingest_noalloc_dev(self, file_ptr, nbytes, fasta, codes_ptr):
+        """ingest_dev with its scratch in a fixed __device__ array: no allocation, at most NOALLOC_MAX_BYTES"""
+        n = C.c_uint64()
+        check(lib().kiss_b200_ingest_noalloc_dev(self._h, file_ptr, nbytes, 1 if fasta else 0, codes_ptr, C.byref(n)))
+        return n.value
+
     def suffix_array_dna_dev(self, S_ptr, n, SA_ptr, k=256, algo=PARALLEL_SORTING):
         """device-resident variant: S_ptr / SA_ptr are device addresses (e.g. torch tensor.data_ptr())"""
         t = Timings()
