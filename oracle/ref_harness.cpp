@@ -56,6 +56,26 @@ double ref_kiss2_suffix_array_dna(const uint8_t* S_, uint64_t n, uint32_t k, uin
   return t1 - t0;
 }
 
+// kISS-2's LMS sort alone: the steps of kiss2_suffix_array_internal (kiss2_core.hpp:835-886) up to and including
+// prefix_doubling (:874), same calls in the same order.  sorted_out receives the m LMS suffixes in the order
+// place_back_lms leaves them (:690-725; sorted_out[0] == n).  Returns m.  n must be > 0.
+uint32_t ref_kiss2_sorted_lms(const uint8_t* S_, uint64_t n_, uint32_t k, uint64_t threads, uint32_t* sorted_out) {
+  vector<uint8_t> S(S_, S_ + n_);
+  vector<uint32_t> SA;
+  uint32_t n = (uint32_t)S.size();
+  SA.reserve((size_t)n + 1);
+  auto states = vector<kiss::ThreadState<uint32_t>>(threads);
+  SA.resize((size_t)n + 1);
+  auto m = kiss::get_lms(S, SA, states);
+  const uint32_t bits_for_character = std::bit_width(4u - 1u);
+  const uint32_t l = 8 * sizeof(uint32_t) / bits_for_character;
+  auto m_encoded = kiss::get_encoded_S_length(SA, m, l, threads, states);
+  if (uint64_t(m_encoded) * 3 > (uint64_t)n + 1) SA.resize(uint64_t(m_encoded) * 3);
+  kiss::prefix_doubling<uint8_t, uint32_t>(S, SA, k, bits_for_character, l, m, m_encoded, threads, states);
+  if (sorted_out) std::memcpy(sorted_out, SA.data(), sizeof(uint32_t) * m);
+  return m;
+}
+
 // Stage replay of kiss1_suffix_array_dna (kiss1_core.hpp:229-268), same calls in the same
 // order, with snapshots.  Any out pointer may be NULL.
 //   lms_out      : m entries  — get_lms output (ascending positions, sentinel n last)

@@ -75,6 +75,9 @@ def ref():
         L.ref_kiss1_stages.argtypes = [_vp, _u64, _u32, _u64, _vp, _vp, _vp, _vp, _vp, _vp]
         L.ref_induce_from_sorted_lms.restype = None
         L.ref_induce_from_sorted_lms.argtypes = [_vp, _u64, _u64, _vp, _vp]
+        if hasattr(L, "ref_kiss2_sorted_lms"):
+            L.ref_kiss2_sorted_lms.restype = _u32
+            L.ref_kiss2_sorted_lms.argtypes = [_vp, _u64, _u32, _u64, _vp]
         if hasattr(L, "ref_read_sequence"):
             L.ref_read_sequence.restype = _u64
             L.ref_read_sequence.argtypes = [_vp, _u64, _vp]
@@ -143,6 +146,14 @@ def ref_kiss2(S, k=256, threads=4):
     SA = np.zeros(S.size + 1, np.uint32)
     ref().ref_kiss2_suffix_array_dna(_ptr(S), S.size, k & 0xFFFFFFFF, threads, _ptr(SA))
     return SA
+
+
+def ref_kiss2_sorted_lms(S, k=256, threads=1):
+    """kISS-2's LMS order (the reference's own encode_S .. place_back_lms, kiss2_core.hpp:728-798), sentinel first"""
+    S = _codes(S)
+    out = np.zeros(S.size // 2 + 2, np.uint32)
+    m = ref().ref_kiss2_sorted_lms(_ptr(S), S.size, k & 0xFFFFFFFF, threads, _ptr(out))
+    return out[:m].copy()
 
 
 def ref_kiss1_stages(S, k=256, threads=4):
