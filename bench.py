@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=0, help="bases of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-full-config", action="store_true", help="reference arm: skip the one full-size run")
+    ap.add_argument("--no-parity", action="store_true")
     args = ap.parse_args()
     args.wl = WORKLOADS[args.workload]
     args.n = args.n or args.wl["n"]
@@ -111,20 +113,24 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------ CPU reference
-def host_sample(wl, sample, full=None):
-    """`sample` bases of the workload for the CPU legs: a prefix of the bench text when it is at hand (`full`; its
-    last 4096 bases are replaced by uniform ones so no repeat touches the text end, as in the generator), else the
-    same generator run at the sample size (numpy only: the reference arm never touches the GPU)."""
+CPU_SAMPLE = 100_000_000  # bases of the bounded CPU sample: the SAME text for the cpu_baseline leg and the reference arm
+
+
+def host_text(wl, n):
+    """the workload's text at n bases, generated on the host with numpy only (the reference arm never touches the GPU);
+    n = the workload's own size gives the bench text itself"""
     import numpy as np
     import textgen as tg
-    if full is not None and sample <= full.size:
-        S = np.ascontiguousarray(full[:sample]).copy()
-        if wl["kind"] != "uniform" and sample > 8192:
-            S[-4096:] = tg.uniform(wl["seed"] + 1, 4096)
-        return S, f"first {sample} bases of the bench text"
-    if wl["kind"] == "uniform":
-        return tg.uniform(wl["seed"], sample), f"first {sample} bases of the bench text"
-    return tg.chm13_like(wl["seed"], sample), f"the bench text's generator (chm13_like, seed {wl['seed']}) at {sample} bases"
+    S = tg.uniform_big(wl["seed"], n)
+    if wl["kind"] != "uniform":
+        S = tg.chm13_like(wl["seed"], n, base=S)
+    return S
+
+
+def host_sample(wl, sample):
+    what = (f"first {sample} bases of the bench text" if wl["kind"] == "uniform" else
+            f"the bench text's generator (chm13_like, seed {wl['seed']}) at {sample} bases")
+    return host_text(wl, sample), what
 
 
 def cpu_reference_run(S, k, threads):
@@ -146,27 +152,28 @@ def cpu_reference_run(S, k, threads):
     return sec, kind
 
 
-def cpu_baseline(wl, k, sample=0, full=None):
+def cpu_baseline(wl, k, sample=0):
+    """the reference on the bounded sample (the same one the reference arm times), all host threads, best of 2"""
     threads = os.cpu_count() or 1
-    if not sample:
-        S, _ = host_sample(wl, 20_000_000, full)
-        sec, kind = cpu_reference_run(S, k, threads)
-        rate = 20_000_001 / sec
-        sample = int(min(400_000_000, max(20_000_000, rate * 12)))
-    S, what = host_sample(wl, sample, full)
-    sec, kind = cpu_reference_run(S, k, threads)
+    sample = min(sample or CPU_SAMPLE, wl["n"])
+    S, what = host_sample(wl, sample)
+    runs = [cpu_reference_run(S, k, threads) for _ in range(2)]
+    sec, kind = min(r[0] for r in runs), runs[0][1]
     return {"value": (sample + 1) / sec / 1e9, "unit": "Gsuffixes/s", "cores": threads, "kind": kind,
-            "sample": f"{what} ({wl['name']}, seed {wl['seed']}), k={k}, kiss1_suffix_array_dna, {sec:.2f} s",
+            "sample": f"{what} ({wl['name']}, seed {wl['seed']}), k={k}, kiss1_suffix_array_dna, best of 2: {sec:.2f} s",
             "seconds": sec}
 
 
 def run_reference_arm(args):
+    """K bounded-sample steps (the line's value), then — unless --no-full-config — ONE run of the full configured text,
+    whose seconds go into `full_config` (the same-config number; 3.1 Gbp takes the reference about half a minute on 16
+    threads), and one run at 32 threads where the host has them."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     wl = args.wl
-    sample = min(args.n, args.cpu_sample or 100_000_000)
+    sample = min(args.n, args.cpu_sample or CPU_SAMPLE)
     S, what = host_sample(wl, sample)
     times = []
     kind = "reference"
@@ -181,24 +188,44 @@ def run_reference_arm(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": f"{wl['name']} {args.n} bp (seed {wl['seed']}), k={args.k}, PARALLEL_SORTING "
-                               f"(reference timed on a {sample}-base sample per step: {what})"},
+                               f"(reference timed on a {sample}-base sample per step: {what}; one full-size run in full_config)"},
         "cpu_baseline": {"value": val, "unit": "Gsuffixes/s", "cores": threads, "kind": kind,
                          "sample": f"{what}, every step"},
         "e2e": {"value": val, "unit": "Gsuffixes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if threads >= 32:
+        s32, _ = cpu_reference_run(S, args.k, 32)
+        line["cpu_baseline"]["threads32"] = {"value": (sample + 1) / s32 / 1e9, "seconds": s32, "sample": "the same sample"}
+    del S
+    if not args.no_full_config and args.n > sample:
+        t0 = time.perf_counter()
+        F = host_text(wl, args.n)
+        gen_s = time.perf_counter() - t0
+        fsec, _ = cpu_reference_run(F, args.k, threads)
+        full = {"n": args.n, "seconds": fsec, "value": (args.n + 1) / fsec / 1e9, "unit": "Gsuffixes/s", "cores": threads,
+                "runs": 1, "text_generation_seconds": round(gen_s, 1),
+                "note": "the whole configured text, kiss1_suffix_array_dna, same call the steps time"}
+        line["full_config"] = full
+        line["cpu_baseline"]["full_config_seconds"] = fsec
+        line["cpu_baseline"]["full_config_value"] = full["value"]
     print(json.dumps(line), flush=True)
 
 
 # ------------------------------------------------------------------------------------------ B200 arm
-# mean DRAM bytes (read + write) per launch, ncu dram__bytes_read.sum + dram__bytes_write.sum of one step
-# (profiles/r1_final_launches_1gbp.txt for c2, profiles/r1_c3_final_launches.txt for c3); None = no capture
-NCU_DRAM_BYTES_PER_LAUNCH = {
-    "c2": {"k_wave_fused": 46.658e9 / 58, "k_radix_scatter": 5.4073e9, "k_groups_tiny": 6.7628e9},
-    # 2 steps under ncu: k_wave_fused + k_wave_tail 331.7 GB / 150 launches, k_groups_medium 32.8 GB / 78
-    "c3": {"k_wave_fused": 331.70e9 / 150, "k_groups_medium": 32.80e9 / 78, "k_radix_scatter": 1.7273e9,
-           "k_groups_tiny": 5.0004e9},
-}
+def ncu_traffic(workload, kernel):
+    """mean dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the newest ncu launch list of this
+    workload: profiles/ncu_dram_per_launch.json, regenerated by tools/profile_c3.sh (tools/ncu_dram_per_kernel.py);
+    None when there is no capture"""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_dram_per_launch.json")))[workload]
+    except Exception:
+        return None, None
+    per = d["dram_bytes_per_launch"]
+    names = {"k_wave_fused": ["k_wave_fused", "k_wave_tail"], "k_radix_scatter": ["k_radix_scatter_p", "k_radix_scatter"]}.get(kernel, [kernel])
+    tot = sum(per[k] * d["launches"][k] for k in names if k in per)
+    cnt = sum(d["launches"][k] for k in names if k in per)
+    return (tot / cnt if cnt else None), d.get("source")
 
 
 def b200_alg_bytes(n, m):
@@ -243,8 +270,8 @@ def run_b200(args):
     n, k, wl = args.n, args.k, args.wl
     ctx = kiss_b200.Context(local)
     lib_stream = torch.cuda.ExternalStream(kiss_b200.lib().kiss_b200_stream(ctx.handle), device=local)
-    want_host = rank == 0 and not (args.no_e2e and (args.no_cpu_baseline or world > 1))
-    S, host_text = make_text(ctx, wl, n, dist, rank, want_host)
+    want_host = rank == 0 and not args.no_e2e
+    S, host_copy = make_text(ctx, wl, n, dist, rank, want_host)
     SA = torch.empty(n + 1, dtype=torch.int32, device="cuda")
 
     if world > 1:
@@ -306,6 +333,22 @@ def run_b200(args):
         "waves": [last.get("waves_L"), last.get("waves_S")],
         "lms_sort_tied": last.get("lms_sort_tied"), "lms_sort_rounds": last.get("lms_sort_rounds"),
     }
+    # parity, outside the timed region: the order-sensitive checksum of the device suffix array of the last step against
+    # the value tests/golden/make_full_size_golden.py computed from the REFERENCE's array of the same text (rank 0 holds
+    # the array at every N, so this covers the sharded path too)
+    if rank == 0 and not args.no_parity:
+        got = ctx.sa_checksum_dev(SA.data_ptr(), n + 1)
+        gold = None
+        try:
+            g = json.load(open(os.path.join(ROOT, "tests", "golden", "full_size_golden.json")))
+            for e in g.values():
+                if (e["n"], e["seed"], e["kind"], e["k"]) == (n, wl["seed"], wl["kind"], k):
+                    gold = e["sa_mixed_sum"]
+        except Exception:
+            pass
+        line["parity"] = {"sa_mixed_sum": f"{got:016x}", "golden": gold, "ok": (gold == f"{got:016x}") if gold else None,
+                          "golden_source": "tests/golden/full_size_golden.json (reference kiss1_suffix_array_dna via oracle/_ref)",
+                          "sa0_is_n": int(SA[0].item()) & 0xFFFFFFFF == n}
     if "steps_ms" in last:
         line["sharded_sort_steps_ms"] = last["steps_ms"]
     if "shard_sizes" in last:
@@ -360,11 +403,9 @@ def run_b200(args):
                 kernels[key].setdefault("classes", {})[name] = cls
         line["kernels"] = kernels
         dom = max((kk for kk in kernels if "achieved_gbs" in kernels[kk]), key=lambda kk: kernels[kk]["ms_per_step"])
-        # dram__bytes_read.sum + dram__bytes_write.sum per launch (mean over the launches of one step) from the
-        # ncu capture under profiles/; None when the dominant kernel has no capture at this workload
-        traffic = NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload, {}).get(dom) if n == wl["n"] and world == 1 else None
+        traffic, traffic_src = ncu_traffic(args.workload, dom) if n == wl["n"] and world == 1 else (None, None)
         line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": kernels[dom]["achieved_gbs"], "peak": peak,
-                            "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": traffic,
+                            "unit": "GB/s", "frac": kernels[dom]["frac"], "traffic": traffic, "traffic_source": traffic_src,
                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650 GB/s",
                             "share_of_step": kernels[dom]["ms_per_step"] / ms_step,
                             "launches_per_step": kernels[dom]["launches_per_step"]}
@@ -386,8 +427,8 @@ def run_b200(args):
         if rank == 0:
             hS = torch.empty(n, dtype=torch.uint8).pin_memory()
             hSA = torch.empty(n + 1, dtype=torch.int32).pin_memory()
-            if host_text is not None:
-                hS.copy_(torch.from_numpy(host_text))
+            if host_copy is not None:
+                hS.copy_(torch.from_numpy(host_copy))
             else:
                 hS.copy_(S[:n])
             torch.cuda.synchronize()
@@ -440,7 +481,7 @@ def run_b200(args):
         del hS, hSA
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            line["cpu_baseline"] = cpu_baseline(wl, k, args.cpu_sample, host_text)
+            line["cpu_baseline"] = cpu_baseline(wl, k, args.cpu_sample)
         except Exception as e:  # the checker is optional for the number, never for the product
             line["cpu_baseline"] = {"value": None, "unit": "Gsuffixes/s", "cores": os.cpu_count(), "kind": "unavailable",
                                     "sample": f"failed: {e}"}

@@ -173,6 +173,35 @@ int kiss_b200_suffix_sort_file_u32(kiss_b200_ctx* ctx, const uint8_t* file_host,
 int kiss_b200_ingest_dev(kiss_b200_ctx* ctx, const uint8_t* file_dev, uint64_t nbytes, int fasta, uint8_t* codes_dev,
                          uint64_t* n_out);
 
+/* ---- FM-index construction: the step after the path -----------------
+ * The reference's `fmindex_build` command (include/command/fmindex_build.hpp:27-34) builds
+ * FMIndex<SA_INTV = 4, uint32_t, KISS1Sorter<uint32_t>>{.LOOKUP_LEN = 0}: suffix array with k = 32 (fm_index.hpp:385-386),
+ * then build_occ (fm_index.hpp:278-307), build_bwt (:311-328), build_sa (:332-372), build_lookup (:237-269; {0, n + 1}
+ * for LOOKUP_LEN = 0), and writes it with FMIndex::save (:591-617) through Serializer::save
+ * (include/biovoltron/utility/archive/serializer.hpp:95-112).  Here the suffix array stays in device memory: the BWT,
+ * both occ tables, the sampled-entry bit vector with its prefix sums and the sampled suffix array are built by kernels
+ * (csrc/fmindex.cu) and only they cross PCIe (1.75 bytes per suffix instead of 4), laid out in `image_host` as exactly
+ * the bytes of the reference's .fmi file — its `fmindex_query` loads the result.  (The reference leaves the bits past the
+ * last element in the last byte of bwt_ and the last word of b_ uninitialised; they are zero here.)
+ * sa_intv = the reference's SA_INTV template argument (4 in its command; 1 stores the whole array and no bit vector).
+ * fmindex_image_bytes: size of the image for a text of n bases.
+ * fmindex_build_dna: S_host = n codes 0..3; k / algo as kiss_b200_suffix_sort_dna_u32 (the reference uses 32 / kISS-1).
+ * fmindex_build_file: the bytes of a FASTA / text file in (read_sequence semantics, see the ingest section); *n_out =
+ *   text length; capacity kiss_b200_fmindex_image_bytes(nbytes, sa_intv) always suffices.
+ * fmindex_from_sa_dev: from a suffix array already in device memory (S_dev: codes, 16-byte aligned; SA_dev: n + 1).
+ * *image_bytes = bytes written; KISS_B200_ERR_ARG when capacity is too small.  t, fm_seconds (device seconds of the
+ * FM-index kernels) may be NULL. */
+uint64_t kiss_b200_fmindex_image_bytes(uint64_t n, uint32_t sa_intv);
+int kiss_b200_fmindex_build_dna_u32(kiss_b200_ctx* ctx, const uint8_t* S_host, uint64_t n, uint32_t k, int algo,
+                                    uint32_t sa_intv, uint8_t* image_host, uint64_t capacity, uint64_t* image_bytes,
+                                    kiss_b200_timings* t, double* fm_seconds);
+int kiss_b200_fmindex_build_file_u32(kiss_b200_ctx* ctx, const uint8_t* file_host, uint64_t nbytes, uint32_t k, int algo,
+                                     uint32_t sa_intv, uint8_t* image_host, uint64_t capacity, uint64_t* image_bytes,
+                                     uint64_t* n_out, kiss_b200_timings* t, double* fm_seconds);
+int kiss_b200_fmindex_from_sa_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, const uint32_t* SA_dev,
+                                  uint32_t sa_intv, uint8_t* image_host, uint64_t capacity, uint64_t* image_bytes,
+                                  double* fm_seconds);
+
 /* ---- allocation-free ingest ---------------------------------------------------------------------
  * kiss_b200_ingest_noalloc_dev has NO COUNTERPART IN THE REFERENCE: it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
@@ -195,6 +224,13 @@ int kiss_b200_profile_read(kiss_b200_ctx* ctx, int idx, const char** name, doubl
 /* algorithmic bytes of the launches of class idx, where the launcher knows them (radix passes: keys and positions
  * read + written; tie-group classes: 16 B per LMS suffix in the groups refined); else 0 */
 int kiss_b200_profile_alg_bytes(kiss_b200_ctx* ctx, int idx, uint64_t* bytes);
+
+/* ---- result digest (parity at sizes where the array itself cannot be kept: SURVEY.md 8(c), tests/golden) -----------
+ * *out = sum over i < count of splitmix64((i << 32) | SA_dev[i]) mod 2^64: an order-sensitive checksum of a suffix array
+ * that is a plain sum, so one streaming pass computes it on the device.  tests/golden/full_size_golden.json holds the
+ * value for the REFERENCE's own suffix array (kiss1_suffix_array_dna, kiss1_core.hpp:229-268) of the BASELINE.json
+ * configurations; bench.py compares after every run, outside the timed region. */
+int kiss_b200_sa_checksum_dev(kiss_b200_ctx* ctx, const uint32_t* SA_dev, uint64_t count, uint64_t* out);
 
 /* ---- synthetic inputs ---------------------------------------------------------
  * Fill S_dev[0..n) with the counter-hash uniform stream `seed` (identical to tests/textgen.py uniform). */

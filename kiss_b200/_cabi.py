@@ -56,10 +56,17 @@ SIGNATURES = {
     "kiss_b200_lms_contexts_dev": (_int, [_vp, _vp, _u64, _vp]),
     "kiss_b200_suffix_sort_file_u32": (_int, [_vp, _vp, _u64, _u32, _int, _vp, _u64, C.POINTER(_u64), C.POINTER(Timings)]),
     "kiss_b200_ingest_dev": (_int, [_vp, _vp, _u64, _int, _vp, C.POINTER(_u64)]),
+    "kiss_b200_fmindex_image_bytes": (_u64, [_u64, _u32]),
+    "kiss_b200_fmindex_build_dna_u32": (_int, [_vp, _vp, _u64, _u32, _int, _u32, _vp, _u64, C.POINTER(_u64),
+                                               C.POINTER(Timings), C.POINTER(C.c_double)]),
+    "kiss_b200_fmindex_build_file_u32": (_int, [_vp, _vp, _u64, _u32, _int, _u32, _vp, _u64, C.POINTER(_u64),
+                                                C.POINTER(_u64), C.POINTER(Timings), C.POINTER(C.c_double)]),
+    "kiss_b200_fmindex_from_sa_dev": (_int, [_vp, _vp, _u64, _vp, _u32, _vp, _u64, C.POINTER(_u64), C.POINTER(C.c_double)]),
     "kiss_b200_ingest_noalloc_dev": (_int, [_vp, _vp, _u64, _int, _vp, C.POINTER(_u64)]),
     "kiss_b200_profile_enable": (_int, [_vp, _int]),
     "kiss_b200_profile_read": (_int, [_vp, _int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(_u64)]),
     "kiss_b200_profile_alg_bytes": (_int, [_vp, _int, C.POINTER(_u64)]),
+    "kiss_b200_sa_checksum_dev": (_int, [_vp, _vp, _u64, C.POINTER(_u64)]),
     "kiss_b200_synth_uniform_dev": (_int, [_vp, _vp, _u64, _u64]),
 }
 

@@ -3,6 +3,7 @@
 // Driver = kiss1_suffix_array_dna (kiss1_core.hpp:229-268): get_lms -> lms_suffix_direct_sort_dna ->
 // put_lms_suffix -> induced_sort, each stage a set of kernels on one stream.  There is no CPU path: every
 // entry either runs the kernels or returns an error code.
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -777,6 +778,142 @@ void run_host(kiss_b200_ctx* c, const u8* S_host, u64 n, u32 k, int algo, u32* o
   if (m_out) *m_out = m;
 }
 
+// ---- FM-index image (fmindex.cu): the bytes FMIndex<SA_INTV, uint32_t, Sorter>{.LOOKUP_LEN = 0}::save writes
+// (fm_index.hpp:591-617; Serializer::save, serializer.hpp:95-112: element count as size_t, then the raw bytes)
+struct FmLayout {
+  u64 N, n1, n2, nb, nsa, b_words;
+  u64 o_bwt, o_occ1, o_occ2, o_sa, o_lookup, o_b, o_bocc, total;  // offsets of the DATA of each section (its count sits 8 bytes before)
+  u64 by_bwt, by_occ1, by_occ2, by_sa, by_b, by_bocc;
+};
+FmLayout fm_layout(u64 n, u32 intv) {
+  FmLayout L{};
+  L.N = n + 1;
+  L.n1 = L.N / 256 + 1; L.n2 = L.N / 16 + 1; L.nb = L.N / 64 + 1;
+  L.nsa = intv == 1 ? L.N : (L.N + intv - 1) / intv;
+  L.b_words = (L.N + 63) / 64;
+  L.by_bwt = (L.N + 3) / 4; L.by_occ1 = 16 * L.n1; L.by_occ2 = 4 * L.n2; L.by_sa = 4 * L.nsa;
+  L.by_b = 8 * L.b_words; L.by_bocc = 4 * L.nb;
+  u64 off = 20;  // cnt_[4], pri_
+  L.o_bwt = off + 8; off = L.o_bwt + L.by_bwt;
+  L.o_occ1 = off + 8; off = L.o_occ1 + L.by_occ1;
+  L.o_occ2 = off + 8; off = L.o_occ2 + L.by_occ2;
+  L.o_sa = off + 8; off = L.o_sa + L.by_sa;
+  L.o_lookup = off + 8; off = L.o_lookup + 8;
+  if (intv != 1) {
+    L.o_b = off + 8; off = L.o_b + L.by_b;
+    L.o_bocc = off + 8; off = L.o_bocc + L.by_bocc;
+  }
+  L.total = off;
+  return L;
+}
+
+void put_u64(u8* p, u64 v) { memcpy(p, &v, 8); }
+
+// T = packed text (may be null when n == 0), dSA = the n + 1 suffix array entries on the device; writes the image
+void do_fmindex(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const u32* dSA, u32 intv, u8* image, float* ms) {
+  cudaStream_t st = c->st;
+  const FmLayout L = fm_layout(n, intv);
+  CK(cudaEventRecord(c->ev[7], st));
+  u32* bwt32 = pool.alloc<u32>((L.N + 15) / 16 + 4);
+  const u64 n1p = (L.n1 + 3) & ~3ull;  // plane stride: the scan reads 16 bytes at a time
+  u32* tot = pool.alloc<u32>(4 * n1p);
+  u8* occ2 = pool.alloc<u8>(4 * L.n2);
+  u32* occ1 = pool.alloc<u32>(4 * L.n1);
+  u32* totals = pool.alloc<u32>(8);  // [0..3] symbol totals, [4] pri
+  u32* partials = pool.alloc<u32>(scan_partials_len(L.n1 > L.nb ? L.n1 : L.nb));
+  u32 *b32 = nullptr, *bocc = nullptr, *sa_out = nullptr;
+  CK(cudaMemsetAsync(tot, 0, 4 * n1p * sizeof(u32), st));
+  CK(cudaMemsetAsync(occ2, 0, 4 * L.n2, st));
+  if (intv != 1) {
+    b32 = pool.alloc<u32>(2 * L.b_words);
+    bocc = pool.alloc<u32>(L.nb);
+    sa_out = pool.alloc<u32>(L.nsa);
+    CK(cudaMemsetAsync(b32 + 2 * (L.b_words - 1), 0, 8, st));  // the last word may be written by half
+    CK(cudaMemsetAsync(bocc, 0, L.nb * sizeof(u32), st));
+  }
+  fm_scan(dSA, L.N, T, intv, bwt32, tot, n1p, occ2, L.n2, b32, bocc, totals + 4, st);
+  for (int s = 0; s < 4; s++) scan_excl_u32(tot + s * n1p, L.n1, partials, totals + s, st);
+  fm_occ1(tot, n1p, L.n1, occ1, st);
+  if (intv != 1) {
+    scan_excl_u32(bocc, L.nb, partials, nullptr, st);
+    fm_sample(dSA, L.N, intv, b32, bocc, sa_out, st);
+  }
+  CK(cudaEventRecord(c->ev[0], st));
+  u32 h[5];
+  CK(cudaMemcpyAsync(h, totals, 5 * sizeof(u32), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(image + L.o_bwt, bwt32, L.by_bwt, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(image + L.o_occ1, occ1, L.by_occ1, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(image + L.o_occ2, occ2, L.by_occ2, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(image + L.o_sa, intv == 1 ? dSA : sa_out, L.by_sa, cudaMemcpyDeviceToHost, st));
+  if (intv != 1) {
+    CK(cudaMemcpyAsync(image + L.o_b, b32, L.by_b, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(image + L.o_bocc, bocc, L.by_bocc, cudaMemcpyDeviceToHost, st));
+  }
+  CK(cudaStreamSynchronize(st));
+  // cnt_[c] = 1 + number of symbols smaller than c (fm_index.hpp:305-309); pri_; the section counts; lookup_ = {0, N}
+  u32 cnt[4], acc = 1;
+  for (int s = 0; s < 4; s++) { cnt[s] = acc; acc += h[s]; }
+  memcpy(image, cnt, 16);
+  memcpy(image + 16, &h[4], 4);
+  put_u64(image + L.o_bwt - 8, L.N);
+  put_u64(image + L.o_occ1 - 8, L.n1);
+  put_u64(image + L.o_occ2 - 8, L.n2);
+  put_u64(image + L.o_sa - 8, L.nsa);
+  put_u64(image + L.o_lookup - 8, 2);
+  const u32 lookup[2] = {0u, (u32)L.N};
+  memcpy(image + L.o_lookup, lookup, 8);
+  if (intv != 1) {
+    put_u64(image + L.o_b - 8, L.N);
+    put_u64(image + L.o_bocc - 8, L.nb);
+  }
+  if (ms) CK(cudaEventElapsedTime(ms, c->ev[7], c->ev[0]));
+}
+
+// host text (codes or file bytes) -> suffix array on the device -> FM-index image on the host
+void run_fm_host(kiss_b200_ctx* c, const u8* S_host, u64 n, int input, u32 k, int algo, u32 intv, u8* image, u64 capacity,
+                 uint64_t* image_bytes, uint64_t* n_text, kiss_b200_timings* t, double* fm_seconds) {
+  cudaStream_t st = c->st;
+  begin_call(c);
+  Pool pool(st, &c->arena);
+  u8* dS = pool.alloc<u8>(n + 16);
+  const auto w0 = std::chrono::steady_clock::now();
+  if (n) CK(cudaMemcpyAsync(dS, S_host, n, cudaMemcpyHostToDevice, st));
+  if (input == IN_FILE) {
+    u8* dC = pool.alloc<u8>(n + 16);
+    const bool fasta = n && S_host[0] == '>';
+    n = do_ingest(c, pool, dS, n, fasta, dC);
+    pool.release(dS);
+    dS = dC;
+    if (n + 1 >= 0xFFFFFFFFull) throw CudaError(KISS_B200_ERR_TOO_LARGE, "text too large for 32-bit suffix indices");
+  }
+  if (n_text) *n_text = n;
+  const FmLayout L = fm_layout(n, intv);
+  *image_bytes = L.total;
+  if (L.total > capacity) throw CudaError(KISS_B200_ERR_ARG, "image buffer smaller than kiss_b200_fmindex_image_bytes(n, sa_intv)");
+  CK(cudaStreamSynchronize(st));
+  const double h2d = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
+  u32* dSA = pool.alloc<u32>(n + 1);
+  kiss_b200_timings tt;
+  memset(&tt, 0, sizeof(tt));
+  const u64* T = nullptr;
+  if (n) {
+    run_pipeline(c, dS, n, k, algo, dSA, STOP_FULL, &tt);
+    T = c->prep.T;
+  } else {
+    CK(cudaMemsetAsync(dSA, 0, sizeof(u32), st));
+    tt.m = 1;
+  }
+  pool.release(dS);
+  float ms = 0;
+  const auto w1 = std::chrono::steady_clock::now();
+  do_fmindex(c, pool, T, n, dSA, intv, image, &ms);
+  tt.h2d = h2d;
+  tt.d2h = std::chrono::duration<double>(std::chrono::steady_clock::now() - w1).count() - ms * 1e-3;
+  if (t) *t = tt;
+  if (fm_seconds) *fm_seconds = ms * 1e-3;
+  free_prepared(c);
+}
+
 }  // namespace
 
 // ---- accessors for the entry points that live in other files (noalloc.cu)
@@ -1140,6 +1277,66 @@ int kiss_b200_profile_alg_bytes(kiss_b200_ctx* c, int idx, uint64_t* bytes) {
   if (!c || !bytes || idx < 0 || idx >= PK_COUNT) return KISS_B200_ERR_ARG;
   *bytes = c->prof.bytes[idx];
   return KISS_B200_OK;
+}
+
+uint64_t kiss_b200_fmindex_image_bytes(uint64_t n, uint32_t sa_intv) { return sa_intv ? fm_layout(n, sa_intv).total : 0; }
+
+static int fm_args_ok(kiss_b200_ctx* c, const void* in, uint64_t n, int algo, uint32_t sa_intv, const void* image,
+                      const uint64_t* image_bytes) {
+  if (!c || !image || !image_bytes || (n && !in) || (algo != 0 && algo != 1) || sa_intv == 0) {
+    g_last_error = "bad argument";
+    return KISS_B200_ERR_ARG;
+  }
+  return 0;
+}
+
+int kiss_b200_fmindex_build_dna_u32(kiss_b200_ctx* c, const uint8_t* S_host, uint64_t n, uint32_t k, int algo,
+                                    uint32_t sa_intv, uint8_t* image_host, uint64_t capacity, uint64_t* image_bytes,
+                                    kiss_b200_timings* t, double* fm_seconds) {
+  if (int r = fm_args_ok(c, S_host, n, algo, sa_intv, image_host, image_bytes)) return r;
+  if (int r = check_n(n)) return r;
+  return guarded(c, [&] {
+    run_fm_host(c, S_host, n, IN_CODES, k, algo, sa_intv, image_host, capacity, image_bytes, nullptr, t, fm_seconds);
+  });
+}
+
+int kiss_b200_fmindex_build_file_u32(kiss_b200_ctx* c, const uint8_t* file_host, uint64_t nbytes, uint32_t k, int algo,
+                                     uint32_t sa_intv, uint8_t* image_host, uint64_t capacity, uint64_t* image_bytes,
+                                     uint64_t* n_out, kiss_b200_timings* t, double* fm_seconds) {
+  if (int r = fm_args_ok(c, file_host, nbytes, algo, sa_intv, image_host, image_bytes)) return r;
+  return guarded(c, [&] {
+    run_fm_host(c, file_host, nbytes, IN_FILE, k, algo, sa_intv, image_host, capacity, image_bytes, n_out, t, fm_seconds);
+  });
+}
+
+int kiss_b200_fmindex_from_sa_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, const uint32_t* SA_dev,
+                                  uint32_t sa_intv, uint8_t* image_host, uint64_t capacity, uint64_t* image_bytes,
+                                  double* fm_seconds) {
+  if (int r = fm_args_ok(c, S_dev, n, 0, sa_intv, image_host, image_bytes)) return r;
+  if (!SA_dev || ((uintptr_t)S_dev & 15)) { g_last_error = "bad argument (SA_dev null or S_dev not 16-byte aligned)"; return KISS_B200_ERR_ARG; }
+  if (int r = check_n(n)) return r;
+  return guarded(c, [&] {
+    const FmLayout L = fm_layout(n, sa_intv);
+    *image_bytes = L.total;
+    if (L.total > capacity) throw CudaError(KISS_B200_ERR_ARG, "image buffer smaller than kiss_b200_fmindex_image_bytes(n, sa_intv)");
+    Pool pool(c->st, &c->arena);
+    u64* T = pool.alloc<u64>(packed_words(n));
+    if (n) pack_codes(S_dev, n, T, c->st);
+    float ms = 0;
+    do_fmindex(c, pool, T, n, SA_dev, sa_intv, image_host, &ms);
+    if (fm_seconds) *fm_seconds = ms * 1e-3;
+  });
+}
+
+int kiss_b200_sa_checksum_dev(kiss_b200_ctx* c, const uint32_t* SA_dev, uint64_t count, uint64_t* out) {
+  if (!out || (count && !SA_dev)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  return guarded(c, [&] {
+    Pool pool(c->st, &c->arena);
+    u64* d = pool.alloc<u64>(1);
+    mixed_sum(SA_dev, count, d, c->st);
+    CK(cudaMemcpyAsync(out, d, sizeof(u64), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+  });
 }
 
 int kiss_b200_synth_uniform_dev(kiss_b200_ctx* c, uint8_t* S_dev, uint64_t n, uint64_t seed) {

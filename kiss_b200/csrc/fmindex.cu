@@ -1,0 +1,114 @@
+// fmindex.cu — the step after the path: BWT, occurrence tables and sampled suffix array from
+// the suffix array, on the device, so that the 4(n+1)-byte array never crosses PCIe (1.75 bytes per suffix do instead).
+//
+// Replaces FMIndex::build_occ / build_bwt / build_sa (include/biovoltron/algo/align/exact_match/fm_index.hpp:278-307,
+// 311-328, 332-372) as instantiated by the reference's fmindex_build command (include/command/fmindex_build.hpp:27-34:
+// FMIndex<SA_INTV = 4, uint32_t, KISS1Sorter<uint32_t>>{.LOOKUP_LEN = 0}).  With N = n + 1 entries:
+//   bwt_    DibitVector: entry i = S[SA[i] - 1] (0 where SA[i] == 0, whose index is pri_), element e in byte e / 4 at
+//           bits 2 (e % 4)  (xbit_vector.hpp:21-27)
+//   occ_    first: per 256 entries the exclusive prefix of the symbol counts (u32 x 4, N / 256 + 1 rows);
+//           second: per 16 entries the counts since the row's 256-boundary (u8 x 4, N / 16 + 1 rows); the entry with
+//           SA == 0 counts for nothing (:295-297); cnt_[c] = 1 + number of symbols smaller than c
+//   b_      one bit per entry: SA[i] % SA_INTV == 0; b_occ_: per 64 entries the exclusive prefix of its popcounts
+//   sa_     the entries with SA[i] % SA_INTV == 0, in suffix-array order
+// One pass over SA (k_fm_scan: one block = one 256-entry row; the only random access is the text gather, one base per
+// entry), three small scans, one more pass over SA for the compaction (k_fm_sample).  Algorithmic bytes: 2 x 4N (SA
+// reads) + N / 4 (gathered text, ideal) + 1.75 N written.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace kiss {
+
+#define FM_ROW 256u
+
+__global__ void __launch_bounds__(FM_ROW) k_fm_scan(const u32* __restrict__ SA, u64 N, const u64* __restrict__ T, u32 intv,
+                                                   u32* __restrict__ bwt32, u32* __restrict__ tot /* [4][n1: the plane stride] */, u64 n1,
+                                                   u8* __restrict__ occ2, u64 n2, u32* __restrict__ b32,
+                                                   u32* __restrict__ bocc_raw, u32* __restrict__ pri) {
+  __shared__ u32 s_seg[16][4];  // counts per 16-entry segment and symbol
+  __shared__ u32 s_hit[8];      // sampled entries per warp
+  const u32 t = threadIdx.x, lane = t & 31u, w = t >> 5;
+  const u64 i = (u64)blockIdx.x * FM_ROW + t;
+  const bool valid = i < N;
+  const u32 v = valid ? SA[i] : 1u;
+  const bool counted = valid && v != 0;
+  const u32 c = counted ? base_at(T, (u64)v - 1) : 0u;
+  if (valid && v == 0) *pri = (u32)i;
+  // bwt: 4 entries per byte, 16 per word; lanes 0 and 16 of a warp store one word each
+  u32 x = c << (2 * (lane & 15u));
+  x |= __shfl_xor_sync(0xffffffffu, x, 1);
+  x |= __shfl_xor_sync(0xffffffffu, x, 2);
+  x |= __shfl_xor_sync(0xffffffffu, x, 4);
+  x |= __shfl_xor_sync(0xffffffffu, x, 8);
+  if ((lane & 15u) == 0 && (i & ~15ull) < N) bwt32[i >> 4] = x;
+  // symbol counts per half warp = per 16-entry segment
+#pragma unroll
+  for (u32 s = 0; s < 4; s++) {
+    const u32 m = __ballot_sync(0xffffffffu, counted && c == s);
+    if (lane == 0) {
+      s_seg[2 * w][s] = (u32)__popc(m & 0xFFFFu);
+      s_seg[2 * w + 1][s] = (u32)__popc(m >> 16);
+    }
+  }
+  // sampled-entry bits; b_occ raw = popcount per 64 entries = per warp pair
+  if (b32) {
+    const u32 hit = __ballot_sync(0xffffffffu, valid && v % intv == 0);
+    if (lane == 0) {
+      if ((i & ~31ull) < N) b32[i >> 5] = hit;
+      s_hit[w] = (u32)__popc(hit);
+    }
+  }
+  __syncthreads();
+  if (b32 && t < 4) {
+    const u64 j = (u64)blockIdx.x * 4 + t;  // 64-entry block
+    if (j * 64 < N) bocc_raw[j] = s_hit[2 * t] + s_hit[2 * t + 1];
+  }
+  if (t < 4) {
+    u32 run = 0;
+    for (u32 s = 0; s < 16; s++) {
+      const u64 j = (u64)blockIdx.x * 16 + s;
+      const u32 cur = s_seg[s][t];
+      if (j < n2) occ2[4 * j + t] = (u8)run;
+      run += cur;
+    }
+    tot[(u64)t * n1 + blockIdx.x] = run;
+  }
+}
+
+// occ1 rows from the four scanned planes
+__global__ void k_fm_occ1(const u32* __restrict__ tot, u64 stride, u64 n1, u32* __restrict__ occ1) {
+  const u64 b = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= n1) return;
+  *reinterpret_cast<uint4*>(occ1 + 4 * b) = make_uint4(tot[b], tot[stride + b], tot[2 * stride + b], tot[3 * stride + b]);
+}
+
+// sa_[b_occ[i / 64] + (sampled entries of the 64-block before i)] = SA[i] for the sampled entries
+__global__ void __launch_bounds__(256) k_fm_sample(const u32* __restrict__ SA, u64 N, u32 intv, const u32* __restrict__ b32,
+                                                  const u32* __restrict__ bocc, u32* __restrict__ sa_out) {
+  const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  const u32 v = SA[i];
+  if (v % intv != 0) return;
+  const u64 w0 = (i >> 6) * 2;  // first 32-bit word of the 64-entry block
+  const u32 bit = (u32)(i & 63);
+  u32 before = bit >= 32 ? (u32)__popc(b32[w0]) + (u32)__popc(b32[w0 + 1] & ((1u << (bit - 32)) - 1u))
+                         : (u32)__popc(b32[w0] & ((1u << bit) - 1u));
+  sa_out[bocc[i >> 6] + before] = v;
+}
+
+void fm_scan(const u32* SA, u64 N, const u64* T, u32 intv, u32* bwt32, u32* tot, u64 n1, u8* occ2, u64 n2, u32* b32,
+             u32* bocc_raw, u32* pri, cudaStream_t st) {
+  const u64 rows = (N + FM_ROW - 1) / FM_ROW;
+  k_fm_scan<<<(unsigned)rows, FM_ROW, 0, st>>>(SA, N, T, intv, bwt32, tot, n1, occ2, n2, b32, bocc_raw, pri);
+  CK_LAUNCH(); g_launches++;
+}
+void fm_occ1(const u32* tot, u64 stride, u64 n1, u32* occ1, cudaStream_t st) {
+  k_fm_occ1<<<(unsigned)((n1 + 255) / 256), 256, 0, st>>>(tot, stride, n1, occ1);
+  CK_LAUNCH(); g_launches++;
+}
+void fm_sample(const u32* SA, u64 N, u32 intv, const u32* b32, const u32* bocc, u32* sa_out, cudaStream_t st) {
+  k_fm_sample<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(SA, N, intv, b32, bocc, sa_out);
+  CK_LAUNCH(); g_launches++;
+}
+
+}  // namespace kiss

@@ -83,6 +83,8 @@ u64 packed_words(u64 n);  // words in the packed text including padding
 void pack_codes(const u8* S, u64 n, u64* T, cudaStream_t st);
 void ascii_to_codes(const u8* ascii, u64 n, u8* S, cudaStream_t st);
 void synth_uniform(u8* S, u64 n, u64 seed, cudaStream_t st);
+// *out_dev = sum_i splitmix64((i << 32) | a[i]) mod 2^64 (order-sensitive checksum of a suffix array)
+void mixed_sum(const u32* a, u64 count, u64* out_dev, cudaStream_t st);
 
 // ---------------------------------------------------------------- ingest.cu
 // file bytes -> codes with the reference's read_sequence semantics (FASTA headers and newlines dropped, see ingest.cu)
@@ -167,6 +169,15 @@ void dest_by_splitters(const u32* key, u32 N, const u32* spl, u32 nspl, u32* des
 void shorts_order(const u32* shorts, u32 ns, SortParams sp, u32* rank0, u32* sorted_shorts, cudaStream_t st);
 void shorts_insertions(const u32* sorted_shorts, u32 ns, const u32* longs, u32 nl, SortParams sp, u32* ins,
                        cudaStream_t st);
+
+// ---------------------------------------------------------------- fmindex.cu
+// N = n + 1 suffix array entries.  bwt32: ceil(N / 16) words; tot: 4 planes (stride n1 >= N / 256 + 1, a multiple of 4) of block counts (zeroed by the
+// caller; scanned per plane afterwards); occ2: n2 = N / 16 + 1 rows of 4 bytes (zeroed by the caller); b32 (nullable:
+// SA_INTV = 1): ceil(N / 32) words; bocc_raw: N / 64 + 1 counts (zeroed by the caller); pri: one word
+void fm_scan(const u32* SA, u64 N, const u64* T, u32 intv, u32* bwt32, u32* tot, u64 n1, u8* occ2, u64 n2, u32* b32,
+             u32* bocc_raw, u32* pri, cudaStream_t st);
+void fm_occ1(const u32* tot_scanned, u64 stride, u64 n1, u32* occ1, cudaStream_t st);
+void fm_sample(const u32* SA, u64 N, u32 intv, const u32* b32, const u32* bocc_scanned, u32* sa_out, cudaStream_t st);
 
 // ---------------------------------------------------------------- induce.cu
 struct Buckets {

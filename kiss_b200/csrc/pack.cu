@@ -111,4 +111,23 @@ void synth_uniform(u8* S, u64 n, u64 seed, cudaStream_t st) {
   g_launches++;
 }
 
+// Position-mixed checksum of an array of suffix indices: sum_i splitmix64((i << 32) | a[i]) mod 2^64 — sensitive to
+// the order of the entries, yet a plain sum, so it is one streaming pass (tests/golden/make_full_size_golden.py computes
+// the same number from the reference's array).  *out must be zeroed by the caller.
+__global__ void __launch_bounds__(256) k_mixed_sum(const u32* __restrict__ a, u64 count, u64* __restrict__ out) {
+  u64 acc = 0;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (u64)gridDim.x * blockDim.x)
+    acc += splitmix64((i << 32) | (u64)a[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31u) == 0) atomicAdd((unsigned long long*)out, (unsigned long long)acc);
+}
+void mixed_sum(const u32* a, u64 count, u64* out_dev, cudaStream_t st) {
+  CK(cudaMemsetAsync(out_dev, 0, sizeof(u64), st));
+  if (!count) return;
+  k_mixed_sum<<<148 * 8, 256, 0, st>>>(a, count, out_dev);
+  CK_LAUNCH();
+  g_launches++;
+}
+
 }  // namespace kiss

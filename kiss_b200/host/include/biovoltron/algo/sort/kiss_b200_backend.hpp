@@ -63,10 +63,29 @@ inline kiss_b200_timings& last_timings() {
   return t;
 }
 
-// kiss1_suffix_array_dna / kiss2_suffix_array_dna (kiss1_core.hpp:229-235, kiss2_core.hpp:888-896)
+// kiss1_suffix_array_dna / kiss2_suffix_array_dna (kiss1_core.hpp:229-235, kiss2_core.hpp:888-896); `codes` = n bytes of
+// any one-byte character type (the reference's callers pass uint8_t, int8_t or char: only the low two bits are read)
+inline void suffix_array_dna(const void* codes, std::size_t n, vector<std::uint32_t>& SA, std::uint32_t k, int algo) {
+  SA.resize(n + 1);
+  raise(kiss_b200_suffix_sort_dna_u32(context(), static_cast<const std::uint8_t*>(codes), n, k, algo, SA.data(),
+                                      &last_timings()));
+}
 inline void suffix_array_dna(const vector<std::uint8_t>& S, vector<std::uint32_t>& SA, std::uint32_t k, int algo) {
-  SA.resize(S.size() + 1);
-  raise(kiss_b200_suffix_sort_dna_u32(context(), S.data(), S.size(), k, algo, SA.data(), &last_timings()));
+  suffix_array_dna(S.data(), S.size(), SA, k, algo);
+}
+
+// fmindex_build (include/command/fmindex_build.hpp:27-34): the bytes of a FASTA / text file -> the bytes of the .fmi file
+// FMIndex<sa_intv, uint32_t, Sorter>{.LOOKUP_LEN = 0}::save writes (fm_index.hpp:591-617); the suffix array stays on the
+// device.  Returns the text length.
+inline std::uint64_t fmindex_image_file(const std::vector<std::uint8_t>& file, std::vector<std::uint8_t>& image,
+                                        std::uint32_t k = 32u, int algo = KISS_B200_PARALLEL_SORTING,
+                                        std::uint32_t sa_intv = 4u, double* fm_seconds = nullptr) {
+  image.resize(kiss_b200_fmindex_image_bytes(file.size(), sa_intv));
+  std::uint64_t n = 0, bytes = 0;
+  raise(kiss_b200_fmindex_build_file_u32(context(), file.data(), file.size(), k, algo, sa_intv, image.data(), image.size(),
+                                         &bytes, &n, &last_timings(), fm_seconds));
+  image.resize(bytes);
+  return n;
 }
 
 // read_sequence (include/utils/io.hpp:6-18) + `% 4` + the sorter in one call: `file` holds the bytes of a FASTA or
@@ -87,13 +106,13 @@ inline std::uint64_t suffix_array_file(const std::vector<std::uint8_t>& file, ve
 template<typename char_type, typename size_type>
 void kiss1_suffix_array_dna(const vector<char_type>& S, vector<size_type>& SA, size_type k, std::size_t /*num_threads*/) {
   static_assert(sizeof(char_type) == 1 && sizeof(size_type) == 4, "the B200 path implements <uint8_t, uint32_t>");
-  b200::suffix_array_dna(reinterpret_cast<const vector<std::uint8_t>&>(S), SA, k, KISS_B200_PARALLEL_SORTING);
+  b200::suffix_array_dna(S.data(), S.size(), SA, k, KISS_B200_PARALLEL_SORTING);
 }
 
 template<typename char_type, typename size_type>
 void kiss2_suffix_array_dna(const vector<char_type>& S, vector<size_type>& SA, size_type k, std::size_t /*num_threads*/) {
   static_assert(sizeof(char_type) == 1 && sizeof(size_type) == 4, "the B200 path implements <uint8_t, uint32_t>");
-  b200::suffix_array_dna(reinterpret_cast<const vector<std::uint8_t>&>(S), SA, k, KISS_B200_PREFIX_DOUBLING);
+  b200::suffix_array_dna(S.data(), S.size(), SA, k, KISS_B200_PREFIX_DOUBLING);
 }
 
 }  // namespace kiss

@@ -5,7 +5,9 @@
 // default 256, `-k -1` = unbounded, -s/--sorting-algorithm PARALLEL_SORTING|PREFIX_DOUBLING case-insensitive,
 // one positional file), include/command/suffix_sort.hpp:21-62 (the command) and include/utils/io.hpp:6-18
 // (FASTA when the first byte is '>', else every line is sequence).  Boost.program_options is not available in
-// this image, so the parser is hand-written; the fmindex_* sub-commands are out of scope.
+// this image, so the parser is hand-written.  `fmindex_build` (include/command/fmindex_build.hpp:14-36) is built too: it
+// writes <file>.fmi, byte-compatible with the reference's FMIndex::save, without moving the suffix array off the device;
+// `fmindex_query` stays with the reference (it loads that file).
 // Extra opt-in flags (defaults unchanged): --gpu IDX, --out FILE (raw little-endian uint32 suffix array —
 // the reference never writes it, suffix_sort.hpp:57-61).
 #include <algorithm>
@@ -44,7 +46,9 @@ void usage(std::ostream& os) {
         "                                        first k characters. Using -1 indicates unbounded sorting.\n"
         "  -s [ --sorting-algorithm ] ALGO (=PARALLEL_SORTING)\n"
         "                                        PARALLEL_SORTING or PREFIX_DOUBLING\n"
-        "  --out FILE                            write the suffix array (uint32 little endian)\n";
+        "  --out FILE                            write the suffix array (uint32 little endian)\n\n"
+        "./kISS fmindex_build <FASTA filename/Text filename>\n"
+        "                                        writes <filename>.fmi (FM-index, SA sampling interval 4, k = 32)\n";
 }
 
 std::string stamp() {
@@ -207,6 +211,36 @@ int suffix_sort_main(const Args& a) {
   return 0;
 }
 
+// fmindex_build_main (include/command/fmindex_build.hpp:14-36): read_sequence, `% 4`, FMIndex<4, uint32_t,
+// KISS1Sorter<uint32_t>>{.LOOKUP_LEN = 0}.build (k = 32, fm_index.hpp:385-386), save to <fasta>.fmi
+int fmindex_build_main(const Args& a) {
+  if (a.generic) throw std::invalid_argument("Generic sorting and indexing are currently not supported.");
+  if (a.file.empty()) throw std::invalid_argument("the option '--fasta' is required but missing");
+  std::ifstream fa(a.file, std::ios::binary);
+  if (!fa) throw std::invalid_argument("cannot open " + a.file);
+  biovoltron::kiss::b200::device_index() = a.gpu;
+  fa.seekg(0, std::ios::end);
+  const std::streamoff bytes = fa.tellg();
+  fa.seekg(0, std::ios::beg);
+  std::vector<std::uint8_t> file((std::size_t)(bytes > 0 ? bytes : 0)), image;
+  if (!file.empty()) fa.read(reinterpret_cast<char*>(file.data()), (std::streamsize)file.size());
+  if (!fa && !file.empty()) throw std::runtime_error("cannot read " + a.file);
+  double fm = 0;
+  auto t0 = std::chrono::steady_clock::now();
+  const std::uint64_t n = biovoltron::kiss::b200::fmindex_image_file(file, image, 32u, KISS_B200_PARALLEL_SORTING, 4u, &fm);
+  const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  std::ofstream os(a.file + ".fmi", std::ios::binary);
+  os.write(reinterpret_cast<const char*>(image.data()), (std::streamsize)image.size());
+  if (!os) throw std::runtime_error("cannot write " + a.file + ".fmi");
+  if (a.verbose) {
+    const auto& t = biovoltron::kiss::b200::last_timings();
+    log_line("debug", "kiss_b200", "suffix array (device) elapsed " + std::to_string(t.total_device));
+    log_line("debug", "kiss_b200", "bwt + occ + sampled sa (device) elapsed " + std::to_string(fm));
+  }
+  log_line("info", "fmindex_build", "n = " + std::to_string(n) + ", " + std::to_string(image.size()) + " bytes, index building elapsed " + std::to_string(sec));
+  return 0;
+}
+
 }  // namespace
 
 int main(int argc, char** argv) {
@@ -228,8 +262,9 @@ int main(int argc, char** argv) {
   }
   try {
     if (a.command == "suffix_sort") return suffix_sort_main(a);
-    if (a.command == "fmindex_build" || a.command == "fmindex_query")
-      throw std::invalid_argument("command '" + a.command + "' is outside the B200 suffix_sort path");
+    if (a.command == "fmindex_build") return fmindex_build_main(a);
+    if (a.command == "fmindex_query")
+      throw std::invalid_argument("command 'fmindex_query' is outside the B200 path (the reference's own loads the .fmi written here)");
     throw std::invalid_argument("the argument ('" + a.command + "') for option '--command' is invalid");  // options.hpp:298-299
   } catch (const std::exception& e) {
     std::cerr << "terminate called after throwing: " << e.what() << "\n";

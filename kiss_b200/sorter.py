@@ -91,6 +91,40 @@ class Context:
         check(lib().kiss_b200_ingest_dev(self._h, file_ptr, nbytes, 1 if fasta else 0, codes_ptr, C.byref(n)))
         return n.value
 
+    # ---- FM-index (the step after the path): the reference's .fmi image, the suffix array never leaves the device
+    def fmindex_build(self, S, k=32, algo=PARALLEL_SORTING, sa_intv=4, out=None):
+        """FMIndex<sa_intv, uint32_t, Sorter>{.LOOKUP_LEN = 0}.build(S) + save (fm_index.hpp:380-411, 591-617): the
+        bytes of the .fmi file (numpy uint8; `out`: a preallocated, e.g. pinned, buffer)"""
+        S = _codes(S)
+        need = lib().kiss_b200_fmindex_image_bytes(S.size, sa_intv)
+        img = np.empty(need, np.uint8) if out is None else out
+        nb, t, fm = C.c_uint64(), Timings(), C.c_double()
+        check(lib().kiss_b200_fmindex_build_dna_u32(self._h, S.ctypes.data, S.size, k & 0xFFFFFFFF, algo, sa_intv,
+                                                    img.ctypes.data, img.size, C.byref(nb), C.byref(t), C.byref(fm)))
+        self.last_timings = dict(t.as_dict(), fmindex=fm.value)
+        return img[:nb.value]
+
+    def fmindex_build_file(self, data, k=32, algo=PARALLEL_SORTING, sa_intv=4):
+        """`data` = the bytes of a FASTA / text file: (.fmi image, text length)"""
+        b = np.frombuffer(data, dtype=np.uint8) if isinstance(data, (bytes, bytearray, memoryview)) else data
+        b = np.ascontiguousarray(b, dtype=np.uint8)
+        img = np.empty(lib().kiss_b200_fmindex_image_bytes(b.size, sa_intv), np.uint8)
+        nb, n, t, fm = C.c_uint64(), C.c_uint64(), Timings(), C.c_double()
+        check(lib().kiss_b200_fmindex_build_file_u32(self._h, b.ctypes.data, b.size, k & 0xFFFFFFFF, algo, sa_intv,
+                                                     img.ctypes.data, img.size, C.byref(nb), C.byref(n), C.byref(t),
+                                                     C.byref(fm)))
+        self.last_timings = dict(t.as_dict(), fmindex=fm.value)
+        return img[:nb.value].copy(), n.value
+
+    def fmindex_from_sa_dev(self, S_ptr, n, SA_ptr, sa_intv=4, out=None):
+        need = lib().kiss_b200_fmindex_image_bytes(n, sa_intv)
+        img = np.empty(need, np.uint8) if out is None else out
+        nb, fm = C.c_uint64(), C.c_double()
+        check(lib().kiss_b200_fmindex_from_sa_dev(self._h, S_ptr, n, SA_ptr, sa_intv, img.ctypes.data, img.size,
+                                                  C.byref(nb), C.byref(fm)))
+        self.last_fm_seconds = fm.value
+        return img[:nb.value]
+
     def ingest_noalloc_dev(self, file_ptr, nbytes, fasta, codes_ptr):
         """ingest_dev with its scratch in a fixed __device__ array: no allocation, at most NOALLOC_MAX_BYTES"""
         n = C.c_uint64()
@@ -194,6 +228,12 @@ class Context:
                 out[name.value.decode()] = units.value
             i += 1
         return out
+
+    def sa_checksum_dev(self, SA_ptr, count):
+        """order-sensitive checksum of a device suffix array (sum of splitmix64((i << 32) | SA[i]) mod 2^64)"""
+        out = C.c_uint64()
+        check(lib().kiss_b200_sa_checksum_dev(self._h, SA_ptr, count, C.byref(out)))
+        return out.value
 
     def synth_uniform_dev(self, S_ptr, n, seed):
         check(lib().kiss_b200_synth_uniform_dev(self._h, S_ptr, n, seed))

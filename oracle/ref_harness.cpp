@@ -13,8 +13,10 @@
 #define SPDLOG_ACTIVE_LEVEL SPDLOG_LEVEL_OFF
 #include <biovoltron/algo/sort/kiss1_sorter.hpp>
 #include <biovoltron/algo/sort/kiss2_sorter.hpp>
+#include <biovoltron/algo/align/exact_match/fm_index.hpp>
 #include <biovoltron/file_io/fasta.hpp>
 #include <utils/io.hpp>
+#include <fstream>
 #include <sstream>
 
 #include <chrono>
@@ -155,6 +157,18 @@ uint64_t ref_read_sequence(const uint8_t* file, uint64_t nbytes, uint8_t* out) {
   auto seq = read_sequence(fin);
   uint64_t n = seq.size();
   for (uint64_t i = 0; i < n; i++) out[i] = (uint8_t)(seq[i] % 4);
+  return n;
+}
+
+// The reference's fmindex_build command (include/command/fmindex_build.hpp:27-34) on a code text: FMIndex<4, uint32_t,
+// KISS1Sorter<uint32_t>>{.LOOKUP_LEN = 0}, build() (fm_index.hpp:380-388: suffix array with k = 32, then build_occ /
+// build_bwt / build_sa / build_lookup) and save() (:591-617) into the file `path`.  Returns the text length.
+uint64_t ref_fmindex_build_file(const uint8_t* S_, uint64_t n, const char* path) {
+  biovoltron::istring seq(reinterpret_cast<const biovoltron::ichar*>(S_), n);
+  auto fmi = biovoltron::FMIndex<4, uint32_t, biovoltron::KISS1Sorter<uint32_t>>{.LOOKUP_LEN = 0};
+  fmi.build(seq);
+  auto fout = std::ofstream{path};
+  fmi.save(fout);
   return n;
 }
 

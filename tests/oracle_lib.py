@@ -78,6 +78,9 @@ def ref():
         if hasattr(L, "ref_kiss2_sorted_lms"):
             L.ref_kiss2_sorted_lms.restype = _u32
             L.ref_kiss2_sorted_lms.argtypes = [_vp, _u64, _u32, _u64, _vp]
+        if hasattr(L, "ref_fmindex_build_file"):
+            L.ref_fmindex_build_file.restype = _u64
+            L.ref_fmindex_build_file.argtypes = [_vp, _u64, C.c_char_p]
         if hasattr(L, "ref_read_sequence"):
             L.ref_read_sequence.restype = _u64
             L.ref_read_sequence.argtypes = [_vp, _u64, _vp]
@@ -178,6 +181,16 @@ def naive_suffix_array(S):
     S = bytes(_codes(S).tolist())
     n = len(S)
     return np.array([n] + sorted(range(n), key=lambda i: S[i:]), np.uint32)
+
+
+def ref_fmindex_image(S):
+    """the bytes of the .fmi file the reference's fmindex_build writes for the code text S (FMIndex<4, u32, KISS1Sorter>
+    {.LOOKUP_LEN = 0}: build with k = 32, save; include/command/fmindex_build.hpp:27-34)"""
+    import tempfile
+    S = _codes(S)
+    with tempfile.NamedTemporaryFile(suffix=".fmi") as f:
+        ref().ref_fmindex_build_file(_ptr(S), S.size, f.name.encode())
+        return open(f.name, "rb").read()
 
 
 def ref_read_sequence(data):

@@ -83,7 +83,8 @@ def test_empty_file(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["fasta_80_crlf", "blank_lines", "gt_inside_line", "long_header", "text_mode_gt_line"])
+@pytest.mark.parametrize("name", ["fasta_80_crlf", "blank_lines", "gt_inside_line", "long_header", "text_mode_gt_line",
+                                  "two_headers_in_a_row", "header_run_across_chunks", "long_header_run_odd"])
 def test_device_ingest_equals_host_ingest(tmp_path, name):
     """default = the file's bytes are stripped / encoded on the device (read_sequence semantics, io.hpp:6-18);
     --host-ingest = the serial getline loop on the host: same n, same suffix array"""
@@ -100,3 +101,26 @@ def test_device_ingest_equals_host_ingest(tmp_path, name):
         outs.append((n, np.fromfile(out, dtype=np.uint32)))
     assert outs[0][0] == outs[1][0] and np.array_equal(outs[0][1], outs[1][1])
     assert outs[0][1].size == outs[0][0] + 1
+
+
+@pytest.mark.gpu
+def test_fmindex_build_writes_the_reference_fmi_file(tmp_path):
+    """`kISS fmindex_build <file>` (include/command/fmindex_build.hpp:14-36) writes <file>.fmi: the bytes of the reference's
+    FMIndex<4, uint32_t, KISS1Sorter<uint32_t>>{.LOOKUP_LEN = 0}::save — compared with the file the reference itself writes
+    (oracle/_ref) when the harness is there, and with the restatement"""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import fmindex_oracle as fo
+    import ingest_cases as ic
+    import ingest_oracle as io_
+    data = ic.big_cases()["fasta_60"]
+    f = tmp_path / "g.fa"
+    f.write_bytes(data)
+    r = run("--verbose", "fmindex_build", str(f))
+    assert r.returncode == 0, r.stderr
+    S = io_.read_sequence(data)
+    assert re.search(rf"n = {S.size}, \d+ bytes, index building elapsed", r.stderr)
+    img = (tmp_path / "g.fa.fmi").read_bytes()
+    assert img == fo.fmi_image(S, ol.oracle_kiss1(S, k=32))
+    if ol.have_ref() and hasattr(ol.ref(), "ref_fmindex_build_file"):
+        assert img == fo.mask_padding(ol.ref_fmindex_image(S), S.size + 1)

@@ -246,3 +246,37 @@ def test_sharded_building_blocks_on_one_gpu(ctx, name, gen, with_ctx):
     ctx.finish_from_sorted_dev(buf.data_ptr(), n_long, SA.data_ptr(), cbuf.data_ptr() if cbuf is not None else None)
     got = SA.cpu().numpy().view(np.uint32)
     assert np.array_equal(got, ol.oracle_kiss1(S, k=256))
+
+
+@pytest.mark.parametrize("name", ["c1", "c3_200m"])
+def test_full_size_golden_checksums_of_the_reference(ctx, name):
+    """BASELINE.json configs at sizes the oracle does not finish in seconds: the device suffix array against the digests
+    tests/golden/make_full_size_golden.py took from the REFERENCE's own array (48.8 Mbp uniform = the drosophila stand-in,
+    200 Mbp chm13-like = the headline text's generator): the device-side position-mixed sum and FNV-1a of the host copy"""
+    import json
+    import os
+    import torch
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "full_size_golden.json")))[name]
+    n = g["n"]
+    S = tg.uniform_big(g["seed"], n)
+    if g["kind"] == "chm13":
+        S = tg.chm13_like(g["seed"], n, base=S)
+    assert ol.sha_bytes(S[:1 << 20]) == g["text_sha256_head"]          # the same text as the generator script's
+    dS = torch.zeros(n + 64, dtype=torch.uint8, device="cuda")
+    dS[:n] = torch.from_numpy(S).cuda()
+    SA = torch.empty(n + 1, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ctx.suffix_array_dna_dev(dS.data_ptr(), n, SA.data_ptr(), g["k"])
+    assert f"{ctx.sa_checksum_dev(SA.data_ptr(), n + 1):016x}" == g["sa_mixed_sum"]
+    host = SA.cpu().numpy().view(np.uint32)
+    assert f"{ol.fnv1a(host):016x}" == g["sa_fnv"]
+
+
+def test_sa_checksum_is_the_documented_sum(ctx):
+    import torch
+    a = tg.sm64(np.arange(100_003, dtype=np.uint64)).astype(np.uint32)
+    d = torch.from_numpy(a.view(np.int32)).cuda()
+    with np.errstate(over="ignore"):
+        want = int(tg.sm64((np.arange(a.size, dtype=np.uint64) << np.uint64(32)) | a.astype(np.uint64)).sum(dtype=np.uint64))
+    assert ctx.sa_checksum_dev(d.data_ptr(), a.size) == want
+    assert ctx.sa_checksum_dev(d.data_ptr(), 0) == 0

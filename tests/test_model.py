@@ -29,3 +29,10 @@ def test_model_equals_oracle(ci, k):
         lms = mg.lms_positions(S)
         assert np.array_equal(lms, o["lms"][:-1])
     assert np.array_equal(sa, exp)
+
+
+def test_uniform_big_is_the_same_stream():
+    import textgen as tg
+    for seed, n in [(3, 0), (3, 1), (5, 33), (9, 100_001)]:
+        assert np.array_equal(tg.uniform_big(seed, n), tg.uniform(seed, n))
+    assert np.array_equal(tg.uniform_big(11, 300, step=64), tg.uniform(11, 300))

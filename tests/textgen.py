@@ -5,6 +5,8 @@ The uniform stream is the same counter-based generator the product's synthetic-i
 seed' = splitmix64(seed).  Everything else here builds adversarial small/medium inputs for the
 parity tests: planted exact repeats, tandem arrays, homopolymer runs, low-entropy alphabets.
 """
+import sys
+
 import numpy as np
 
 _M = np.uint64(0xFFFFFFFFFFFFFFFF)
@@ -27,6 +29,22 @@ def uniform(seed, n, start=0):
     i = np.arange(start, start + n, dtype=np.uint64)
     x = sm64(s ^ (i >> np.uint64(5)))
     return ((x >> (np.uint64(2) * (i & np.uint64(31)))) & np.uint64(3)).astype(np.uint8)
+
+
+def uniform_big(seed, n, step=1 << 27):
+    """uniform(seed, n) for large n: one hash per 32-base word instead of one per base, in chunks (same values)"""
+    out = np.empty(n, np.uint8)
+    s = sm64(np.uint64(seed))
+    for lo in range(0, n, step):          # step is a multiple of 32
+        hi = min(n, lo + step)
+        nw = (hi - lo + 31) // 32
+        x = sm64(s ^ np.arange(lo // 32, lo // 32 + nw, dtype=np.uint64))
+        b = x.view(np.uint8) if sys.byteorder == "little" else x.byteswap().view(np.uint8)   # byte j: bases 4j .. 4j+3
+        q = np.empty((b.size, 4), np.uint8)
+        for t in range(4):
+            q[:, t] = (b >> (2 * t)) & 3
+        out[lo:hi] = q.reshape(-1)[:hi - lo]
+    return out
 
 
 class _Rng:

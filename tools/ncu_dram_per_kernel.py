@@ -1,13 +1,14 @@
 #!/usr/bin/env python
 """Per kernel function: launches, total time, DRAM bytes read+written (sum and mean per launch) from
-`ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --csv` output."""
+`ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --csv` output.
+python tools/ncu_dram_per_kernel.py launches.csv [profiles/ncu_dram_per_launch.json workload]"""
 import collections
 import csv
 import re
 import sys
 
 
-def main(path):
+def main(path, json_out=None, workload=None):
     lines = [l for l in open(path) if not l.startswith("==")]
     t = collections.defaultdict(float)
     rd = collections.defaultdict(float)
@@ -35,7 +36,15 @@ def main(path):
         n = len(ids[k])
         b = rd[k] + wr[k]
         print(f"{v:9.3f} {100 * v / tot:5.1f}% {n:8d} {b / 1e9:9.3f} {b / n / 1e9:10.4f}  {k}")
+    if json_out:  # per-launch DRAM bytes per kernel, keyed by workload: bench.py's `roofline.traffic` reads this file
+        import json
+        import os
+        cur = json.load(open(json_out)) if os.path.exists(json_out) else {}
+        cur[workload or "c3"] = {"source": os.path.basename(path),
+                                 "dram_bytes_per_launch": {k: (rd[k] + wr[k]) / len(ids[k]) for k in t},
+                                 "launches": {k: len(ids[k]) for k in t}}
+        json.dump(cur, open(json_out, "w"), indent=1, sort_keys=True)
 
 
 if __name__ == "__main__":
-    main(sys.argv[1])
+    main(*sys.argv[1:4])
