@@ -30,9 +30,10 @@ extern "C" {
 #define KISS_B200_EMPTY 0xFFFFFFFFu
 
 /* -s / --sorting-algorithm (reference: include/utils/options.hpp:67-81 SortingAlgorithm).
- * PREFIX_DOUBLING with k = 0xFFFFFFFF is the unique suffix array; with a bounded k the LMS suffixes are ordered by their
- * first max(4096, 16 * 2^ceil(log2 k)) bases (an upper bound of the depth kISS-2's doubling reaches,
- * kiss2_core.hpp:764-766), then by position — the reference's own order of deeper ties depends on its thread count. */
+ * PREFIX_DOUBLING runs rank doubling over kISS-2's 16-base words (kiss2_core.hpp:728-798; csrc/pd.cu).  With
+ * k = 0xFFFFFFFF the result is the unique suffix array; with a bounded k the loop stops at offset >= k like the
+ * reference's (:764-766) and LMS suffixes whose first 2^ceil(log2 k) words are equal stay tied, in ascending text
+ * position here — the reference leaves them in an order that depends on its thread count. */
 #define KISS_B200_PARALLEL_SORTING 0
 #define KISS_B200_PREFIX_DOUBLING 1
 

@@ -139,6 +139,8 @@ struct kiss_b200_ctx {
   cudaStream_t st = nullptr;
   cudaEvent_t ev[8] = {};
   cudaStream_t st_copy = nullptr;  // device-to-host copies of finished SA regions, concurrent with the S pass
+  cudaStream_t st_aux = nullptr;   // the tie-group teams of the LMS sort, concurrent with the big-group radix rounds
+  cudaEvent_t ev_aux = nullptr;
   u32* pinned = nullptr;  // 64 u32 of pinned host memory for small read-backs (+ 8 u64 for the wave tail)
   Profiler prof;          // optional per-kernel timing
   Arena arena;
@@ -153,6 +155,7 @@ struct kiss_b200_ctx {
     u64 bT = 0, bpos = 0, bkey = 0;  // block sizes (arena bookkeeping)
     u64 counters[8] = {};
     SortParams sp = {};
+    int algo = 0;
   } prep;
 };
 
@@ -234,6 +237,7 @@ void do_prepare(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, float* t
   }
   bool unbounded = (algo == KISS_B200_PREFIX_DOUBLING) || ((u64)k >= n);
   P.sp.T = T; P.sp.n = n; P.sp.k = k;
+  P.algo = algo;
   u32 n_long;
   if (unbounded) {
     P.sp.D = (algo == KISS_B200_PREFIX_DOUBLING && pd_depth < n) ? pd_depth : KISS_UNBOUNDED;
@@ -267,6 +271,16 @@ struct SortStats { u64 tied = 0, rounds = 0; };
 template <typename K>
 u32 run_groups(kiss_b200_ctx* c, const K* keys, u32* pos, u32 N, const SortParams& sp, u64 h, GroupLists gl, int kind = 0);
 
+// The teams of a level (k_groups_medium) only touch the slots of their own groups, and so do the pivot rounds of the big
+// groups (k_big_fill, the radix passes, the levels below): the teams run on a second stream next to them.  They are
+// launched after a host-side wait on the main stream (the read-back of the class counts), so everything before them on
+// the main stream has finished; what comes after them — the write-back of a level, the final join — is ordered on the
+// second stream / by ev_aux.  KISS_B200_ONE_STREAM=1 keeps everything on the main stream (A/B timing).
+cudaStream_t team_stream(kiss_b200_ctx* c) {
+  static const bool one = getenv("KISS_B200_ONE_STREAM") != nullptr;
+  return one ? c->st : c->st_aux;
+}
+
 // KISS_B200_DEBUG_GROUPS=1: per level, how many groups of each class and the size histogram of the medium ones
 void debug_groups(kiss_b200_ctx* c, const char* tag, u32 N, u64 h, const u32* cn, const GroupLists& gl) {
   static const bool on = getenv("KISS_B200_DEBUG_GROUPS") != nullptr;
@@ -291,7 +305,7 @@ u32 run_groups<u32>(kiss_b200_ctx* c, const u32* keys, u32* pos, u32 N, const So
   sync.read(gl.counters, GL_COUNTERS, cn);
   cn[1] = cn[4] + cn[5] + cn[6] + cn[7] + cn[8] + cn[9];
   debug_groups(c, "u32", N, h, cn, gl);
-  groups_medium(pos, gl.med, gl.medN, cn + 4, cn + 10, sp, h, c->st);
+  groups_medium(pos, gl.med, gl.medN, cn + 4, cn + 10, sp, h, team_stream(c));
   return cn[2];
 }
 template <>
@@ -307,7 +321,7 @@ u32 run_groups<u64>(kiss_b200_ctx* c, const u64* keys, u32* pos, u32 N, const So
   sync.read(gl.counters, GL_COUNTERS, cn);
   cn[1] = cn[4] + cn[5] + cn[6] + cn[7] + cn[8] + cn[9];
   debug_groups(c, "u64", N, h, cn, gl);
-  groups_medium(pos, gl.med, gl.medN, cn + 4, cn + 10, sp, h, c->st);
+  groups_medium(pos, gl.med, gl.medN, cn + 4, cn + 10, sp, h, team_stream(c));
   return cn[2];
 }
 
@@ -321,9 +335,6 @@ GroupLists alloc_lists(Pool& pool, u32 N, u64* tied) {
   gl.counters = pool.alloc<u32>(GL_COUNTERS);
   gl.tied = tied;
   return gl;
-}
-void free_lists(Pool& pool, GroupLists& gl) {
-  pool.release(gl.glist); pool.release(gl.med); pool.release(gl.big); pool.release(gl.counters);
 }
 
 // Sort `N` long LMS suffixes given in ascending text order with their first-16-base keys.
@@ -359,7 +370,6 @@ void sort_long_lms(kiss_b200_ctx* c, Pool& pool, u32* key, u32* pos, u32 N, cons
   const bool unb = sp.D == KISS_UNBOUNDED || sp.D > 4000;  // the bounded key layout holds depths < 4096
   const int field_bits = unb ? 37 : 42;
   struct Level { u64 *wkey = nullptr, *wkey_alt = nullptr; u32 *wpos = nullptr, *wpos_alt = nullptr, *wslot = nullptr; u32 total = 0; };
-  Level prev;
   const u32* pos_prev = pos;
   const u32* slot_prev = nullptr;
   GroupLists gl_prev = gl;
@@ -389,19 +399,18 @@ void sort_long_lms(kiss_b200_ctx* c, Pool& pool, u32* key, u32* pos, u32 N, cons
     GroupLists gl_cur = alloc_lists(pool, total, tied);
     u32 nbig_next = 0;
     if (h < sp.D) nbig_next = run_groups<u64>(c, cur.wkey, cur.wpos, total, sp, h, gl_cur, unb ? 2 : 1);
-    big_writeback(pos, cur.wslot, cur.wpos, total, st);
-    // retire the previous level
-    free_lists(pool, gl_prev);
-    if (prev.wkey) {
-      pool.release(prev.wkey); pool.release(prev.wkey_alt); pool.release(prev.wpos); pool.release(prev.wpos_alt);
-      pool.release(prev.wslot);
-    }
-    prev = cur;
+    else CK(cudaStreamSynchronize(st));  // (the write-back below runs on the team stream)
+    // after this level's teams (same stream); the levels below overwrite the slots of their own groups later, in order
+    big_writeback(pos, cur.wslot, cur.wpos, total, team_stream(c));
+    // (nothing of a level is released before the join: its teams and its write-back may still be running)
     gl_prev = gl_cur;
     pos_prev = cur.wpos;
     slot_prev = cur.wslot;
     nbig = nbig_next;
   }
+  // join the team stream
+  CK(cudaEventRecord(c->ev_aux, team_stream(c)));
+  CK(cudaStreamWaitEvent(st, c->ev_aux, 0));
   u64 tied_h;
   CK(cudaMemcpyAsync(&tied_h, tied, sizeof(u64), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
@@ -422,6 +431,116 @@ void sort_long_lms(kiss_b200_ctx* c, Pool& pool, u32* key, u32* pos, u32 N, cons
               (unsigned long long)x[3], (unsigned long long)x[4], (unsigned long long)x[5], (unsigned long long)x[6], (unsigned long long)x[8]);
     }
   }
+}
+
+// ---- K3' (pd.cu): rank doubling over kISS-2's word indices.  `lms` = the m1 LMS positions in text order; returns the
+// sorted positions (pool-owned).  k = the caller's k: the doubling loop runs while offset < k (kiss2_core.hpp:764-766).
+u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const u32* lms, u32 m1, u32 k, SortStats* stats) {
+  cudaStream_t st = c->st;
+  Sync sync{c};
+  u32* out = pool.alloc<u32>(m1);
+  if (!m1) return out;
+  u32* cnt = pool.alloc<u32>((u64)m1 + 1);
+  u32* first = pool.alloc<u32>((u64)m1 + 1);
+  u32* small = pool.alloc<u32>(4);
+  pd_count(lms, m1, n, cnt, st);
+  CK(cudaMemcpyAsync(first, cnt, (u64)m1 * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+  u32* part_m = pool.alloc<u32>(scan_partials_len(m1));
+  scan_excl_u32(first, m1, part_m, small, st);
+  pd_ntail(lms, cnt, m1, n, small + 1, st);
+  u32 hv[2];
+  sync.read(small, 2, hv);
+  pool.release(part_m);
+  const u64 W64 = hv[0];
+  const u32 W = hv[0], ntail = hv[1];
+  if (W64 >= 0xFFFFFFF0ull) throw CudaError(KISS_B200_ERR_TOO_LARGE, "too many kISS-2 words for 32-bit indices");
+  u32* wstart = pool.alloc<u32>(W);
+  u8* isstart = pool.alloc<u8>(W);
+  u32* key = pool.alloc<u32>(W);
+  u32* idx = pool.alloc<u32>(W);
+  u32* key_alt = pool.alloc<u32>(W);
+  u32* idx_alt = pool.alloc<u32>(W);
+  pd_words(lms, first, cnt, m1, T, W, ntail, wstart, isstart, key, idx, st);
+  pool.release(cnt); pool.release(first);
+  u32* H = pool.alloc<u32>(256 * radix_tiles(W));
+  u32* partials = pool.alloc<u32>(scan_partials_len(256 * radix_tiles(W) > W ? 256 * radix_tiles(W) : W));
+  radix_sort_u32(key, idx, key_alt, idx_alt, W, 0, 32, H, partials, st);  // stable: initialize_sa, kiss2_core.hpp:135-184
+  u32* head = pool.alloc<u32>(W);
+  u32* ord = pool.alloc<u32>(W);
+  u32* headslot = pool.alloc<u32>(W);
+  u32* rank = pool.alloc<u32>(W);
+  u32* sa_final = pool.alloc<u32>(W);
+  pd_heads0(key, idx, W, ntail, head, st);
+  pool.release(key); pool.release(key_alt); pool.release(idx_alt);
+  CK(cudaMemcpyAsync(ord, head, (u64)W * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+  scan_excl_u32(ord, W, partials, nullptr, st);
+  pd_headslot(head, ord, W, headslot, st);
+  pd_rank(idx, head, ord, headslot, nullptr, W, rank, st);
+  // first compaction: singletons are final
+  u32* keep = pool.alloc<u32>(W);
+  u32* dst = pool.alloc<u32>(W);
+  pd_keep(head, W, keep, st);
+  CK(cudaMemcpyAsync(dst, keep, (u64)W * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+  scan_excl_u32(dst, W, partials, small, st);
+  u32 A;
+  sync.read(small, 1, &A);
+  u32* elem = pool.alloc<u32>(A);
+  u32* gslot = pool.alloc<u32>(A);
+  u32* ghead = pool.alloc<u32>(A);
+  pd_compact(idx, nullptr, head, keep, dst, W, sa_final, elem, gslot, ghead, st);
+  CK(cudaStreamSynchronize(st));
+  pool.release(idx); pool.release(head); pool.release(ord); pool.release(headslot); pool.release(keep); pool.release(dst);
+  pool.release(H);
+  stats->tied = A;
+  int rb = 1;  // bits of a rank (<= W)
+  while (rb < 32 && (1ull << rb) <= (u64)W) rb++;
+  for (u64 off = 1; off < (u64)k && off <= 0x7FFFFFFFull && A > 1; off *= 2) {
+    stats->rounds++;
+    u32* o = pool.alloc<u32>(A);
+    u32* hs = pool.alloc<u32>(A);
+    u64* comp = pool.alloc<u64>(A);
+    u64* comp_alt = pool.alloc<u64>(A);
+    u32* elem_alt = pool.alloc<u32>(A);
+    u32* H2 = pool.alloc<u32>(256 * radix_tiles(A));
+    CK(cudaMemcpyAsync(o, ghead, (u64)A * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    scan_excl_u32(o, A, partials, small, st);
+    u32 ngroups;
+    sync.read(small, 1, &ngroups);
+    pd_key2(elem, ghead, o, rank, A, W, (u32)off, rb, comp, st);
+    int gb = 1;
+    while (gb < 32 && (1u << gb) < ngroups) gb++;
+    radix_sort_u64(comp, elem, comp_alt, elem_alt, A, 0, rb + gb, H2, partials, st);
+    pd_heads(comp, A, ghead, st);
+    CK(cudaMemcpyAsync(o, ghead, (u64)A * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    scan_excl_u32(o, A, partials, nullptr, st);
+    pd_headslot(ghead, o, A, hs, st);
+    pd_rank(elem, ghead, o, hs, gslot, A, rank, st);
+    u32* kp = pool.alloc<u32>(A);
+    u32* ds = pool.alloc<u32>(A);
+    pd_keep(ghead, A, kp, st);
+    CK(cudaMemcpyAsync(ds, kp, (u64)A * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    scan_excl_u32(ds, A, partials, small, st);
+    u32 A2;
+    sync.read(small, 1, &A2);
+    u32* elem2 = pool.alloc<u32>(A2);
+    u32* gslot2 = pool.alloc<u32>(A2);
+    u32* ghead2 = pool.alloc<u32>(A2);
+    pd_compact(elem, gslot, ghead, kp, ds, A, sa_final, elem2, gslot2, ghead2, st);
+    CK(cudaStreamSynchronize(st));
+    pool.release(o); pool.release(hs); pool.release(comp); pool.release(comp_alt); pool.release(elem); pool.release(elem_alt);
+    pool.release(H2); pool.release(kp); pool.release(ds); pool.release(gslot); pool.release(ghead);
+    elem = elem2; gslot = gslot2; ghead = ghead2;
+    A = A2;
+  }
+  pd_flush(elem, gslot, A, sa_final, st);  // bounded k: what is still tied keeps ascending text position
+  u32* flag = pool.alloc<u32>(W);
+  pd_startflags(sa_final, isstart, W, flag, st);
+  scan_excl_u32(flag, W, partials, nullptr, st);
+  pd_emit(sa_final, isstart, flag, wstart, W, out, st);
+  CK(cudaStreamSynchronize(st));
+  pool.release(flag); pool.release(elem); pool.release(gslot); pool.release(ghead); pool.release(rank); pool.release(sa_final);
+  pool.release(wstart); pool.release(isstart); pool.release(partials); pool.release(small);
+  return out;
 }
 
 Buckets make_buckets(const u64 counters[8], u64 n) {
@@ -559,6 +678,19 @@ void do_shorts(kiss_b200_ctx* c, Pool& pool, const u32* shorts_text, u32 ns, con
 void do_sort(kiss_b200_ctx* c, Pool& pool, SortedLms* out, SortStats* stats) {
   auto& P = c->prep;
   u32 ns = (u32)(P.m1 - P.n_long);
+  // PREFIX_DOUBLING, and the unbounded order with either -s, go through rank doubling (pd.cu): O(log) rounds whatever
+  // the repeats look like.  KISS_B200_PD=pivot keeps the pivot rounds of lms_sort.cu at the depth of do_prepare (A/B timing;
+  // no bound on texts with very long exact duplicates).  Tiny texts (n < 64) take the pivot path: the reference's own
+  // tail-word rule degenerates there (its `n - l` wraps for n < 16, kiss2_core.hpp:81).
+  static const bool pd_pivot = [] { const char* e = getenv("KISS_B200_PD"); return e && std::string(e) == "pivot"; }();
+  const bool unbounded = P.sp.D == KISS_UNBOUNDED;
+  if (!pd_pivot && P.n >= 64 && ns == 0 && P.m1 && (P.algo == KISS_B200_PREFIX_DOUBLING || unbounded)) {
+    const u32 kk = P.algo == KISS_B200_PREFIX_DOUBLING ? P.sp.k : 0xFFFFFFFFu;
+    out->longs = sort_lms_doubling(c, pool, P.T, P.n, P.pos, (u32)P.m1, kk, stats);
+    out->nl = (u32)P.m1;
+    out->ns = 0;
+    return;
+  }
   if (ns > SHORT_MAX)
     throw CudaError(KISS_B200_ERR_UNSUPPORTED, "bounded k too large: more than 16384 LMS suffixes within D(k) of the text end");
   // the shorts are the tail of the text-ordered list; copy them out before the sort permutes the buffers
@@ -646,12 +778,14 @@ int guarded(kiss_b200_ctx* c, F&& f) {
     f();
     cudaStreamSynchronize(c->st);
     cudaStreamSynchronize(c->st_copy);
+    cudaStreamSynchronize(c->st_aux);
     c->prof.collect();
     c->arena.settle();
     return KISS_B200_OK;
   } catch (const CudaError& e) {
     g_last_error = e.what();
     cudaStreamSynchronize(c->st_copy);  // no copy into the caller's buffer may outlive the call
+    cudaStreamSynchronize(c->st_aux);
     cudaGetLastError();
     return e.code;
   } catch (const std::bad_alloc&) {
@@ -958,8 +1092,14 @@ int kiss_b200_create(kiss_b200_ctx** out, int device) {
   c->device = device;
   try {
     CK(cudaSetDevice(device));
-    CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+    // (the main stream outranks the team stream: the many small kernels of the big-group rounds are latency-bound and
+    // slip in between the long-running team kernels)
+    int prio_lo = 0, prio_hi = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CK(cudaStreamCreateWithPriority(&c->st, cudaStreamNonBlocking, prio_hi));
     CK(cudaStreamCreateWithFlags(&c->st_copy, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithPriority(&c->st_aux, cudaStreamNonBlocking, prio_lo));
+    CK(cudaEventCreateWithFlags(&c->ev_aux, cudaEventDisableTiming));
     for (auto& ev : c->ev) CK(cudaEventCreate(&ev));
     CK(cudaHostAlloc((void**)&c->pinned, 64 * sizeof(u32) + 8 * sizeof(u64), cudaHostAllocMapped | cudaHostAllocPortable));
     cudaMemPool_t mp;
@@ -986,6 +1126,8 @@ void kiss_b200_destroy(kiss_b200_ctx* c) {
   for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
   if (c->pinned) cudaFreeHost(c->pinned);
   if (c->st_copy) cudaStreamDestroy(c->st_copy);
+  if (c->st_aux) cudaStreamDestroy(c->st_aux);
+  if (c->ev_aux) cudaEventDestroy(c->ev_aux);
   if (c->st) cudaStreamDestroy(c->st);
   delete c;
 }

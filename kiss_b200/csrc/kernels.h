@@ -170,6 +170,25 @@ void shorts_order(const u32* shorts, u32 ns, SortParams sp, u32* rank0, u32* sor
 void shorts_insertions(const u32* sorted_shorts, u32 ns, const u32* longs, u32 nl, SortParams sp, u32* ins,
                        cudaStream_t st);
 
+// ---------------------------------------------------------------- pd.cu (rank doubling over kISS-2's words; see api.cu)
+void pd_count(const u32* lms, u32 m1, u64 n, u32* cnt, cudaStream_t st);
+void pd_ntail(const u32* lms, const u32* cnt, u32 m1, u64 n, u32* out, cudaStream_t st);
+void pd_words(const u32* lms, const u32* first, const u32* cnt, u32 m1, const u64* T, u32 W, u32 ntail, u32* wstart,
+              u8* isstart, u32* key_in, u32* idx_in, cudaStream_t st);
+void pd_heads0(const u32* key, const u32* idx, u32 W, u32 ntail, u32* head, cudaStream_t st);
+void pd_heads(const u64* comp, u32 A, u32* head, cudaStream_t st);
+void pd_headslot(const u32* head, const u32* ord, u32 A, u32* headslot, cudaStream_t st);
+void pd_rank(const u32* elem, const u32* head, const u32* ord, const u32* headslot, const u32* gslot, u32 A, u32* rank,
+             cudaStream_t st);
+void pd_keep(const u32* head, u32 A, u32* keep, cudaStream_t st);
+void pd_compact(const u32* elem, const u32* gslot, const u32* head, const u32* keep, const u32* dst, u32 A, u32* sa_final,
+                u32* elem2, u32* gslot2, u32* head2, cudaStream_t st);
+void pd_key2(const u32* elem, const u32* head, const u32* ord, const u32* rank, u32 A, u32 W, u32 off, int rb, u64* comp,
+             cudaStream_t st);
+void pd_flush(const u32* elem, const u32* gslot, u32 A, u32* sa_final, cudaStream_t st);
+void pd_startflags(const u32* sa_final, const u8* isstart, u32 W, u32* flag, cudaStream_t st);
+void pd_emit(const u32* sa_final, const u8* isstart, const u32* dst, const u32* wstart, u32 W, u32* out, cudaStream_t st);
+
 // ---------------------------------------------------------------- fmindex.cu
 // N = n + 1 suffix array entries.  bwt32: ceil(N / 16) words; tot: 4 planes (stride n1 >= N / 256 + 1, a multiple of 4) of block counts (zeroed by the
 // caller; scanned per plane afterwards); occ2: n2 = N / 16 + 1 rows of 4 bytes (zeroed by the caller); b32 (nullable:

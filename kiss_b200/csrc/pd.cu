@@ -1,0 +1,202 @@
+// pd.cu — K3': the PREFIX_DOUBLING LMS sort (kiss2_core.hpp:728-798) as rank doubling on the device.
+//
+// The reference chops every LMS substring into words of 16 bases (encode_S, kiss2_core.hpp:20-100: a word starts at the
+// LMS position and every 16 bases after it while it is before the next LMS position; it reads 16 bases whatever follows,
+// zero past the end), orders the words by value with a stable LSD radix sort in which the words that overlap the text
+// end come first in reverse index order and are groups of their own (initialize_sa / initialize_rank, :113-249), and
+// then doubles: groups are ordered by rank[index + offset] for offset = 1, 2, 4, ... < k over WORD indices, split where
+// that rank changes, and singletons leave the work list (:764-785).  The order of the LMS-start words is the LMS order
+// (place_back_lms, :624-726).
+//
+// Here: the same words, the same initial order (radix.cu's stable LSD sort on an input permuted like :130-133), and per
+// round one composite key [group ordinal | rank at index + offset] per ACTIVE element, sorted with the stable radix sort;
+// new group heads where the composite changes; ranks = head slot + 1 as in the reference (a rank never changes once its
+// group is a singleton); singletons are compacted away.  O(log2 of the longest repeat in words) rounds whatever the
+// text looks like — the pivot rounds of lms_sort.cu cost O(LCP / 32) word loads per element, which has no bound on texts
+// with Mbp-scale exact duplicates.  With a bounded k the loop stops at offset >= k like the reference's, and what is still
+// tied keeps ascending word index = ascending text position (every step is stable): exactly the classes of
+// tests/kiss2_words.py, in canonical order — where the reference leaves them in an order that depends on its thread
+// count.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace kiss {
+
+#define PD_T 256
+
+// cnt[i] = words of LMS substring i (kiss2_core.hpp:45-47)
+__global__ void k_pd_count(const u32* __restrict__ lms, u32 m1, u64 n, u32* __restrict__ cnt) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m1) return;
+  const u64 next = i + 1 < m1 ? lms[i + 1] : n;
+  cnt[i] = (u32)((next - lms[i] + 15) >> 4);
+}
+
+// word starts, LMS-start flags and the first 16 bases of every word, written at the word's INPUT SLOT of the initial
+// sort: the `ntail` words that overlap the text end (the last ones by index) first, in reverse index order (:130-133)
+__global__ void k_pd_words(const u32* __restrict__ lms, const u32* __restrict__ first, const u32* __restrict__ cnt, u32 m1,
+                           const u64* __restrict__ T, u32 W, u32 ntail, u32* __restrict__ wstart, u8* __restrict__ isstart,
+                           u32* __restrict__ key_in, u32* __restrict__ idx_in) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m1) return;
+  const u32 f = first[i], c = cnt[i];
+  const u64 p0 = lms[i];
+  for (u32 j = 0; j < c; j++) {
+    const u32 w = f + j;
+    const u64 p = p0 + 16ull * j;
+    wstart[w] = (u32)p;
+    isstart[w] = j == 0;
+    const u32 slot = w >= W - ntail ? W - 1 - w : w + ntail;
+    key_in[slot] = (u32)(word_at(T, p) >> 32);
+    idx_in[slot] = w;
+  }
+}
+
+// number of words starting after n - 16 (:81-84); wstart is ascending
+__global__ void k_pd_ntail(const u32* __restrict__ lms, const u32* __restrict__ cnt, u32 m1, u64 n, u32* __restrict__ out) {
+  // only the last few LMS substrings can reach the last 16 bases: walk back from the end
+  if (threadIdx.x || blockIdx.x) return;
+  u32 t = 0;
+  for (u32 i = m1; i-- > 0;) {
+    const u64 p0 = lms[i];
+    const u32 c = cnt[i];
+    const u64 last = p0 + 16ull * (c - 1);
+    if (last + 16 <= n) break;  // every word of this and of the earlier substrings fits
+    for (u32 j = 0; j < c; j++) t += (p0 + 16ull * j + 16 > n) ? 1u : 0u;
+  }
+  *out = t;
+}
+
+// initial heads (:215-217): the value changes, or the element before is a tail word
+__global__ void k_pd_heads0(const u32* __restrict__ key, const u32* __restrict__ idx, u32 W, u32 ntail, u32* __restrict__ head) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= W) return;
+  head[i] = (i == 0 || key[i] != key[i - 1] || idx[i - 1] >= W - ntail) ? 1u : 0u;
+}
+
+// heads after a round: the composite key changes (it contains the group ordinal, so old boundaries stay)
+__global__ void k_pd_heads(const u64* __restrict__ comp, u32 A, u32* __restrict__ head) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A) return;
+  head[i] = (i == 0 || comp[i] != comp[i - 1]) ? 1u : 0u;
+}
+
+// ord = exclusive scan of head: the head of ordinal o sits at slot headslot[o]
+__global__ void k_pd_headslot(const u32* __restrict__ head, const u32* __restrict__ ord, u32 A, u32* __restrict__ headslot) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < A && head[i]) headslot[ord[i]] = i;
+}
+
+// rank of every element = global position of its group's head + 1 (:226-248, :378-462); gslot == nullptr: slot = position
+__global__ void k_pd_rank(const u32* __restrict__ elem, const u32* __restrict__ head, const u32* __restrict__ ord,
+                          const u32* __restrict__ headslot, const u32* __restrict__ gslot, u32 A, u32* __restrict__ rank) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A) return;
+  const u32 hs = headslot[ord[i] + head[i] - 1u];
+  rank[elem[i]] = (gslot ? gslot[hs] : hs) + 1u;
+}
+
+// keep[i] = the element shares its group with another one
+__global__ void k_pd_keep(const u32* __restrict__ head, u32 A, u32* __restrict__ keep) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A) return;
+  const bool single = head[i] && (i + 1 == A || head[i + 1]);
+  keep[i] = single ? 0u : 1u;
+}
+
+// singletons are final: sa_final[global position] = word; the others move to the compacted work list
+__global__ void k_pd_compact(const u32* __restrict__ elem, const u32* __restrict__ gslot, const u32* __restrict__ head,
+                             const u32* __restrict__ keep, const u32* __restrict__ dst, u32 A, u32* __restrict__ sa_final,
+                             u32* __restrict__ elem2, u32* __restrict__ gslot2, u32* __restrict__ head2) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A) return;
+  const u32 g = gslot ? gslot[i] : i;
+  if (!keep[i]) {
+    sa_final[g] = elem[i];
+  } else {
+    const u32 d = dst[i];
+    elem2[d] = elem[i];
+    gslot2[d] = g;
+    head2[d] = head[i];
+  }
+}
+
+// composite key of a round: [group ordinal | rank[index + offset]] (rank 0 past the last word, :102-111)
+__global__ void k_pd_key2(const u32* __restrict__ elem, const u32* __restrict__ head, const u32* __restrict__ ord,
+                          const u32* __restrict__ rank, u32 A, u32 W, u32 off, int rb, u64* __restrict__ comp) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A) return;
+  const u64 w = (u64)elem[i] + off;
+  const u32 r = w < W ? rank[w] : 0u;
+  comp[i] = ((u64)(ord[i] + head[i] - 1u) << rb) | r;  // rb = bits of a rank: the sort runs over rb + bits(groups) bits
+}
+
+// what is still tied when the loop ends keeps its (stable) order
+__global__ void k_pd_flush(const u32* __restrict__ elem, const u32* __restrict__ gslot, u32 A, u32* __restrict__ sa_final) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < A) sa_final[gslot[i]] = elem[i];
+}
+
+// LMS-start words in final order (:690-725)
+__global__ void k_pd_startflags(const u32* __restrict__ sa_final, const u8* __restrict__ isstart, u32 W, u32* __restrict__ flag) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < W) flag[i] = isstart[sa_final[i]];
+}
+__global__ void k_pd_emit(const u32* __restrict__ sa_final, const u8* __restrict__ isstart, const u32* __restrict__ dst,
+                          const u32* __restrict__ wstart, u32 W, u32* __restrict__ out) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= W) return;
+  const u32 w = sa_final[i];
+  if (isstart[w]) out[dst[i]] = wstart[w];
+}
+
+#define PD_GRID(n) (unsigned)(((u64)(n) + PD_T - 1) / PD_T)
+#define PD_LAUNCH(kern, n, ...)                              \
+  do {                                                       \
+    if (n) {                                                 \
+      kern<<<PD_GRID(n), PD_T, 0, st>>>(__VA_ARGS__);        \
+      CK_LAUNCH();                                           \
+      g_launches++;                                          \
+    }                                                        \
+  } while (0)
+
+void pd_count(const u32* lms, u32 m1, u64 n, u32* cnt, cudaStream_t st) { PD_LAUNCH(k_pd_count, m1, lms, m1, n, cnt); }
+void pd_ntail(const u32* lms, const u32* cnt, u32 m1, u64 n, u32* out, cudaStream_t st) {
+  k_pd_ntail<<<1, 32, 0, st>>>(lms, cnt, m1, n, out);
+  CK_LAUNCH(); g_launches++;
+}
+void pd_words(const u32* lms, const u32* first, const u32* cnt, u32 m1, const u64* T, u32 W, u32 ntail, u32* wstart,
+              u8* isstart, u32* key_in, u32* idx_in, cudaStream_t st) {
+  PD_LAUNCH(k_pd_words, m1, lms, first, cnt, m1, T, W, ntail, wstart, isstart, key_in, idx_in);
+}
+void pd_heads0(const u32* key, const u32* idx, u32 W, u32 ntail, u32* head, cudaStream_t st) {
+  PD_LAUNCH(k_pd_heads0, W, key, idx, W, ntail, head);
+}
+void pd_heads(const u64* comp, u32 A, u32* head, cudaStream_t st) { PD_LAUNCH(k_pd_heads, A, comp, A, head); }
+void pd_headslot(const u32* head, const u32* ord, u32 A, u32* headslot, cudaStream_t st) {
+  PD_LAUNCH(k_pd_headslot, A, head, ord, A, headslot);
+}
+void pd_rank(const u32* elem, const u32* head, const u32* ord, const u32* headslot, const u32* gslot, u32 A, u32* rank,
+             cudaStream_t st) {
+  PD_LAUNCH(k_pd_rank, A, elem, head, ord, headslot, gslot, A, rank);
+}
+void pd_keep(const u32* head, u32 A, u32* keep, cudaStream_t st) { PD_LAUNCH(k_pd_keep, A, head, A, keep); }
+void pd_compact(const u32* elem, const u32* gslot, const u32* head, const u32* keep, const u32* dst, u32 A, u32* sa_final,
+                u32* elem2, u32* gslot2, u32* head2, cudaStream_t st) {
+  PD_LAUNCH(k_pd_compact, A, elem, gslot, head, keep, dst, A, sa_final, elem2, gslot2, head2);
+}
+void pd_key2(const u32* elem, const u32* head, const u32* ord, const u32* rank, u32 A, u32 W, u32 off, int rb, u64* comp,
+             cudaStream_t st) {
+  PD_LAUNCH(k_pd_key2, A, elem, head, ord, rank, A, W, off, rb, comp);
+}
+void pd_flush(const u32* elem, const u32* gslot, u32 A, u32* sa_final, cudaStream_t st) {
+  PD_LAUNCH(k_pd_flush, A, elem, gslot, A, sa_final);
+}
+void pd_startflags(const u32* sa_final, const u8* isstart, u32 W, u32* flag, cudaStream_t st) {
+  PD_LAUNCH(k_pd_startflags, W, sa_final, isstart, W, flag);
+}
+void pd_emit(const u32* sa_final, const u8* isstart, const u32* dst, const u32* wstart, u32 W, u32* out, cudaStream_t st) {
+  PD_LAUNCH(k_pd_emit, W, sa_final, isstart, dst, wstart, W, out);
+}
+
+}  // namespace kiss

@@ -334,6 +334,14 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
     }
     for (u32 i = tid; i < RADIX_WARPS * 256; i += RADIX_THREADS) wcnt[i] = 0;
     __syncthreads();  // registers hold the tile: its buffer becomes the staging area
+    // NMATCH < 0: peers are found through one shared-memory atomicOr per key on a [warp][digit] mask array instead of
+    // eight ballots; the masks live in the tile's own key buffer, which is idle until the keys are staged
+    u32* wmask = reinterpret_cast<u32*>(kb) + w * 256;
+    if (NMATCH < 0) {
+#pragma unroll
+      for (int q = 0; q < 8; q++) wmask[q * 32 + lane] = 0;
+      __syncwarp();
+    }
     {
       u32 next = tile + gridDim.x;
       if (next < ntiles) {
@@ -349,7 +357,13 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
       bool valid = lbase + r * 32 + lane < tile_n;
       u32 d = (u32)(keys[r] >> shift) & mask;
       u32 peers;
-      if (r < NMATCH) {
+      if (NMATCH < 0) {
+        if (valid) atomicOr(&wmask[d], 1u << lane);
+        __syncwarp();
+        peers = valid ? wmask[d] : 0u;
+        __syncwarp();
+        if (valid && (peers & lt_mask) == 0) wmask[d] = 0;  // the lowest peer clears the mask for the next round
+      } else if (r < NMATCH) {
         // a few rounds go through MATCH.ANY (ADU pipe) so that the ballot rounds (ALU pipe) are not the only load
         peers = __match_any_sync(0xffffffffu, valid ? d : 256u + lane);
       } else {
@@ -428,6 +442,8 @@ void radix_init() {
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u64, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
   int dev = 0, sms = 0, b32 = 0, b64 = 0;
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -464,7 +480,9 @@ static void radix_sort_impl(K*& keys, u32*& vals, K*& keys_alt, u32*& vals_alt, 
         u32 grid = (u32)g_radix_grid[sizeof(K) == 4 ? 0 : 1];
         if (grid > ntiles) grid = ntiles;
         static const int nmatch = [] { const char* e = getenv("KISS_B200_NMATCH"); return e ? atoi(e) : RADIX_ITEMS / 4; }();  // 0: 8.16 ms, 4: 7.94 ms, 8: 8.43 ms per 1 Gbp sort
-        if (sizeof(K) == 4 && nmatch == 2)
+        if (nmatch < 0)
+          k_radix_scatter_p<K, -1><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift, mask, H, ntiles);
+        else if (sizeof(K) == 4 && nmatch == 2)
           k_radix_scatter_p<u32, 2><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);
         else if (sizeof(K) == 4 && nmatch == 4)
           k_radix_scatter_p<u32, 4><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);

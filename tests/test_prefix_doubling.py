@@ -108,6 +108,7 @@ def test_bounded_k_tie_heavy_equals_kiss2_after_canonicalising_tied_runs(ctx, na
     got, _ = kw.canonical(got_lms, S, k)
     bad = np.nonzero(got != want)[0]
     assert bad.size == 0, f"{bad.size} mismatches ({tied_runs} tied runs), first at {bad[:5]}: got {got[bad[:5]]} want {want[bad[:5]]}"
+    assert np.array_equal(got_lms, want)      # rank doubling (pd.cu) leaves tied runs in text order: canonical as it is
     # and the suffix array induced from this implementation's order is the one the reference's induction gives for it
     sa = ctx.suffix_array_dna(S, k, kiss_b200.PREFIX_DOUBLING)
     assert np.array_equal(sa, ol.oracle_induce_from_sorted(S, got_lms))
