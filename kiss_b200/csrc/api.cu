@@ -443,6 +443,7 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
   u32* cnt = pool.alloc<u32>((u64)m1 + 1);
   u32* first = pool.alloc<u32>((u64)m1 + 1);
   u32* small = pool.alloc<u32>(4);
+  u32* small8 = pool.alloc<u32>(8);
   pd_count(lms, m1, n, cnt, st);
   CK(cudaMemcpyAsync(first, cnt, (u64)m1 * sizeof(u32), cudaMemcpyDeviceToDevice, st));
   u32* part_m = pool.alloc<u32>(scan_partials_len(m1));
@@ -506,11 +507,32 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
     scan_excl_u32(o, A, partials, small, st);
     u32 ngroups;
     sync.read(small, 1, &ngroups);
-    pd_key2(elem, ghead, o, rank, A, W, (u32)off, rb, comp, st);
-    int gb = 1;
-    while (gb < 32 && (1u << gb) < ngroups) gb++;
-    radix_sort_u64(comp, elem, comp_alt, elem_alt, A, 0, rb + gb, H2, partials, st);
-    pd_heads(comp, A, ghead, st);
+    // segmented sort (one pass) unless a group is larger than a block team holds
+    static const bool no_seg = getenv("KISS_B200_PD_RADIX") != nullptr;  // A/B: the radix sort in every round
+    bool seg_done = false;
+    if (!no_seg) {
+      u32* key2 = reinterpret_cast<u32*>(comp);          // (the composite buffers are free on this path)
+      u32* lists = reinterpret_cast<u32*>(comp_alt);   // 7 lists; a listed group has > 8 elements: at most A / 9 per list
+      const u32 list_cap = A / 9 + 1;
+      pd_headslot(ghead, o, A, hs, st);
+      CK(cudaMemsetAsync(small8, 0, 8 * sizeof(u32), st));
+      pd_key2_plain(elem, rank, A, W, (u32)off, key2, st);
+      pd_seg_small(hs, ngroups, A, elem, key2, lists, list_cap, small8, st);
+      u32 cn[8];
+      sync.read(small8, 8, cn);
+      if (cn[7] == 0) {
+        pd_seg_teams(lists, list_cap, cn, hs, ngroups, A, elem, key2, st);
+        pd_heads_seg(key2, A, ghead, st);
+        seg_done = true;
+      }
+    }
+    if (!seg_done) {
+      pd_key2(elem, ghead, o, rank, A, W, (u32)off, rb, comp, st);
+      int gb = 1;
+      while (gb < 32 && (1u << gb) < ngroups) gb++;
+      radix_sort_u64(comp, elem, comp_alt, elem_alt, A, 0, rb + gb, H2, partials, st);
+      pd_heads(comp, A, ghead, st);
+    }
     CK(cudaMemcpyAsync(o, ghead, (u64)A * sizeof(u32), cudaMemcpyDeviceToDevice, st));
     scan_excl_u32(o, A, partials, nullptr, st);
     pd_headslot(ghead, o, A, hs, st);
@@ -539,7 +561,7 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
   pd_emit(sa_final, isstart, flag, wstart, W, out, st);
   CK(cudaStreamSynchronize(st));
   pool.release(flag); pool.release(elem); pool.release(gslot); pool.release(ghead); pool.release(rank); pool.release(sa_final);
-  pool.release(wstart); pool.release(isstart); pool.release(partials); pool.release(small);
+  pool.release(wstart); pool.release(isstart); pool.release(partials); pool.release(small); pool.release(small8);
   return out;
 }
 

@@ -185,6 +185,14 @@ void pd_compact(const u32* elem, const u32* gslot, const u32* head, const u32* k
                 u32* elem2, u32* gslot2, u32* head2, cudaStream_t st);
 void pd_key2(const u32* elem, const u32* head, const u32* ord, const u32* rank, u32 A, u32 W, u32 off, int rb, u64* comp,
              cudaStream_t st);
+void pd_key2_plain(const u32* elem, const u32* rank, u32 A, u32 W, u32 off, u32* key2, cudaStream_t st);
+// lists: 7 size classes of list_cap group ordinals each; counters[8] (zeroed by the caller): groups per class, [7] = groups
+// > 2048 (then the round is radix-sorted instead)
+void pd_seg_small(const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2, u32* lists, u32 list_cap, u32* counters,
+                  cudaStream_t st);
+void pd_seg_teams(const u32* lists, u32 list_cap, const u32* cn, const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2,
+                  cudaStream_t st);
+void pd_heads_seg(const u32* key2, u32 A, u32* head, cudaStream_t st);
 void pd_flush(const u32* elem, const u32* gslot, u32 A, u32* sa_final, cudaStream_t st);
 void pd_startflags(const u32* sa_final, const u8* isstart, u32 W, u32* flag, cudaStream_t st);
 void pd_emit(const u32* sa_final, const u8* isstart, const u32* dst, const u32* wstart, u32 W, u32* out, cudaStream_t st);

@@ -19,6 +19,7 @@
 // count.
 #include "common.cuh"
 #include "kernels.h"
+#include "team.cuh"
 
 namespace kiss {
 
@@ -150,6 +151,98 @@ __global__ void k_pd_emit(const u32* __restrict__ sa_final, const u8* __restrict
   if (isstart[w]) out[dst[i]] = wstart[w];
 }
 
+// ---- segmented sort of a round.  The active elements are already grouped (a group = a run of slots), so a round only
+// has to order every group by its second rank key2 = rank[index + offset]: groups of at most 8 by one thread, up to 256
+// by a warp team, up to 2048 by a block team (the register-resident bitonic network of team.cuh on [key2 | slot], stable
+// through the slot field), all in ONE pass over the data — the global radix sort of the composite key [group | key2]
+// needs 7 passes (512 Mbp of 512 near-identical copies, -k -1: 27 ms per round against ~5).  A round with a larger
+// group takes the radix sort (the counters tell the host).
+__global__ void k_pd_key2_plain(const u32* __restrict__ elem, const u32* __restrict__ rank, u32 A, u32 W, u32 off,
+                                u32* __restrict__ key2) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A) return;
+  const u64 w = (u64)elem[i] + off;
+  key2[i] = w < W ? rank[w] : 0u;
+}
+
+// one thread per group: orders the groups of <= 8 in place, lists the others by size class (7 lists of list_cap entries);
+// counters: [0..6] groups per class, [7] groups > 2048
+__global__ void k_pd_seg_small(const u32* __restrict__ headslot, u32 ngroups, u32 A, u32* __restrict__ elem,
+                               u32* __restrict__ key2, u32* __restrict__ lists, u32 list_cap, u32* __restrict__ counters) {
+  const u32 g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= ngroups) return;
+  const u32 start = headslot[g], end = g + 1 < ngroups ? headslot[g + 1] : A, size = end - start;
+  if (size <= 8) {
+    u32 k[8], e[8];
+#pragma unroll
+    for (u32 a = 0; a < 8; a++) {
+      k[a] = a < size ? key2[start + a] : 0xFFFFFFFFu;
+      e[a] = a < size ? elem[start + a] : 0u;
+    }
+    // stable insertion network on (key, input order): a compare-exchange only swaps on strictly greater
+#pragma unroll
+    for (u32 a = 1; a < 8; a++)
+#pragma unroll
+      for (u32 b = a; b > 0; b--) {
+        const bool sw = b < size && k[b - 1] > k[b];
+        const u32 tk = k[b], te = e[b];
+        k[b] = sw ? k[b - 1] : k[b];   e[b] = sw ? e[b - 1] : e[b];
+        k[b - 1] = sw ? tk : k[b - 1]; e[b - 1] = sw ? te : e[b - 1];
+      }
+#pragma unroll
+    for (u32 a = 0; a < 8; a++)
+      if (a < size) { key2[start + a] = k[a]; elem[start + a] = e[a]; }
+  } else if (size <= 2048) {
+    // size classes of the teams: <= 32, 64, 128, 256 (a warp with 1..8 keys per lane), <= 512, 1024, 2048 (a block)
+    const u32 cls = size <= 32 ? 0u : size <= 64 ? 1u : size <= 128 ? 2u : size <= 256 ? 3u : size <= 512 ? 4u : size <= 1024 ? 5u : 6u;
+    lists[(u64)cls * list_cap + atomicAdd(&counters[cls], 1u)] = g;
+  } else {
+    atomicAdd(&counters[7], 1u);
+  }
+}
+
+template <int NW, int R>
+__global__ void __launch_bounds__(NW == 1 ? 256 : NW * 32) k_pd_seg_team(const u32* __restrict__ list, u32 nlist,
+                                                                         const u32* __restrict__ headslot, u32 ngroups, u32 A,
+                                                                         u32* __restrict__ elem, u32* __restrict__ key2) {
+  constexpr u32 P = NW * R * 32, TEAMS = NW == 1 ? 8 : 1;
+  __shared__ u64 s_x[NW > 1 ? P : 1];
+  __shared__ u32 s_e[TEAMS * P];
+  const u32 lane = threadIdx.x & 31u, wb = threadIdx.x >> 5;
+  const u32 team = NW == 1 ? wb : 0u, w = NW == 1 ? 0u : wb;
+  u32* se = s_e + team * P;
+  for (u32 gi = blockIdx.x * TEAMS + team; gi < nlist; gi += gridDim.x * TEAMS) {
+    const u32 g = list[gi];
+    const u32 start = headslot[g], end = g + 1 < ngroups ? headslot[g + 1] : A, size = end - start;
+    u64 x[R], xl[R];
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const u32 i = ((w * R + r) << 5) | lane;
+      x[r] = i < size ? (((u64)key2[start + i] << MK_SLOT_BITS) | i) : ~0ull;
+      xl[r] = 0;
+      se[i] = i < size ? elem[start + i] : 0u;
+    }
+    team_sync<NW>();
+    team_sort<NW, R, false>(x, xl, w, lane, s_x, s_x);
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const u32 i = ((w * R + r) << 5) | lane;
+      if (i < size) {
+        key2[start + i] = (u32)(x[r] >> MK_SLOT_BITS);
+        elem[start + i] = se[(u32)x[r] & 0x7FFu];
+      }
+    }
+    team_sync<NW>();
+  }
+}
+
+// heads after a segmented round: the old group starts, and where key2 changes
+__global__ void k_pd_heads_seg(const u32* __restrict__ key2, u32 A, u32* __restrict__ head) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= A) return;
+  if (i > 0 && !head[i] && key2[i] != key2[i - 1]) head[i] = 1u;
+}
+
 #define PD_GRID(n) (unsigned)(((u64)(n) + PD_T - 1) / PD_T)
 #define PD_LAUNCH(kern, n, ...)                              \
   do {                                                       \
@@ -198,5 +291,33 @@ void pd_startflags(const u32* sa_final, const u8* isstart, u32 W, u32* flag, cud
 void pd_emit(const u32* sa_final, const u8* isstart, const u32* dst, const u32* wstart, u32 W, u32* out, cudaStream_t st) {
   PD_LAUNCH(k_pd_emit, W, sa_final, isstart, dst, wstart, W, out);
 }
+
+void pd_key2_plain(const u32* elem, const u32* rank, u32 A, u32 W, u32 off, u32* key2, cudaStream_t st) {
+  PD_LAUNCH(k_pd_key2_plain, A, elem, rank, A, W, off, key2);
+}
+void pd_seg_small(const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2, u32* lists, u32 list_cap, u32* counters,
+                  cudaStream_t st) {
+  PD_LAUNCH(k_pd_seg_small, ngroups, headslot, ngroups, A, elem, key2, lists, list_cap, counters);
+}
+template <int NW, int R>
+static void pd_seg_class(const u32* list, u32 cnt, const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2,
+                         cudaStream_t st) {
+  if (!cnt) return;
+  u32 grid = NW == 1 ? (cnt + 7) / 8 : cnt;
+  if (grid > 524288u) grid = 524288u;
+  k_pd_seg_team<NW, R><<<grid, NW == 1 ? 256 : NW * 32, 0, st>>>(list, cnt, headslot, ngroups, A, elem, key2);
+  CK_LAUNCH(); g_launches++;
+}
+void pd_seg_teams(const u32* lists, u32 list_cap, const u32* cn, const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2,
+                  cudaStream_t st) {
+  pd_seg_class<1, 1>(lists + 0ull * list_cap, cn[0], headslot, ngroups, A, elem, key2, st);
+  pd_seg_class<1, 2>(lists + 1ull * list_cap, cn[1], headslot, ngroups, A, elem, key2, st);
+  pd_seg_class<1, 4>(lists + 2ull * list_cap, cn[2], headslot, ngroups, A, elem, key2, st);
+  pd_seg_class<1, 8>(lists + 3ull * list_cap, cn[3], headslot, ngroups, A, elem, key2, st);
+  pd_seg_class<8, 2>(lists + 4ull * list_cap, cn[4], headslot, ngroups, A, elem, key2, st);
+  pd_seg_class<16, 2>(lists + 5ull * list_cap, cn[5], headslot, ngroups, A, elem, key2, st);
+  pd_seg_class<16, 4>(lists + 6ull * list_cap, cn[6], headslot, ngroups, A, elem, key2, st);
+}
+void pd_heads_seg(const u32* key2, u32 A, u32* head, cudaStream_t st) { PD_LAUNCH(k_pd_heads_seg, A, key2, A, head); }
 
 }  // namespace kiss

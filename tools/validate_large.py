@@ -40,6 +40,12 @@ for _k in (32, 64, 128, 256):
 # the chm13-like text plus 100 runs of 10^4..10^6 identical bases (the induction chain: one wave per
 # base of the longest run, all of them on the device in k_wave_tail)
 CONFIGS["c3h"] = dict(n=500_000_000, seed=5, kind="chm13h", k=256)
+# adversarial for any depth-first comparison: two EXACT copies of a 100 Mbp uniform text (LCP 10^8), -k -1: every LMS
+# suffix of the first copy is tied with its twin for up to 100 Mbp.  Rank doubling needs ~log2 rounds; the reference's
+# kISS-2 is the oracle (its kISS-1 -k -1 compares base by base)
+CONFIGS["dup2x100m"] = dict(n=200_004_096, seed=6, kind="dup2", k=0xFFFFFFFF, algo="PREFIX_DOUBLING")
+CONFIGS["dup2x100m_ps"] = dict(n=200_004_096, seed=6, kind="dup2", k=0xFFFFFFFF, algo="PARALLEL_SORTING", ref_algo="PREFIX_DOUBLING")
+CONFIGS["dup2x10m"] = dict(n=20_004_096, seed=6, kind="dup2", k=0xFFFFFFFF, algo="PREFIX_DOUBLING")
 
 _text_cache = {}
 
@@ -92,6 +98,9 @@ def _text(ctx, cfg):
             L = int(np.exp(rng.uniform(np.log(1e4), np.log(1e6))))
             p = int(rng.integers(0, n - 4096 - L))
             S[p:p + L] = int(rng.integers(0, 4))
+    if cfg["kind"] == "dup2":
+        half = (n - 4096) // 2
+        S[half:2 * half] = S[:half]
     if cfg["kind"] == "replicated":
         unit = 1 << 20
         rng = np.random.default_rng(cfg["seed"])
@@ -126,7 +135,7 @@ def main():
         sa = ctx.suffix_array_dna(S, cfg["k"], algo=algo)
         t_gpu = time.perf_counter() - t0
         tm = ctx.last_timings
-        out = dict(config=name, **{kk: vv for kk, vv in cfg.items() if kk != "property_only"}, m=tm["m"], gpu_host_call_s=t_gpu, gpu_device_s=tm["total_device"],
+        out = dict(config=name, **{kk: vv for kk, vv in cfg.items() if kk not in ("property_only", "ref_algo")}, m=tm["m"], gpu_host_call_s=t_gpu, gpu_device_s=tm["total_device"],
                    lms_sort_s=tm["lms_sort"], induce_s=tm["induce"], tied=tm["lms_sort_tied"], rounds=tm["lms_sort_rounds"],
                    waves=[tm["waves_L"], tm["waves_S"]], sa0_is_n=bool(int(sa[0]) == n), permutation=is_permutation(sa, n))
         if profile:  # second call with CUDA events around every launch (kernel class -> [ms, launches])
@@ -144,7 +153,7 @@ def main():
         elif ol.have_ref() and "--noref" not in args:
             ref = np.empty(n + 1, np.uint32)
             threads = os.cpu_count()
-            fn = ol.ref().ref_kiss2_suffix_array_dna if algo_name == "PREFIX_DOUBLING" else ol.ref().ref_kiss1_suffix_array_dna
+            fn = ol.ref().ref_kiss2_suffix_array_dna if cfg.get("ref_algo", algo_name) == "PREFIX_DOUBLING" else ol.ref().ref_kiss1_suffix_array_dna
             sec = fn(S.ctypes.data, n, cfg["k"], threads, ref.ctypes.data)
             out.update(reference_s=sec, reference_threads=threads, bit_exact=bool(np.array_equal(sa, ref)),
                        speedup_host_call=sec / t_gpu, speedup_device=sec / tm["total_device"])
