@@ -43,7 +43,7 @@ enum {
   KISS_B200_ERR_TOO_LARGE = -2,    /* n + 1 >= 2^32 - 1 (EMPTY would collide, constant.hpp:19-20) */
   KISS_B200_ERR_CUDA = -3,         /* a CUDA runtime call or kernel failed */
   KISS_B200_ERR_NOMEM = -4,        /* device allocation failed (reference: std::bad_alloc, structs.hpp:32-38) */
-  KISS_B200_ERR_UNSUPPORTED = -5,  /* bounded k so large that > 16384 LMS suffixes lie within D(k) of the text end */
+  KISS_B200_ERR_UNSUPPORTED = -5,  /* (not returned any more: every k is accepted, like the reference) */
   KISS_B200_ERR_NO_DEVICE = -6     /* no CUDA device / the CUDA library cannot run: there is no CPU fallback */
 };
 

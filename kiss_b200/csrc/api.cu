@@ -14,7 +14,6 @@
 
 using namespace kiss;
 
-#define SHORT_MAX 16384u
 
 static thread_local std::string g_last_error;
 
@@ -235,7 +234,9 @@ void do_prepare(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, float* t
     while (w < (u64)k) w <<= 1;
     pd_depth = 16ull * w < 4096ull ? 4096ull : 16ull * w;
   }
-  bool unbounded = (algo == KISS_B200_PREFIX_DOUBLING) || ((u64)k >= n);
+  // k >= n - 1 is the unbounded order: the lambda's depth rule (kiss1_core.hpp:131-133) needs two suffixes with >= k bases
+  // each, i.e. two LMS positions <= n - k <= 1, and position 0 is never an LMS position
+  bool unbounded = (algo == KISS_B200_PREFIX_DOUBLING) || ((u64)k + 1 >= n);
   P.sp.T = T; P.sp.n = n; P.sp.k = k;
   P.algo = algo;
   u32 n_long;
@@ -690,7 +691,7 @@ void do_shorts(kiss_b200_ctx* c, Pool& pool, const u32* shorts_text, u32 ns, con
                const SortParams& sp, SortedLms* out) {
   out->ns = ns;
   if (!ns) return;
-  u32* rank0 = pool.alloc<u32>(ns);
+  u32* rank0 = pool.alloc<u32>(shorts_scratch_len(ns));
   out->shorts = pool.alloc<u32>(ns);
   out->ins = pool.alloc<u32>(ns);
   shorts_order(shorts_text, ns, sp, rank0, out->shorts, c->st);
@@ -713,8 +714,6 @@ void do_sort(kiss_b200_ctx* c, Pool& pool, SortedLms* out, SortStats* stats) {
     out->ns = 0;
     return;
   }
-  if (ns > SHORT_MAX)
-    throw CudaError(KISS_B200_ERR_UNSUPPORTED, "bounded k too large: more than 16384 LMS suffixes within D(k) of the text end");
   // the shorts are the tail of the text-ordered list; copy them out before the sort permutes the buffers
   u32* shorts_text = pool.alloc<u32>(ns);
   if (ns) CK(cudaMemcpyAsync(shorts_text, P.pos + P.n_long, ns * sizeof(u32), cudaMemcpyDeviceToDevice, c->st));
@@ -1375,7 +1374,6 @@ static int finish_from_sorted(kiss_b200_ctx* c, const uint32_t* sorted_long_dev,
     auto& P = c->prep;
     u64 l0 = g_launches;
     u32 ns = (u32)(P.m1 - P.n_long);
-    if (ns > SHORT_MAX) throw CudaError(KISS_B200_ERR_UNSUPPORTED, "bounded k too large");
     CK(cudaEventRecord(c->ev[4], st));
     SortedLms sl;
     sl.longs = const_cast<u32*>(sorted_long_dev);

@@ -166,7 +166,9 @@ void gather_keys(const u64* T, const u32* pos, u32 N, u32* key, cudaStream_t st)
 void dest_by_splitters(const u32* key, u32 N, const u32* spl, u32 nspl, u32* dest, u32* counts, cudaStream_t st);
 
 // short suffixes (fewer than D bases left): exact reference comparator (kiss1_core.hpp:94-135)
+// rank0: scratch of shorts_scratch_len(ns) entries
 void shorts_order(const u32* shorts, u32 ns, SortParams sp, u32* rank0, u32* sorted_shorts, cudaStream_t st);
+inline u64 shorts_scratch_len(u64 ns) { u64 p = 1; while (p < ns) p <<= 1; return p; }
 void shorts_insertions(const u32* sorted_shorts, u32 ns, const u32* longs, u32 nl, SortParams sp, u32* ins,
                        cudaStream_t st);
 

@@ -1039,9 +1039,40 @@ __global__ void __launch_bounds__(128) k_short_place(const u32* __restrict__ sho
   sorted_shorts[r] = shorts[s];
 }
 
+// Many short suffixes (a bounded k that is a large part of n): a bitonic network in global memory with the same
+// comparator — O(ns log^2 ns) comparisons where the all-pairs ranking above is O(ns^2).  The comparator is a total order
+// on distinct positions whenever it is transitive; where it is not the reference's own std::sort result
+// is unspecified too.  a[] is padded to a power of two with KISS_EMPTY = +infinity.
+__global__ void __launch_bounds__(256) k_short_bitonic(u32* __restrict__ a, u32 npad, u32 k2, u32 j, SortParams sp) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npad) return;
+  const u32 p = i ^ j;
+  if (p <= i) return;
+  const u32 x = a[i], y = a[p];
+  const bool y_first = x == KISS_EMPTY ? y != KISS_EMPTY : (y != KISS_EMPTY && ref_less(sp, y, x));
+  const bool asc = (i & k2) == 0;
+  if (y_first == asc) { a[i] = y; a[p] = x; }
+}
+#define SHORT_ALLPAIRS_MAX 4096u
+
 void shorts_order(const u32* shorts, u32 ns, SortParams sp, u32* rank0, u32* sorted_shorts, cudaStream_t st) {
   if (!ns) return;
   ProfScope ps(PK_SHORTS, st);
+  if (ns > SHORT_ALLPAIRS_MAX) {
+    // rank0 is the network's work array here: shorts_scratch_len(ns) entries
+    u32 npad = 1;
+    while (npad < ns) npad <<= 1;
+    CK(cudaMemsetAsync(rank0, 0xFF, (u64)npad * sizeof(u32), st));
+    CK(cudaMemcpyAsync(rank0, shorts, (u64)ns * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    for (u32 k2 = 2; k2 <= npad; k2 <<= 1)
+      for (u32 j = k2 >> 1; j > 0; j >>= 1) {
+        k_short_bitonic<<<(npad + 255) / 256, 256, 0, st>>>(rank0, npad, k2, j, sp);
+        CK_LAUNCH();
+        g_launches++;
+      }
+    CK(cudaMemcpyAsync(sorted_shorts, rank0, (u64)ns * sizeof(u32), cudaMemcpyDeviceToDevice, st));
+    return;
+  }
   k_short_rank<<<(ns + 127) / 128, 128, 0, st>>>(shorts, ns, sp, rank0);
   CK_LAUNCH();
   k_short_place<<<(ns + 127) / 128, 128, 0, st>>>(shorts, ns, rank0, sorted_shorts);

@@ -287,3 +287,22 @@ def test_sa_checksum_is_the_documented_sum(ctx):
         want = int(tg.sm64((np.arange(a.size, dtype=np.uint64) << np.uint64(32)) | a.astype(np.uint64)).sum(dtype=np.uint64))
     assert ctx.sa_checksum_dev(d.data_ptr(), a.size) == want
     assert ctx.sa_checksum_dev(d.data_ptr(), 0) == 0
+
+
+@pytest.mark.parametrize("kname", ["60000", "n-1", "n-2", "n/2", "n/3"])
+@pytest.mark.parametrize("name,gen", [c for c in CASES if c[0] in ("uniform200k", "repeats", "mixed", "uniform4097", "uniform100")],
+                         ids=["uniform100", "uniform4097", "uniform200k", "repeats", "mixed"])
+def test_any_bounded_k_is_accepted(ctx, name, gen, kname):
+    """k that is a large part of n: tens of thousands of LMS suffixes have fewer than D(k) bases left and go through the
+    reference's depth-shrinking comparator (kiss1_core.hpp:94-135) — a bitonic network on it above 4096 of them; k >= n - 1
+    is the unbounded order.  The reference accepts every k; so does this (round 1 refused above 16384 short suffixes)."""
+    S = gen()
+    n = S.size
+    k = {"60000": 60000, "n-1": n - 1, "n-2": n - 2, "n/2": n // 2, "n/3": n // 3}[kname]
+    if k < 2:
+        pytest.skip("k < 2")
+    want = ol.oracle_kiss1(S, k=k)
+    got = ctx.suffix_array_dna(S, k)
+    bad = np.nonzero(got != want)[0]
+    assert bad.size == 0, f"{bad.size} mismatches, first at {bad[:5]}"
+    assert np.array_equal(ctx.sorted_lms(S, k), ol.oracle_kiss1(S, k=k, stages=True)["sorted"])
