@@ -733,8 +733,9 @@ void fill_timings(kiss_b200_timings* t, float pack, float lms, float sort, float
 enum Stop { STOP_LMS, STOP_SORT, STOP_PUT, STOP_FULL };
 
 // the whole path on device-resident data; `stage_out` receives the stage's array when stopping early
+// `keep_ctx` (n + 1 words, caller-owned): the induction's context array is left there (the FM-index scan reads it)
 void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* dSA, Stop stop, kiss_b200_timings* t,
-                  CopyOut* co = nullptr) {
+                  CopyOut* co = nullptr, u32* keep_ctx = nullptr) {
   cudaStream_t st = c->st;
   u64 launches0 = g_launches;
   float t_pack = 0, t_lms = 0, t_sort = 0, t_put = 0, t_ind = 0;
@@ -762,7 +763,7 @@ void run_pipeline(kiss_b200_ctx* c, const u8* dS, u64 n, u32 k, int algo, u32* d
       place_lms(sl.longs, sl.nl, sl.shorts, sl.ins, sl.ns, bk, n, dSA, nullptr, st);
     } else {
       // the full path never places: the L pass scans the sorted list itself (put_lms_suffix is folded into it)
-      dCTX = pool.alloc<u32>(n + 1);
+      dCTX = keep_ctx ? keep_ctx : pool.alloc<u32>(n + 1);
       lms = sl.longs;  // the LMS waves read the merged list on the fly (induce_wave, VIRT): no merge pass
     }
     CK(cudaEventRecord(c->ev[5], st));
@@ -965,7 +966,8 @@ FmLayout fm_layout(u64 n, u32 intv) {
 void put_u64(u8* p, u64 v) { memcpy(p, &v, 8); }
 
 // T = packed text (may be null when n == 0), dSA = the n + 1 suffix array entries on the device; writes the image
-void do_fmindex(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const u32* dSA, u32 intv, u8* image, float* ms) {
+void do_fmindex(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const u32* dSA, const u32* dCTX, u32 intv, u8* image,
+                float* ms) {
   cudaStream_t st = c->st;
   const FmLayout L = fm_layout(n, intv);
   CK(cudaEventRecord(c->ev[7], st));
@@ -986,7 +988,13 @@ void do_fmindex(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const u32* dS
     CK(cudaMemsetAsync(b32 + 2 * (L.b_words - 1), 0, 8, st));  // the last word may be written by half
     CK(cudaMemsetAsync(bocc, 0, L.nb * sizeof(u32), st));
   }
-  fm_scan(dSA, L.N, T, intv, bwt32, tot, n1p, occ2, L.n2, b32, bocc, totals + 4, st);
+  fm_scan(dSA, dCTX, L.N, T, intv, bwt32, tot, n1p, occ2, L.n2, b32, bocc, totals + 4, st);
+  // what the scan finished leaves on the copy stream while the prefix sums and the compaction run
+  CK(cudaEventRecord(c->ev_aux, st));
+  CK(cudaStreamWaitEvent(c->st_copy, c->ev_aux, 0));
+  CK(cudaMemcpyAsync(image + L.o_bwt, bwt32, L.by_bwt, cudaMemcpyDeviceToHost, c->st_copy));
+  CK(cudaMemcpyAsync(image + L.o_occ2, occ2, L.by_occ2, cudaMemcpyDeviceToHost, c->st_copy));
+  if (intv != 1) CK(cudaMemcpyAsync(image + L.o_b, b32, L.by_b, cudaMemcpyDeviceToHost, c->st_copy));
   for (int s = 0; s < 4; s++) scan_excl_u32(tot + s * n1p, L.n1, partials, totals + s, st);
   fm_occ1(tot, n1p, L.n1, occ1, st);
   if (intv != 1) {
@@ -996,15 +1004,11 @@ void do_fmindex(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const u32* dS
   CK(cudaEventRecord(c->ev[0], st));
   u32 h[5];
   CK(cudaMemcpyAsync(h, totals, 5 * sizeof(u32), cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(image + L.o_bwt, bwt32, L.by_bwt, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(image + L.o_occ1, occ1, L.by_occ1, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(image + L.o_occ2, occ2, L.by_occ2, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(image + L.o_sa, intv == 1 ? dSA : sa_out, L.by_sa, cudaMemcpyDeviceToHost, st));
-  if (intv != 1) {
-    CK(cudaMemcpyAsync(image + L.o_b, b32, L.by_b, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(image + L.o_bocc, bocc, L.by_bocc, cudaMemcpyDeviceToHost, st));
-  }
+  if (intv != 1) CK(cudaMemcpyAsync(image + L.o_bocc, bocc, L.by_bocc, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  CK(cudaStreamSynchronize(c->st_copy));
   // cnt_[c] = 1 + number of symbols smaller than c (fm_index.hpp:305-309); pri_; the section counts; lookup_ = {0, N}
   u32 cnt[4], acc = 1;
   for (int s = 0; s < 4; s++) { cnt[s] = acc; acc += h[s]; }
@@ -1048,11 +1052,12 @@ void run_fm_host(kiss_b200_ctx* c, const u8* S_host, u64 n, int input, u32 k, in
   CK(cudaStreamSynchronize(st));
   const double h2d = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
   u32* dSA = pool.alloc<u32>(n + 1);
+  u32* dCTX = n ? pool.alloc<u32>(n + 1) : nullptr;
   kiss_b200_timings tt;
   memset(&tt, 0, sizeof(tt));
   const u64* T = nullptr;
   if (n) {
-    run_pipeline(c, dS, n, k, algo, dSA, STOP_FULL, &tt);
+    run_pipeline(c, dS, n, k, algo, dSA, STOP_FULL, &tt, nullptr, dCTX);
     T = c->prep.T;
   } else {
     CK(cudaMemsetAsync(dSA, 0, sizeof(u32), st));
@@ -1061,7 +1066,7 @@ void run_fm_host(kiss_b200_ctx* c, const u8* S_host, u64 n, int input, u32 k, in
   pool.release(dS);
   float ms = 0;
   const auto w1 = std::chrono::steady_clock::now();
-  do_fmindex(c, pool, T, n, dSA, intv, image, &ms);
+  do_fmindex(c, pool, T, n, dSA, dCTX, intv, image, &ms);
   tt.h2d = h2d;
   tt.d2h = std::chrono::duration<double>(std::chrono::steady_clock::now() - w1).count() - ms * 1e-3;
   if (t) *t = tt;
@@ -1485,7 +1490,7 @@ int kiss_b200_fmindex_from_sa_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64
     u64* T = pool.alloc<u64>(packed_words(n));
     if (n) pack_codes(S_dev, n, T, c->st);
     float ms = 0;
-    do_fmindex(c, pool, T, n, SA_dev, sa_intv, image_host, &ms);
+    do_fmindex(c, pool, T, n, SA_dev, nullptr, sa_intv, image_host, &ms);
     if (fm_seconds) *fm_seconds = ms * 1e-3;
   });
 }

@@ -11,8 +11,9 @@
 //           SA == 0 counts for nothing (:295-297); cnt_[c] = 1 + number of symbols smaller than c
 //   b_      one bit per entry: SA[i] % SA_INTV == 0; b_occ_: per 64 entries the exclusive prefix of its popcounts
 //   sa_     the entries with SA[i] % SA_INTV == 0, in suffix-array order
-// One pass over SA (k_fm_scan: one block = one 256-entry row; the only random access is the text gather, one base per
-// entry), three small scans, one more pass over SA for the compaction (k_fm_sample).  Algorithmic bytes: 2 x 4N (SA
+// One pass over SA (k_fm_scan: one block = one 256-entry row; the base before a suffix comes from the context word the
+// induction left beside every entry, so only one entry in sixteen gathers from the text: C3 69.6 -> see DESIGN.md),
+// three small scans, one more pass over SA for the compaction (k_fm_sample).  Algorithmic bytes: 2 x 4N (SA
 // reads) + N / 4 (gathered text, ideal) + 1.75 N written.
 #include "common.cuh"
 #include "kernels.h"
@@ -21,7 +22,8 @@ namespace kiss {
 
 #define FM_ROW 256u
 
-__global__ void __launch_bounds__(FM_ROW) k_fm_scan(const u32* __restrict__ SA, u64 N, const u64* __restrict__ T, u32 intv,
+__global__ void __launch_bounds__(FM_ROW) k_fm_scan(const u32* __restrict__ SA, const u32* __restrict__ CTX, u64 N,
+                                                   const u64* __restrict__ T, u32 intv,
                                                    u32* __restrict__ bwt32, u32* __restrict__ tot /* [4][n1: the plane stride] */, u64 n1,
                                                    u8* __restrict__ occ2, u64 n2, u32* __restrict__ b32,
                                                    u32* __restrict__ bocc_raw, u32* __restrict__ pri) {
@@ -32,7 +34,13 @@ __global__ void __launch_bounds__(FM_ROW) k_fm_scan(const u32* __restrict__ SA, 
   const bool valid = i < N;
   const u32 v = valid ? SA[i] : 1u;
   const bool counted = valid && v != 0;
-  const u32 c = counted ? base_at(T, (u64)v - 1) : 0u;
+  // the base before the suffix: the induction left it in the low bits of the entry's context word (induce.cu); the text
+  // is gathered only where a context had run out (about one entry in sixteen)
+  u32 c = 0;
+  if (counted) {
+    const u32 cx = CTX ? CTX[i] : 1u;
+    c = cx > 1u ? (cx & 3u) : base_at(T, (u64)v - 1);
+  }
   if (valid && v == 0) *pri = (u32)i;
   // bwt: 4 entries per byte, 16 per word; lanes 0 and 16 of a warp store one word each
   u32 x = c << (2 * (lane & 15u));
@@ -96,10 +104,10 @@ __global__ void __launch_bounds__(256) k_fm_sample(const u32* __restrict__ SA, u
   sa_out[bocc[i >> 6] + before] = v;
 }
 
-void fm_scan(const u32* SA, u64 N, const u64* T, u32 intv, u32* bwt32, u32* tot, u64 n1, u8* occ2, u64 n2, u32* b32,
+void fm_scan(const u32* SA, const u32* CTX, u64 N, const u64* T, u32 intv, u32* bwt32, u32* tot, u64 n1, u8* occ2, u64 n2, u32* b32,
              u32* bocc_raw, u32* pri, cudaStream_t st) {
   const u64 rows = (N + FM_ROW - 1) / FM_ROW;
-  k_fm_scan<<<(unsigned)rows, FM_ROW, 0, st>>>(SA, N, T, intv, bwt32, tot, n1, occ2, n2, b32, bocc_raw, pri);
+  k_fm_scan<<<(unsigned)rows, FM_ROW, 0, st>>>(SA, CTX, N, T, intv, bwt32, tot, n1, occ2, n2, b32, bocc_raw, pri);
   CK_LAUNCH(); g_launches++;
 }
 void fm_occ1(const u32* tot, u64 stride, u64 n1, u32* occ1, cudaStream_t st) {

@@ -203,7 +203,8 @@ void pd_emit(const u32* sa_final, const u8* isstart, const u32* dst, const u32* 
 // N = n + 1 suffix array entries.  bwt32: ceil(N / 16) words; tot: 4 planes (stride n1 >= N / 256 + 1, a multiple of 4) of block counts (zeroed by the
 // caller; scanned per plane afterwards); occ2: n2 = N / 16 + 1 rows of 4 bytes (zeroed by the caller); b32 (nullable:
 // SA_INTV = 1): ceil(N / 32) words; bocc_raw: N / 64 + 1 counts (zeroed by the caller); pri: one word
-void fm_scan(const u32* SA, u64 N, const u64* T, u32 intv, u32* bwt32, u32* tot, u64 n1, u8* occ2, u64 n2, u32* b32,
+// CTX (nullable): the induction's context word of every entry (low two bits = the base before the suffix when > 1)
+void fm_scan(const u32* SA, const u32* CTX, u64 N, const u64* T, u32 intv, u32* bwt32, u32* tot, u64 n1, u8* occ2, u64 n2, u32* b32,
              u32* bocc_raw, u32* pri, cudaStream_t st);
 void fm_occ1(const u32* tot_scanned, u64 stride, u64 n1, u32* occ1, cudaStream_t st);
 void fm_sample(const u32* SA, u64 N, u32 intv, const u32* b32, const u32* bocc_scanned, u32* sa_out, cudaStream_t st);
