@@ -92,6 +92,15 @@ void* kiss_b200_stream(kiss_b200_ctx* ctx);
 int kiss_b200_suffix_sort_dna_u32(kiss_b200_ctx* ctx, const uint8_t* S_host, uint64_t n, uint32_t k,
                                   int algo, uint32_t* SA_host, kiss_b200_timings* t);
 
+/* The same call over several GPUs of one node (the `n_gpus` argument; 8(e)): ctxs[0..n_gpus) are contexts
+ * on the GPUs to use (one each; several contexts on one device also work and are what the 1-GPU tests use).  Only the LMS
+ * sort shards — the text is uploaded to every GPU over its own PCIe link, rank r sorts the key range chosen by sampled
+ * first-16-base splitters, LMS positions move by peer copies over NVLink, placement and induction run on ctxs[0] — and the
+ * result is bit-identical to the single-GPU call.  One host thread per GPU inside the call; PREFIX_DOUBLING, k >= n - 1
+ * and texts below 64 Ki bases run on ctxs[0] alone. */
+int kiss_b200_suffix_sort_dna_u32_multi(kiss_b200_ctx** ctxs, int n_gpus, const uint8_t* S_host, uint64_t n, uint32_t k,
+                                        int algo, uint32_t* SA_host, kiss_b200_timings* t);
+
 /* Same, text and suffix array resident in device memory (no PCIe in the timed region).
  * S_dev must be 16-byte aligned. */
 int kiss_b200_suffix_sort_dna_u32_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, uint32_t k,

@@ -6,7 +6,7 @@ include/kiss_b200.h).  This package is the thin Python host side used by the tes
 (include/biovoltron/algo/sort/kiss1_sorter.hpp:7-50, kiss2_sorter.hpp:7-50).
 """
 from ._cabi import (EMPTY, PARALLEL_SORTING, PREFIX_DOUBLING, UNBOUNDED_K, KissB200Error, Timings, lib)
-from .sorter import Context, KISS1Sorter, KISS2Sorter, default_context
+from .sorter import Context, KISS1Sorter, KISS2Sorter, default_context, suffix_array_dna_multi
 
-__all__ = ["Context", "KISS1Sorter", "KISS2Sorter", "default_context", "KissB200Error", "Timings", "lib",
+__all__ = ["Context", "KISS1Sorter", "KISS2Sorter", "default_context", "suffix_array_dna_multi", "KissB200Error", "Timings", "lib",
            "EMPTY", "PARALLEL_SORTING", "PREFIX_DOUBLING", "UNBOUNDED_K"]

@@ -10,6 +10,7 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <cstdlib>
 #include <iterator>
 #include <memory>
 #include <new>
@@ -52,6 +53,25 @@ inline kiss_b200_ctx* context() {
   return ctx.get();
 }
 
+// number of GPUs the sorter facades use: the opt-in knob of SURVEY.md 8(b) — `gpus() = N`, or the environment variable
+// KISS_B200_GPUS; default 1 (the reference has no such notion).  Devices device_index() .. device_index() + N - 1.
+inline int& gpus() {
+  static int g = [] { const char* e = std::getenv("KISS_B200_GPUS"); int v = e ? std::atoi(e) : 1; return v > 0 ? v : 1; }();
+  return g;
+}
+inline std::vector<kiss_b200_ctx*>& contexts_multi(int n) {
+  thread_local std::vector<std::unique_ptr<kiss_b200_ctx, CtxDeleter>> own;
+  thread_local std::vector<kiss_b200_ctx*> raw;
+  while ((int)own.size() < n) {
+    kiss_b200_ctx* r = nullptr;
+    int rc = kiss_b200_create(&r, device_index() + (int)own.size());
+    if (rc != KISS_B200_OK) throw std::runtime_error(std::string("kiss_b200: ") + kiss_b200_last_error());
+    own.emplace_back(r);
+    raw.push_back(r);
+  }
+  return raw;
+}
+
 inline void raise(int rc) {
   if (rc == KISS_B200_OK) return;
   if (rc == KISS_B200_ERR_NOMEM) throw std::bad_alloc();
@@ -67,6 +87,12 @@ inline kiss_b200_timings& last_timings() {
 // any one-byte character type (the reference's callers pass uint8_t, int8_t or char: only the low two bits are read)
 inline void suffix_array_dna(const void* codes, std::size_t n, vector<std::uint32_t>& SA, std::uint32_t k, int algo) {
   SA.resize(n + 1);
+  if (gpus() > 1) {
+    auto& cs = contexts_multi(gpus());
+    raise(kiss_b200_suffix_sort_dna_u32_multi(cs.data(), gpus(), static_cast<const std::uint8_t*>(codes), n, k, algo,
+                                              SA.data(), &last_timings()));
+    return;
+  }
   raise(kiss_b200_suffix_sort_dna_u32(context(), static_cast<const std::uint8_t*>(codes), n, k, algo, SA.data(),
                                       &last_timings()));
 }

@@ -39,6 +39,7 @@ void usage(std::ostream& os) {
         "  -t [ --num_threads ] NUM  number of thread (accepted, unused: the GPU path has no host threads)\n"
         "  --verbose                 print more information\n"
         "  --gpu IDX                 CUDA device (default 0)\n"
+        "  --gpus N                  shard the LMS sort over N GPUs starting at --gpu (default 1; implies --host-ingest)\n"
         "  --host-ingest             parse the file on the host (the reference's serial getline loop) instead of on the device\n\n"
         "./kISS suffix_sort [--option ...] <FASTA filename/Text filename>\n\n"
         "Options:\n"
@@ -97,7 +98,7 @@ std::vector<std::uint8_t> read_sequence(std::istream& fin) {
 struct Args {
   bool help = false, version = false, generic = false, verbose = false, host_ingest = false;
   std::size_t threads = std::thread::hardware_concurrency();
-  int gpu = 0;
+  int gpu = 0, gpus = 1;
   std::string command, file, out;
   std::size_t k = 256;
   int algo = KISS_B200_PARALLEL_SORTING;
@@ -140,6 +141,7 @@ Args parse(int argc, char** argv) {
     else if (flag == "--verbose") a.verbose = true;
     else if (flag == "-t" || flag == "--num_threads") a.threads = parse_size(value(flag));
     else if (flag == "--gpu") a.gpu = (int)parse_size(value(flag));
+    else if (flag == "--gpus") a.gpus = (int)parse_size(value(flag));
     else if (flag == "--out") a.out = value(flag);
     else if (flag == "--host-ingest") a.host_ingest = true;
     else if (flag == "-k" || flag == "--kordered") a.k = parse_size(value(flag));
@@ -165,12 +167,14 @@ int suffix_sort_main(const Args& a) {
   std::ifstream fa(a.file, std::ios::binary);
   if (!fa) throw std::invalid_argument("cannot open " + a.file);
   biovoltron::kiss::b200::device_index() = a.gpu;
+  if (a.gpus > 1) biovoltron::kiss::b200::gpus() = a.gpus;
   auto k32 = (std::uint32_t)a.k;  // narrows at the call like suffix_sort.hpp:59
   biovoltron::kiss::vector<std::uint32_t> sa;
   std::uint64_t n_text = 0;
   double sec = 0;
-  if (a.host_ingest) {
-    // the reference's way: parse on the host (serial getline), then the sorter facade on the codes
+  if (a.host_ingest || a.gpus > 1) {
+    // the reference's way: parse on the host (serial getline), then the sorter facade on the codes (the facade shards the
+    // LMS sort over --gpus N GPUs: kiss_b200_suffix_sort_dna_u32_multi)
     auto seq = read_sequence(fa);
     n_text = seq.size();
     auto t0 = std::chrono::steady_clock::now();

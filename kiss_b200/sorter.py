@@ -239,6 +239,18 @@ class Context:
         check(lib().kiss_b200_synth_uniform_dev(self._h, S_ptr, n, seed))
 
 
+def suffix_array_dna_multi(contexts, S, k=256, algo=PARALLEL_SORTING):
+    """kiss_b200_suffix_sort_dna_u32_multi: the sharded LMS sort over the GPUs of `contexts` (a list of Context), host
+    buffers in and out; returns (suffix array, timings dict)"""
+    S = _codes(S)
+    SA = np.empty(S.size + 1, np.uint32)
+    arr = (C.c_void_p * len(contexts))(*[c.handle.value for c in contexts])
+    t = Timings()
+    check(lib().kiss_b200_suffix_sort_dna_u32_multi(arr, len(contexts), S.ctypes.data, S.size, k & 0xFFFFFFFF, algo,
+                                                    SA.ctypes.data, C.byref(t)))
+    return SA, t.as_dict()
+
+
 _default = None
 
 
