@@ -475,14 +475,62 @@ def run_b200(args):
             del himg, himg_np
             hSA = None
         else:
+            # N > 1: ONE host text buffer and ONE host suffix-array buffer shared by the rank processes (POSIX shared
+            # memory, page-locked in every process).  Rank r uploads slice r of the text over ITS OWN PCIe link, an NCCL
+            # all-gather over NVLink completes the text on every GPU, the sharded sort and the induction run, rank 0
+            # scatters the suffix array over NVLink and every rank drains its slice through its own link into the shared
+            # buffer: the 15.6 GB that cross PCIe are spread over N links instead of rank 0's one.
+            from multiprocessing import shared_memory
+            chunk = ((n + world - 1) // world + 15) // 16 * 16
+            cs = (n + 1 + world - 1) // world
+            off_sa = (n + 4095) // 4096 * 4096
+            size = off_sa + 4 * (n + 1)
+            name = f"kiss_b200_bench_{os.environ.get('MASTER_PORT', '0')}"
+            if rank == 0:
+                try:
+                    shared_memory.SharedMemory(name=name).unlink()
+                except Exception:
+                    pass
+                shm = shared_memory.SharedMemory(create=True, size=size, name=name)
+            dist.barrier()
+            if rank != 0:
+                shm = shared_memory.SharedMemory(name=name)
+            hb = np.ndarray((size,), np.uint8, buffer=shm.buf)
+            sh_S = torch.from_numpy(hb[:n])
+            sh_SA = torch.from_numpy(hb[off_sa:off_sa + 4 * (n + 1)].view(np.int32))
+            if rank == 0:
+                sh_S.copy_(hS)
+            del hS, hSA
+            hS = hSA = None
+            dist.barrier()
+            Sg = torch.empty(chunk * world + 64, dtype=torch.uint8, device="cuda")   # the text, gathered
+            myslice = torch.empty(cs, dtype=torch.int32, device="cuda")
+            SAp = torch.empty(cs * world, dtype=torch.int32, device="cuda") if rank == 0 else None
+            del S, SA
+            torch.cuda.empty_cache()
+            lo, hi = min(n, rank * chunk), min(n, (rank + 1) * chunk)
+            slo, shi = min(n + 1, rank * cs), min(n + 1, (rank + 1) * cs)
+            # page-lock what this rank moves: its slice of the text and its slice of the array (whole pages)
+            registered = []
+            for b0, b1 in ((lo, hi), (off_sa + 4 * slo, off_sa + 4 * shi)):
+                p0, p1 = b0 // 4096 * 4096, min(size, (b1 + 4095) // 4096 * 4096)
+                if p1 > p0:
+                    hb[p0:p1:4096] |= 0                                   # (touch: the pages exist before they are locked)
+                    rc = int(torch.cuda.cudart().cudaHostRegister(hb.ctypes.data + p0, p1 - p0, 0))
+                    if rc == 0:
+                        registered.append(hb.ctypes.data + p0)
+                    else:
+                        print(f"[bench] rank {rank}: cudaHostRegister failed with code {rc}; that slice stays pageable", file=sys.stderr)
+
             def e2e_step():
-                if rank == 0:
-                    S[:n].copy_(hS, non_blocking=True)
-                dist.broadcast(S, src=0)
+                if hi > lo:
+                    Sg[lo:hi].copy_(sh_S[lo:hi], non_blocking=True)
+                dist.all_gather_into_tensor(Sg[:chunk * world], Sg[rank * chunk:(rank + 1) * chunk])
                 torch.cuda.synchronize()
-                sharded_suffix_array_dev(ctx, S, n, SA, k, dist)
-                if rank == 0:
-                    hSA.copy_(SA, non_blocking=True)
+                sharded_suffix_array_dev(ctx, Sg, n, SAp if rank == 0 else myslice, k, dist)
+                dist.scatter(myslice, [SAp[i * cs:(i + 1) * cs] for i in range(world)] if rank == 0 else None, src=0)
+                if shi > slo:
+                    sh_SA[slo:shi].copy_(myslice[:shi - slo], non_blocking=True)
                 torch.cuda.synchronize()
             for _ in range(2):  # warm-up
                 e2e_step()
@@ -495,11 +543,25 @@ def run_b200(args):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             sec = float(tt.item())
             if rank == 0:
-                assert (int(hSA[0]) & 0xFFFFFFFF) == n
+                # the shared host buffer holds the whole array: its first entry, and 1 M random entries against the device copy
+                assert (int(sh_SA[0]) & 0xFFFFFFFF) == n
+                idx = torch.randint(0, n + 1, (1_000_000,))
+                assert torch.equal(sh_SA[idx], SAp[idx.cuda()].cpu()), "host suffix array differs from the device copy"
                 line["e2e"] = {"value": (n + 1) / sec / 1e9, "unit": "Gsuffixes/s", "h2d_bytes_per_step": n,
                                "d2h_bytes_per_step": 4 * (n + 1), "ms_per_step": sec * 1e3,
-                               "note": "rank 0 uploads, NCCL broadcast of the text to the other ranks, rank 0 reads the SA back"}
-        del hS, hSA
+                               "pinned": len(registered) == 2,
+                               "note": f"one shared host buffer (page-locked slice by slice); every rank uploads 1/{world} of the text and drains "
+                                       f"1/{world} of the suffix array through its own PCIe link; NCCL all-gather of the text "
+                                       "and scatter of the array over NVLink in between"}
+            del sh_S, sh_SA
+            for ptr in registered:
+                torch.cuda.cudart().cudaHostUnregister(ptr)
+            del hb
+            dist.barrier()
+            shm.close()
+            if rank == 0:
+                shm.unlink()
+        hS = hSA = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_baseline(wl, k, args.cpu_sample)

@@ -235,6 +235,10 @@ int kiss_b200_profile_read(kiss_b200_ctx* ctx, int idx, const char** name, doubl
  * read + written; tie-group classes: 16 B per LMS suffix in the groups refined); else 0 */
 int kiss_b200_profile_alg_bytes(kiss_b200_ctx* ctx, int idx, uint64_t* bytes);
 
+/* kernels launched so far by the calling host thread through this library (a counter, not a CUDA query): callers that
+ * drive the device-stage entries themselves (kiss_b200/multi_gpu.py) report the difference as their launch count */
+uint64_t kiss_b200_launch_count(void);
+
 /* ---- result digest (parity at sizes where the array itself cannot be kept: SURVEY.md 8(c), tests/golden) -----------
  * *out = sum over i < count of splitmix64((i << 32) | SA_dev[i]) mod 2^64: an order-sensitive checksum of a suffix array
  * that is a plain sum, so one streaming pass computes it on the device.  tests/golden/full_size_golden.json holds the

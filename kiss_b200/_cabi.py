@@ -67,6 +67,7 @@ SIGNATURES = {
     "kiss_b200_profile_enable": (_int, [_vp, _int]),
     "kiss_b200_profile_read": (_int, [_vp, _int, C.POINTER(C.c_char_p), C.POINTER(C.c_double), C.POINTER(_u64)]),
     "kiss_b200_profile_alg_bytes": (_int, [_vp, _int, C.POINTER(_u64)]),
+    "kiss_b200_launch_count": (_u64, []),
     "kiss_b200_sa_checksum_dev": (_int, [_vp, _vp, _u64, C.POINTER(_u64)]),
     "kiss_b200_synth_uniform_dev": (_int, [_vp, _vp, _u64, _u64]),
 }

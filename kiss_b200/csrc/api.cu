@@ -1495,6 +1495,8 @@ int kiss_b200_fmindex_from_sa_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64
   });
 }
 
+uint64_t kiss_b200_launch_count(void) { return g_launches; }
+
 int kiss_b200_sa_checksum_dev(kiss_b200_ctx* c, const uint32_t* SA_dev, uint64_t count, uint64_t* out) {
   if (!out || (count && !SA_dev)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   return guarded(c, [&] {

@@ -290,7 +290,38 @@ __device__ __forceinline__ void tile_fetch(E* sdst, const E* __restrict__ g, u32
   }
 }
 
-template <typename K, int NMATCH>
+// ---- TMA bulk copies (cp.async.bulk, SASS UBLKCP) for full tiles: ONE elected thread arms an mbarrier with the tile's byte
+// count and issues two bulk copies (keys, values: 16 / 32 KB + 16 KB), the copy engine moves the tile and completes the
+// barrier's transaction count, every thread waits on the barrier's phase — against 8-12 LDGSTS (cp.async 16 B) plus
+// address arithmetic per thread and tile.  The shared-memory buffers are also written by ordinary stores (the staging
+// of the previous tile): a fence.proxy.async orders those before the copy engine's writes.
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64* bar, u32 count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(u64* bar, u32 bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, u32 bytes, u64* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64* bar, u32 parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+
+template <typename K, int NMATCH, bool BULK = false>
 __global__ void __launch_bounds__(RADIX_THREADS, (sizeof(K) == 4 ? RADIX_MINB32 : (RADIX_THREADS == 256 ? 2 : 1)))
 k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __restrict__ kout, u32* __restrict__ vout,
                   u32 N, int shift, u32 mask, const u32* __restrict__ H, u32 ntiles) {
@@ -308,12 +339,35 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
   const u32 lt_mask = (1u << lane) - 1u;
   u32 tile = blockIdx.x;
   if (tile >= ntiles) return;
-  {
-    u32 tb = tile * RADIX_TILE, nv = min((u32)RADIX_TILE, N - tb);
-    tile_fetch<K>(kbuf0, kin, tb, nv);
-    tile_fetch<u32>(vbuf0, vin, tb, nv);
+  __shared__ __align__(8) u64 s_bar[2];  // one per buffer (BULK)
+  // fetch of one tile into buffer `b`: a full tile by two bulk copies, a ragged one by the per-thread cp.async loop
+  auto fetch = [&](u32 t, u32 b) {
+    const u32 tb = t * RADIX_TILE, nv = min((u32)RADIX_TILE, N - tb);
+    K* kd = b ? kbuf1 : kbuf0;
+    u32* vd = b ? vbuf1 : vbuf0;
+    if (BULK && nv == RADIX_TILE) {
+      if (tid == 0) {
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+        mbar_expect_tx(&s_bar[b], RADIX_TILE * (u32)(sizeof(K) + 4));
+        bulk_g2s(kd, kin + tb, RADIX_TILE * (u32)sizeof(K), &s_bar[b]);
+        bulk_g2s(vd, vin + tb, RADIX_TILE * 4u, &s_bar[b]);
+      }
+    } else {
+      tile_fetch<K>(kd, kin, tb, nv);
+      tile_fetch<u32>(vd, vin, tb, nv);
+    }
     asm volatile("cp.async.commit_group;\n" ::);
+  };
+  u32 uses[2] = {0u, 0u};  // bulk fills waited for, per buffer (the barrier's phase parity)
+  if (BULK) {
+    if (tid == 0) {
+      mbar_init(&s_bar[0], 1);
+      mbar_init(&s_bar[1], 1);
+      asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    }
+    __syncthreads();
   }
+  fetch(tile, 0);
   u32 hb_next = tid < 256 ? H[(u64)tid * ntiles + tile] : 0u;
   for (u32 it = 0; tile < ntiles; tile += gridDim.x, it++) {
     K* kb = (it & 1) ? kbuf1 : kbuf0;
@@ -322,6 +376,10 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
     const u32 tile_base = tile * RADIX_TILE;
     const u32 tile_n = min((u32)RADIX_TILE, N - tile_base);
     asm volatile("cp.async.wait_group 0;\n" ::);
+    if (BULK && tile_n == RADIX_TILE) {
+      mbar_wait(&s_bar[it & 1], uses[it & 1] & 1u);
+      uses[it & 1]++;
+    }
     __syncthreads();  // the whole tile has landed
     K keys[RADIX_ITEMS];
     u32 vals[RADIX_ITEMS];
@@ -345,12 +403,9 @@ k_radix_scatter_p(const K* __restrict__ kin, const u32* __restrict__ vin, K* __r
     {
       u32 next = tile + gridDim.x;
       if (next < ntiles) {
-        u32 tb = next * RADIX_TILE, nv = min((u32)RADIX_TILE, N - tb);
-        tile_fetch<K>((it & 1) ? kbuf0 : kbuf1, kin, tb, nv);
-        tile_fetch<u32>((it & 1) ? vbuf0 : vbuf1, vin, tb, nv);
+        fetch(next, (it & 1) ^ 1u);
         if (tid < 256) hb_next = H[(u64)tid * ntiles + next];
       }
-      asm volatile("cp.async.commit_group;\n" ::);
     }
 #pragma unroll
     for (int r = 0; r < RADIX_ITEMS; r++) {
@@ -442,6 +497,8 @@ void radix_init() {
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u64, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
+  CK(cudaFuncSetAttribute(k_radix_scatter_p<u64, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u32, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u32>()));
   CK(cudaFuncSetAttribute(k_radix_scatter_p<u64, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)radix_smem_p<u64>()));
   int dev = 0, sms = 0, b32 = 0, b64 = 0;
@@ -480,7 +537,12 @@ static void radix_sort_impl(K*& keys, u32*& vals, K*& keys_alt, u32*& vals_alt, 
         u32 grid = (u32)g_radix_grid[sizeof(K) == 4 ? 0 : 1];
         if (grid > ntiles) grid = ntiles;
         static const int nmatch = [] { const char* e = getenv("KISS_B200_NMATCH"); return e ? atoi(e) : RADIX_ITEMS / 4; }();  // 0: 8.16 ms, 4: 7.94 ms, 8: 8.43 ms per 1 Gbp sort
-        if (nmatch < 0)
+        static const bool bulk = getenv("KISS_B200_RADIX_BULK") != nullptr;
+        if (bulk && sizeof(K) == 4)
+          k_radix_scatter_p<u32, 4, true><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);
+        else if (bulk)
+          k_radix_scatter_p<K, 0, true><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift, mask, H, ntiles);
+        else if (nmatch < 0)
           k_radix_scatter_p<K, -1><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>(keys, vals, keys_alt, vals_alt, N, shift, mask, H, ntiles);
         else if (sizeof(K) == 4 && nmatch == 2)
           k_radix_scatter_p<u32, 2><<<grid, RADIX_THREADS, radix_smem_p<K>(), st>>>((const u32*)keys, vals, (u32*)keys_alt, vals_alt, N, shift, mask, H, ntiles);

@@ -93,22 +93,36 @@ class PeerBuffers:
 
     def __init__(self, torch, dist, n_long):
         self.cap, self.ok = n_long, False
-        flag = 1
+
+        def agree(flag):  # every rank learns whether ALL ranks got this far (a collective every rank always enters)
+            t = torch.tensor([1 if flag else 0], dtype=torch.int32, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            return bool(int(t.item()))
+
+        # 1. the module and the local allocations: nothing collective yet, so a rank that fails here cannot leave the
+        # others waiting inside a rendezvous
+        symm = None
         try:
             import torch.distributed._symmetric_memory as symm
             dev = torch.device("cuda", torch.cuda.current_device())
             self.pos = symm.empty(max(n_long, 4), dtype=torch.int32, device=dev)
             self.ctx = symm.empty(max(n_long, 4), dtype=torch.int32, device=dev)
+        except Exception as e:  # no symmetric memory on this system: the NCCL concatenation is used
+            self.err = repr(e)
+            symm = None
+        if not agree(symm is not None):
+            return
+        # 2. the rendezvous is collective and every rank enters it; its outcome is agreed on again
+        good = True
+        try:
             self.hpos = symm.rendezvous(self.pos, dist.group.WORLD)
             self.hctx = symm.rendezvous(self.ctx, dist.group.WORLD)
             self.pos0 = self.hpos.get_buffer(0, (max(n_long, 4),), torch.int32)
             self.ctx0 = self.hctx.get_buffer(0, (max(n_long, 4),), torch.int32)
-        except Exception as e:  # no peer access / symmetric memory on this system: the NCCL concatenation is used
+        except Exception as e:
             self.err = repr(e)
-            flag = 0
-        t = torch.tensor([flag], dtype=torch.int32, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MIN)
-        self.ok = bool(int(t.item()))
+            good = False
+        self.ok = agree(good)
 
 
 def peer_buffers(backend, dist, n_long):
@@ -228,7 +242,9 @@ def sharded_suffix_array_dev(ctx, S, n, SA, k, dist):
     import time
     import torch
     rank, world = dist.get_rank(), dist.get_world_size()
+    import kiss_b200
     be = GpuBackend(ctx, torch)
+    launches0 = kiss_b200.lib().kiss_b200_launch_count()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     n_long = be.prepare(S, n, k)
@@ -236,16 +252,16 @@ def sharded_suffix_array_dev(ctx, S, n, SA, k, dist):
     sorted_long, stats = sharded_lms_sort(be, dist, n_long, rank, world)
     torch.cuda.synchronize()
     t2 = time.perf_counter()
-    out = {"kernel_launches": 12, "m": be.m, "get_lms": t1 - t0, "lms_sort": t2 - t1, "put_lms": 0.0, "induce": 0.0,
+    out = {"kernel_launches": 0, "m": be.m, "get_lms": t1 - t0, "lms_sort": t2 - t1, "put_lms": 0.0, "induce": 0.0,
            "pack": 0.0, "shard_sizes": stats["shard_sizes"], "imbalance": stats["imbalance"]}
     if "steps_ms" in stats:
         out["steps_ms"] = stats["steps_ms"]
     out["concat"] = stats.get("concat")
     if rank == 0:
         ft = be.finish(sorted_long, n_long, SA, stats.get("ctx"))
-        out.update(put_lms=ft["put_lms"], induce=ft["induce"], waves_L=ft["waves_L"], waves_S=ft["waves_S"],
-                   kernel_launches=out["kernel_launches"] + ft["kernel_launches"])
-    out["kernel_launches"] += stats["sort"]["kernel_launches"]
+        out.update(put_lms=ft["put_lms"], induce=ft["induce"], waves_L=ft["waves_L"], waves_S=ft["waves_S"])
+    # this rank's own kernels, counted by the library (prepare, partition, subset sort, contexts, finish)
+    out["kernel_launches"] = int(kiss_b200.lib().kiss_b200_launch_count() - launches0)
     out["total_device"] = out["get_lms"] + out["lms_sort"] + out["put_lms"] + out["induce"]
     dist.barrier()
     return out
