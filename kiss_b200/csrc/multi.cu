@@ -1,14 +1,15 @@
 // multi.cu — kiss_b200_suffix_sort_dna_u32_multi: the sharded LMS sort behind the C ABI, one process,
 // one host thread and one context per GPU.
 //
-// Same partitioning as kiss_b200/multi_gpu.py (which runs it one PROCESS per GPU over torch.distributed for bench.py): the
-// text is uploaded to every GPU over its own PCIe link, every GPU packs and classifies it, rank r owns slice r of the
-// text-ordered LMS list, splitters come from sampled first-16-base keys, ONE personalised exchange moves LMS positions
-// (4 bytes each) — here as peer copies over NVLink / NVSwitch (cudaMemcpyPeerAsync), no NCCL needed inside one process —
-// every GPU sorts its key range with the single-GPU kernels and fetches the induction contexts of its suffixes, the
-// (position, context) ranges are concatenated on rank 0 by peer copies, and rank 0 places and induces (a single
-// dependency chain: it does not shard).  Equal first keys share a rank, so tie rules stay local and the result is
-// bit-identical to the single-GPU path.  The steps are the public device-stage entries of include/kiss_b200.h.
+// Same partitioning as kiss_b200/multi_gpu.py (which runs it one PROCESS per GPU over torch.distributed for bench.py):
+// rank r uploads slice r of the text over its own PCIe link and the GPUs complete it among themselves over NVLink; every
+// GPU packs and classifies the text; rank r owns slice r of the text-ordered LMS list; splitters come from sampled
+// first-16-base keys; ONE personalised exchange moves LMS positions (4 bytes each) — here as peer copies over NVLink /
+// NVSwitch (cudaMemcpyPeerAsync): no NCCL is needed inside one process; every GPU sorts its key range with the
+// single-GPU kernels and fetches the induction contexts of its suffixes; the (position, context) ranges are concatenated
+// on rank 0 by peer copies; rank 0 places and induces (a single dependency chain: it does not shard); the finished array
+// leaves in slices through every GPU's PCIe link.  Equal first keys share a rank, so tie rules stay local and the result
+// is bit-identical to the single-GPU path.  The steps are the public device-stage entries of include/kiss_b200.h.
 // PREFIX_DOUBLING and the unbounded order are not sharded (rank doubling is one global computation): they run on ctxs[0].
 #include <algorithm>
 #include <chrono>
@@ -46,6 +47,8 @@ struct Shared {
   std::vector<u32*> recv;                    // per rank: received positions
   std::vector<u64> recv_total;
   u32 *pos0 = nullptr, *ctx0 = nullptr;      // rank 0: the concatenated sorted order and its contexts
+  std::vector<u8*> dS;                       // per rank: the text on its GPU
+  u32* dSA0 = nullptr;                       // rank 0: the finished suffix array
   std::vector<int> device;
   std::mutex err_m;
   int err = 0;
@@ -66,7 +69,11 @@ void rank_main(int r, Shared& sh, Barrier& bar, kiss_b200_ctx** ctxs, const uint
   const int G = sh.G;
   kiss_b200_ctx* c = ctxs[r];
   u8* dS = nullptr;
-  u32 *send = nullptr, *ctxbuf = nullptr, *dSA = nullptr;
+  u32 *send = nullptr, *ctxbuf = nullptr, *dSA = nullptr, *slice = nullptr;
+  // slice r of the text (16-byte granules) and of the suffix array: what rank r moves over its own PCIe link
+  const uint64_t tchunk = ((n + G - 1) / G + 15) / 16 * 16, schunk = (n + 1 + G - 1) / G;
+  const uint64_t tlo = std::min<uint64_t>(n, r * tchunk), thi = std::min<uint64_t>(n, (r + 1) * tchunk);
+  const uint64_t slo = std::min<uint64_t>(n + 1, r * schunk), shi = std::min<uint64_t>(n + 1, (r + 1) * schunk);
   uint64_t m = 0, n_long = 0, lo = 0, hi = 0, total = 0;
   const uint32_t *keys = nullptr, *pos = nullptr;
   cudaStream_t st = nullptr;
@@ -90,7 +97,18 @@ void rank_main(int r, Shared& sh, Barrier& bar, kiss_b200_ctx** ctxs, const uint
     for (int p = 0; p < G; p++)
       if (p != r) { cudaDeviceEnablePeerAccess(sh.device[p], 0); cudaGetLastError(); }  // (already enabled / unsupported: staged copies)
     CK(cudaMalloc(&dS, n + 64));
-    CK(cudaMemcpy(dS, S_host, n, cudaMemcpyHostToDevice));  // every GPU through its own PCIe link, concurrently
+    sh.dS[r] = dS;
+    // 1 / G of the text through this GPU's own PCIe link ...
+    if (thi > tlo) CK(cudaMemcpy(dS + tlo, S_host + tlo, thi - tlo, cudaMemcpyHostToDevice));
+  });
+  bar.wait();
+  step([&] {
+    // ... and the other slices from the GPUs that uploaded them, over NVLink (an all-gather by peer copies)
+    for (int p = 0; p < G; p++) {
+      const uint64_t plo = std::min<uint64_t>(n, p * tchunk), phi = std::min<uint64_t>(n, (p + 1) * tchunk);
+      if (p != r && phi > plo) CK(cudaMemcpyPeerAsync(dS + plo, sh.device[r], sh.dS[p] + plo, sh.device[p], phi - plo, st));
+    }
+    CK(cudaStreamSynchronize(st));
     t_h2d = now_s() - t0;
     api(kiss_b200_prepare_dev(c, dS, n, k, &m));
     api(kiss_b200_lms_keys_dev(c, &keys, &pos, &n_long));
@@ -167,21 +185,37 @@ void rank_main(int r, Shared& sh, Barrier& bar, kiss_b200_ctx** ctxs, const uint
       CK(cudaMalloc(&dSA, (n + 1) * sizeof(u32)));
       kiss_b200_timings ft;
       api(kiss_b200_finish_from_sorted_ctx_dev(c, sh.pos0, sh.ctx0, n_long, dSA, &ft));
-      const double d0 = now_s();
-      CK(cudaMemcpy(SA_host, dSA, (n + 1) * sizeof(u32), cudaMemcpyDeviceToHost));
+      sh.dSA0 = dSA;
       if (t_out) {
         *t_out = ft;
-        t_out->h2d = t_h2d; t_out->get_lms = t_prep; t_out->lms_sort = t_sort; t_out->d2h = now_s() - d0;
+        t_out->h2d = t_h2d; t_out->get_lms = t_prep; t_out->lms_sort = t_sort;
         t_out->n = n; t_out->m = m;
         t_out->total_device = t_out->get_lms + t_out->lms_sort + t_out->put_lms + t_out->induce;
       }
     });
   bar.wait();
+  // the array leaves through every GPU's PCIe link: slice r crosses NVLink to GPU r and goes to the host from there
+  const double d0 = now_s();
+  step([&] {
+    if (shi > slo) {
+      const u32* src = sh.dSA0 + slo;
+      if (r != 0) {
+        CK(cudaMalloc(&slice, (shi - slo) * sizeof(u32)));
+        CK(cudaMemcpyPeerAsync(slice, sh.device[r], sh.dSA0 + slo, sh.device[0], (shi - slo) * sizeof(u32), st));
+        CK(cudaStreamSynchronize(st));
+        src = slice;
+      }
+      CK(cudaMemcpy(SA_host + slo, src, (shi - slo) * sizeof(u32), cudaMemcpyDeviceToHost));
+    }
+  });
+  bar.wait();
+  if (r == 0 && t_out) t_out->d2h = now_s() - d0;
   // release (peers are done with this rank's buffers after the last barrier)
   cudaSetDevice(sh.device[r]);
   if (dS) cudaFree(dS);
   if (send) cudaFree(send);
   if (ctxbuf) cudaFree(ctxbuf);
+  if (slice) cudaFree(slice);
   if (sh.recv[r]) cudaFree(sh.recv[r]);
   if (r == 0) {
     if (sh.pos0) cudaFree(sh.pos0);
@@ -206,7 +240,7 @@ extern "C" int kiss_b200_suffix_sort_dna_u32_multi(kiss_b200_ctx** ctxs, int n_g
   if (n + 1 >= 0xFFFFFFFFull) { api_set_last_error("text too long for 32-bit suffix indices"); return KISS_B200_ERR_TOO_LARGE; }
   Shared sh;
   sh.G = n_gpus;
-  sh.samples.resize(n_gpus); sh.counts.resize(n_gpus); sh.recv.assign(n_gpus, nullptr); sh.recv_total.assign(n_gpus, 0);
+  sh.samples.resize(n_gpus); sh.counts.resize(n_gpus); sh.dS.assign(n_gpus, nullptr); sh.recv.assign(n_gpus, nullptr); sh.recv_total.assign(n_gpus, 0);
   for (int r = 0; r < n_gpus; r++) sh.device.push_back(api_ctx_device(ctxs[r]));
   Barrier bar(n_gpus);
   std::vector<std::thread> th;
