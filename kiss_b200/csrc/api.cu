@@ -709,7 +709,49 @@ void do_sort(kiss_b200_ctx* c, Pool& pool, SortedLms* out, SortStats* stats) {
   const bool unbounded = P.sp.D == KISS_UNBOUNDED;
   if (!pd_pivot && P.n >= 64 && ns == 0 && P.m1 && (P.algo == KISS_B200_PREFIX_DOUBLING || unbounded)) {
     const u32 kk = P.algo == KISS_B200_PREFIX_DOUBLING ? P.sp.k : 0xFFFFFFFFu;
-    out->longs = sort_lms_doubling(c, pool, P.T, P.n, P.pos, (u32)P.m1, kk, stats);
+    // The unbounded order first tries the pivot rounds under a work cap: they skip a common prefix in one step where
+    // doubling needs log2 of it (C4, 512 near-identical copies: 0.083 s against 0.26 s), but cost O(LCP / 32) loads per
+    // element.  A comparison that runs past 16384 bases raises the abort flag, everything in flight gives up within 32
+    // words, and the sort starts over as rank doubling (two exact 100 Mbp copies: aborted after a few ms).
+    // KISS_B200_PD=doubling skips the attempt.
+    static const bool pd_only = [] { const char* e = getenv("KISS_B200_PD"); return e && std::string(e) == "doubling"; }();
+    if (kk == 0xFFFFFFFFu && !pd_only) {
+      u32* flag = pool.alloc<u32>(1);
+      CK(cudaMemsetAsync(flag, 0, sizeof(u32), c->st));
+      SortParams sp = P.sp;
+      sp.D = KISS_UNBOUNDED;
+      sp.abort = flag;
+      sp.cap_words = 512;
+      u32* sorted;
+      SortStats ss;
+      sort_long_lms(c, pool, P.key, P.pos, (u32)P.m1, sp, &sorted, &ss);
+      u32 aborted = 0;
+      CK(cudaMemcpyAsync(&aborted, flag, sizeof(u32), cudaMemcpyDeviceToHost, c->st));
+      CK(cudaStreamSynchronize(c->st));
+      if (!aborted) {
+        *stats = ss;
+        out->longs = sorted;
+        out->nl = (u32)P.m1;
+        out->ns = 0;
+        return;
+      }
+      // back to text order (ascending positions) for the doubling: P.pos / its twin hold a permutation of the list
+      u32* vals = pool.alloc<u32>(P.m1);
+      u32* keys_alt = pool.alloc<u32>(P.m1);
+      u32* vals_alt = pool.alloc<u32>(P.m1);
+      u32* H = pool.alloc<u32>(256 * radix_tiles(P.m1));
+      u32* partials = pool.alloc<u32>(scan_partials_len(256 * radix_tiles(P.m1)));
+      u32* keys = sorted;
+      radix_sort_u32(keys, vals, keys_alt, vals_alt, (u32)P.m1, 0, 32, H, partials, c->st);
+      if (keys != P.pos) CK(cudaMemcpyAsync(P.pos, keys, P.m1 * sizeof(u32), cudaMemcpyDeviceToDevice, c->st));
+      CK(cudaStreamSynchronize(c->st));
+      pool.release(vals); pool.release(vals_alt); pool.release(H); pool.release(partials); pool.release(flag);
+      stats->rounds = 1000;  // (marks the fallback in the timings: rounds >= 1000)
+    }
+    SortStats sd;
+    out->longs = sort_lms_doubling(c, pool, P.T, P.n, P.pos, (u32)P.m1, kk, &sd);
+    stats->tied = sd.tied;
+    stats->rounds += sd.rounds;
     out->nl = (u32)P.m1;
     out->ns = 0;
     return;

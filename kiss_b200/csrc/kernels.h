@@ -109,6 +109,10 @@ struct SortParams {
   u64 n;
   u64 D;  // comparison depth in bases; KISS_UNBOUNDED = compare to the end of the text
   u32 k;  // the caller's k (only the short-suffix comparator needs it)
+  // work cap of the unbounded pivot rounds (null = none): a single comparison that runs past `cap_words` 32-base words sets
+  // *abort, every other comparison gives up as soon as it sees the flag, and the caller falls back to rank doubling
+  u32* abort;
+  u32 cap_words;
 };
 #define KISS_UNBOUNDED 0xFFFFFFFFFFFFFFFFull
 #define TINY_MAX 8u

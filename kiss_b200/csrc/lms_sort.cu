@@ -23,8 +23,17 @@ namespace kiss {
 // true iff suffix p sorts before suffix q; both are known equal on their first h bases.
 // Bounded mode: both suffixes have at least D bases.  Unbounded (D = KISS_UNBOUNDED): the shorter suffix
 // first when one is a prefix of the other (kiss1_core.hpp:134).
+// the work cap of the unbounded pivot rounds: `it` = words compared so far by this comparison
+__device__ __forceinline__ bool over_cap(const SortParams& sp, u32 it) {
+  if (!sp.abort) return false;
+  if (it >= sp.cap_words) { *sp.abort = 1u; return true; }
+  return (it & 31u) == 31u && *reinterpret_cast<volatile u32*>(sp.abort) != 0u;
+}
+
 __device__ __forceinline__ bool suffix_less(const SortParams& sp, u32 p, u32 q, u64 h) {
+  u32 it = 0;
   for (u64 off = h; off < sp.D; off += 32) {
+    if (over_cap(sp, it++)) return p < q;  // (the result is discarded)
     if ((u64)p + off >= sp.n || (u64)q + off >= sp.n) return p > q;
     u64 a = word_at(sp.T, (u64)p + off), b = word_at(sp.T, (u64)q + off);
     u64 rem = sp.D - off;
@@ -381,7 +390,9 @@ __device__ __forceinline__ u64 pivot_key_u(const SortParams& sp, u32 p, u32 ph, 
   u64 q = d, side = MK_EQUAL;
   const u64 lp = sp.n - p, lh = sp.n - ph, lim = lp < lh ? lp : lh;  // bases both suffixes have
   const u64 L = lim < sp.D ? lim : sp.D;
+  u32 it = 0;
   while (q < L) {
+    if (over_cap(sp, it++)) return MK_EQUAL << MK_SIDE_SHIFT;  // (the result is discarded)
     u64 wa = word_at(sp.T, (u64)p + q), wb = word_at(sp.T, (u64)ph + q);
     const u64 rem = L - q;
     if (rem < 32) { const u64 mk = ~0ull << (64 - 2 * rem); wa &= mk; wb &= mk; }
