@@ -8,11 +8,17 @@
 //
 // After the stable LSD radix sort on the first 16 bases (radix.cu) equal keys are adjacent and in ascending
 // text position.  Groups of equal keys are finished by size:
-//   tiny   (<= 8)     one thread, insertion sort with the word-wise suffix comparator
-//   medium (<= 2048)  one block, bitonic sort in shared memory with the same comparator
-//   big               radix rounds: composite key (group id, next 16 bases) sorted with the LSD sort, the
-//                     resulting sub-groups go through the same three cases at the next depth
+//   tiny   (<= 8)     k_groups_tiny: one thread per group, insertion sort on (next 32 bases, deeper words, position)
+//   medium (<= 2048)  k_groups_medium: one team (a warp up to 256 elements, a block above) runs PIVOT ROUNDS — every
+//                     element is compared with its segment's pivot (block teams: the base-wise majority of 3-5 copies)
+//                     and gets one key [segment | side | first differing base | next 14 bases | slot]; the first round of
+//                     a block team is ordered by a counting sort on (side, q, base) + in-bucket ranking, later rounds by
+//                     ranking inside the short segments or the bitonic network of team.cuh; segments of <= 4 are finished
+//                     by one thread each
+//   big               the same pivot keys in global memory (k_big_fill), ordered with the LSD radix sort; the resulting
+//                     classes go through the same three cases at the next level
 // All paths are stable with respect to text position, which is the reference's final tie-break (:131-133).
+// The unbounded order runs under a work cap (SortParams::abort) and falls back to rank doubling (pd.cu, api.cu).
 #include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
