@@ -413,6 +413,11 @@ def run_b200(args):
             sort_s = stage["lms_sort"] / args.steps
             line["lms_sort_stage"] = {"ms": sort_s * 1e3, "m": m, "value": m / sort_s / 1e9, "unit": "G LMS suffixes/s",
                                       "alg_bytes": 16 * m, "frac": 16 * m / sort_s / 1e9 / peak}
+            # the stage that carries most of the step, in the same shape as `roofline` (the largest single kernel above)
+            line["roofline_lms_sort_stage"] = {"bound": "hbm", "stage": "lms_sort (K3: radix passes + tie-group kernels)",
+                                               "achieved": 16 * m / sort_s / 1e9, "peak": peak, "unit": "GB/s",
+                                               "frac": 16 * m / sort_s / 1e9 / peak, "share_of_step": sort_s * 1e3 / ms_step,
+                                               "alg_bytes": 16 * m}
         balg = b200_alg_bytes(n, m)
         dev_s = stage.get("total_device", ms * 1e-3) / args.steps
         line["roofline_whole_path"] = {"alg_bytes": balg, "achieved": balg / dev_s / 1e9, "frac": balg / dev_s / 1e9 / peak,
@@ -522,16 +527,27 @@ def run_b200(args):
                     else:
                         print(f"[bench] rank {rank}: cudaHostRegister failed with code {rc}; that slice stays pageable", file=sys.stderr)
 
-            def e2e_step():
+            def e2e_step(marks=None):
+                def mark(name):  # (only in the one extra, untimed step that reports the phases)
+                    if marks is not None:
+                        torch.cuda.synchronize()
+                        dist.barrier()
+                        marks.append((name, time.perf_counter()))
+                mark("start")
                 if hi > lo:
                     Sg[lo:hi].copy_(sh_S[lo:hi], non_blocking=True)
+                mark("h2d_slice")
                 dist.all_gather_into_tensor(Sg[:chunk * world], Sg[rank * chunk:(rank + 1) * chunk])
                 torch.cuda.synchronize()
+                mark("all_gather_text")
                 sharded_suffix_array_dev(ctx, Sg, n, SAp if rank == 0 else myslice, k, dist)
+                mark("suffix_array")
                 dist.scatter(myslice, [SAp[i * cs:(i + 1) * cs] for i in range(world)] if rank == 0 else None, src=0)
+                mark("scatter_sa")
                 if shi > slo:
                     sh_SA[slo:shi].copy_(myslice[:shi - slo], non_blocking=True)
                 torch.cuda.synchronize()
+                mark("d2h_slice")
             for _ in range(2):  # warm-up
                 e2e_step()
             barrier()
@@ -542,6 +558,9 @@ def run_b200(args):
             tt = torch.tensor([(time.perf_counter() - t0) / reps], device="cuda", dtype=torch.float64)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             sec = float(tt.item())
+            marks = []
+            e2e_step(marks)   # one more step with a barrier after every phase: where the time goes (rank 0's clock)
+            phases = {marks[i][0]: round((marks[i][1] - marks[i - 1][1]) * 1e3, 2) for i in range(1, len(marks))}
             if rank == 0:
                 # the shared host buffer holds the whole array: its first entry, and 1 M random entries against the device copy
                 assert (int(sh_SA[0]) & 0xFFFFFFFF) == n
@@ -549,7 +568,8 @@ def run_b200(args):
                 assert torch.equal(sh_SA[idx], SAp[idx.cuda()].cpu()), "host suffix array differs from the device copy"
                 line["e2e"] = {"value": (n + 1) / sec / 1e9, "unit": "Gsuffixes/s", "h2d_bytes_per_step": n,
                                "d2h_bytes_per_step": 4 * (n + 1), "ms_per_step": sec * 1e3,
-                               "pinned": len(registered) == 2,
+                               "pinned": len(registered) == 2, "phases_ms": phases,
+                               "torch_sees_pinned": bool(sh_S.is_pinned()),
                                "note": f"one shared host buffer (page-locked slice by slice); every rank uploads 1/{world} of the text and drains "
                                        f"1/{world} of the suffix array through its own PCIe link; NCCL all-gather of the text "
                                        "and scatter of the array over NVLink in between"}
