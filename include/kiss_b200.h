@@ -112,6 +112,26 @@ int kiss_b200_suffix_sort_dna_u32_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, 
 int kiss_b200_suffix_sort_ascii_u32(kiss_b200_ctx* ctx, const char* seq_host, uint64_t n, uint32_t k,
                                     int algo, uint32_t* SA_host, kiss_b200_timings* t);
 
+/* General alphabet: replaces
+ *   KISS1Sorter<uint32_t>::get_suffix_array(const kiss::vector<uint8_t>& S, uint32_t k, size_t threads)
+ *     (kiss1_sorter.hpp:38-44) -> kiss::kiss1_suffix_array (kiss1_core.hpp:270-311)        [algo 0]
+ *   KISS2Sorter<uint32_t>::get_suffix_array (kiss2_sorter.hpp) -> kiss::kiss2_suffix_array  [algo 1]
+ * S: n bytes of ANY values; SA: n + 1 slots (SA[0] = n; n == 0 gives {0}).  The text is reduced on the device to the
+ * 2-bit alphabet — the byte values that occur are replaced by their ranks, written as b = 1..4 two-bit digits — and run
+ * through the DNA path with k' = b * k; the entries at symbol boundaries are the result (general.cu).  b * n must stay
+ * below 2^32 - 2 (KISS_B200_ERR_TOO_LARGE otherwise).
+ * Order contract: every suffix is ordered by at least its first k symbols (the property tests/kiss.cpp:61-65 asserts);
+ * k >= n - 1 gives the true suffix array.  Wherever the reference's result is unique — no two suffixes share their
+ * first k symbols, or the true suffix array — the result is identical to it.  Among suffixes that share k symbols the
+ * reference's own order is unspecified for n < 10^8 (an unstable std::sort on "first k symbols", kiss1_core.hpp:208-219);
+ * here they are ordered deeper, as the DNA path orders the reduced text.
+ * kiss_b200_general_digits reports the number of distinct byte values and b for a device-resident text. */
+int kiss_b200_suffix_sort_u32(kiss_b200_ctx* ctx, const uint8_t* S_host, uint64_t n, uint32_t k, int algo,
+                              uint32_t* SA_host, kiss_b200_timings* t);
+int kiss_b200_suffix_sort_u32_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, uint32_t k, int algo,
+                                  uint32_t* SA_dev, kiss_b200_timings* t);
+int kiss_b200_general_digits(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, uint32_t* sigma, uint32_t* digits);
+
 /* ---- stage-level entries (used by the parity tests and the multi-GPU LMS sort) -------------------
  * Each one runs pack + the named stage(s) on the device and copies the stage's result to the host.
  *

@@ -74,6 +74,35 @@ class Context:
         self.last_timings = t.as_dict()
         return SA
 
+    def suffix_array(self, S, k=256, algo=PARALLEL_SORTING):
+        """general alphabet: KISS1Sorter / KISS2Sorter ::get_suffix_array (kiss1_sorter.hpp:28-44).  `S`: bytes, str or
+        a uint8 array of any values.  See include/kiss_b200.h for the order among suffixes that share k symbols."""
+        if isinstance(S, str):
+            S = S.encode("latin-1")
+        b = np.frombuffer(S, dtype=np.uint8) if isinstance(S, (bytes, bytearray, memoryview)) else np.asarray(S)
+        if b.dtype != np.uint8:
+            raise TypeError("general-alphabet text must be bytes or a uint8 array")
+        b = np.ascontiguousarray(b)
+        SA = np.empty(b.size + 1, np.uint32)
+        t = Timings()
+        check(lib().kiss_b200_suffix_sort_u32(self._h, b.ctypes.data, b.size, k & 0xFFFFFFFF, algo, SA.ctypes.data,
+                                              C.byref(t)))
+        self.last_timings = t.as_dict()
+        return SA
+
+    def suffix_array_dev(self, S_ptr, n, SA_ptr, k=256, algo=PARALLEL_SORTING):
+        """general alphabet, text and result resident in device memory"""
+        t = Timings()
+        check(lib().kiss_b200_suffix_sort_u32_dev(self._h, S_ptr, n, k & 0xFFFFFFFF, algo, SA_ptr, C.byref(t)))
+        self.last_timings = t.as_dict()
+        return self.last_timings
+
+    def general_digits(self, S_ptr, n):
+        """(distinct byte values, two-bit digits per symbol) of a device-resident text"""
+        s, d = C.c_uint32(), C.c_uint32()
+        check(lib().kiss_b200_general_digits(self._h, S_ptr, n, C.byref(s), C.byref(d)))
+        return s.value, d.value
+
     def suffix_array_file(self, data, k=256, algo=PARALLEL_SORTING):
         """`data` = the bytes of a FASTA / plain-text file (read_sequence semantics, include/utils/io.hpp:6-18):
         returns (suffix array, text length)"""
@@ -268,6 +297,11 @@ class KISS1Sorter:
     @classmethod
     def get_suffix_array_dna(cls, S, k=256, num_threads=None):
         return default_context().suffix_array_dna(S, k, cls.algo)
+
+    @classmethod
+    def get_suffix_array(cls, S, k=256, num_threads=None):
+        """general alphabet (kiss1_sorter.hpp:28-44)"""
+        return default_context().suffix_array(S, k, cls.algo)
 
     @staticmethod
     def prepare_aligned_ref(ref):

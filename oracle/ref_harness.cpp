@@ -58,6 +58,26 @@ double ref_kiss2_suffix_array_dna(const uint8_t* S_, uint64_t n, uint32_t k, uin
   return t1 - t0;
 }
 
+// General alphabet (kiss1_core.hpp:270-311 / kiss2_core.hpp:898-906): S_ holds n bytes of any values.
+double ref_kiss1_suffix_array(const uint8_t* S_, uint64_t n, uint32_t k, uint64_t threads, uint32_t* SA_out) {
+  vector<uint8_t> S(S_, S_ + n);
+  vector<uint32_t> SA;
+  double t0 = now_s();
+  kiss::kiss1_suffix_array<uint8_t, uint32_t>(S, SA, k, threads);
+  double t1 = now_s();
+  if (SA_out) std::memcpy(SA_out, SA.data(), sizeof(uint32_t) * (n + 1));
+  return t1 - t0;
+}
+double ref_kiss2_suffix_array(const uint8_t* S_, uint64_t n, uint32_t k, uint64_t threads, uint32_t* SA_out) {
+  vector<uint8_t> S(S_, S_ + n);
+  vector<uint32_t> SA;
+  double t0 = now_s();
+  kiss::kiss2_suffix_array<uint8_t, uint32_t>(S, SA, k, threads);
+  double t1 = now_s();
+  if (SA_out) std::memcpy(SA_out, SA.data(), sizeof(uint32_t) * (n + 1));
+  return t1 - t0;
+}
+
 // kISS-2's LMS sort alone: the steps of kiss2_suffix_array_internal (kiss2_core.hpp:835-886) up to and including
 // prefix_doubling (:874), same calls in the same order.  sorted_out receives the m LMS suffixes in the order
 // place_back_lms leaves them (:690-725; sorted_out[0] == n).  Returns m.  n must be > 0.

@@ -54,6 +54,10 @@ def oracle():
         L.oracle_kiss1_suffix_array_dna.argtypes = [_vp, _u32, _u32, _vp, _vp, _vp, _vp, _vp, _vp]
         L.oracle_induce_from_sorted_lms.restype = None
         L.oracle_induce_from_sorted_lms.argtypes = [_vp, _u32, _vp, _u32, _vp]
+        L.oracle_kiss1_suffix_array.restype = _u32
+        L.oracle_kiss1_suffix_array.argtypes = [_vp, _u32, _u32, _vp]
+        L.oracle_general_less_big.restype = C.c_int
+        L.oracle_general_less_big.argtypes = [_vp, _u32, _u32, _u32, _u32]
         L.oracle_fnv1a_u32.restype = _u64
         L.oracle_fnv1a_u32.argtypes = [_vp, _u64]
         _oracle = L
@@ -75,6 +79,10 @@ def ref():
         L.ref_kiss1_stages.argtypes = [_vp, _u64, _u32, _u64, _vp, _vp, _vp, _vp, _vp, _vp]
         L.ref_induce_from_sorted_lms.restype = None
         L.ref_induce_from_sorted_lms.argtypes = [_vp, _u64, _u64, _vp, _vp]
+        for name in ("ref_kiss1_suffix_array", "ref_kiss2_suffix_array"):
+            if hasattr(L, name):
+                getattr(L, name).restype = _dbl
+                getattr(L, name).argtypes = [_vp, _u64, _u32, _u64, _vp]
         if hasattr(L, "ref_kiss2_sorted_lms"):
             L.ref_kiss2_sorted_lms.restype = _u32
             L.ref_kiss2_sorted_lms.argtypes = [_vp, _u64, _u32, _u64, _vp]
@@ -131,6 +139,22 @@ def oracle_induce_from_sorted(S, sorted_lms):
     return SA
 
 
+def _bytes(S):
+    if isinstance(S, str):
+        S = S.encode("latin-1")
+    if isinstance(S, (bytes, bytearray, memoryview)):
+        return np.frombuffer(bytes(S), dtype=np.uint8)
+    return np.ascontiguousarray(S, dtype=np.uint8)
+
+
+def oracle_general(S, k=256):
+    """general alphabet (oracle/general_oracle.c): LMS suffixes that share k symbols stay in text order"""
+    S = _bytes(S)
+    SA = np.zeros(S.size + 1, np.uint32)
+    oracle().oracle_kiss1_suffix_array(_ptr(S) if S.size else None, S.size, k & 0xFFFFFFFF, _ptr(SA))
+    return SA
+
+
 def fnv1a(a):
     a = np.ascontiguousarray(a, dtype=np.uint32)
     return int(oracle().oracle_fnv1a_u32(_ptr(a), a.size))
@@ -148,6 +172,15 @@ def ref_kiss2(S, k=256, threads=4):
     S = _codes(S)
     SA = np.zeros(S.size + 1, np.uint32)
     ref().ref_kiss2_suffix_array_dna(_ptr(S), S.size, k & 0xFFFFFFFF, threads, _ptr(SA))
+    return SA
+
+
+def ref_general(S, k=256, threads=4, algo=0):
+    """the reference's general-alphabet kiss1_suffix_array / kiss2_suffix_array on bytes of any values"""
+    S = _bytes(S)
+    SA = np.zeros(S.size + 1, np.uint32)
+    f = ref().ref_kiss1_suffix_array if algo == 0 else ref().ref_kiss2_suffix_array
+    f(_ptr(S) if S.size else None, S.size, k & 0xFFFFFFFF, threads, _ptr(SA))
     return SA
 
 
