@@ -100,6 +100,13 @@ inline void suffix_array_dna(const vector<std::uint8_t>& S, vector<std::uint32_t
   suffix_array_dna(S.data(), S.size(), SA, k, algo);
 }
 
+// kiss1_suffix_array / kiss2_suffix_array, the general-alphabet drivers (kiss1_core.hpp:270-311, kiss2_core.hpp:898-906):
+// `S` = n bytes of any values (include/kiss_b200.h: kiss_b200_suffix_sort_u32 for the order among suffixes sharing k symbols)
+inline void suffix_array(const void* S, std::size_t n, vector<std::uint32_t>& SA, std::uint32_t k, int algo) {
+  SA.resize(n + 1);
+  raise(kiss_b200_suffix_sort_u32(context(), static_cast<const std::uint8_t*>(S), n, k, algo, SA.data(), &last_timings()));
+}
+
 // fmindex_build (include/command/fmindex_build.hpp:27-34): the bytes of a FASTA / text file -> the bytes of the .fmi file
 // FMIndex<sa_intv, uint32_t, Sorter>{.LOOKUP_LEN = 0}::save writes (fm_index.hpp:591-617); the suffix array stays on the
 // device.  Returns the text length.
@@ -141,6 +148,18 @@ void kiss2_suffix_array_dna(const vector<char_type>& S, vector<size_type>& SA, s
   b200::suffix_array_dna(S.data(), S.size(), SA, k, KISS_B200_PREFIX_DOUBLING);
 }
 
+template<typename char_type, typename size_type>
+void kiss1_suffix_array(const vector<char_type>& S, vector<size_type>& SA, size_type k, std::size_t /*num_threads*/) {
+  static_assert(sizeof(char_type) == 1 && sizeof(size_type) == 4, "the B200 path implements <uint8_t, uint32_t>");
+  b200::suffix_array(S.data(), S.size(), SA, k, KISS_B200_PARALLEL_SORTING);
+}
+
+template<typename char_type, typename size_type>
+void kiss2_suffix_array(const vector<char_type>& S, vector<size_type>& SA, size_type k, std::size_t /*num_threads*/) {
+  static_assert(sizeof(char_type) == 1 && sizeof(size_type) == 4, "the B200 path implements <uint8_t, uint32_t>");
+  b200::suffix_array(S.data(), S.size(), SA, k, KISS_B200_PREFIX_DOUBLING);
+}
+
 }  // namespace kiss
 
 namespace detail {
@@ -159,6 +178,20 @@ struct B200Sorter {
                                    const std::size_t /*num_threads*/ = std::thread::hardware_concurrency()) {
     auto SA = SA_t{};
     kiss::b200::suffix_array_dna(S, SA, k, ALGO);
+    return SA;
+  }
+
+  // general alphabet (kiss1_sorter.hpp:28-44)
+  static auto get_suffix_array(const std::ranges::random_access_range auto& ref, size_type k = 256u,
+                               const std::size_t num_threads = std::thread::hardware_concurrency()) {
+    auto S = kiss::vector<std::uint8_t>(std::ranges::begin(ref), std::ranges::end(ref));
+    return get_suffix_array(S, k, num_threads);
+  }
+
+  static auto get_suffix_array(const kiss::vector<std::uint8_t>& S, size_type k = 256u,
+                               const std::size_t /*num_threads*/ = std::thread::hardware_concurrency()) {
+    auto SA = SA_t{};
+    kiss::b200::suffix_array(S.data(), S.size(), SA, k, ALGO);
     return SA;
   }
 
