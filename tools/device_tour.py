@@ -1,7 +1,8 @@
 #!/usr/bin/env python
-"""A small tour of every device path, sized for compute-sanitizer (memcheck / racecheck slow kernels down 10-100x):
-    compute-sanitizer --tool memcheck python tools/sanitize_run.py
-Each case is checked against the CPU oracle, so a sanitizer-clean run is also a correct one."""
+"""A small tour of every device path (DNA, unbounded, PREFIX_DOUBLING, stage entries, file ingest, FM-index image, general
+alphabet, several contexts through the multi entry), each case checked against the CPU oracle; sized so that it also fits
+under a memory checker where one is available (compute-sanitizer is closed on this run's GPU pool):
+    python tools/device_tour.py [--small]"""
 import os
 import sys
 
