@@ -521,8 +521,34 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
       pd_seg_small(hs, ngroups, A, elem, key2, lists, list_cap, small8, st);
       u32 cn[8];
       sync.read(small8, 8, cn);
-      if (cn[7] == 0) {
+      static const bool no_mixed = getenv("KISS_B200_PD_NO_MIXED") != nullptr;  // A/B: the radix sort of everything instead
+      if (cn[7] == 0 || !no_mixed) {
         pd_seg_teams(lists, list_cap, cn, hs, ngroups, A, elem, key2, st);
+        if (cn[7]) {
+          // the groups no block team holds: only THEIR elements go through the radix sort
+          const u32 nb = cn[7];
+          const u32* biglist = lists + 7ull * list_cap;
+          u32* boff = pool.alloc<u32>((u64)nb + 1);
+          u32* bpart = pool.alloc<u32>(scan_partials_len(nb));
+          pd_big_sizes(biglist, nb, hs, ngroups, A, boff, st);
+          scan_excl_u32(boff, nb, bpart, small, st);
+          u32 B;
+          sync.read(small, 1, &B);
+          u64* bcomp = pool.alloc<u64>(B);
+          u64* bcomp_alt = pool.alloc<u64>(B);
+          u32* bval = pool.alloc<u32>(B);
+          u32* bval_alt = pool.alloc<u32>(B);
+          u32* bslot = pool.alloc<u32>(B);
+          u32* Hb = pool.alloc<u32>(256 * radix_tiles(B));
+          u32* partb = pool.alloc<u32>(scan_partials_len(256 * radix_tiles(B)));
+          pd_big_fill(biglist, boff, nb, B, hs, elem, key2, rb, bcomp, bval, bslot, st);
+          int gb = 0;
+          while (gb < 31 && (1u << gb) < nb) gb++;
+          radix_sort_u64(bcomp, bval, bcomp_alt, bval_alt, B, 0, rb + gb, Hb, partb, st);
+          pd_big_writeback(bcomp, bval, bslot, B, rb, elem, key2, st);
+          pool.release(boff); pool.release(bpart); pool.release(bcomp); pool.release(bcomp_alt); pool.release(bval);
+          pool.release(bval_alt); pool.release(bslot); pool.release(Hb); pool.release(partb);
+        }
         pd_heads_seg(key2, A, ghead, st);
         seg_done = true;
       }

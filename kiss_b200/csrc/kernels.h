@@ -199,6 +199,10 @@ void pd_seg_small(const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2,
 void pd_seg_teams(const u32* lists, u32 list_cap, const u32* cn, const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2,
                   cudaStream_t st);
 void pd_heads_seg(const u32* key2, u32 A, u32* head, cudaStream_t st);
+void pd_big_sizes(const u32* biglist, u32 nb, const u32* headslot, u32 ngroups, u32 A, u32* bsize, cudaStream_t st);
+void pd_big_fill(const u32* biglist, const u32* boff, u32 nb, u32 B, const u32* headslot, const u32* elem, const u32* key2,
+                 int rb, u64* comp, u32* val, u32* bslot, cudaStream_t st);
+void pd_big_writeback(const u64* comp, const u32* val, const u32* bslot, u32 B, int rb, u32* elem, u32* key2, cudaStream_t st);
 void pd_flush(const u32* elem, const u32* gslot, u32 A, u32* sa_final, cudaStream_t st);
 void pd_startflags(const u32* sa_final, const u8* isstart, u32 W, u32* flag, cudaStream_t st);
 void pd_emit(const u32* sa_final, const u8* isstart, const u32* dst, const u32* wstart, u32 W, u32* out, cudaStream_t st);

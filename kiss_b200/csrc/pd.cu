@@ -197,8 +197,43 @@ __global__ void k_pd_seg_small(const u32* __restrict__ headslot, u32 ngroups, u3
     const u32 cls = size <= 32 ? 0u : size <= 64 ? 1u : size <= 128 ? 2u : size <= 256 ? 3u : size <= 512 ? 4u : size <= 1024 ? 5u : 6u;
     lists[(u64)cls * list_cap + atomicAdd(&counters[cls], 1u)] = g;
   } else {
-    atomicAdd(&counters[7], 1u);
+    // larger than a block team: listed after the seven class lists (at most A / 2049 of them) for the radix sort of the
+    // subset (pd_big_*)
+    lists[7ull * list_cap + atomicAdd(&counters[7], 1u)] = g;
   }
+}
+
+// ---- groups larger than a block team: their elements are copied out with the composite key [group ordinal | key2],
+// radix-sorted (stable), and copied back.  bsize = sizes of the listed groups (to be scanned into boff).
+__global__ void k_pd_big_sizes(const u32* __restrict__ biglist, u32 nb, const u32* __restrict__ headslot, u32 ngroups, u32 A,
+                               u32* __restrict__ bsize) {
+  const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nb) return;
+  const u32 g = biglist[j];
+  bsize[j] = (g + 1 < ngroups ? headslot[g + 1] : A) - headslot[g];
+}
+__global__ void k_pd_big_fill(const u32* __restrict__ biglist, const u32* __restrict__ boff, u32 nb, u32 B,
+                              const u32* __restrict__ headslot, const u32* __restrict__ elem, const u32* __restrict__ key2,
+                              int rb, u64* __restrict__ comp, u32* __restrict__ val, u32* __restrict__ bslot) {
+  const u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= B) return;
+  u32 lo = 0, hi = nb;  // last listed group with boff <= t
+  while (hi - lo > 1) {
+    const u32 mid = lo + (hi - lo) / 2;
+    if (boff[mid] <= t) lo = mid; else hi = mid;
+  }
+  const u32 slot = headslot[biglist[lo]] + (t - boff[lo]);
+  comp[t] = ((u64)lo << rb) | key2[slot];
+  val[t] = elem[slot];
+  bslot[t] = slot;  // (a function of t alone: position t of the sorted subset goes back to the same slot)
+}
+__global__ void k_pd_big_writeback(const u64* __restrict__ comp, const u32* __restrict__ val, const u32* __restrict__ bslot,
+                                   u32 B, int rb, u32* __restrict__ elem, u32* __restrict__ key2) {
+  const u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= B) return;
+  const u32 slot = bslot[t];
+  elem[slot] = val[t];
+  key2[slot] = (u32)(comp[t] & ((1ull << rb) - 1ull));
 }
 
 template <int NW, int R>
@@ -319,5 +354,15 @@ void pd_seg_teams(const u32* lists, u32 list_cap, const u32* cn, const u32* head
   pd_seg_class<16, 4>(lists + 6ull * list_cap, cn[6], headslot, ngroups, A, elem, key2, st);
 }
 void pd_heads_seg(const u32* key2, u32 A, u32* head, cudaStream_t st) { PD_LAUNCH(k_pd_heads_seg, A, key2, A, head); }
+void pd_big_sizes(const u32* biglist, u32 nb, const u32* headslot, u32 ngroups, u32 A, u32* bsize, cudaStream_t st) {
+  PD_LAUNCH(k_pd_big_sizes, nb, biglist, nb, headslot, ngroups, A, bsize);
+}
+void pd_big_fill(const u32* biglist, const u32* boff, u32 nb, u32 B, const u32* headslot, const u32* elem, const u32* key2,
+                 int rb, u64* comp, u32* val, u32* bslot, cudaStream_t st) {
+  PD_LAUNCH(k_pd_big_fill, B, biglist, boff, nb, B, headslot, elem, key2, rb, comp, val, bslot);
+}
+void pd_big_writeback(const u64* comp, const u32* val, const u32* bslot, u32 B, int rb, u32* elem, u32* key2, cudaStream_t st) {
+  PD_LAUNCH(k_pd_big_writeback, B, comp, val, bslot, B, rb, elem, key2);
+}
 
 }  // namespace kiss

@@ -24,6 +24,8 @@ TIE_HEAVY = [
     ("copies1500", lambda: tg.near_identical_copies(19, 150, 1500, 0.005)),
     ("low_entropy", lambda: np.concatenate([tg.low_entropy(11, 50_000), tg.uniform(12, 1024)])),
     ("homopolymers", lambda: tg.tandem(16, 120_000, arrays=12, max_unit=1, max_len=9000)),
+    # 13 000 identical words: classes larger than a block team in every doubling round (the radix sort of the subset, pd.cu)
+    ("periodic_long", lambda: np.concatenate([tg.uniform(17, 3000), tg.periodic(40_000, [1, 0, 2]), tg.uniform(18, 900)])),
 ]
 TIE_FREE = [
     ("uniform200k", lambda: tg.uniform(7, 200_000)),
@@ -33,7 +35,7 @@ TIE_FREE = [
     ("uniform100", lambda: tg.uniform(4, 100)),
 ]
 UNBOUNDED = TIE_HEAVY[:5] + TIE_FREE[:2] + [("periodic_CA", lambda: np.concatenate([tg.periodic(5000, [1, 0]), tg.uniform(14, 700)])),
-                                             ("all_A", lambda: np.zeros(500, np.uint8))]
+                                             ("all_A", lambda: np.zeros(500, np.uint8)), TIE_HEAVY[7]]
 
 
 # ------------------------------------------------------------------------------------------------ CPU: the model
@@ -73,7 +75,7 @@ def test_unbounded_is_bit_exact_against_kiss2(ctx, name, gen):
     S = gen()
     # (the reference's kISS-2 with more than one thread does not come back in minutes on the small periodic texts, and
     # returned a wrong array once it did — its single-threaded run is correct: those cases compare with T = 1)
-    want = ol.ref_kiss2(S, 0xFFFFFFFF, 1 if name in ("periodic_CA", "all_A") else 4)
+    want = ol.ref_kiss2(S, 0xFFFFFFFF, 1 if name in ("periodic_CA", "all_A", "periodic_long") else 4)
     for algo in (kiss_b200.PREFIX_DOUBLING, kiss_b200.PARALLEL_SORTING):   # `-k -1` with either -s
         got = ctx.suffix_array_dna(S, 0xFFFFFFFF, algo)
         bad = np.nonzero(got != want)[0]
