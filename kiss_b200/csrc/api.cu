@@ -446,9 +446,8 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
   u32* small = pool.alloc<u32>(4);
   u32* small8 = pool.alloc<u32>(8);
   pd_count(lms, m1, n, cnt, st);
-  CK(cudaMemcpyAsync(first, cnt, (u64)m1 * sizeof(u32), cudaMemcpyDeviceToDevice, st));
   u32* part_m = pool.alloc<u32>(scan_partials_len(m1));
-  scan_excl_u32(first, m1, part_m, small, st);
+  scan_excl_u32_to(cnt, first, m1, part_m, small, st);
   pd_ntail(lms, cnt, m1, n, small + 1, st);
   u32 hv[2];
   sync.read(small, 2, hv);
@@ -474,16 +473,14 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
   u32* sa_final = pool.alloc<u32>(W);
   pd_heads0(key, idx, W, ntail, head, st);
   pool.release(key); pool.release(key_alt); pool.release(idx_alt);
-  CK(cudaMemcpyAsync(ord, head, (u64)W * sizeof(u32), cudaMemcpyDeviceToDevice, st));
-  scan_excl_u32(ord, W, partials, nullptr, st);
+  scan_excl_u32_to(head, ord, W, partials, nullptr, st);
   pd_headslot(head, ord, W, headslot, st);
   pd_rank(idx, head, ord, headslot, nullptr, W, rank, st);
   // first compaction: singletons are final
   u32* keep = pool.alloc<u32>(W);
   u32* dst = pool.alloc<u32>(W);
   pd_keep(head, W, keep, st);
-  CK(cudaMemcpyAsync(dst, keep, (u64)W * sizeof(u32), cudaMemcpyDeviceToDevice, st));
-  scan_excl_u32(dst, W, partials, small, st);
+  scan_excl_u32_to(keep, dst, W, partials, small, st);
   u32 A;
   sync.read(small, 1, &A);
   u32* elem = pool.alloc<u32>(A);
@@ -504,8 +501,7 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
     u64* comp_alt = pool.alloc<u64>(A);
     u32* elem_alt = pool.alloc<u32>(A);
     u32* H2 = pool.alloc<u32>(256 * radix_tiles(A));
-    CK(cudaMemcpyAsync(o, ghead, (u64)A * sizeof(u32), cudaMemcpyDeviceToDevice, st));
-    scan_excl_u32(o, A, partials, small, st);
+    scan_excl_u32_to(ghead, o, A, partials, small, st);
     u32 ngroups;
     sync.read(small, 1, &ngroups);
     // segmented sort (one pass) unless a group is larger than a block team holds
@@ -560,15 +556,13 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
       radix_sort_u64(comp, elem, comp_alt, elem_alt, A, 0, rb + gb, H2, partials, st);
       pd_heads(comp, A, ghead, st);
     }
-    CK(cudaMemcpyAsync(o, ghead, (u64)A * sizeof(u32), cudaMemcpyDeviceToDevice, st));
-    scan_excl_u32(o, A, partials, nullptr, st);
+    scan_excl_u32_to(ghead, o, A, partials, nullptr, st);
     pd_headslot(ghead, o, A, hs, st);
     pd_rank(elem, ghead, o, hs, gslot, A, rank, st);
     u32* kp = pool.alloc<u32>(A);
     u32* ds = pool.alloc<u32>(A);
     pd_keep(ghead, A, kp, st);
-    CK(cudaMemcpyAsync(ds, kp, (u64)A * sizeof(u32), cudaMemcpyDeviceToDevice, st));
-    scan_excl_u32(ds, A, partials, small, st);
+    scan_excl_u32_to(kp, ds, A, partials, small, st);
     u32 A2;
     sync.read(small, 1, &A2);
     u32* elem2 = pool.alloc<u32>(A2);
@@ -583,9 +577,9 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
   }
   pd_flush(elem, gslot, A, sa_final, st);  // bounded k: what is still tied keeps ascending text position
   u32* flag = pool.alloc<u32>(W);
-  pd_startflags(sa_final, isstart, W, flag, st);
+  pd_startflags(sa_final, isstart, wstart, W, flag, rank, st);  // (the rank array is free now: it takes the positions)
   scan_excl_u32(flag, W, partials, nullptr, st);
-  pd_emit(sa_final, isstart, flag, wstart, W, out, st);
+  pd_emit(rank, flag, W, out, st);
   CK(cudaStreamSynchronize(st));
   pool.release(flag); pool.release(elem); pool.release(gslot); pool.release(ghead); pool.release(rank); pool.release(sa_final);
   pool.release(wstart); pool.release(isstart); pool.release(partials); pool.release(small); pool.release(small8);

@@ -65,6 +65,7 @@ struct ProfScope {
 // in-place exclusive prefix sum of data[0..N); `partials` needs N/4096 + 2 entries of scratch;
 // the grand total goes to *total_dev when non-null.
 void scan_excl_u32(u32* data, u64 N, u32* partials, u32* total_dev, cudaStream_t st);
+void scan_excl_u32_to(const u32* in, u32* out, u64 N, u32* partials, u32* total_dev, cudaStream_t st);
 inline u64 scan_partials_len(u64 N) { return N / 4096 + 2; }
 
 // ---------------------------------------------------------------- radix.cu
@@ -204,8 +205,8 @@ void pd_big_fill(const u32* biglist, const u32* boff, u32 nb, u32 B, const u32* 
                  int rb, u64* comp, u32* val, u32* bslot, cudaStream_t st);
 void pd_big_writeback(const u64* comp, const u32* val, const u32* bslot, u32 B, int rb, u32* elem, u32* key2, cudaStream_t st);
 void pd_flush(const u32* elem, const u32* gslot, u32 A, u32* sa_final, cudaStream_t st);
-void pd_startflags(const u32* sa_final, const u8* isstart, u32 W, u32* flag, cudaStream_t st);
-void pd_emit(const u32* sa_final, const u8* isstart, const u32* dst, const u32* wstart, u32 W, u32* out, cudaStream_t st);
+void pd_startflags(const u32* sa_final, const u8* isstart, const u32* wstart, u32 W, u32* flag, u32* val, cudaStream_t st);
+void pd_emit(const u32* val, const u32* dst, u32 W, u32* out, cudaStream_t st);
 
 // ---------------------------------------------------------------- fmindex.cu
 // N = n + 1 suffix array entries.  bwt32: ceil(N / 16) words; tot: 4 planes (stride n1 >= N / 256 + 1, a multiple of 4) of block counts (zeroed by the

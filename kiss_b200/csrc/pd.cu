@@ -138,17 +138,22 @@ __global__ void k_pd_flush(const u32* __restrict__ elem, const u32* __restrict__
   if (i < A) sa_final[gslot[i]] = elem[i];
 }
 
-// LMS-start words in final order (:690-725)
-__global__ void k_pd_startflags(const u32* __restrict__ sa_final, const u8* __restrict__ isstart, u32 W, u32* __restrict__ flag) {
-  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < W) flag[i] = isstart[sa_final[i]];
-}
-__global__ void k_pd_emit(const u32* __restrict__ sa_final, const u8* __restrict__ isstart, const u32* __restrict__ dst,
-                          const u32* __restrict__ wstart, u32 W, u32* __restrict__ out) {
+// LMS-start words in final order (:690-725): flag = the word starts an LMS substring, val = its text position (> 0) or 0;
+// after the scan of the flags the positions go out in order
+__global__ void k_pd_startflags(const u32* __restrict__ sa_final, const u8* __restrict__ isstart, const u32* __restrict__ wstart,
+                                u32 W, u32* __restrict__ flag, u32* __restrict__ val) {
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= W) return;
   const u32 w = sa_final[i];
-  if (isstart[w]) out[dst[i]] = wstart[w];
+  const u32 s = isstart[w];
+  flag[i] = s;
+  val[i] = s ? wstart[w] : 0u;
+}
+__global__ void k_pd_emit(const u32* __restrict__ val, const u32* __restrict__ dst, u32 W, u32* __restrict__ out) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= W) return;
+  const u32 v = val[i];
+  if (v) out[dst[i]] = v;
 }
 
 // ---- segmented sort of a round.  The active elements are already grouped (a group = a run of slots), so a round only
@@ -320,13 +325,10 @@ void pd_key2(const u32* elem, const u32* head, const u32* ord, const u32* rank, 
 void pd_flush(const u32* elem, const u32* gslot, u32 A, u32* sa_final, cudaStream_t st) {
   PD_LAUNCH(k_pd_flush, A, elem, gslot, A, sa_final);
 }
-void pd_startflags(const u32* sa_final, const u8* isstart, u32 W, u32* flag, cudaStream_t st) {
-  PD_LAUNCH(k_pd_startflags, W, sa_final, isstart, W, flag);
+void pd_startflags(const u32* sa_final, const u8* isstart, const u32* wstart, u32 W, u32* flag, u32* val, cudaStream_t st) {
+  PD_LAUNCH(k_pd_startflags, W, sa_final, isstart, wstart, W, flag, val);
 }
-void pd_emit(const u32* sa_final, const u8* isstart, const u32* dst, const u32* wstart, u32 W, u32* out, cudaStream_t st) {
-  PD_LAUNCH(k_pd_emit, W, sa_final, isstart, dst, wstart, W, out);
-}
-
+void pd_emit(const u32* val, const u32* dst, u32 W, u32* out, cudaStream_t st) { PD_LAUNCH(k_pd_emit, W, val, dst, W, out); }
 void pd_key2_plain(const u32* elem, const u32* rank, u32 A, u32 W, u32 off, u32* key2, cudaStream_t st) {
   PD_LAUNCH(k_pd_key2_plain, A, elem, rank, A, W, off, key2);
 }

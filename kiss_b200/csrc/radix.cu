@@ -88,13 +88,14 @@ __global__ void __launch_bounds__(1024) k_scan_partials(u32* __restrict__ partia
   if (threadIdx.x == 0 && total_out) *total_out = carry;
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_down(u32* __restrict__ data, u64 N, const u32* __restrict__ partials) {
+// (`in` == `data` for the in-place scan: no __restrict__ on the two)
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_down(const u32* in, u32* data, u64 N, const u32* __restrict__ partials) {
   __shared__ u32 ws[33];
   u64 base = (u64)blockIdx.x * SCAN_TILE + (u64)threadIdx.x * SCAN_ITEMS;
   u32 v[SCAN_ITEMS];
   bool full = base + SCAN_ITEMS <= N;
   if (full) {
-    const uint4* p = reinterpret_cast<const uint4*>(data + base);
+    const uint4* p = reinterpret_cast<const uint4*>(in + base);
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS / 4; i++) {
       uint4 q = p[i];
@@ -102,7 +103,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_down(u32* __restrict__ da
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < N) ? data[base + i] : 0;
+    for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < N) ? in[base + i] : 0;
   }
   u32 s = 0;
 #pragma unroll
@@ -121,20 +122,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_down(u32* __restrict__ da
   }
 }
 
-void scan_excl_u32(u32* data, u64 N, u32* partials, u32* total_dev, cudaStream_t st) {
+// out = exclusive prefix sums of in (in == out: in place); both 16-byte aligned
+void scan_excl_u32_to(const u32* in, u32* out, u64 N, u32* partials, u32* total_dev, cudaStream_t st) {
   if (N == 0) {
     if (total_dev) CK(cudaMemsetAsync(total_dev, 0, sizeof(u32), st));
     return;
   }
   ProfScope ps(PK_SCAN, st);
   u32 P = (u32)((N + SCAN_TILE - 1) / SCAN_TILE);
-  k_scan_reduce<<<P, SCAN_THREADS, 0, st>>>(data, N, partials);
+  k_scan_reduce<<<P, SCAN_THREADS, 0, st>>>(in, N, partials);
   CK_LAUNCH();
   k_scan_partials<<<1, 1024, 0, st>>>(partials, P, total_dev);
   CK_LAUNCH();
-  k_scan_down<<<P, SCAN_THREADS, 0, st>>>(data, N, partials);
+  k_scan_down<<<P, SCAN_THREADS, 0, st>>>(in, out, N, partials);
   CK_LAUNCH();
   g_launches += 3;
+}
+void scan_excl_u32(u32* data, u64 N, u32* partials, u32* total_dev, cudaStream_t st) {
+  scan_excl_u32_to(data, data, N, partials, total_dev, st);
 }
 
 // =================================================================================== radix
