@@ -1,5 +1,5 @@
 // Drop-in for the reference's kiss1_sorter.hpp:7-50 (PARALLEL_SORTING) — GPU backed, see kiss_b200_backend.hpp.
-// The general-alphabet get_suffix_array overloads are out of scope (never reached from the CLI, suffix_sort.hpp:58-60).
+// get_suffix_array_dna and the general-alphabet get_suffix_array (kiss1_sorter.hpp:28-44) are both provided.
 #pragma once
 #include "kiss_b200_backend.hpp"
 

@@ -40,7 +40,8 @@ void usage(std::ostream& os) {
         "  --verbose                 print more information\n"
         "  --gpu IDX                 CUDA device (default 0)\n"
         "  --gpus N                  shard the LMS sort over N GPUs starting at --gpu (default 1; implies --host-ingest)\n"
-        "  --host-ingest             parse the file on the host (the reference's serial getline loop) instead of on the device\n\n"
+        "  --host-ingest             parse the file on the host (the reference's serial getline loop) instead of on the device\n"
+        "  --general                 (extension) sort the sequence lines' bytes as they are, any alphabet (proteins, text)\n\n"
         "./kISS suffix_sort [--option ...] <FASTA filename/Text filename>\n\n"
         "Options:\n"
         "  -k [ --kordered ] NUM (=256)          a k-ordered value, where each suffix is sorted based on the\n"
@@ -82,7 +83,8 @@ inline std::uint8_t code_of(unsigned char c) {
 // records concatenated without separators; text mode: every line is sequence.  '\r', N and IUPAC codes all
 // become A, as in the reference.  The line after a header is sequence whatever it starts with
 // (include/biovoltron/file_io/fasta.hpp:129-133), so a '>' line is a header only when the line before it was not one.
-std::vector<std::uint8_t> read_sequence(std::istream& fin) {
+// `raw`: the bytes of the sequence lines as they are (--general), instead of their base codes
+std::vector<std::uint8_t> read_sequence(std::istream& fin, bool raw = false) {
   std::vector<std::uint8_t> seq;
   bool fasta = fin.peek() == '>', prev_header = false;
   std::string line;
@@ -90,13 +92,13 @@ std::vector<std::uint8_t> read_sequence(std::istream& fin) {
     const bool header = fasta && !line.empty() && line[0] == '>' && !prev_header;
     prev_header = header;
     if (header) continue;
-    for (unsigned char c : line) seq.push_back(code_of(c));
+    for (unsigned char c : line) seq.push_back(raw ? c : code_of(c));
   }
   return seq;
 }
 
 struct Args {
-  bool help = false, version = false, generic = false, verbose = false, host_ingest = false;
+  bool help = false, version = false, generic = false, verbose = false, host_ingest = false, general = false;
   std::size_t threads = std::thread::hardware_concurrency();
   int gpu = 0, gpus = 1;
   std::string command, file, out;
@@ -138,6 +140,7 @@ Args parse(int argc, char** argv) {
     if (flag == "-h" || flag == "--help") a.help = true;
     else if (flag == "-v" || flag == "--version") a.version = true;
     else if (flag == "-g" || flag == "--generic") a.generic = true;
+    else if (flag == "--general") a.general = true;
     else if (flag == "--verbose") a.verbose = true;
     else if (flag == "-t" || flag == "--num_threads") a.threads = parse_size(value(flag));
     else if (flag == "--gpu") a.gpu = (int)parse_size(value(flag));
@@ -172,7 +175,16 @@ int suffix_sort_main(const Args& a) {
   biovoltron::kiss::vector<std::uint32_t> sa;
   std::uint64_t n_text = 0;
   double sec = 0;
-  if (a.host_ingest || a.gpus > 1) {
+  if (a.general) {
+    // extension (not in the reference's CLI, whose -g is refused above): the sequence lines' bytes as they are — a protein
+    // FASTA, any text — through the general-alphabet sorters (kiss1_sorter.hpp:28-44 -> kiss_b200_suffix_sort_u32)
+    auto seq = read_sequence(fa, true);
+    n_text = seq.size();
+    auto t0 = std::chrono::steady_clock::now();
+    if (a.algo == KISS_B200_PARALLEL_SORTING) sa = biovoltron::KISS1Sorter<std::uint32_t>::get_suffix_array(seq, k32, a.threads);
+    else sa = biovoltron::KISS2Sorter<std::uint32_t>::get_suffix_array(seq, k32, a.threads);
+    sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  } else if (a.host_ingest || a.gpus > 1) {
     // the reference's way: parse on the host (serial getline), then the sorter facade on the codes (the facade shards the
     // LMS sort over --gpus N GPUs: kiss_b200_suffix_sort_dna_u32_multi)
     auto seq = read_sequence(fa);

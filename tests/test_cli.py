@@ -124,3 +124,22 @@ def test_fmindex_build_writes_the_reference_fmi_file(tmp_path):
     assert img == fo.fmi_image(S, ol.oracle_kiss1(S, k=32))
     if ol.have_ref() and hasattr(ol.ref(), "ref_fmindex_build_file"):
         assert img == fo.mask_padding(ol.ref_fmindex_image(S), S.size + 1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("algo", ["PARALLEL_SORTING", "PREFIX_DOUBLING"])
+def test_general_extension_sorts_a_protein_fasta(tmp_path, algo):
+    """--general (an extension: the reference's CLI refuses -g): the sequence lines' bytes as they are, through the
+    general-alphabet sorters (kiss1_sorter.hpp:28-44); records concatenated and headers dropped like read_sequence"""
+    import general_cases as gc
+    S = gc.hashed(71, 40_000, gc.AMINO)
+    lines = [S[i:i + 60].tobytes().decode() for i in range(0, S.size, 60)]
+    half = len(lines) // 2
+    f = tmp_path / "p.fa"
+    f.write_text(">sp|P1 first\n" + "\n".join(lines[:half]) + "\n>sp|P2 second\n" + "\n".join(lines[half:]) + "\n")
+    out = tmp_path / "sa.bin"
+    r = run("suffix_sort", str(f), "--general", "-k", "256", "-s", algo, "--out", str(out))
+    assert r.returncode == 0, r.stderr
+    assert f"n = {S.size}" in r.stderr
+    sa = np.fromfile(out, dtype=np.uint32)
+    assert np.array_equal(sa, ol.oracle_general(S, 256))
