@@ -349,6 +349,10 @@ def run_b200(args):
         line["parity"] = {"sa_mixed_sum": f"{got:016x}", "golden": gold, "ok": (gold == f"{got:016x}") if gold else None,
                           "golden_source": "tests/golden/full_size_golden.json (reference kiss1_suffix_array_dna via oracle/_ref)",
                           "sa0_is_n": int(SA[0].item()) & 0xFFFFFFFF == n}
+        # the reference's own test predicate (tests/kiss.cpp:25-33) over the whole device array: every adjacent pair ordered
+        # by its first k bases, and the array a permutation of 0..n — size-independent, checked at the full size every run
+        v = ctx.verify_sa_dev(S.data_ptr(), n, SA.data_ptr(), k)
+        line["parity"]["k_order"] = dict(v, ok=not any(v.values()))
     if "steps_ms" in last:
         line["sharded_sort_steps_ms"] = last["steps_ms"]
     if "shard_sizes" in last:

@@ -266,6 +266,15 @@ uint64_t kiss_b200_launch_count(void);
  * configurations; bench.py compares after every run, outside the timed region. */
 int kiss_b200_sa_checksum_dev(kiss_b200_ctx* ctx, const uint32_t* SA_dev, uint64_t count, uint64_t* out);
 
+/* The property the reference's own tests assert (tests/kiss.cpp:25-33: REQUIRE(substr(sa[i-1], k) <= substr(sa[i], k))),
+ * checked on the device over the whole array, plus SA[0] == n and "SA is a permutation of 0..n".  No counterpart in the
+ * reference's library (its check is that test loop).  S_dev: n codes, 16-byte aligned; SA_dev: n + 1 entries.
+ * counts[0] = adjacent pairs in the wrong order, [1] = values that occur twice, [2] = values out of range (or SA[0] != n),
+ * [3] = pairs whose comparison was cut after 4096 equal 32-base words (only with k beyond 131 072 on repetitive text).
+ * A correct k-ordered suffix array gives {0, 0, 0, 0}. */
+int kiss_b200_verify_sa_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, const uint32_t* SA_dev, uint32_t k,
+                            uint64_t counts[4]);
+
 /* ---- synthetic inputs ---------------------------------------------------------
  * Fill S_dev[0..n) with the counter-hash uniform stream `seed` (identical to tests/textgen.py uniform). */
 int kiss_b200_synth_uniform_dev(kiss_b200_ctx* ctx, uint8_t* S_dev, uint64_t n, uint64_t seed);

@@ -1570,6 +1570,23 @@ int kiss_b200_sa_checksum_dev(kiss_b200_ctx* c, const uint32_t* SA_dev, uint64_t
   });
 }
 
+int kiss_b200_verify_sa_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, const uint32_t* SA_dev, uint32_t k,
+                            uint64_t counts[4]) {
+  if (!counts || !SA_dev || (n && !S_dev) || ((uintptr_t)S_dev & 15)) { g_last_error = "bad argument (null pointer or S_dev not 16-byte aligned)"; return KISS_B200_ERR_ARG; }
+  if (int rc = check_n(n)) return rc;
+  return guarded(c, [&] {
+    Pool pool(c->st, &c->arena);
+    u64* T = pool.alloc<u64>(packed_words(n));
+    if (n) pack_codes(S_dev, n, T, c->st);
+    else CK(cudaMemsetAsync(T, 0, packed_words(0) * sizeof(u64), c->st));
+    u32* bitmap = pool.alloc<u32>((n + 1 + 31) / 32);
+    u64* d = pool.alloc<u64>(4);
+    verify_sa(T, n, SA_dev, n + 1, k, 4096u, bitmap, d, c->st);
+    CK(cudaMemcpyAsync(counts, d, 4 * sizeof(u64), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+  });
+}
+
 int kiss_b200_synth_uniform_dev(kiss_b200_ctx* c, uint8_t* S_dev, uint64_t n, uint64_t seed) {
   if (!S_dev && n) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   return guarded(c, [&] {

@@ -97,6 +97,13 @@ class Context:
         self.last_timings = t.as_dict()
         return self.last_timings
 
+    def verify_sa_dev(self, S_ptr, n, SA_ptr, k=256):
+        """tests/kiss.cpp's REQUIRE loop on the device: dict(order_violations, duplicates, out_of_range, cut) — all zero for
+        a correct k-ordered suffix array"""
+        out = np.zeros(4, np.uint64)
+        check(lib().kiss_b200_verify_sa_dev(self._h, S_ptr, n, SA_ptr, k & 0xFFFFFFFF, out.ctypes.data))
+        return dict(order_violations=int(out[0]), duplicates=int(out[1]), out_of_range=int(out[2]), cut=int(out[3]))
+
     def general_digits(self, S_ptr, n):
         """(distinct byte values, two-bit digits per symbol) of a device-resident text"""
         s, d = C.c_uint32(), C.c_uint32()
