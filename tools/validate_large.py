@@ -144,6 +144,13 @@ def main():
             out["kernels"] = {k: [round(v[0], 3), v[1]] for k, v in ctx.profile().items()}
             out["profiled_stages_s"] = {k: ctx.last_timings[k] for k in ("get_lms", "lms_sort", "put_lms", "induce")}
             ctx.profile_enable(False)
+        # the reference's test predicate over ALL adjacent pairs, on the device (kiss_b200_verify_sa_dev)
+        dS = torch.zeros(n + 64, dtype=torch.uint8, device="cuda")
+        dS[:n] = torch.from_numpy(S)
+        dSA = torch.from_numpy(sa.view(np.int32)).cuda()
+        torch.cuda.synchronize()
+        out["k_order_all_pairs"] = ctx.verify_sa_dev(dS.data_ptr(), n, dSA.data_ptr(), cfg["k"])
+        del dS, dSA
         if cfg.get("property_only"):
             out["k_order_violations_in_2M_samples"] = k_order_violations(S, sa, cfg["k"])
             ps = ctx.suffix_array_dna(S, cfg["k"], algo=kiss_b200.PARALLEL_SORTING)
