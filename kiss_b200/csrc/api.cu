@@ -456,7 +456,8 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
   const u32 W = hv[0], ntail = hv[1];
   if (W64 >= 0xFFFFFFF0ull) throw CudaError(KISS_B200_ERR_TOO_LARGE, "too many kISS-2 words for 32-bit indices");
   u32* wstart = pool.alloc<u32>(W);
-  u8* isstart = pool.alloc<u8>(W);
+  u32* isstart = pool.alloc<u32>(((u64)W + 31) / 32);  // bit per word: the word starts an LMS substring
+  CK(cudaMemsetAsync(isstart, 0, (((u64)W + 31) / 32) * sizeof(u32), st));
   u32* key = pool.alloc<u32>(W);
   u32* idx = pool.alloc<u32>(W);
   u32* key_alt = pool.alloc<u32>(W);
@@ -475,7 +476,7 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
   pool.release(key); pool.release(key_alt); pool.release(idx_alt);
   scan_excl_u32_to(head, ord, W, partials, nullptr, st);
   pd_headslot(head, ord, W, headslot, st);
-  pd_rank(idx, head, ord, headslot, nullptr, W, rank, st);
+  pd_rank(idx, head, ord, headslot, nullptr, nullptr, W, rank, st);
   // first compaction: singletons are final
   u32* keep = pool.alloc<u32>(W);
   u32* dst = pool.alloc<u32>(W);
@@ -507,6 +508,7 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
     // segmented sort (one pass) unless a group is larger than a block team holds
     static const bool no_seg = getenv("KISS_B200_PD_RADIX") != nullptr;  // A/B: the radix sort in every round
     bool seg_done = false;
+    u32* isnew = nullptr;  // (segmented rounds) bit per slot: a head this round made
     if (!no_seg) {
       u32* key2 = reinterpret_cast<u32*>(comp);          // (the composite buffers are free on this path)
       u32* lists = reinterpret_cast<u32*>(comp_alt);   // 7 lists; a listed group has > 8 elements: at most A / 9 per list
@@ -545,7 +547,8 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
           pool.release(boff); pool.release(bpart); pool.release(bcomp); pool.release(bcomp_alt); pool.release(bval);
           pool.release(bval_alt); pool.release(bslot); pool.release(Hb); pool.release(partb);
         }
-        pd_heads_seg(key2, A, ghead, st);
+        isnew = pool.alloc<u32>(((u64)A + 31) / 32);
+        pd_heads_seg(key2, A, ghead, isnew, st);
         seg_done = true;
       }
     }
@@ -558,7 +561,7 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
     }
     scan_excl_u32_to(ghead, o, A, partials, nullptr, st);
     pd_headslot(ghead, o, A, hs, st);
-    pd_rank(elem, ghead, o, hs, gslot, A, rank, st);
+    pd_rank(elem, ghead, o, hs, gslot, isnew, A, rank, st);
     u32* kp = pool.alloc<u32>(A);
     u32* ds = pool.alloc<u32>(A);
     pd_keep(ghead, A, kp, st);
@@ -572,6 +575,7 @@ u32* sort_lms_doubling(kiss_b200_ctx* c, Pool& pool, const u64* T, u64 n, const 
     CK(cudaStreamSynchronize(st));
     pool.release(o); pool.release(hs); pool.release(comp); pool.release(comp_alt); pool.release(elem); pool.release(elem_alt);
     pool.release(H2); pool.release(kp); pool.release(ds); pool.release(gslot); pool.release(ghead);
+    if (isnew) pool.release(isnew);
     elem = elem2; gslot = gslot2; ghead = ghead2;
     A = A2;
   }

@@ -183,12 +183,12 @@ void shorts_insertions(const u32* sorted_shorts, u32 ns, const u32* longs, u32 n
 void pd_count(const u32* lms, u32 m1, u64 n, u32* cnt, cudaStream_t st);
 void pd_ntail(const u32* lms, const u32* cnt, u32 m1, u64 n, u32* out, cudaStream_t st);
 void pd_words(const u32* lms, const u32* first, const u32* cnt, u32 m1, const u64* T, u32 W, u32 ntail, u32* wstart,
-              u8* isstart, u32* key_in, u32* idx_in, cudaStream_t st);
+              u32* isstart, u32* key_in, u32* idx_in, cudaStream_t st);
 void pd_heads0(const u32* key, const u32* idx, u32 W, u32 ntail, u32* head, cudaStream_t st);
 void pd_heads(const u64* comp, u32 A, u32* head, cudaStream_t st);
 void pd_headslot(const u32* head, const u32* ord, u32 A, u32* headslot, cudaStream_t st);
-void pd_rank(const u32* elem, const u32* head, const u32* ord, const u32* headslot, const u32* gslot, u32 A, u32* rank,
-             cudaStream_t st);
+void pd_rank(const u32* elem, const u32* head, const u32* ord, const u32* headslot, const u32* gslot, const u32* isnew, u32 A,
+             u32* rank, cudaStream_t st);
 void pd_keep(const u32* head, u32 A, u32* keep, cudaStream_t st);
 void pd_compact(const u32* elem, const u32* gslot, const u32* head, const u32* keep, const u32* dst, u32 A, u32* sa_final,
                 u32* elem2, u32* gslot2, u32* head2, cudaStream_t st);
@@ -201,13 +201,13 @@ void pd_seg_small(const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2,
                   cudaStream_t st);
 void pd_seg_teams(const u32* lists, u32 list_cap, const u32* cn, const u32* headslot, u32 ngroups, u32 A, u32* elem, u32* key2,
                   cudaStream_t st);
-void pd_heads_seg(const u32* key2, u32 A, u32* head, cudaStream_t st);
+void pd_heads_seg(const u32* key2, u32 A, u32* head, u32* isnew, cudaStream_t st);
 void pd_big_sizes(const u32* biglist, u32 nb, const u32* headslot, u32 ngroups, u32 A, u32* bsize, cudaStream_t st);
 void pd_big_fill(const u32* biglist, const u32* boff, u32 nb, u32 B, const u32* headslot, const u32* elem, const u32* key2,
                  int rb, u64* comp, u32* val, u32* bslot, cudaStream_t st);
 void pd_big_writeback(const u64* comp, const u32* val, const u32* bslot, u32 B, int rb, u32* elem, u32* key2, cudaStream_t st);
 void pd_flush(const u32* elem, const u32* gslot, u32 A, u32* sa_final, cudaStream_t st);
-void pd_startflags(const u32* sa_final, const u8* isstart, const u32* wstart, u32 W, u32* flag, u32* val, cudaStream_t st);
+void pd_startflags(const u32* sa_final, const u32* isstart, const u32* wstart, u32 W, u32* flag, u32* val, cudaStream_t st);
 void pd_emit(const u32* val, const u32* dst, u32 W, u32* out, cudaStream_t st);
 
 // ---------------------------------------------------------------- fmindex.cu

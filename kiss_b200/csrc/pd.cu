@@ -36,7 +36,7 @@ __global__ void k_pd_count(const u32* __restrict__ lms, u32 m1, u64 n, u32* __re
 // word starts, LMS-start flags and the first 16 bases of every word, written at the word's INPUT SLOT of the initial
 // sort: the `ntail` words that overlap the text end (the last ones by index) first, in reverse index order (:130-133)
 __global__ void k_pd_words(const u32* __restrict__ lms, const u32* __restrict__ first, const u32* __restrict__ cnt, u32 m1,
-                           const u64* __restrict__ T, u32 W, u32 ntail, u32* __restrict__ wstart, u8* __restrict__ isstart,
+                           const u64* __restrict__ T, u32 W, u32 ntail, u32* __restrict__ wstart, u32* __restrict__ isstart /* bit per word, zeroed */,
                            u32* __restrict__ key_in, u32* __restrict__ idx_in) {
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m1) return;
@@ -46,7 +46,7 @@ __global__ void k_pd_words(const u32* __restrict__ lms, const u32* __restrict__ 
     const u32 w = f + j;
     const u64 p = p0 + 16ull * j;
     wstart[w] = (u32)p;
-    isstart[w] = j == 0;
+    if (j == 0) atomicOr(&isstart[w >> 5], 1u << (w & 31u));  // (a bitmap: W / 8 bytes stay in L2 for the final gathers)
     const u32 slot = w >= W - ntail ? W - 1 - w : w + ntail;
     key_in[slot] = (u32)(word_at(T, p) >> 32);
     idx_in[slot] = w;
@@ -89,11 +89,15 @@ __global__ void k_pd_headslot(const u32* __restrict__ head, const u32* __restric
 }
 
 // rank of every element = global position of its group's head + 1 (:226-248, :378-462); gslot == nullptr: slot = position
+// `isnew` (nullable): bit per slot, set where this round made a new head.  A group whose head was a head before starts
+// where its elements' old group started, so their rank is what it was: the random 4-byte write is skipped.
 __global__ void k_pd_rank(const u32* __restrict__ elem, const u32* __restrict__ head, const u32* __restrict__ ord,
-                          const u32* __restrict__ headslot, const u32* __restrict__ gslot, u32 A, u32* __restrict__ rank) {
+                          const u32* __restrict__ headslot, const u32* __restrict__ gslot, const u32* __restrict__ isnew, u32 A,
+                          u32* __restrict__ rank) {
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= A) return;
   const u32 hs = headslot[ord[i] + head[i] - 1u];
+  if (isnew && !((isnew[hs >> 5] >> (hs & 31u)) & 1u)) return;
   rank[elem[i]] = (gslot ? gslot[hs] : hs) + 1u;
 }
 
@@ -140,12 +144,12 @@ __global__ void k_pd_flush(const u32* __restrict__ elem, const u32* __restrict__
 
 // LMS-start words in final order (:690-725): flag = the word starts an LMS substring, val = its text position (> 0) or 0;
 // after the scan of the flags the positions go out in order
-__global__ void k_pd_startflags(const u32* __restrict__ sa_final, const u8* __restrict__ isstart, const u32* __restrict__ wstart,
+__global__ void k_pd_startflags(const u32* __restrict__ sa_final, const u32* __restrict__ isstart, const u32* __restrict__ wstart,
                                 u32 W, u32* __restrict__ flag, u32* __restrict__ val) {
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= W) return;
   const u32 w = sa_final[i];
-  const u32 s = isstart[w];
+  const u32 s = (isstart[w >> 5] >> (w & 31u)) & 1u;
   flag[i] = s;
   val[i] = s ? wstart[w] : 0u;
 }
@@ -277,10 +281,15 @@ __global__ void __launch_bounds__(NW == 1 ? 256 : NW * 32) k_pd_seg_team(const u
 }
 
 // heads after a segmented round: the old group starts, and where key2 changes
-__global__ void k_pd_heads_seg(const u32* __restrict__ key2, u32 A, u32* __restrict__ head) {
-  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= A) return;
-  if (i > 0 && !head[i] && key2[i] != key2[i - 1]) head[i] = 1u;
+__global__ void k_pd_heads_seg(const u32* __restrict__ key2, u32 A, u32* __restrict__ head, u32* __restrict__ isnew) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
+  bool nh = false;
+  if (i < A && i > 0 && !head[i] && key2[i] != key2[i - 1]) {
+    head[i] = 1u;
+    nh = true;
+  }
+  const u32 m = __ballot_sync(0xffffffffu, nh);  // (32 consecutive slots per warp: one bitmap word)
+  if (lane == 0 && i < A) isnew[i >> 5] = m;
 }
 
 #define PD_GRID(n) (unsigned)(((u64)(n) + PD_T - 1) / PD_T)
@@ -299,7 +308,7 @@ void pd_ntail(const u32* lms, const u32* cnt, u32 m1, u64 n, u32* out, cudaStrea
   CK_LAUNCH(); g_launches++;
 }
 void pd_words(const u32* lms, const u32* first, const u32* cnt, u32 m1, const u64* T, u32 W, u32 ntail, u32* wstart,
-              u8* isstart, u32* key_in, u32* idx_in, cudaStream_t st) {
+              u32* isstart, u32* key_in, u32* idx_in, cudaStream_t st) {
   PD_LAUNCH(k_pd_words, m1, lms, first, cnt, m1, T, W, ntail, wstart, isstart, key_in, idx_in);
 }
 void pd_heads0(const u32* key, const u32* idx, u32 W, u32 ntail, u32* head, cudaStream_t st) {
@@ -309,9 +318,9 @@ void pd_heads(const u64* comp, u32 A, u32* head, cudaStream_t st) { PD_LAUNCH(k_
 void pd_headslot(const u32* head, const u32* ord, u32 A, u32* headslot, cudaStream_t st) {
   PD_LAUNCH(k_pd_headslot, A, head, ord, A, headslot);
 }
-void pd_rank(const u32* elem, const u32* head, const u32* ord, const u32* headslot, const u32* gslot, u32 A, u32* rank,
-             cudaStream_t st) {
-  PD_LAUNCH(k_pd_rank, A, elem, head, ord, headslot, gslot, A, rank);
+void pd_rank(const u32* elem, const u32* head, const u32* ord, const u32* headslot, const u32* gslot, const u32* isnew, u32 A,
+             u32* rank, cudaStream_t st) {
+  PD_LAUNCH(k_pd_rank, A, elem, head, ord, headslot, gslot, isnew, A, rank);
 }
 void pd_keep(const u32* head, u32 A, u32* keep, cudaStream_t st) { PD_LAUNCH(k_pd_keep, A, head, A, keep); }
 void pd_compact(const u32* elem, const u32* gslot, const u32* head, const u32* keep, const u32* dst, u32 A, u32* sa_final,
@@ -325,7 +334,7 @@ void pd_key2(const u32* elem, const u32* head, const u32* ord, const u32* rank, 
 void pd_flush(const u32* elem, const u32* gslot, u32 A, u32* sa_final, cudaStream_t st) {
   PD_LAUNCH(k_pd_flush, A, elem, gslot, A, sa_final);
 }
-void pd_startflags(const u32* sa_final, const u8* isstart, const u32* wstart, u32 W, u32* flag, u32* val, cudaStream_t st) {
+void pd_startflags(const u32* sa_final, const u32* isstart, const u32* wstart, u32 W, u32* flag, u32* val, cudaStream_t st) {
   PD_LAUNCH(k_pd_startflags, W, sa_final, isstart, wstart, W, flag, val);
 }
 void pd_emit(const u32* val, const u32* dst, u32 W, u32* out, cudaStream_t st) { PD_LAUNCH(k_pd_emit, W, val, dst, W, out); }
@@ -355,7 +364,7 @@ void pd_seg_teams(const u32* lists, u32 list_cap, const u32* cn, const u32* head
   pd_seg_class<16, 2>(lists + 5ull * list_cap, cn[5], headslot, ngroups, A, elem, key2, st);
   pd_seg_class<16, 4>(lists + 6ull * list_cap, cn[6], headslot, ngroups, A, elem, key2, st);
 }
-void pd_heads_seg(const u32* key2, u32 A, u32* head, cudaStream_t st) { PD_LAUNCH(k_pd_heads_seg, A, key2, A, head); }
+void pd_heads_seg(const u32* key2, u32 A, u32* head, u32* isnew, cudaStream_t st) { PD_LAUNCH(k_pd_heads_seg, A, key2, A, head, isnew); }
 void pd_big_sizes(const u32* biglist, u32 nb, const u32* headslot, u32 ngroups, u32 A, u32* bsize, cudaStream_t st) {
   PD_LAUNCH(k_pd_big_sizes, nb, biglist, nb, headslot, ngroups, A, bsize);
 }
