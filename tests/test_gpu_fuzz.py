@@ -134,3 +134,24 @@ def test_device_ingest_against_the_oracle(ctx, seed):
         sa, n = ctx.suffix_array_file(data, 256)
         assert n == want_text.size, f"seed {seed}: {data[:120]!r}"
         assert np.array_equal(sa, ol.oracle_kiss1(want_text, 256)), f"seed {seed}: {data[:120]!r}"
+
+
+@pytest.mark.skipif(not ol.have_ref() or not hasattr(ol.ref(), "ref_kiss2_sorted_lms"), reason="reference harness not built")
+@pytest.mark.parametrize("seed", range(4))
+def test_bounded_prefix_doubling_against_kiss2_itself(ctx, seed):
+    """bounded-k PREFIX_DOUBLING: the LMS order equals the reference's kISS-2 (single-threaded, its deterministic run) after
+    putting every run of equal word classes in text order (tests/kiss2_words.py)"""
+    import kiss2_words as kw
+    import kiss_b200
+    r = tg._Rng(5000 + seed)
+    done = 0
+    while done < 25:
+        S = fuzz_text(r)
+        if S.size < 64:          # (below 64 bases the entry takes the pivot path: the reference's tail-word rule degenerates)
+            continue
+        k = [1, 2, 3, 8, 16, 17, 32, 100, 256][r.below(9)]
+        ref_lms = ol.ref_kiss2_sorted_lms(S, k, 1)
+        got_lms = ctx.sorted_lms(S, k, kiss_b200.PREFIX_DOUBLING)
+        want, _ = kw.canonical(ref_lms, S, k)
+        assert np.array_equal(got_lms, want), f"seed {seed}: n={S.size} k={k} text={S[:80].tolist()}"
+        done += 1
