@@ -274,6 +274,10 @@ int kiss_b200_sa_checksum_dev(kiss_b200_ctx* ctx, const uint32_t* SA_dev, uint64
  * A correct k-ordered suffix array gives {0, 0, 0, 0}. */
 int kiss_b200_verify_sa_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, const uint32_t* SA_dev, uint32_t k,
                             uint64_t counts[4]);
+/* The same for a byte text and the array of the general-alphabet entry (symbols compared as unsigned bytes; [3] counts
+ * pairs cut after 131 072 equal symbols). */
+int kiss_b200_verify_sa_bytes_dev(kiss_b200_ctx* ctx, const uint8_t* S_dev, uint64_t n, const uint32_t* SA_dev, uint32_t k,
+                                  uint64_t counts[4]);
 
 /* ---- synthetic inputs ---------------------------------------------------------
  * Fill S_dev[0..n) with the counter-hash uniform stream `seed` (identical to tests/textgen.py uniform). */

@@ -48,6 +48,7 @@ SIGNATURES = {
     "kiss_b200_suffix_sort_u32_dev": (_int, [_vp, _vp, _u64, _u32, _int, _vp, C.POINTER(Timings)]),
     "kiss_b200_general_digits": (_int, [_vp, _vp, _u64, C.POINTER(_u32), C.POINTER(_u32)]),
     "kiss_b200_verify_sa_dev": (_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
+    "kiss_b200_verify_sa_bytes_dev": (_int, [_vp, _vp, _u64, _vp, _u32, _vp]),
     "kiss_b200_get_lms": (_int, [_vp, _vp, _u64, _vp, C.POINTER(_u64), _vp, _vp]),
     "kiss_b200_sorted_lms": (_int, [_vp, _vp, _u64, _u32, _int, _vp, C.POINTER(_u64)]),
     "kiss_b200_put_lms": (_int, [_vp, _vp, _u64, _u32, _int, _vp]),

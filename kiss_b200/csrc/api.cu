@@ -1591,6 +1591,20 @@ int kiss_b200_verify_sa_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, 
   });
 }
 
+int kiss_b200_verify_sa_bytes_dev(kiss_b200_ctx* c, const uint8_t* S_dev, uint64_t n, const uint32_t* SA_dev, uint32_t k,
+                                  uint64_t counts[4]) {
+  if (!counts || !SA_dev || (n && !S_dev)) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
+  if (int rc = check_n(n)) return rc;
+  return guarded(c, [&] {
+    Pool pool(c->st, &c->arena);
+    u32* bitmap = pool.alloc<u32>((n + 1 + 31) / 32);
+    u64* d = pool.alloc<u64>(4);
+    verify_sa_bytes(S_dev, n, SA_dev, n + 1, k, 131072u, bitmap, d, c->st);
+    CK(cudaMemcpyAsync(counts, d, 4 * sizeof(u64), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+  });
+}
+
 int kiss_b200_synth_uniform_dev(kiss_b200_ctx* c, uint8_t* S_dev, uint64_t n, uint64_t seed) {
   if (!S_dev && n) { g_last_error = "bad argument"; return KISS_B200_ERR_ARG; }
   return guarded(c, [&] {

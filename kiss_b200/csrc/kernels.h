@@ -87,6 +87,7 @@ void synth_uniform(u8* S, u64 n, u64 seed, cudaStream_t st);
 // *out_dev = sum_i splitmix64((i << 32) | a[i]) mod 2^64 (order-sensitive checksum of a suffix array)
 void mixed_sum(const u32* a, u64 count, u64* out_dev, cudaStream_t st);
 // verify.cu: bitmap = (N + 31) / 32 words, out = 4 counters (see k_verify_sa)
+void verify_sa_bytes(const u8* S, u64 n, const u32* SA, u64 N, u64 k, u32 cap, u32* bitmap, u64* out, cudaStream_t st);
 void verify_sa(const u64* T, u64 n, const u32* SA, u64 N, u64 k, u32 cap_words, u32* bitmap, u64* out, cudaStream_t st);
 
 // ---------------------------------------------------------------- ingest.cu

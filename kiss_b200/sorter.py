@@ -97,11 +97,12 @@ class Context:
         self.last_timings = t.as_dict()
         return self.last_timings
 
-    def verify_sa_dev(self, S_ptr, n, SA_ptr, k=256):
+    def verify_sa_dev(self, S_ptr, n, SA_ptr, k=256, byte_text=False):
         """tests/kiss.cpp's REQUIRE loop on the device: dict(order_violations, duplicates, out_of_range, cut) — all zero for
-        a correct k-ordered suffix array"""
+        a correct k-ordered suffix array.  `byte_text`: S is a general-alphabet text (any byte values), not codes 0..3"""
         out = np.zeros(4, np.uint64)
-        check(lib().kiss_b200_verify_sa_dev(self._h, S_ptr, n, SA_ptr, k & 0xFFFFFFFF, out.ctypes.data))
+        f = lib().kiss_b200_verify_sa_bytes_dev if byte_text else lib().kiss_b200_verify_sa_dev
+        check(f(self._h, S_ptr, n, SA_ptr, k & 0xFFFFFFFF, out.ctypes.data))
         return dict(order_violations=int(out[0]), duplicates=int(out[1]), out_of_range=int(out[2]), cut=int(out[3]))
 
     def general_digits(self, S_ptr, n):

@@ -88,3 +88,34 @@ def test_general_alphabet_arrays_verify_through_their_reduction(ctx):
     S = gc.hashed(41, 60_000, gc.ABCD)
     SA = ctx.suffix_array(S, 256)
     assert verify(ctx, S - 65, SA, 256) == CLEAN
+
+
+def verify_bytes(ctx, S, SA, k):
+    import torch
+    dS = torch.zeros(S.size + 16, dtype=torch.uint8, device="cuda")
+    dS[:S.size] = torch.from_numpy(np.ascontiguousarray(S))
+    dSA = torch.from_numpy(np.ascontiguousarray(SA).view(np.int32)).cuda()
+    torch.cuda.synchronize()
+    return ctx.verify_sa_dev(dS.data_ptr(), S.size, dSA.data_ptr(), k, byte_text=True)
+
+
+def test_byte_text_verifier(ctx):
+    """kiss_b200_verify_sa_bytes_dev: the same predicate over a general-alphabet text, agreeing with the host checker of
+    tests/general_cases.py"""
+    import general_cases as gc
+    for name, (build, k) in list(gc.UNIQUE.items()) + list(gc.TIED.items()):
+        S = build()
+        SA = ctx.suffix_array(S, k)
+        assert verify_bytes(ctx, S, SA, k) == CLEAN, name
+    S = gc.hashed(51, 30_000, gc.AMINO)
+    SA = ol.oracle_general(S, 256)
+    assert verify_bytes(ctx, S, SA, 256) == CLEAN
+    bad = SA.copy(); bad[[200, 201]] = bad[[201, 200]]
+    v = verify_bytes(ctx, S, bad, 256)
+    assert v["order_violations"] == gc.k_order_violations(S, bad, 256) >= 1
+    bad = SA.copy(); bad[9] = bad[10]
+    assert verify_bytes(ctx, S, bad, 256)["duplicates"] == 1
+    # bytes above 127 compare unsigned
+    S = np.array([200, 100, 200, 50, 255, 0], np.uint8)
+    SA = ol.oracle_general(S, 256)
+    assert verify_bytes(ctx, S, SA, 256) == CLEAN

@@ -55,7 +55,13 @@ def main():
         t0 = time.perf_counter()
         ref = ol.ref_general(S, cfg["k"], threads, 0)
         ref_s = time.perf_counter() - t0
-        rec = dict(config=name, n=cfg["n"], sigma=int(len(cfg["alphabet"])), k=cfg["k"], gpu_host_call_s=round(best, 4),
+        import torch
+        dS = torch.from_numpy(S).cuda()
+        dSA = torch.from_numpy(SA.view(np.int32)).cuda()
+        torch.cuda.synchronize()
+        allpairs = ctx.verify_sa_dev(dS.data_ptr(), cfg["n"], dSA.data_ptr(), cfg["k"], byte_text=True)
+        del dS, dSA
+        rec = dict(config=name, k_order_all_pairs=allpairs, n=cfg["n"], sigma=int(len(cfg["alphabet"])), k=cfg["k"], gpu_host_call_s=round(best, 4),
                    gpu_device_s=round(t["total_device"], 4), ref_s=round(ref_s, 3), ref_threads=threads,
                    bit_exact=bool((SA == ref).all()), mismatches=int((SA != ref).sum()),
                    sa0_is_n=bool(SA[0] == cfg["n"]), fnv1a="%016x" % ol.fnv1a(SA))
