@@ -20,7 +20,7 @@ def ctx():
 def verify(ctx, S, SA, k):
     import torch
     dS = torch.zeros(S.size + 64, dtype=torch.uint8, device="cuda")
-    dS[:S.size] = torch.from_numpy(np.ascontiguousarray(S))
+    dS[:S.size] = torch.from_numpy(np.array(S, dtype=np.uint8, copy=True))
     dSA = torch.from_numpy(np.ascontiguousarray(SA).view(np.int32)).cuda()
     torch.cuda.synchronize()
     return ctx.verify_sa_dev(dS.data_ptr(), S.size, dSA.data_ptr(), k)
@@ -93,7 +93,7 @@ def test_general_alphabet_arrays_verify_through_their_reduction(ctx):
 def verify_bytes(ctx, S, SA, k):
     import torch
     dS = torch.zeros(S.size + 16, dtype=torch.uint8, device="cuda")
-    dS[:S.size] = torch.from_numpy(np.ascontiguousarray(S))
+    dS[:S.size] = torch.from_numpy(np.array(S, dtype=np.uint8, copy=True))
     dSA = torch.from_numpy(np.ascontiguousarray(SA).view(np.int32)).cuda()
     torch.cuda.synchronize()
     return ctx.verify_sa_dev(dS.data_ptr(), S.size, dSA.data_ptr(), k, byte_text=True)
