@@ -15,6 +15,7 @@
 // induction left beside every entry, so only one entry in sixteen gathers from the text: C3 69.6 -> see DESIGN.md),
 // three small scans, one more pass over SA for the compaction (k_fm_sample).  Algorithmic bytes: 2 x 4N (SA
 // reads) + N / 4 (gathered text, ideal) + 1.75 N written.
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -104,10 +105,132 @@ __global__ void __launch_bounds__(256) k_fm_sample(const u32* __restrict__ SA, u
   sa_out[bocc[i >> 6] + before] = v;
 }
 
+// ---- the same scan with FOUR consecutive entries per thread (two 16-byte loads): the one-entry kernel above keeps 2048
+// four-byte loads in flight per SM, half of what the HBM latency needs, and ran at 1 TB/s (profiles/r2_fm_kernels.txt).
+// One block = 1024 entries = four occ1 rows; a row is two warps, a 16-entry occ2 segment four lanes, a b_ word eight,
+// a b_occ block sixteen.  Needs SA (and CTX) 16-byte aligned; the launcher falls back to the kernel above otherwise.
+#define FM4_THREADS 256u
+#define FM4_TILE (4u * FM4_THREADS)
+__global__ void __launch_bounds__(FM4_THREADS) k_fm_scan4(const u32* __restrict__ SA, const u32* __restrict__ CTX, u64 N,
+                                                         const u64* __restrict__ T, u32 intv, u32* __restrict__ bwt32,
+                                                         u32* __restrict__ tot, u64 n1p, u64 n1, u32* __restrict__ occ2w, u64 n2,
+                                                         u32* __restrict__ b32, u32* __restrict__ bocc_raw, u32* __restrict__ pri) {
+  __shared__ u64 s_wtot[FM4_THREADS / 32];  // symbol counts per warp, 4 x 16 bits
+  const u32 t = threadIdx.x, lane = t & 31u, w = t >> 5;
+  const u64 i0 = (u64)blockIdx.x * FM4_TILE + 4ull * t;
+  u32 v[4] = {1u, 1u, 1u, 1u}, cx[4] = {1u, 1u, 1u, 1u};
+  if (i0 + 4 <= N) {
+    const uint4 q = *reinterpret_cast<const uint4*>(SA + i0);
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+    if (CTX) {
+      const uint4 c = *reinterpret_cast<const uint4*>(CTX + i0);
+      cx[0] = c.x; cx[1] = c.y; cx[2] = c.z; cx[3] = c.w;
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < 4; e++)
+      if (i0 + e < N) { v[e] = SA[i0 + e]; if (CTX) cx[e] = CTX[i0 + e]; }
+  }
+  u32 byte = 0, hit4 = 0;
+  u64 pc = 0;
+#pragma unroll
+  for (int e = 0; e < 4; e++) {
+    const bool valid = i0 + e < N, counted = valid && v[e] != 0;
+    u32 c = 0;
+    if (counted) c = cx[e] > 1u ? (cx[e] & 3u) : base_at(T, (u64)v[e] - 1);
+    if (valid && v[e] == 0) *pri = (u32)(i0 + e);
+    byte |= c << (2 * e);
+    if (counted) pc += 1ull << (16 * c);
+    if (valid && v[e] % intv == 0) hit4 |= 1u << e;
+  }
+  // bwt: 16 entries per word = four lanes
+  u32 x = byte << (8 * (lane & 3u));
+  x |= __shfl_xor_sync(0xffffffffu, x, 1);
+  x |= __shfl_xor_sync(0xffffffffu, x, 2);
+  if ((lane & 3u) == 0 && i0 < N) bwt32[i0 >> 4] = x;
+  // symbol counts: inclusive scan over the lanes, warp totals to shared memory
+  u64 incl = pc;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const u64 y = __shfl_up_sync(0xffffffffu, incl, o);
+    if ((int)lane >= o) incl += y;
+  }
+  if (lane == 31) s_wtot[w] = incl;
+  // sampled-entry bits: a b_ word = eight lanes, a b_occ block = sixteen
+  if (b32) {
+    u32 hb = hit4 << (4 * (lane & 7u));
+    hb |= __shfl_xor_sync(0xffffffffu, hb, 1);
+    hb |= __shfl_xor_sync(0xffffffffu, hb, 2);
+    hb |= __shfl_xor_sync(0xffffffffu, hb, 4);
+    if ((lane & 7u) == 0 && i0 < N) b32[i0 >> 5] = hb;
+    u32 hc = (u32)__popc(hit4);
+    hc += __shfl_xor_sync(0xffffffffu, hc, 1);
+    hc += __shfl_xor_sync(0xffffffffu, hc, 2);
+    hc += __shfl_xor_sync(0xffffffffu, hc, 4);
+    hc += __shfl_xor_sync(0xffffffffu, hc, 8);
+    if ((lane & 15u) == 0 && i0 < N) bocc_raw[i0 >> 6] = hc;
+  }
+  __syncthreads();
+  // occ2: counts since the row's start before every 16-entry segment (its first lane writes the four bytes at once)
+  const u64 before_seg = __shfl_sync(0xffffffffu, incl, (lane & ~3u) - 1u & 31u);  // inclusive count of the lane before the segment
+  if ((lane & 3u) == 0) {
+    u64 p = lane ? before_seg : 0ull;
+    if (w & 1u) p += s_wtot[w - 1];  // the second warp of the row
+    const u64 j = i0 >> 4;
+    if (j < n2)
+      occ2w[j] = (u32)(p & 0xFFu) | ((u32)((p >> 16) & 0xFFu) << 8) | ((u32)((p >> 32) & 0xFFu) << 16) | ((u32)((p >> 48) & 0xFFu) << 24);
+  }
+  if (t < 16) {
+    const u32 row = t >> 2, sym = t & 3u;
+    const u64 r = (u64)blockIdx.x * 4 + row;
+    if (r < n1 && r * FM_ROW < N) {
+      const u64 sum = s_wtot[2 * row] + s_wtot[2 * row + 1];
+      tot[(u64)sym * n1p + r] = (u32)((sum >> (16 * sym)) & 0xFFFFu);
+    }
+  }
+}
+
+// the compaction with four entries per thread
+__global__ void __launch_bounds__(256) k_fm_sample4(const u32* __restrict__ SA, u64 N, u32 intv, const u32* __restrict__ b32,
+                                                   const u32* __restrict__ bocc, u32* __restrict__ sa_out) {
+  const u64 i0 = ((u64)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i0 >= N) return;
+  u32 v[4] = {1u, 1u, 1u, 1u};
+  if (i0 + 4 <= N) {
+    const uint4 q = *reinterpret_cast<const uint4*>(SA + i0);
+    v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+  } else {
+    for (int e = 0; e < 4; e++)
+      if (i0 + e < N) v[e] = SA[i0 + e];
+  }
+  bool any = false;
+#pragma unroll
+  for (int e = 0; e < 4; e++) any |= (i0 + e < N) && (v[e] % intv == 0);
+  if (!any) return;
+  const u64 w0 = (i0 >> 6) * 2;
+  const u64 bits = (u64)b32[w0] | ((u64)b32[w0 + 1] << 32);
+  const u32 base = bocc[i0 >> 6];
+#pragma unroll
+  for (int e = 0; e < 4; e++) {
+    if (i0 + e < N && v[e] % intv == 0) {
+      const u32 bit = (u32)((i0 + e) & 63);
+      sa_out[base + (u32)__popcll(bits & ((1ull << bit) - 1ull))] = v[e];
+    }
+  }
+}
+
 void fm_scan(const u32* SA, const u32* CTX, u64 N, const u64* T, u32 intv, u32* bwt32, u32* tot, u64 n1, u8* occ2, u64 n2, u32* b32,
              u32* bocc_raw, u32* pri, cudaStream_t st) {
-  const u64 rows = (N + FM_ROW - 1) / FM_ROW;
-  k_fm_scan<<<(unsigned)rows, FM_ROW, 0, st>>>(SA, CTX, N, T, intv, bwt32, tot, n1, occ2, n2, b32, bocc_raw, pri);
+  static const bool one = getenv("KISS_B200_FM_ONE") != nullptr;  // A/B: one entry per thread
+  const bool aligned = (((uintptr_t)SA | (uintptr_t)CTX | (uintptr_t)occ2) & 15) == 0;
+  if (aligned && !one) {
+    const u64 blocks = (N + FM4_TILE - 1) / FM4_TILE;
+    k_fm_scan4<<<(unsigned)blocks, FM4_THREADS, 0, st>>>(SA, CTX, N, T, intv, bwt32, tot, n1, N / FM_ROW + 1, reinterpret_cast<u32*>(occ2),
+                                                        n2, b32, bocc_raw, pri);
+  } else {
+    const u64 rows = (N + FM_ROW - 1) / FM_ROW;
+    k_fm_scan<<<(unsigned)rows, FM_ROW, 0, st>>>(SA, CTX, N, T, intv, bwt32, tot, n1, occ2, n2, b32, bocc_raw, pri);
+  }
   CK_LAUNCH(); g_launches++;
 }
 void fm_occ1(const u32* tot, u64 stride, u64 n1, u32* occ1, cudaStream_t st) {
@@ -115,7 +238,11 @@ void fm_occ1(const u32* tot, u64 stride, u64 n1, u32* occ1, cudaStream_t st) {
   CK_LAUNCH(); g_launches++;
 }
 void fm_sample(const u32* SA, u64 N, u32 intv, const u32* b32, const u32* bocc, u32* sa_out, cudaStream_t st) {
-  k_fm_sample<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(SA, N, intv, b32, bocc, sa_out);
+  static const bool one = getenv("KISS_B200_FM_ONE") != nullptr;
+  if ((((uintptr_t)SA) & 15) == 0 && !one)
+    k_fm_sample4<<<(unsigned)((N + 1023) / 1024), 256, 0, st>>>(SA, N, intv, b32, bocc, sa_out);
+  else
+    k_fm_sample<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(SA, N, intv, b32, bocc, sa_out);
   CK_LAUNCH(); g_launches++;
 }
 
