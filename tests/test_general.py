@@ -194,3 +194,26 @@ def test_reduced_text_beyond_32_bit_indices_is_refused(ctx):
     with pytest.raises(kiss_b200.KissB200Error) as e:
         ctx.suffix_array_dev(d.data_ptr(), n, out.data_ptr(), 256)
     assert "32-bit" in str(e.value)
+
+
+# ------------------------------------------------------------------------------------------ CPU fuzz of the oracle
+@pytest.mark.parametrize("seed", range(6))
+def test_oracle_fuzz_against_the_naive_suffix_array_and_the_reference(seed):
+    """random small byte texts (1..6 distinct symbols: ties everywhere), full order: the restatement, the naive suffix
+    array and — when built — the reference's kISS-2 agree (kISS-2: its general kISS-1 breaks on n = 1 and k = 2^32 - 1)"""
+    r = gc.tg._Rng(7000 + seed)
+    for _ in range(60):
+        n = [1, 2, 3, 4, 7, 16, 33, 100, 257, 600][r.below(10)]
+        sigma = 1 + r.below(6)
+        vals = sorted({r.below(256) for _ in range(sigma)})
+        S = np.array([vals[r.below(len(vals))] for _ in range(n)], np.uint8)
+        want = np.array([n] + sorted(range(n), key=lambda i: bytes(S[i:])), np.uint32)
+        assert (ol.oracle_general(S, gc.FULL) == want).all(), S.tolist()
+        if ol.have_ref():
+            assert (ol.ref_general(S, gc.FULL, 1, 1) == want).all(), S.tolist()
+            # kISS-1's general driver reserves n / 2 slots for the LMS list (kiss1_core.hpp:289-293), one short when n is odd
+            # and every other position is LMS ([1, 0, 2]: one LMS position + the sentinel in one slot): it then returns
+            # EMPTY entries.  Wherever its array is a permutation at all it must be the suffix array.
+            r1 = ol.ref_general(S, gc.FULL, 1, 0)
+            if (np.sort(r1) == np.arange(n + 1)).all():
+                assert (r1 == want).all(), S.tolist()
