@@ -109,6 +109,9 @@ __global__ void __launch_bounds__(256) k_fm_sample(const u32* __restrict__ SA, u
 // four-byte loads in flight per SM, half of what the HBM latency needs, and ran at 1 TB/s (profiles/r2_fm_kernels.txt).
 // One block = 1024 entries = four occ1 rows; a row is two warps, a 16-entry occ2 segment four lanes, a b_ word eight,
 // a b_occ block sixteen.  Needs SA (and CTX) 16-byte aligned; the launcher falls back to the kernel above otherwise.
+// v % intv == 0 (a mask when the interval is a power of two, as the reference's SA_INTV = 4 is: the division was a quarter
+// of the scan's instructions, profiles/r2_ncu_fm_scan4.txt)
+__device__ __forceinline__ bool fm_sampled(u32 v, u32 intv, u32 mask) { return mask != 0xFFFFFFFFu ? (v & mask) == 0u : v % intv == 0u; }
 #define FM4_THREADS 256u
 #define FM4_TILE (4u * FM4_THREADS)
 __global__ void __launch_bounds__(FM4_THREADS) k_fm_scan4(const u32* __restrict__ SA, const u32* __restrict__ CTX, u64 N,
@@ -131,6 +134,7 @@ __global__ void __launch_bounds__(FM4_THREADS) k_fm_scan4(const u32* __restrict_
     for (int e = 0; e < 4; e++)
       if (i0 + e < N) { v[e] = SA[i0 + e]; if (CTX) cx[e] = CTX[i0 + e]; }
   }
+  const u32 imask = (intv & (intv - 1u)) == 0u ? intv - 1u : 0xFFFFFFFFu;
   u32 byte = 0, hit4 = 0;
   u64 pc = 0;
 #pragma unroll
@@ -141,7 +145,7 @@ __global__ void __launch_bounds__(FM4_THREADS) k_fm_scan4(const u32* __restrict_
     if (valid && v[e] == 0) *pri = (u32)(i0 + e);
     byte |= c << (2 * e);
     if (counted) pc += 1ull << (16 * c);
-    if (valid && v[e] % intv == 0) hit4 |= 1u << e;
+    if (valid && fm_sampled(v[e], intv, imask)) hit4 |= 1u << e;
   }
   // bwt: 16 entries per word = four lanes
   u32 x = byte << (8 * (lane & 3u));
@@ -203,16 +207,17 @@ __global__ void __launch_bounds__(256) k_fm_sample4(const u32* __restrict__ SA, 
     for (int e = 0; e < 4; e++)
       if (i0 + e < N) v[e] = SA[i0 + e];
   }
+  const u32 imask = (intv & (intv - 1u)) == 0u ? intv - 1u : 0xFFFFFFFFu;
   bool any = false;
 #pragma unroll
-  for (int e = 0; e < 4; e++) any |= (i0 + e < N) && (v[e] % intv == 0);
+  for (int e = 0; e < 4; e++) any |= (i0 + e < N) && fm_sampled(v[e], intv, imask);
   if (!any) return;
   const u64 w0 = (i0 >> 6) * 2;
   const u64 bits = (u64)b32[w0] | ((u64)b32[w0 + 1] << 32);
   const u32 base = bocc[i0 >> 6];
 #pragma unroll
   for (int e = 0; e < 4; e++) {
-    if (i0 + e < N && v[e] % intv == 0) {
+    if (i0 + e < N && fm_sampled(v[e], intv, imask)) {
       const u32 bit = (u32)((i0 + e) & 63);
       sa_out[base + (u32)__popcll(bits & ((1ull << bit) - 1ull))] = v[e];
     }

@@ -83,7 +83,7 @@ def test_device_fmindex_image_equals_oracle(ctx, name):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("sa_intv", [1, 2, 8, 32])
+@pytest.mark.parametrize("sa_intv", [1, 2, 3, 8, 10, 32])
 @pytest.mark.parametrize("name", ["uniform1", "uniform255", "uniform4097", "repeats"])
 def test_device_fmindex_other_sampling_intervals(ctx, name, sa_intv):
     S = CASES[name]()

@@ -102,7 +102,7 @@ def test_fmindex_image_against_the_oracle(ctx, seed):
         S = fuzz_text(r)
         if S.size == 0:
             continue
-        intv = [1, 2, 4, 8, 16][r.below(5)]
+        intv = [1, 2, 3, 4, 5, 8, 16][r.below(7)]
         img = ctx.fmindex_build(S, 32, sa_intv=intv)
         want = fo.fmi_image(S, ol.oracle_kiss1(S, 32), intv)
         N = S.size + 1
